@@ -1,0 +1,251 @@
+/*
+ * h3dgs_b200.h -- C ABI of the B200-native hierarchical Gaussian rasterizer, hierarchy cut and
+ * sparse-Adam step.  Plain pointers and sizes only: no torch, no C++ types.
+ *
+ * Every entry point names the reference interface it replaces (paths relative to the reference
+ * checkout; HR = submodules/hierarchy-rasterizer, GH = submodules/gaussianhierarchy).
+ *
+ * Conventions
+ *   - all device pointers are contiguous fp32 / int32 unless stated otherwise;
+ *   - a NULL pointer means "absent" exactly where the reference accepts an empty tensor
+ *     (HR/rasterize_points.cu:109-120);
+ *   - every function returns 0 on success, a negative H3DGS_E* code on a usage error, or a positive
+ *     cudaError_t value; h3dgs_last_error() returns a static description of the last failure
+ *     of the calling thread;
+ *   - nothing here allocates device memory: workspaces are sized by the *_bytes() queries and owned
+ *     by the caller (mirrors required<T>(P), HR/cuda_rasterizer/rasterizer_impl.h:68-74);
+ *   - all kernels are enqueued on the stream that is passed in (the reference used legacy stream 0,
+ *     HR/rasterize_points.cu:102-133).
+ */
+#ifndef H3DGS_B200_H_
+#define H3DGS_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define H3DGS_ABI_VERSION 1
+
+#if defined(__GNUC__)
+#define H3DGS_API __attribute__((visibility("default")))
+#else
+#define H3DGS_API
+#endif
+
+#define H3DGS_EINVAL    (-1)  /* bad argument (NULL where required, negative size, ...) */
+#define H3DGS_ENOSPACE  (-2)  /* a caller-provided workspace is too small */
+#define H3DGS_EIO       (-3)  /* file could not be opened / short read */
+#define H3DGS_ELOSSY    (-4)  /* write_hierarchy: node counters exceed the fp16 container ("Would lose information!") */
+
+typedef void* h3dgs_stream_t; /* a cudaStream_t */
+
+H3DGS_API int h3dgs_abi_version(void);
+H3DGS_API const char* h3dgs_last_error(void);
+
+/* ------------------------------------------------------------------------------------------------
+ * Rasterizer.  Replaces CudaRasterizer::Rasterizer::{forward,backward,markVisible}
+ * (HR/cuda_rasterizer/rasterizer.h:21-105, rasterizer_impl.cu:145-510) as driven by
+ * RasterizeGaussiansCUDA / RasterizeGaussiansBackwardCUDA (HR/rasterize_points.cu:35-242).
+ * ------------------------------------------------------------------------------------------------ */
+
+/* Camera + image: fields of GaussianRasterizationSettings (HR/diff_gaussian_rasterization/__init__.py:146-163). */
+typedef struct H3dgsView {
+  int32_t image_width, image_height;
+  float tan_fovx, tan_fovy;
+  const float* viewmatrix; /* device [16], world->view, transposed (column-major when read linearly) */
+  const float* projmatrix; /* device [16], full projection, same convention */
+  const float* campos;     /* device [3] */
+  const float* background; /* device [3] */
+} H3dgsView;
+
+/*
+ * Gaussians submitted to one render.
+ *
+ * Plain mode (render_indices == NULL): P == store_rows, slot i reads row i.
+ *
+ * Fused-cut mode (render_indices != NULL): the attribute arrays are the whole model store
+ * [store_rows, ...]; slot i < K = P - skyboxnum renders row render_indices[i] blended with row
+ * parent_indices[i] by ts[i] exactly as gaussian_renderer.render_post does in Python
+ * (gaussian_renderer/__init__.py:202-235): x = t*x_child + (1-t)*x_parent for means, scales, SH and
+ * opacities, and rotations with the parent sign-flipped when dot(child,parent) < 0;
+ * parent_indices[i] == -1 means "no parent".  Slots i >= K are the skybox: store rows
+ * store_rows - skyboxnum + (i - K), never interpolated (HR/cuda_rasterizer/forward.cu:267-277 gives
+ * the same slot layout).  The same arithmetic is what the reference's native index path does in
+ * forward.cu:290-343,425; its backward for that path is incomplete (backward.cu:458-494), so the
+ * gradient contract here is the Python one.
+ *
+ * ts / kids are indexed by slot and may be longer than P (train_post.py:62-63).  When both are
+ * non-NULL, slots < P - skyboxnum use alpha = t*a + (1-t)*(1-(1-a)^(1/kids)) (forward.cu:537-546).
+ */
+typedef struct H3dgsGaussians {
+  int32_t P;          /* render slots */
+  int32_t store_rows; /* rows of the attribute arrays */
+  int32_t sh_degree;  /* active degree D, 0..3 */
+  int32_t sh_coeffs;  /* M = coefficients per row in shs (16 at degree 3); 0 when shs == NULL */
+  int32_t skyboxnum;
+  float scale_modifier;
+  const float* means3D;        /* [rows,3] */
+  const float* shs;            /* [rows,M,3] or NULL */
+  const float* colors_precomp; /* [rows,3] or NULL (exactly one of shs / colors_precomp) */
+  const float* opacities;      /* [rows,1] */
+  const float* scales;         /* [rows,3] or NULL */
+  const float* rotations;      /* [rows,4] or NULL */
+  const float* cov3D_precomp;  /* [rows,6] or NULL (exactly one of scales+rotations / cov3D_precomp) */
+  const int32_t* render_indices; /* [K] or NULL */
+  const int32_t* parent_indices; /* [K] or NULL */
+  const float* ts;               /* [>=P] or NULL */
+  const int32_t* kids;           /* [>=P] or NULL */
+} H3dgsGaussians;
+
+/* Workspace sizes.  geom: per-slot state (GeometryState, rasterizer_impl.cu:159-175);
+ * image: per-pixel + per-tile state (ImageState, :177-184);
+ * binning: instance keys/values + sort workspace (BinningState, :186-199). */
+H3DGS_API size_t h3dgs_geom_bytes(int32_t P);
+H3DGS_API size_t h3dgs_image_bytes(int32_t image_width, int32_t image_height);
+H3DGS_API size_t h3dgs_binning_bytes(int64_t num_rendered, int32_t image_width, int32_t image_height);
+
+/*
+ * Forward, stage 1: preprocess (EWA projection, SH, culling, fused interpolation) + tile-count scan.
+ * Replaces FORWARD::preprocess + cub::DeviceScan::InclusiveSum + the num_rendered read-back
+ * (rasterizer_impl.cu:275-325).  Writes radii[P] (0 = culled) and, after synchronising `stream`,
+ * *num_rendered_host.
+ */
+H3DGS_API int h3dgs_forward_preprocess(const H3dgsView* view, const H3dgsGaussians* g,
+                             int32_t* radii, void* geom, size_t geom_bytes,
+                             int64_t* num_rendered_host, int debug, h3dgs_stream_t stream);
+
+/*
+ * Forward, stage 2: instance emission, onesweep radix sort by (tile, depth), tile ranges, alpha blend.
+ * Replaces duplicateWithKeys + cub::DeviceRadixSort::SortPairs + identifyTileRanges + FORWARD::render
+ * (rasterizer_impl.cu:336-390).  out_color is [3,H,W]; out_invdepth is [1,H,W] or NULL.
+ * num_rendered == 0 only fills out_color with the background.
+ */
+H3DGS_API int h3dgs_forward_render(const H3dgsView* view, const H3dgsGaussians* g,
+                         void* geom, void* binning, size_t binning_bytes, void* image,
+                         int64_t num_rendered, float* out_color, float* out_invdepth,
+                         int debug, h3dgs_stream_t stream);
+
+/* Gradient outputs of the backward pass; any pointer may be NULL (that gradient is not produced).
+ * Row counts: dL_dmeans2D is per slot [P,3]; every other tensor is per store row [store_rows, ...]
+ * (in plain mode the two coincide, which is the reference layout, rasterize_points.cu:168-198).
+ * All non-NULL outputs are completely overwritten (no caller-side zero fill needed). */
+typedef struct H3dgsGrads {
+  float* dL_dmeans2D;   /* [P,3]  (z component is always 0) */
+  float* dL_dmeans3D;   /* [rows,3] */
+  float* dL_dsh;        /* [rows,M,3] */
+  float* dL_dcolors;    /* [rows,3]   (gradient of colors_precomp) */
+  float* dL_dopacity;   /* [rows,1] */
+  float* dL_dscales;    /* [rows,3] */
+  float* dL_drotations; /* [rows,4] */
+  float* dL_dcov3D;     /* [rows,6]   (gradient of cov3D_precomp) */
+} H3dgsGrads;
+
+H3DGS_API size_t h3dgs_backward_workspace_bytes(int32_t P);
+
+/*
+ * Backward.  Replaces BACKWARD::render + computeCov2DCUDA + BACKWARD::preprocess
+ * (rasterizer_impl.cu:397-510; HR/cuda_rasterizer/backward.cu:147-721).
+ * dL_dout_color is [3,H,W]; dL_dout_invdepth is [1,H,W] or NULL.  geom/binning/image are the
+ * buffers the forward filled for the same (view, g).
+ */
+H3DGS_API int h3dgs_backward(const H3dgsView* view, const H3dgsGaussians* g, const int32_t* radii,
+                   const void* geom, const void* binning, const void* image, int64_t num_rendered,
+                   const float* dL_dout_color, const float* dL_dout_invdepth,
+                   const H3dgsGrads* grads, void* workspace, size_t workspace_bytes,
+                   int debug, h3dgs_stream_t stream);
+
+/* Near-plane visibility mask; replaces Rasterizer::markVisible / checkFrustum
+ * (rasterizer_impl.cu:54-66,145-157).  present is uint8 [P] (torch.bool storage). */
+H3DGS_API int h3dgs_mark_visible(int32_t P, const float* means3D, const float* viewmatrix,
+                       const float* projmatrix, uint8_t* present, h3dgs_stream_t stream);
+
+/* Parity / debugging view into the opaque buffers (all device pointers into the given buffers).
+ * keys/values are the sorted instance list (BinningState::point_list_keys / point_list),
+ * ranges is uint2 per tile (ImageState::ranges). */
+typedef struct H3dgsDebugView {
+  const uint64_t* point_list_keys;
+  const uint32_t* point_list;
+  const uint32_t* ranges;        /* [tiles,2] */
+  const float* final_T;          /* [H*W] */
+  const uint32_t* n_contrib;     /* [H*W] */
+  const float* depths;           /* [P] */
+  const uint32_t* tiles_touched; /* [P] */
+  const uint32_t* point_offsets; /* [P] inclusive scan */
+  const float* records;          /* [P,16] packed per-slot record, see DESIGN.md */
+  const float* cov3D;            /* [P,6] */
+  const uint16_t* tile_rects;    /* [P,4] x0,y0,x1,y1 in tiles */
+} H3dgsDebugView;
+H3DGS_API int h3dgs_debug_view(int32_t P, int32_t image_width, int32_t image_height, int64_t num_rendered,
+                     const void* geom, const void* binning, const void* image, H3dgsDebugView* out);
+
+/* ------------------------------------------------------------------------------------------------
+ * Hierarchy cut.  Replaces Switching::expandToSize / getTsIndexed (GH/runtime_switching.cu:402-540)
+ * and Traversal::expandToTarget (GH/traversal.cpp:15-38) as bound by GH/torch/torch_interface.cpp:69-120.
+ * nodes is int32 [N,7] = (depth,parent,start,count_leafs,count_merged,start_children,count_children)
+ * (GH/types.h:51-60); boxes is fp32 [N,2,4] (GH/types.h:43-47).
+ * ------------------------------------------------------------------------------------------------ */
+H3DGS_API size_t h3dgs_expand_workspace_bytes(int32_t num_nodes);
+
+/* viewpoint is a DEVICE pointer to 3 floats (as in the reference, torch_interface.cpp:92).
+ * Writes render_indices / parent_indices / nodes_for_render_indices (each may be NULL except
+ * render_indices) and, after synchronising `stream`, the number of entries to *count_host. */
+H3DGS_API int h3dgs_expand_to_size(int32_t num_nodes, float target_size, const int32_t* nodes,
+                         const float* boxes, const float* viewpoint_dev,
+                         int32_t* render_indices, int32_t* parent_indices,
+                         int32_t* nodes_for_render_indices,
+                         void* workspace, size_t workspace_bytes,
+                         int32_t* count_host, h3dgs_stream_t stream);
+
+/* Viewpoint by value (the reference reads it on the host, torch_interface.cpp:116-117). */
+H3DGS_API int h3dgs_interpolation_weights(int32_t num_entries, const int32_t* node_indices, float target_size,
+                                const int32_t* nodes, const float* boxes,
+                                float vx, float vy, float vz,
+                                float* ts, int32_t* kids, h3dgs_stream_t stream);
+
+/* Host function on HOST nodes: DFS pre-order leaf/merged cut.  Call with out == NULL to get the
+ * count; returns the number of indices (>= 0) or a negative error. */
+H3DGS_API int64_t h3dgs_expand_to_target(int32_t num_nodes, const int32_t* nodes_host, int32_t target,
+                               int32_t* out_host, int64_t capacity);
+
+/* ------------------------------------------------------------------------------------------------
+ * .hier files.  Replaces HierarchyLoader::load / HierarchyWriter::write
+ * (GH/hierarchy_loader.cpp:26-128, GH/hierarchy_writer.cpp:27-118).  Host pointers.
+ * ------------------------------------------------------------------------------------------------ */
+H3DGS_API int h3dgs_hier_read_header(const char* path, int64_t* num_gaussians, int64_t* num_nodes, int* compressed);
+H3DGS_API int h3dgs_hier_read(const char* path, float* pos /*[P,3]*/, float* shs /*[P,48]*/, float* alphas /*[P]*/,
+                    float* scales /*[P,3]*/, float* rot /*[P,4]*/, int32_t* nodes /*[N,7]*/,
+                    float* boxes /*[N,8]*/);
+H3DGS_API int h3dgs_hier_write(const char* path, int64_t num_gaussians, int64_t num_nodes,
+                     const float* pos, const float* shs, const float* alphas, const float* log_scales,
+                     const float* rot, const int32_t* nodes, const float* boxes, int compressed);
+
+/* ------------------------------------------------------------------------------------------------
+ * Sparse Adam.  Replaces scene/OurAdam.py:249-337 (_single_tensor_adam: gather rows `relevant`,
+ * update moments and parameter, scatter back) for all parameter tensors of one step in one launch.
+ * step_size = lr / (1 - beta1^step) and bias_correction2_sqrt = sqrt(1 - beta2^step) are computed
+ * by the caller in double precision exactly as the reference does on the host.
+ * ------------------------------------------------------------------------------------------------ */
+typedef struct H3dgsAdamTensor {
+  float* param;        /* [rows,width] */
+  const float* grad;   /* [rows,width] */
+  float* exp_avg;      /* [rows,width] */
+  float* exp_avg_sq;   /* [rows,width] */
+  int32_t width;       /* floats per row */
+  float step_size;
+  float bias_correction2_sqrt;
+  float beta1, beta2, eps;
+} H3dgsAdamTensor;
+
+#define H3DGS_ADAM_MAX_TENSORS 8
+/* relevant: device int64 [num_relevant] row ids, or NULL for a dense update of rows [0,num_rows). */
+H3DGS_API int h3dgs_sparse_adam(const H3dgsAdamTensor* tensors, int32_t num_tensors,
+                      const int64_t* relevant, int64_t num_relevant, int64_t num_rows,
+                      h3dgs_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* H3DGS_B200_H_ */

@@ -1,0 +1,69 @@
+#!/usr/bin/env python
+"""TEST INFRASTRUCTURE ONLY -- builds the *unmodified* reference CUDA extensions for sm_100a.
+
+The reference sources are compiled where they lie under /root/reference (never copied);
+only build products land in ``oracle/_ref/`` (git-ignored, but shipped to the GPU box):
+
+    oracle/_ref/ref_hr_C.so   <- submodules/hierarchy-rasterizer  (rasterize_gaussians[_backward])
+    oracle/_ref/ref_gh_C.so   <- submodules/gaussianhierarchy     (expand_to_size, get_interpolation_weights, ...)
+
+These are the bit-exact oracle for ``tests/ -m gpu`` and the timed arm of
+``bench.py --impl reference``.  The product path never imports them.
+
+The reference's own build system (setup.py / cmake) is not run.  The one deviation from a
+stock build is ``-include cstdint``: cuda_rasterizer/rasterizer_impl.h uses std::uintptr_t
+without the header, which gcc 13 rejects.
+"""
+import os
+import sys
+import shutil
+
+REF = os.environ.get("H3DGS_REFERENCE_ROOT", "/root/reference")
+HERE = os.path.dirname(os.path.abspath(__file__))
+OUT = os.path.join(HERE, "_ref")
+
+
+def build(which=("hr", "gh"), verbose=True):
+    if not os.path.isdir(REF):
+        print(f"[build_ref] {REF} not present; nothing to do", file=sys.stderr)
+        return False
+    os.environ["TORCH_CUDA_ARCH_LIST"] = "10.0a"
+    os.environ.setdefault("MAX_JOBS", str(os.cpu_count() or 4))
+    from torch.utils.cpp_extension import load
+
+    os.makedirs(OUT, exist_ok=True)
+    ok = True
+    if "hr" in which and not os.path.exists(os.path.join(OUT, "ref_hr_C.so")):
+        hr = os.path.join(REF, "submodules/hierarchy-rasterizer")
+        bdir = os.path.join(OUT, "build_hr")
+        os.makedirs(bdir, exist_ok=True)
+        load(
+            name="ref_hr_C",
+            sources=[os.path.join(hr, s) for s in (
+                "cuda_rasterizer/rasterizer_impl.cu", "cuda_rasterizer/forward.cu",
+                "cuda_rasterizer/backward.cu", "rasterize_points.cu", "ext.cpp")],
+            extra_include_paths=[os.path.join(hr, "third_party/glm")],
+            extra_cflags=["-O3", "-include", "cstdint", "-w"],
+            extra_cuda_cflags=["-include", "cstdint", "-w", "-Xcompiler", "-fno-gnu-unique"],
+            build_directory=bdir, verbose=verbose, is_python_module=False)
+        shutil.copy2(os.path.join(bdir, "ref_hr_C.so"), os.path.join(OUT, "ref_hr_C.so"))
+    if "gh" in which and not os.path.exists(os.path.join(OUT, "ref_gh_C.so")):
+        gh = os.path.join(REF, "submodules/gaussianhierarchy")
+        bdir = os.path.join(OUT, "build_gh")
+        os.makedirs(bdir, exist_ok=True)
+        load(
+            name="ref_gh_C",
+            sources=[os.path.join(gh, s) for s in (
+                "hierarchy_loader.cpp", "hierarchy_writer.cpp", "traversal.cpp",
+                "runtime_switching.cu", "torch/torch_interface.cpp", "ext.cpp")],
+            extra_include_paths=[os.path.join(gh, "dependencies/eigen")],
+            extra_cflags=["-O3", "-include", "cstdint", "-w"],
+            extra_cuda_cflags=["-include", "cstdint", "-w"],
+            build_directory=bdir, verbose=verbose, is_python_module=False)
+        shutil.copy2(os.path.join(bdir, "ref_gh_C.so"), os.path.join(OUT, "ref_gh_C.so"))
+    return ok
+
+
+if __name__ == "__main__":
+    build(tuple(sys.argv[1:]) or ("hr", "gh"))
+    print("[build_ref] done:", sorted(f for f in os.listdir(OUT) if f.endswith(".so")))

@@ -1,0 +1,329 @@
+// extern "C" entry points of libh3dgs_b200.so (include/h3dgs_b200.h): argument checks, workspace carving,
+// kernel sequencing.  No torch, no allocation.
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+
+#include "common.cuh"
+
+namespace h3dgs {
+
+static thread_local char g_err[512] = "";
+
+int fail(int code, const char* what) {
+  std::snprintf(g_err, sizeof(g_err), "%s", what);
+  return code;
+}
+int cuda_fail(cudaError_t e, const char* what) {
+  std::snprintf(g_err, sizeof(g_err), "CUDA error %d (%s) in %s", (int)e, cudaGetErrorString(e), what);
+  return (int)e;
+}
+
+// H3DGS_STAGE=tma|ldgsts selects how the blend kernels stage records into shared memory.
+int blend_stage_mode() {
+  static int mode = -1;
+  if (mode < 0) {
+    const char* e = std::getenv("H3DGS_STAGE");
+    mode = (e && (std::strcmp(e, "tma") == 0 || std::strcmp(e, "bulk") == 0)) ? 1 : 0;
+  }
+  return mode;
+}
+
+size_t expand_ws_bytes(int N);
+cudaError_t run_expand_to_size(int N, float target_size, const int* nodes, const float* boxes,
+                               const float* viewpoint, int* render_indices, int* parent_indices,
+                               int* nodes_for_render_indices, void* workspace, int* count_host,
+                               cudaStream_t s);
+cudaError_t run_interpolation_weights(int K, const int* indices, float target_size, const int* nodes,
+                                      const float* boxes, float vx, float vy, float vz, float* ts,
+                                      int* kids, cudaStream_t s);
+cudaError_t run_sparse_adam(const H3dgsAdamTensor* tensors, int n, const long long* relevant,
+                            long long num_relevant, long long num_rows, cudaStream_t s);
+
+namespace {
+
+int check_scene(const H3dgsView* v, const H3dgsGaussians* g) {
+  if (!v || !g) return fail(H3DGS_EINVAL, "null view / gaussians");
+  if (v->image_width <= 0 || v->image_height <= 0) return fail(H3DGS_EINVAL, "image size must be positive");
+  if (!v->viewmatrix || !v->projmatrix || !v->campos || !v->background)
+    return fail(H3DGS_EINVAL, "viewmatrix, projmatrix, campos and background are required");
+  if (g->P < 0 || g->store_rows < 0) return fail(H3DGS_EINVAL, "negative sizes");
+  if (g->P == 0) return 0;
+  if (!g->means3D || !g->opacities) return fail(H3DGS_EINVAL, "means3D and opacities are required");
+  if ((g->shs == nullptr) == (g->colors_precomp == nullptr))
+    return fail(H3DGS_EINVAL, "Please provide excatly one of either SHs or precomputed colors!");
+  const bool sr = g->scales != nullptr && g->rotations != nullptr;
+  if ((!sr && g->cov3D_precomp == nullptr) || ((g->scales || g->rotations) && g->cov3D_precomp))
+    return fail(H3DGS_EINVAL,
+                "Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!");
+  if (g->shs && (g->sh_degree < 0 || g->sh_degree > 3 || (g->sh_degree + 1) * (g->sh_degree + 1) > g->sh_coeffs))
+    return fail(H3DGS_EINVAL, "sh_degree must be 0..3 and fit in sh_coeffs");
+  if (g->skyboxnum < 0 || g->skyboxnum > g->P) return fail(H3DGS_EINVAL, "skyboxnum out of range");
+  if (g->render_indices == nullptr) {
+    if (g->P != g->store_rows) return fail(H3DGS_EINVAL, "plain mode needs P == store_rows");
+  } else {
+    if (g->skyboxnum > g->store_rows) return fail(H3DGS_EINVAL, "skyboxnum exceeds store_rows");
+    if (g->parent_indices && !g->ts) return fail(H3DGS_EINVAL, "parent_indices needs interpolation weights");
+  }
+  if (g->rotations && (reinterpret_cast<size_t>(g->rotations) & 15))
+    return fail(H3DGS_EINVAL, "rotations must be 16-byte aligned");
+  return 0;
+}
+
+PreArgs make_pre(const H3dgsView* v, const H3dgsGaussians* g, int* radii, void* geom) {
+  PreArgs a;
+  std::memset(&a, 0, sizeof(a));
+  a.P = g->P; a.rows = g->store_rows; a.D = g->sh_degree; a.M = g->sh_coeffs; a.skyboxnum = g->skyboxnum;
+  a.W = v->image_width; a.H = v->image_height;
+  a.grid_x = (a.W + TILE_X - 1) / TILE_X; a.grid_y = (a.H + TILE_Y - 1) / TILE_Y;
+  a.scale_modifier = g->scale_modifier;
+  a.tan_fovx = v->tan_fovx; a.tan_fovy = v->tan_fovy;
+  a.focal_y = a.H / (2.0f * a.tan_fovy);   // rasterizer_impl.cu:241-242
+  a.focal_x = a.W / (2.0f * a.tan_fovx);
+  a.means = g->means3D; a.shs = g->shs; a.colors = g->colors_precomp; a.opac = g->opacities;
+  a.scales = g->scales; a.rots = g->rotations; a.cov3D_pre = g->cov3D_precomp;
+  a.idx = g->render_indices; a.pidx = g->render_indices ? g->parent_indices : nullptr;
+  a.ts = g->ts; a.kids = g->kids;
+  a.view = v->viewmatrix; a.proj = v->projmatrix; a.campos = v->campos;
+  a.radii = radii;
+  a.ws = GeomWs::make(geom, g->P);
+  return a;
+}
+
+int debug_sync(int debug, cudaStream_t s, const char* where) {
+  if (!debug) return 0;
+  cudaError_t e = cudaStreamSynchronize(s);
+  if (e == cudaSuccess) e = cudaGetLastError();
+  if (e != cudaSuccess) return cuda_fail(e, where);
+  return 0;
+}
+
+}  // namespace
+}  // namespace h3dgs
+
+using namespace h3dgs;
+
+extern "C" {
+
+int h3dgs_abi_version(void) { return H3DGS_ABI_VERSION; }
+const char* h3dgs_last_error(void) { return g_err; }
+
+size_t h3dgs_geom_bytes(int32_t P) { return GeomWs::make(nullptr, P).bytes; }
+size_t h3dgs_image_bytes(int32_t W, int32_t H) { return ImageWs::make(nullptr, W, H).bytes; }
+size_t h3dgs_binning_bytes(int64_t R, int32_t W, int32_t H) { return BinWs::make(nullptr, R, W, H).bytes; }
+size_t h3dgs_backward_workspace_bytes(int32_t P) { return BwdWs::make(nullptr, P).bytes; }
+size_t h3dgs_expand_workspace_bytes(int32_t N) { return expand_ws_bytes(N); }
+
+int h3dgs_forward_preprocess(const H3dgsView* view, const H3dgsGaussians* g, int32_t* radii, void* geom,
+                             size_t geom_bytes, int64_t* num_rendered_host, int debug,
+                             h3dgs_stream_t stream) {
+  int rc = check_scene(view, g);
+  if (rc) return rc;
+  if (!num_rendered_host) return fail(H3DGS_EINVAL, "num_rendered_host is required");
+  *num_rendered_host = 0;
+  if (g->P == 0) return 0;
+  if (!radii || !geom) return fail(H3DGS_EINVAL, "radii and geom are required");
+  if (geom_bytes < h3dgs_geom_bytes(g->P)) return fail(H3DGS_ENOSPACE, "geom workspace too small");
+  if (reinterpret_cast<size_t>(geom) & 15) return fail(H3DGS_EINVAL, "geom must be 16-byte aligned");
+  cudaStream_t s = (cudaStream_t)stream;
+  PreArgs a = make_pre(view, g, radii, geom);
+  H3_CUDA(launch_preprocess_fwd(a, s));
+  if ((rc = debug_sync(debug, s, "preprocess_fwd"))) return rc;
+  H3_CUDA(launch_scan_inclusive(a.ws.tiles_touched, a.ws.offsets, g->P, a.ws.scan_status, a.ws.counters, s));
+  unsigned long long total = 0;
+  H3_CUDA(cudaMemcpyAsync(&total, a.ws.counters + 2, sizeof(total), cudaMemcpyDeviceToHost, s));
+  H3_CUDA(cudaStreamSynchronize(s));
+  if (total >= (1ull << 30)) return fail(H3DGS_EINVAL, "more than 2^30 tile instances");
+  *num_rendered_host = (int64_t)total;
+  return 0;
+}
+
+int h3dgs_forward_render(const H3dgsView* view, const H3dgsGaussians* g, void* geom, void* binning,
+                         size_t binning_bytes, void* image, int64_t R, float* out_color,
+                         float* out_invdepth, int debug, h3dgs_stream_t stream) {
+  int rc = check_scene(view, g);
+  if (rc) return rc;
+  if (!out_color) return fail(H3DGS_EINVAL, "out_color is required");
+  cudaStream_t s = (cudaStream_t)stream;
+  const int W = view->image_width, H = view->image_height;
+  const size_t plane = (size_t)W * H;
+  if (g->P == 0 || R <= 0) {
+    // nothing to blend: the reference returns the zero-initialised image here (rasterizer_impl.cu:327-328)
+    H3_CUDA(cudaMemsetAsync(out_color, 0, plane * 3 * sizeof(float), s));
+    if (out_invdepth) H3_CUDA(cudaMemsetAsync(out_invdepth, 0, plane * sizeof(float), s));
+    if (image) {
+      ImageWs iw = ImageWs::make(image, W, H);
+      H3_CUDA(cudaMemsetAsync(iw.n_contrib, 0, plane * sizeof(uint32_t), s));
+    }
+    return 0;
+  }
+  if (!geom || !binning || !image) return fail(H3DGS_EINVAL, "geom, binning and image are required");
+  if (binning_bytes < h3dgs_binning_bytes(R, W, H)) return fail(H3DGS_ENOSPACE, "binning workspace too small");
+  GeomWs gw = GeomWs::make(geom, g->P);
+  BinWs bw = BinWs::make(binning, R, W, H);
+  ImageWs iw = ImageWs::make(image, W, H);
+  const int grid_x = (W + TILE_X - 1) / TILE_X, grid_y = (H + TILE_Y - 1) / TILE_Y;
+  const SortPlan plan = make_sort_plan(W, H);
+
+  // radii > 0 <=> tiles_touched > 0; use the workspace copy so that radii need not be passed again
+  H3_CUDA(launch_emit_instances(g->P, reinterpret_cast<const int*>(gw.tiles_touched), gw, grid_x,
+                                bw.keys[0], bw.vals[0], s));
+  if ((rc = debug_sync(debug, s, "emit_instances"))) return rc;
+  H3_CUDA(launch_radix_sort(bw, R, plan, s));
+  if ((rc = debug_sync(debug, s, "radix_sort"))) return rc;
+  H3_CUDA(launch_tile_ranges(R, bw.keys[bw.sorted], iw.ranges, grid_x * grid_y, s));
+  if ((rc = debug_sync(debug, s, "tile_ranges"))) return rc;
+
+  BlendArgs b;
+  std::memset(&b, 0, sizeof(b));
+  b.W = W; b.H = H; b.grid_x = grid_x; b.grid_y = grid_y; b.P = g->P; b.skyboxnum = g->skyboxnum;
+  b.interp = (g->ts != nullptr && g->kids != nullptr) ? 1 : 0;
+  b.ranges = iw.ranges; b.point_list = bw.vals[bw.sorted]; b.rec = gw.rec; b.bg = view->background;
+  b.final_T = iw.final_T; b.n_contrib = iw.n_contrib; b.accum = iw.accum;
+  b.out_color = out_color; b.out_invdepth = out_invdepth;
+  H3_CUDA(launch_blend_fwd(b, s));
+  if ((rc = debug_sync(debug, s, "blend_fwd"))) return rc;
+  return 0;
+}
+
+int h3dgs_backward(const H3dgsView* view, const H3dgsGaussians* g, const int32_t* radii, const void* geom,
+                   const void* binning, const void* image, int64_t R, const float* dL_dout_color,
+                   const float* dL_dout_invdepth, const H3dgsGrads* grads, void* workspace,
+                   size_t workspace_bytes, int debug, h3dgs_stream_t stream) {
+  int rc = check_scene(view, g);
+  if (rc) return rc;
+  if (!grads) return fail(H3DGS_EINVAL, "grads is required");
+  cudaStream_t s = (cudaStream_t)stream;
+  const int P = g->P, W = view->image_width, H = view->image_height;
+  const size_t rows = (size_t)g->store_rows;
+  const int M = g->sh_coeffs;
+  const bool fused = g->render_indices != nullptr;
+
+  auto zero = [&](float* p, size_t n) -> cudaError_t {
+    return p ? cudaMemsetAsync(p, 0, n * sizeof(float), s) : cudaSuccess;
+  };
+  if (P == 0 || R <= 0 || fused) {
+    // fused-cut mode scatters into store rows; empty renders produce all-zero gradients
+    H3_CUDA(zero(grads->dL_dmeans3D, rows * 3));
+    H3_CUDA(zero(grads->dL_dsh, rows * (size_t)M * 3));
+    H3_CUDA(zero(grads->dL_dcolors, rows * 3));
+    H3_CUDA(zero(grads->dL_dopacity, rows));
+    H3_CUDA(zero(grads->dL_dscales, rows * 3));
+    H3_CUDA(zero(grads->dL_drotations, rows * 4));
+    H3_CUDA(zero(grads->dL_dcov3D, rows * 6));
+  }
+  if (P == 0 || R <= 0) {
+    H3_CUDA(zero(grads->dL_dmeans2D, (size_t)P * 3));
+    return 0;
+  }
+  if (!radii || !geom || !binning || !image || !dL_dout_color || !workspace)
+    return fail(H3DGS_EINVAL, "radii, geom, binning, image, dL_dout_color and workspace are required");
+  if (workspace_bytes < h3dgs_backward_workspace_bytes(P)) return fail(H3DGS_ENOSPACE, "backward workspace too small");
+
+  GeomWs gw = GeomWs::make(const_cast<void*>(geom), P);
+  BinWs bw = BinWs::make(const_cast<void*>(binning), R, W, H);
+  ImageWs iw = ImageWs::make(const_cast<void*>(image), W, H);
+  BwdWs ww = BwdWs::make(workspace, P);
+  H3_CUDA(cudaMemsetAsync(ww.grad, 0, sizeof(GradRec) * (size_t)P, s));
+
+  BlendArgs b;
+  std::memset(&b, 0, sizeof(b));
+  b.W = W; b.H = H; b.grid_x = (W + TILE_X - 1) / TILE_X; b.grid_y = (H + TILE_Y - 1) / TILE_Y;
+  b.P = P; b.skyboxnum = g->skyboxnum;
+  b.interp = (g->ts != nullptr && g->kids != nullptr) ? 1 : 0;
+  b.ranges = iw.ranges; b.point_list = bw.vals[bw.sorted]; b.rec = gw.rec; b.bg = view->background;
+  b.final_T = iw.final_T; b.n_contrib = iw.n_contrib; b.accum = iw.accum;
+  b.dL_dcolor = dL_dout_color; b.dL_dinvdepth = dL_dout_invdepth; b.grad = ww.grad;
+  H3_CUDA(launch_blend_bwd(b, s));
+  if ((rc = debug_sync(debug, s, "blend_bwd"))) return rc;
+
+  PreBwdArgs pb;
+  pb.f = make_pre(view, g, const_cast<int*>(radii), const_cast<void*>(geom));
+  pb.grad = ww.grad;
+  pb.has_invdepth = dL_dout_invdepth != nullptr;
+  pb.out = *grads;
+  H3_CUDA(launch_preprocess_bwd(pb, s));
+  if ((rc = debug_sync(debug, s, "preprocess_bwd"))) return rc;
+  return 0;
+}
+
+int h3dgs_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                       uint8_t* present, h3dgs_stream_t stream) {
+  if (P < 0) return fail(H3DGS_EINVAL, "negative P");
+  if (P == 0) return 0;
+  if (!means3D || !viewmatrix || !projmatrix || !present) return fail(H3DGS_EINVAL, "null argument");
+  H3_CUDA(launch_mark_visible(P, means3D, viewmatrix, projmatrix, present, (cudaStream_t)stream));
+  return 0;
+}
+
+int h3dgs_debug_view(int32_t P, int32_t W, int32_t H, int64_t R, const void* geom, const void* binning,
+                     const void* image, H3dgsDebugView* out) {
+  if (!out) return fail(H3DGS_EINVAL, "null out");
+  std::memset(out, 0, sizeof(*out));
+  if (geom) {
+    GeomWs gw = GeomWs::make(const_cast<void*>(geom), P);
+    out->depths = gw.depth;
+    out->tiles_touched = gw.tiles_touched;
+    out->point_offsets = gw.offsets;
+    out->records = reinterpret_cast<const float*>(gw.rec);
+    out->cov3D = gw.cov3D;
+    out->tile_rects = reinterpret_cast<const uint16_t*>(gw.tile_rect);
+  }
+  if (binning && R > 0) {
+    BinWs bw = BinWs::make(const_cast<void*>(binning), R, W, H);
+    out->point_list_keys = reinterpret_cast<const uint64_t*>(bw.keys[bw.sorted]);
+    out->point_list = bw.vals[bw.sorted];
+  }
+  if (image) {
+    ImageWs iw = ImageWs::make(const_cast<void*>(image), W, H);
+    out->ranges = reinterpret_cast<const uint32_t*>(iw.ranges);
+    out->final_T = iw.final_T;
+    out->n_contrib = iw.n_contrib;
+  }
+  return 0;
+}
+
+int h3dgs_expand_to_size(int32_t N, float target_size, const int32_t* nodes, const float* boxes,
+                         const float* viewpoint_dev, int32_t* render_indices, int32_t* parent_indices,
+                         int32_t* nodes_for_render_indices, void* workspace, size_t workspace_bytes,
+                         int32_t* count_host, h3dgs_stream_t stream) {
+  if (N < 0) return fail(H3DGS_EINVAL, "negative node count");
+  if (!count_host) return fail(H3DGS_EINVAL, "count_host is required");
+  *count_host = 0;
+  if (N == 0) return 0;
+  if (!nodes || !boxes || !viewpoint_dev || !render_indices || !workspace)
+    return fail(H3DGS_EINVAL, "nodes, boxes, viewpoint, render_indices and workspace are required");
+  if (reinterpret_cast<size_t>(boxes) & 15) return fail(H3DGS_EINVAL, "boxes must be 16-byte aligned");
+  if (workspace_bytes < expand_ws_bytes(N)) return fail(H3DGS_ENOSPACE, "expand workspace too small");
+  H3_CUDA(run_expand_to_size(N, target_size, nodes, boxes, viewpoint_dev, render_indices, parent_indices,
+                             nodes_for_render_indices, workspace, count_host, (cudaStream_t)stream));
+  return 0;
+}
+
+int h3dgs_interpolation_weights(int32_t K, const int32_t* node_indices, float target_size,
+                                const int32_t* nodes, const float* boxes, float vx, float vy, float vz,
+                                float* ts, int32_t* kids, h3dgs_stream_t stream) {
+  if (K < 0) return fail(H3DGS_EINVAL, "negative entry count");
+  if (K == 0) return 0;
+  if (!node_indices || !nodes || !boxes || !ts || !kids) return fail(H3DGS_EINVAL, "null argument");
+  if (reinterpret_cast<size_t>(boxes) & 15) return fail(H3DGS_EINVAL, "boxes must be 16-byte aligned");
+  H3_CUDA(run_interpolation_weights(K, node_indices, target_size, nodes, boxes, vx, vy, vz, ts, kids,
+                                    (cudaStream_t)stream));
+  return 0;
+}
+
+int h3dgs_sparse_adam(const H3dgsAdamTensor* tensors, int32_t num_tensors, const int64_t* relevant,
+                      int64_t num_relevant, int64_t num_rows, h3dgs_stream_t stream) {
+  if (!tensors || num_tensors <= 0 || num_tensors > H3DGS_ADAM_MAX_TENSORS)
+    return fail(H3DGS_EINVAL, "1..H3DGS_ADAM_MAX_TENSORS tensors required");
+  for (int i = 0; i < num_tensors; ++i) {
+    if (!tensors[i].param || !tensors[i].grad || !tensors[i].exp_avg || !tensors[i].exp_avg_sq || tensors[i].width <= 0)
+      return fail(H3DGS_EINVAL, "adam tensor with null pointer or non-positive width");
+  }
+  if (num_relevant < 0 || num_rows < 0) return fail(H3DGS_EINVAL, "negative row count");
+  H3_CUDA(run_sparse_adam(tensors, num_tensors, reinterpret_cast<const long long*>(relevant), num_relevant,
+                          num_rows, (cudaStream_t)stream));
+  return 0;
+}
+
+}  // extern "C"

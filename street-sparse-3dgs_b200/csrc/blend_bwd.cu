@@ -1,0 +1,274 @@
+// Backward tile alpha blend.  Replaces renderCUDA of HR/cuda_rasterizer/backward.cu:498-721.
+//
+// Same tiling, staging and per-warp culling as the forward kernel, walking each pixel's list front to
+// back so that T and alpha are recomputed by the very operations the forward used.  The reference's
+// back-to-front recursion  dL/dalpha_i = T_i (c_i - A_i).g - T_final/(1-alpha_i) bg.g  is evaluated
+// in the equivalent prefix form
+//     dL/dalpha_i = T_i u_i - (U_total + T_final bg.g - sum_{j<=i} w_j u_j) / (1 - alpha_i),
+// with u_j = c_j.g + invdepth_j gD and U_total taken from the per-pixel sums the forward stored.
+//
+// Gradient reduction: per (warp, Gaussian) the ten partial sums are reduced with warp shuffles, added
+// into a per-CTA shared-memory accumulator, and flushed once per (tile, Gaussian) with three vector
+// red.global.add instructions -- instead of the reference's ten global atomics per (pixel, Gaussian).
+#include "blend_common.cuh"
+
+namespace h3dgs {
+
+namespace {
+
+constexpr int ACC_W = 12;  // 10 sums, padded to a multiple of four words
+
+struct BwdSmem {
+  Rec rec[2][BLEND_BATCH];
+  float acc[BLEND_BATCH][ACC_W];
+  unsigned long long bar[2];
+  int red[BLEND_THREADS / 32];
+};
+
+template <bool INTERP, bool DEPTH, bool TMA>
+__global__ void __launch_bounds__(BLEND_THREADS) blend_bwd_kernel(const BlendArgs a) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  BwdSmem& sm = *reinterpret_cast<BwdSmem*>(smem_raw);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int tile = blockIdx.x;
+  const int tx = tile % a.grid_x, ty = tile / a.grid_x;
+  const int bx0 = tx * TILE_X + (warp & 1) * SUB_W;
+  const int by0 = ty * TILE_Y + (warp >> 1) * SUB_H;
+  const int px = bx0 + (lane & 7), py = by0 + (lane >> 3);
+  const bool inside = px < a.W && py < a.H;
+  const float pixx = (float)px, pixy = (float)py;
+  const float fx0 = (float)bx0, fy0 = (float)by0;
+  const size_t pix = (size_t)py * a.W + px;
+  const size_t plane = (size_t)a.W * a.H;
+
+  const uint2 range = a.ranges[tile];
+  const int n = (int)(range.y - range.x);
+  const uint32_t* __restrict__ list = a.point_list + range.x;
+  constexpr unsigned REC_BYTES = INTERP ? 64u : 48u;
+
+  // per-pixel constants
+  int last = 0;
+  float g0 = 0.f, g1 = 0.f, g2 = 0.f, gD = 0.f, Urest = 0.f;
+  if (inside) {
+    last = (int)a.n_contrib[pix];
+    g0 = a.dL_dcolor[pix];
+    g1 = a.dL_dcolor[plane + pix];
+    g2 = a.dL_dcolor[2 * plane + pix];
+    if (DEPTH) gD = a.dL_dinvdepth[pix];
+    const float4 acc = a.accum[pix];
+    const float Tf = a.final_T[pix];
+    const float bgdot = a.bg[0] * g0 + a.bg[1] * g1 + a.bg[2] * g2;
+    Urest = acc.x * g0 + acc.y * g1 + acc.z * g2 + (DEPTH ? acc.w * gD : 0.f) + Tf * bgdot;
+  }
+  // how far does this warp / this CTA have to walk?
+  int wlast = last;
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) wlast = max(wlast, __shfl_xor_sync(0xffffffffu, wlast, d));
+  if (lane == 0) sm.red[warp] = wlast;
+  for (int i = tid; i < BLEND_BATCH * ACC_W; i += BLEND_THREADS) (&sm.acc[0][0])[i] = 0.f;
+  if (TMA && tid == 0) {
+    mbar_init(&sm.bar[0], 1);
+    mbar_init(&sm.bar[1], 1);
+    mbar_fence_init();
+  }
+  __syncthreads();
+  int blast = 0;
+#pragma unroll
+  for (int w = 0; w < BLEND_THREADS / 32; ++w) blast = max(blast, sm.red[w]);
+  const int rounds = (min(blast, n) + BLEND_BATCH - 1) / BLEND_BATCH;
+  if (rounds == 0) return;
+  const int nn = min(blast, n);  // entries that matter to anyone in this tile
+
+  auto issue = [&](int b, uint32_t id) {
+    const int j = b * BLEND_BATCH + tid;
+    const int s = b & 1;
+    if (TMA) {
+      if (tid == 0) {
+        const int cnt = min(BLEND_BATCH, nn - b * BLEND_BATCH);
+        mbar_expect_tx(&sm.bar[s], (unsigned)cnt * REC_BYTES);
+      }
+      if (j < nn) bulk_g2s(&sm.rec[s][tid], a.rec + id, REC_BYTES, &sm.bar[s]);
+    } else {
+      if (j < nn) {
+        const char* src = reinterpret_cast<const char*>(a.rec + id);
+        char* dst = reinterpret_cast<char*>(&sm.rec[s][tid]);
+        cp_async16(dst, src);
+        cp_async16(dst + 16, src + 16);
+        cp_async16(dst + 32, src + 32);
+        if (INTERP) cp_async16(dst + 48, src + 48);
+      }
+      cp_async_commit();
+    }
+  };
+
+  float T = 1.0f, Upre = 0.f;
+  const float half_w = 0.5f * (float)a.W, half_h = 0.5f * (float)a.H;
+
+  uint32_t id_cur = (tid < nn) ? __ldg(list + tid) : 0u;
+  issue(0, id_cur);
+  uint32_t id_next = (BLEND_BATCH + tid < nn) ? __ldg(list + BLEND_BATCH + tid) : 0u;
+
+  for (int b = 0; b < rounds; ++b) {
+    const int s = b & 1;
+    uint32_t id_after = 0;
+    if (b + 1 < rounds) {
+      issue(b + 1, id_next);
+      const int j2 = (b + 2) * BLEND_BATCH + tid;
+      id_after = (j2 < nn) ? __ldg(list + j2) : 0u;
+      if (!TMA) cp_async_wait<1>();
+    } else {
+      if (!TMA) cp_async_wait<0>();
+    }
+    if (TMA) mbar_wait(&sm.bar[s], (unsigned)((b >> 1) & 1));
+    __syncthreads();  // records of round b visible; accumulator zeroed by the previous flush
+
+    const int base = b * BLEND_BATCH;
+    const int cnt = min(BLEND_BATCH, nn - base);
+    const int wcnt = min(cnt, wlast - base);  // entries this warp still cares about
+    const Rec* __restrict__ recs = sm.rec[s];
+    for (int c = 0; c < wcnt; c += 32) {
+      const int j = c + lane;
+      bool hit = false;
+      if (j < wcnt) hit = block_hit(recs[j].q0, fx0, fy0);
+      unsigned m = __ballot_sync(0xffffffffu, hit);
+      while (m) {
+        const int jj = c + __ffs(m) - 1;
+        m &= m - 1;
+        float v0 = 0.f, v1 = 0.f, v2 = 0.f, v3 = 0.f, v4 = 0.f, v5 = 0.f, v6 = 0.f, v7 = 0.f,
+              v8 = 0.f, v9 = 0.f;
+        bool contrib = false;
+        if (base + jj < last) {
+          const float4 q0 = recs[jj].q0;
+          const float4 con_o = recs[jj].q1;
+          const float dx = q0.x - pixx, dy = q0.y - pixy;
+          const float power = -0.5f * (con_o.x * dx * dx + con_o.z * dy * dy) - con_o.y * dx * dy;
+          if (!(power > 0.0f)) {
+            const float G = exp(power);
+            const float test_alpha = con_o.w * G;
+            const float my_alpha = min(0.99f, test_alpha);
+            float alpha = my_alpha;
+            float opac_mult = 1.0f;
+            if (INTERP) {
+              const float4 q3 = recs[jj].q3;
+              if (q3.x != 1.0f) {
+                const float om = 1.0f - my_alpha;
+                const float root = __powf(om, q3.y);  // (1-a)^(1/k), as the forward evaluated it
+                alpha = q3.x * my_alpha + (1.0f - q3.x) * (1.0f - root);
+                // d alpha / d a = t + (1-t) (1/k) (1-a)^(1/k - 1)      (backward.cu:714)
+                opac_mult = q3.x - __fdividef(root, om) * (q3.x - 1.0f) * q3.y;
+              }
+            }
+            if (!(alpha < 1.0f / 255.0f)) {
+              contrib = true;
+              const float4 q2 = recs[jj].q2;
+              const float one_m = 1 - alpha;
+              const float w = alpha * T;
+              float u = q2.x * g0 + q2.y * g1 + q2.z * g2;
+              if (DEPTH) u += q2.w * gD;
+              Upre += w * u;
+              float dL_dalpha = T * u - __fdividef(Urest - Upre, one_m);
+              T = T * one_m;
+              if (test_alpha > 0.99f) dL_dalpha = 0.f;  // clamped alpha passes no gradient (backward.cu:619,693)
+              const float dL_dG = con_o.w * dL_dalpha;
+              const float gdx = G * dx, gdy = G * dy;
+              v0 = dL_dG * gdx;
+              v1 = dL_dG * gdy;
+              v2 = v0 * dx;
+              v3 = v0 * dy;
+              v4 = v1 * dy;
+              v5 = opac_mult * G * dL_dalpha;
+              v6 = w * g0;
+              v7 = w * g1;
+              v8 = w * g2;
+              if (DEPTH) v9 = w * gD;
+            }
+          }
+        }
+        if (__any_sync(0xffffffffu, contrib)) {
+#pragma unroll
+          for (int d = 16; d > 0; d >>= 1) {
+            v0 += __shfl_xor_sync(0xffffffffu, v0, d);
+            v1 += __shfl_xor_sync(0xffffffffu, v1, d);
+            v2 += __shfl_xor_sync(0xffffffffu, v2, d);
+            v3 += __shfl_xor_sync(0xffffffffu, v3, d);
+            v4 += __shfl_xor_sync(0xffffffffu, v4, d);
+            v5 += __shfl_xor_sync(0xffffffffu, v5, d);
+            v6 += __shfl_xor_sync(0xffffffffu, v6, d);
+            v7 += __shfl_xor_sync(0xffffffffu, v7, d);
+            v8 += __shfl_xor_sync(0xffffffffu, v8, d);
+            if (DEPTH) v9 += __shfl_xor_sync(0xffffffffu, v9, d);
+          }
+          // lane k deposits sum k: ten lanes, ten different banks
+          float mine = v0;
+          mine = lane == 1 ? v1 : mine;
+          mine = lane == 2 ? v2 : mine;
+          mine = lane == 3 ? v3 : mine;
+          mine = lane == 4 ? v4 : mine;
+          mine = lane == 5 ? v5 : mine;
+          mine = lane == 6 ? v6 : mine;
+          mine = lane == 7 ? v7 : mine;
+          mine = lane == 8 ? v8 : mine;
+          mine = lane == 9 ? v9 : mine;
+          if (lane < (DEPTH ? 10 : 9)) atomicAdd(&sm.acc[jj][lane], mine);
+        }
+      }
+    }
+    __syncthreads();  // all partial sums of this round are in the accumulator
+
+    // flush: thread t owns list entry base + t
+    if (tid < cnt) {
+      float4 s0 = *reinterpret_cast<float4*>(&sm.acc[tid][0]);
+      float4 s1 = *reinterpret_cast<float4*>(&sm.acc[tid][4]);
+      float2 s2 = *reinterpret_cast<float2*>(&sm.acc[tid][8]);
+      const bool any = (s0.x != 0.f) | (s0.y != 0.f) | (s0.z != 0.f) | (s0.w != 0.f) | (s1.x != 0.f) |
+                       (s1.y != 0.f) | (s1.z != 0.f) | (s1.w != 0.f) | (s2.x != 0.f) | (s2.y != 0.f);
+      if (any) {
+        const float4 con_o = recs[tid].q1;
+        // dL/dmean2D from dG/ddelta (backward.cu:699-704), dL/dconic (backward.cu:707-709)
+        const float mx = -(s0.x * con_o.x + s0.y * con_o.y) * half_w;
+        const float my = -(s0.y * con_o.z + s0.x * con_o.y) * half_h;
+        float* gr = a.grad[id_cur].v;
+        red_add_v4(gr, mx, my, -0.5f * s0.z, -0.5f * s0.w);
+        red_add_v4(gr + 4, -0.5f * s1.x, s1.y, s1.z, s1.w);
+        red_add_v2(gr + 8, s2.x, s2.y);
+        *reinterpret_cast<float4*>(&sm.acc[tid][0]) = make_float4(0.f, 0.f, 0.f, 0.f);
+        *reinterpret_cast<float4*>(&sm.acc[tid][4]) = make_float4(0.f, 0.f, 0.f, 0.f);
+        *reinterpret_cast<float2*>(&sm.acc[tid][8]) = make_float2(0.f, 0.f);
+      }
+    }
+    id_cur = id_next;
+    id_next = id_after;
+  }
+}
+
+template <bool INTERP, bool DEPTH>
+cudaError_t launch2(const BlendArgs& a, bool tma, cudaStream_t s) {
+  const int tiles = a.grid_x * a.grid_y;
+  const size_t smem = sizeof(BwdSmem);
+  cudaError_t e;
+  if (tma) {
+    auto k = blend_bwd_kernel<INTERP, DEPTH, true>;
+    e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    k<<<tiles, BLEND_THREADS, smem, s>>>(a);
+  } else {
+    auto k = blend_bwd_kernel<INTERP, DEPTH, false>;
+    e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    k<<<tiles, BLEND_THREADS, smem, s>>>(a);
+  }
+  return cudaGetLastError();
+}
+
+}  // namespace
+
+int blend_stage_mode();
+
+cudaError_t launch_blend_bwd(const BlendArgs& a, cudaStream_t s) {
+  const bool tma = blend_stage_mode() == 1;
+  const bool depth = a.dL_dinvdepth != nullptr;
+  if (a.interp) return depth ? launch2<true, true>(a, tma, s) : launch2<true, false>(a, tma, s);
+  return depth ? launch2<false, true>(a, tma, s) : launch2<false, false>(a, tma, s);
+}
+
+}  // namespace h3dgs

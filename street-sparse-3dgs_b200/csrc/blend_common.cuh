@@ -1,0 +1,82 @@
+// Shared-memory staging of per-slot records for the tile blend kernels, and the per-pair alpha
+// evaluation used identically by the forward and backward passes.
+#pragma once
+#include "common.cuh"
+
+namespace h3dgs {
+
+constexpr int BLEND_THREADS = 256;
+constexpr int BLEND_BATCH = 256;   // list entries staged per round (HR/cuda_rasterizer/forward.cu:478-512 uses 256 too)
+constexpr int SUB_W = 8;           // each warp owns an 8x4 pixel block of the 16x16 tile
+constexpr int SUB_H = 4;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+
+// ---- Ampere-style async copy (LDGSTS), 16 bytes per instruction ----
+__device__ __forceinline__ void cp_async16(void* dst_smem, const void* src_gmem) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(smem_u32(dst_smem)), "l"(src_gmem)
+               : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory");
+}
+
+// ---- bulk async copy engine (TMA, 1-D): one instruction moves a whole record, completion by mbarrier ----
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_fence_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(smem_u32(bar)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(unsigned long long* bar, unsigned parity) {
+  unsigned ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}\n"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity) {
+  unsigned spins = 0;
+  while (!mbar_try_wait(bar, parity)) {
+    if (++spins > (1u << 26)) __trap();  // never hang the GPU on a lost transaction
+  }
+}
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, unsigned bytes,
+                                         unsigned long long* bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::"r"(
+          smem_u32(dst_smem)),
+      "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+      : "memory");
+}
+
+// vector reduction to global memory (sm_90+): one instruction adds four floats
+__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};\n" ::"l"(addr), "f"(a), "f"(b), "f"(c),
+               "f"(d)
+               : "memory");
+}
+__device__ __forceinline__ void red_add_v2(float* addr, float a, float b) {
+  asm volatile("red.global.add.v2.f32 [%0], {%1, %2};\n" ::"l"(addr), "f"(a), "f"(b) : "memory");
+}
+
+// Does the region where a Gaussian can reach alpha >= 1/255 (centre q0.xy, half extents q0.zw) touch the
+// pixel block [x0, x0+SUB_W-1] x [y0, y0+SUB_H-1]?
+__device__ __forceinline__ bool block_hit(const float4& q0, float x0, float y0) {
+  return (q0.x + q0.z >= x0) && (q0.x - q0.z <= x0 + (float)(SUB_W - 1)) && (q0.y + q0.w >= y0) &&
+         (q0.y - q0.w <= y0 + (float)(SUB_H - 1));
+}
+
+}  // namespace h3dgs

@@ -1,0 +1,182 @@
+// Forward tile alpha blend.  Replaces renderCUDA of HR/cuda_rasterizer/forward.cu:439-584.
+//
+// One CTA per 16x16 tile, eight warps each owning an 8x4 pixel block.  Per round, 256 list entries are
+// staged into shared memory as 64-byte records (double buffered; by the bulk-copy engine or LDGSTS).
+// Each warp first tests 32 staged entries at a time against its pixel block (one entry per lane, a
+// ballot gives the survivors) and only evaluates survivors per pixel, in list order, so every pixel
+// sees exactly the sequence of blends the reference performs: alpha, the 1/255 and T<1e-4 decisions,
+// n_contrib and final_T are bit-identical.  Warps retire as soon as their 32 pixels are saturated.
+#include "blend_common.cuh"
+
+namespace h3dgs {
+
+namespace {
+
+struct FwdSmem {
+  Rec rec[2][BLEND_BATCH];
+  unsigned long long bar[2];
+};
+
+template <bool INTERP, bool DEPTH, bool TMA>
+__global__ void __launch_bounds__(BLEND_THREADS) blend_fwd_kernel(const BlendArgs a) {
+  __shared__ FwdSmem sm;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int tile = blockIdx.x;
+  const int tx = tile % a.grid_x, ty = tile / a.grid_x;
+  const int bx0 = tx * TILE_X + (warp & 1) * SUB_W;
+  const int by0 = ty * TILE_Y + (warp >> 1) * SUB_H;
+  const int px = bx0 + (lane & 7), py = by0 + (lane >> 3);
+  const bool inside = px < a.W && py < a.H;
+  const float pixx = (float)px, pixy = (float)py;
+  const float fx0 = (float)bx0, fy0 = (float)by0;
+
+  const uint2 range = a.ranges[tile];
+  const int n = (int)(range.y - range.x);
+  const int rounds = (n + BLEND_BATCH - 1) / BLEND_BATCH;
+  const uint32_t* __restrict__ list = a.point_list + range.x;
+  constexpr unsigned REC_BYTES = INTERP ? 64u : 48u;
+
+  if (TMA) {
+    if (tid == 0) {
+      mbar_init(&sm.bar[0], 1);
+      mbar_init(&sm.bar[1], 1);
+      mbar_fence_init();
+    }
+    __syncthreads();
+  }
+
+  auto issue = [&](int b, uint32_t id) {
+    const int j = b * BLEND_BATCH + tid;
+    const int s = b & 1;
+    if (TMA) {
+      if (tid == 0) {
+        const int cnt = min(BLEND_BATCH, n - b * BLEND_BATCH);
+        mbar_expect_tx(&sm.bar[s], (unsigned)cnt * REC_BYTES);
+      }
+      if (j < n) bulk_g2s(&sm.rec[s][tid], a.rec + id, REC_BYTES, &sm.bar[s]);
+    } else {
+      if (j < n) {
+        const char* src = reinterpret_cast<const char*>(a.rec + id);
+        char* dst = reinterpret_cast<char*>(&sm.rec[s][tid]);
+        cp_async16(dst, src);
+        cp_async16(dst + 16, src + 16);
+        cp_async16(dst + 32, src + 32);
+        if (INTERP) cp_async16(dst + 48, src + 48);
+      }
+      cp_async_commit();
+    }
+  };
+
+  float T = 1.0f;
+  float C0 = 0.f, C1 = 0.f, C2 = 0.f, D = 0.f;
+  uint32_t last_contributor = 0;
+  bool done = !inside;
+
+  // software pipeline: ids two rounds ahead, records one round ahead
+  uint32_t id_next = 0;
+  if (rounds > 0) {
+    uint32_t id0 = (tid < n) ? __ldg(list + tid) : 0u;
+    issue(0, id0);
+    if (rounds > 1) id_next = (BLEND_BATCH + tid < n) ? __ldg(list + BLEND_BATCH + tid) : 0u;
+  }
+
+  for (int b = 0; b < rounds; ++b) {
+    const int s = b & 1;
+    if (b + 1 < rounds) {
+      issue(b + 1, id_next);
+      const int j2 = (b + 2) * BLEND_BATCH + tid;
+      id_next = (j2 < n) ? __ldg(list + j2) : 0u;
+      if (!TMA) cp_async_wait<1>();
+    } else {
+      if (!TMA) cp_async_wait<0>();
+    }
+    if (TMA) mbar_wait(&sm.bar[s], (unsigned)((b >> 1) & 1));
+    else __syncthreads();
+
+    const bool warp_live = __any_sync(0xffffffffu, !done);
+    if (warp_live) {
+      const int cnt = min(BLEND_BATCH, n - b * BLEND_BATCH);
+      const Rec* __restrict__ recs = sm.rec[s];
+      for (int c = 0; c < cnt; c += 32) {
+        const int j = c + lane;
+        bool hit = false;
+        if (j < cnt) hit = block_hit(recs[j].q0, fx0, fy0);
+        unsigned m = __ballot_sync(0xffffffffu, hit);
+        while (m) {
+          const int jj = c + __ffs(m) - 1;
+          m &= m - 1;
+          if (!done) {
+            const float4 q0 = recs[jj].q0;
+            const float4 con_o = recs[jj].q1;
+            const float dx = q0.x - pixx, dy = q0.y - pixy;
+            const float power = -0.5f * (con_o.x * dx * dx + con_o.z * dy * dy) - con_o.y * dx * dy;
+            if (!(power > 0.0f)) {
+              const float my_alpha = min(0.99f, con_o.w * exp(power));
+              float alpha = my_alpha;
+              if (INTERP) {
+                const float4 q3 = recs[jj].q3;
+                if (q3.x != 1.0f) {  // t == 1 gives alpha == my_alpha exactly
+                  // slot gate (forward.cu:537): skybox slots carry t = 1 in their record already
+                  const float kidsqrt_alpha = 1.0f - __powf(1.0f - my_alpha, q3.y);
+                  alpha = q3.x * my_alpha + (1.0f - q3.x) * kidsqrt_alpha;
+                }
+              }
+              if (!(alpha < 1.0f / 255.0f)) {
+                const float test_T = T * (1 - alpha);
+                if (test_T < 0.0001f) {
+                  done = true;
+                } else {
+                  const float4 q2 = recs[jj].q2;
+                  C0 += q2.x * alpha * T;
+                  C1 += q2.y * alpha * T;
+                  C2 += q2.z * alpha * T;
+                  if (DEPTH) D += q2.w * alpha * T;
+                  T = test_T;
+                  last_contributor = (uint32_t)(b * BLEND_BATCH + jj + 1);
+                }
+              }
+            }
+          }
+        }
+        if (!__any_sync(0xffffffffu, !done)) break;
+      }
+    }
+    // all warps saturated -> stop; the barrier also frees stage s for the copy issued next round
+    if (__syncthreads_and(done ? 1 : 0)) break;
+  }
+
+  if (inside) {
+    const size_t pix = (size_t)py * a.W + px;
+    const size_t plane = (size_t)a.W * a.H;
+    a.final_T[pix] = T;
+    a.n_contrib[pix] = last_contributor;
+    a.accum[pix] = make_float4(C0, C1, C2, D);
+    a.out_color[pix] = C0 + T * a.bg[0];
+    a.out_color[plane + pix] = C1 + T * a.bg[1];
+    a.out_color[2 * plane + pix] = C2 + T * a.bg[2];
+    if (DEPTH) a.out_invdepth[pix] = D;
+  }
+}
+
+template <bool INTERP, bool DEPTH>
+cudaError_t launch2(const BlendArgs& a, bool tma, cudaStream_t s) {
+  const int tiles = a.grid_x * a.grid_y;
+  if (tma)
+    blend_fwd_kernel<INTERP, DEPTH, true><<<tiles, BLEND_THREADS, 0, s>>>(a);
+  else
+    blend_fwd_kernel<INTERP, DEPTH, false><<<tiles, BLEND_THREADS, 0, s>>>(a);
+  return cudaGetLastError();
+}
+
+}  // namespace
+
+int blend_stage_mode();  // api.cu: 0 = LDGSTS, 1 = bulk-copy engine
+
+cudaError_t launch_blend_fwd(const BlendArgs& a, cudaStream_t s) {
+  const bool tma = blend_stage_mode() == 1;
+  const bool depth = a.out_invdepth != nullptr;
+  if (a.interp) return depth ? launch2<true, true>(a, tma, s) : launch2<true, false>(a, tma, s);
+  return depth ? launch2<false, true>(a, tma, s) : launch2<false, false>(a, tma, s);
+}
+
+}  // namespace h3dgs

@@ -1,0 +1,241 @@
+// Shared declarations for the sm_100a kernels behind include/h3dgs_b200.h.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+#include "../../include/h3dgs_b200.h"
+
+namespace h3dgs {
+
+constexpr int TILE_X = 16;            // HR/cuda_rasterizer/config.h:15-16 (BLOCK_X/BLOCK_Y) -- fixed by parity
+constexpr int TILE_Y = 16;
+constexpr int TILE_PIX = TILE_X * TILE_Y;
+
+// Per-slot record written by preprocess and staged into shared memory by the blend kernels.
+//   q0 = (pixel x, pixel y, cull half-extent x, cull half-extent y)
+//   q1 = (conic a, conic b, conic c, opacity * AA-compensation)
+//   q2 = (r, g, b, 1/depth)
+//   q3 = (t, 1/kids, depth, h_convolution_scaling)
+struct __align__(16) Rec {
+  float4 q0, q1, q2, q3;
+};
+static_assert(sizeof(Rec) == 64, "Rec must be 64 bytes");
+
+// Per-slot gradient accumulator filled by blend_bwd (vector red.global.add), consumed by preprocess_bwd.
+//   v[0..1] = dL/dmean2D (pixel units already scaled by 0.5*W, 0.5*H)
+//   v[2..4] = dL/dconic (xx, xy, yy)      v[5] = dL/d(opacity*h)
+//   v[6..8] = dL/drgb                      v[9] = dL/d(1/depth)     v[10..11] = padding
+struct __align__(16) GradRec {
+  float v[12];
+};
+static_assert(sizeof(GradRec) == 48, "GradRec must be 48 bytes");
+
+inline __host__ __device__ size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+template <typename T>
+inline void carve(char*& p, T*& out, size_t count) {
+  p = reinterpret_cast<char*>(align_up(reinterpret_cast<size_t>(p), 256));
+  out = reinterpret_cast<T*>(p);
+  p += count * sizeof(T);
+}
+
+// ---- scan geometry (decoupled look-back) ----
+constexpr int SCAN_THREADS = 256;
+constexpr int SCAN_ITEMS = 16;
+constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
+
+struct GeomWs {
+  Rec* rec;
+  float* depth;
+  float* cov3D;
+  ushort4* tile_rect;
+  uint32_t* tiles_touched;
+  uint32_t* offsets;
+  uint8_t* clamped;
+  unsigned long long* scan_status;  // one per scan tile
+  uint32_t* counters;               // [0] dynamic tile id, [1] unused, [2..3] total (u64)
+  size_t bytes;
+  static GeomWs make(void* base, int P) {
+    GeomWs w;
+    char* p = reinterpret_cast<char*>(base);
+    char* p0 = p;
+    size_t n = (size_t)(P > 0 ? P : 1);
+    carve(p, w.rec, n);
+    carve(p, w.depth, n);
+    carve(p, w.cov3D, n * 6);
+    carve(p, w.tile_rect, n);
+    carve(p, w.tiles_touched, n);
+    carve(p, w.offsets, n);
+    carve(p, w.clamped, n);
+    carve(p, w.scan_status, (n + SCAN_TILE - 1) / SCAN_TILE + 1);
+    carve(p, w.counters, 8);
+    w.bytes = (size_t)(p - p0) + 256;
+    return w;
+  }
+};
+
+struct ImageWs {
+  uint2* ranges;      // per tile
+  float* final_T;     // per pixel
+  uint32_t* n_contrib;
+  float4* accum;      // (C.r, C.g, C.b, D) without background, per pixel
+  size_t bytes;
+  static ImageWs make(void* base, int W, int H) {
+    ImageWs w;
+    char* p = reinterpret_cast<char*>(base);
+    char* p0 = p;
+    size_t npix = (size_t)W * H;
+    size_t tiles = (size_t)((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
+    carve(p, w.ranges, tiles);
+    carve(p, w.final_T, npix);
+    carve(p, w.n_contrib, npix);
+    carve(p, w.accum, npix);
+    w.bytes = (size_t)(p - p0) + 256;
+    return w;
+  }
+};
+
+// ---- onesweep radix sort geometry ----
+constexpr int SORT_RADIX_BITS_MAX = 9;
+constexpr int SORT_RADIX_MAX = 1 << SORT_RADIX_BITS_MAX;
+constexpr int SORT_THREADS = 512;
+constexpr int SORT_ITEMS = 12;
+constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;
+constexpr int SORT_MAX_PASSES = 8;
+
+struct SortPlan {
+  int num_passes;
+  int shift[SORT_MAX_PASSES];
+  int bits[SORT_MAX_PASSES];
+};
+
+// Number of key bits that matter: 32 depth bits + ceil-ish log2 of the tile count, exactly as the
+// reference computes it (getHigherMsb, HR/cuda_rasterizer/rasterizer_impl.cu:35-50,349).
+inline uint32_t higher_msb(uint32_t n) {
+  uint32_t msb = sizeof(n) * 4;
+  uint32_t step = msb;
+  while (step > 1) {
+    step /= 2;
+    if (n >> msb) msb += step; else msb -= step;
+  }
+  if (n >> msb) msb++;
+  return msb;
+}
+
+inline SortPlan make_sort_plan(int W, int H) {
+  uint32_t tiles = (uint32_t)((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
+  int total = 32 + (int)higher_msb(tiles);
+  SortPlan pl;
+  pl.num_passes = (total + SORT_RADIX_BITS_MAX - 1) / SORT_RADIX_BITS_MAX;
+  int base = total / pl.num_passes, extra = total % pl.num_passes, s = 0;
+  for (int i = 0; i < pl.num_passes; ++i) {
+    pl.bits[i] = base + (i < extra ? 1 : 0);
+    pl.shift[i] = s;
+    s += pl.bits[i];
+  }
+  return pl;
+}
+
+struct BinWs {
+  unsigned long long* keys[2];
+  uint32_t* vals[2];
+  uint32_t* hist;     // [SORT_MAX_PASSES][SORT_RADIX_MAX] exclusive-scanned digit bases
+  uint32_t* status;   // [num_passes][tiles][SORT_RADIX_MAX] look-back words
+  uint32_t* counters; // [SORT_MAX_PASSES] dynamic tile ids
+  size_t status_words;
+  size_t zero_bytes;  // hist..counters are contiguous: one memset
+  char* zero_base;
+  int sorted;         // index (0/1) of the buffer holding the sorted result
+  size_t bytes;
+  static BinWs make(void* base, int64_t R, int W, int H) {
+    BinWs w;
+    SortPlan pl = make_sort_plan(W, H);
+    char* p = reinterpret_cast<char*>(base);
+    char* p0 = p;
+    size_t n = (size_t)(R > 0 ? R : 1);
+    size_t tiles = (n + SORT_TILE - 1) / SORT_TILE;
+    carve(p, w.keys[0], n);
+    carve(p, w.keys[1], n);
+    carve(p, w.vals[0], n);
+    carve(p, w.vals[1], n);
+    carve(p, w.hist, (size_t)SORT_MAX_PASSES * SORT_RADIX_MAX);
+    w.zero_base = reinterpret_cast<char*>(w.hist);
+    w.status_words = (size_t)pl.num_passes * tiles * SORT_RADIX_MAX;
+    carve(p, w.status, w.status_words);
+    carve(p, w.counters, 64);
+    w.zero_bytes = (size_t)(p - w.zero_base);
+    w.sorted = pl.num_passes & 1;
+    w.bytes = (size_t)(p - p0) + 256;
+    return w;
+  }
+};
+
+struct BwdWs {
+  GradRec* grad;
+  size_t bytes;
+  static BwdWs make(void* base, int P) {
+    BwdWs w;
+    char* p = reinterpret_cast<char*>(base);
+    char* p0 = p;
+    carve(p, w.grad, (size_t)(P > 0 ? P : 1));
+    w.bytes = (size_t)(p - p0) + 256;
+    return w;
+  }
+};
+
+// error plumbing (api.cu)
+int fail(int code, const char* what);
+int cuda_fail(cudaError_t e, const char* what);
+#define H3_CUDA(expr)                                         \
+  do {                                                        \
+    cudaError_t e__ = (expr);                                 \
+    if (e__ != cudaSuccess) return ::h3dgs::cuda_fail(e__, #expr); \
+  } while (0)
+
+// ---- kernel launchers (one per .cu) ----
+struct PreArgs {
+  int P, rows, D, M, skyboxnum;
+  int W, H, grid_x, grid_y;
+  float scale_modifier, tan_fovx, tan_fovy, focal_x, focal_y;
+  const float* means; const float* shs; const float* colors; const float* opac;
+  const float* scales; const float* rots; const float* cov3D_pre;
+  const int* idx; const int* pidx; const float* ts; const int* kids;
+  const float* view; const float* proj; const float* campos;
+  int* radii;
+  GeomWs ws;
+};
+cudaError_t launch_preprocess_fwd(const PreArgs& a, cudaStream_t s);
+cudaError_t launch_mark_visible(int P, const float* means, const float* view, const float* proj,
+                                uint8_t* present, cudaStream_t s);
+
+// inclusive scan of u32 -> u32, total (u64) written to total_out[0..1]
+cudaError_t launch_scan_inclusive(const uint32_t* in, uint32_t* out, int n, unsigned long long* status,
+                                  uint32_t* counters, cudaStream_t s);
+
+cudaError_t launch_emit_instances(int P, const int* radii, const GeomWs& g, int grid_x,
+                                  unsigned long long* keys, uint32_t* vals, cudaStream_t s);
+cudaError_t launch_tile_ranges(int64_t R, const unsigned long long* keys, uint2* ranges, int tiles,
+                               cudaStream_t s);
+cudaError_t launch_radix_sort(BinWs& b, int64_t R, const SortPlan& plan, cudaStream_t s);
+
+struct BlendArgs {
+  int W, H, grid_x, grid_y, P, skyboxnum;
+  int interp;       // ts && kids
+  const uint2* ranges; const uint32_t* point_list; const Rec* rec;
+  const float* bg;
+  float* final_T; uint32_t* n_contrib; float4* accum;
+  float* out_color; float* out_invdepth;   // fwd
+  const float* dL_dcolor; const float* dL_dinvdepth; GradRec* grad;  // bwd
+};
+cudaError_t launch_blend_fwd(const BlendArgs& a, cudaStream_t s);
+cudaError_t launch_blend_bwd(const BlendArgs& a, cudaStream_t s);
+
+struct PreBwdArgs {
+  PreArgs f;
+  const GradRec* grad;
+  int has_invdepth;
+  H3dgsGrads out;
+};
+cudaError_t launch_preprocess_bwd(const PreBwdArgs& a, cudaStream_t s);
+
+}  // namespace h3dgs

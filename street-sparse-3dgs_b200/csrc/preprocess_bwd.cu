@@ -1,0 +1,394 @@
+// Per-slot backward preprocessing: from the reduced screen-space gradients (GradRec) to gradients of
+// means, SH / colours, opacity, scales, rotations (or the precomputed covariance), including the
+// chain through the fused child/parent interpolation.
+//
+// One kernel replaces computeCov2DCUDA + preprocessCUDA<backward> (HR/cuda_rasterizer/backward.cu:147-495)
+// and the caller-side zero fill of the gradient tensors (HR/rasterize_points.cu:168-198): in plain mode
+// every output row is written exactly once (zeros for culled slots); in fused-cut mode outputs are
+// zeroed by the entry point and visible slots scatter t*g to the child row and (1-t)*g to the parent
+// row, which is what autograd does for the Python lerp (gaussian_renderer/__init__.py:202-235).
+#include "common.cuh"
+#include "gsmath.cuh"
+
+namespace h3dgs {
+
+namespace {
+
+__device__ __forceinline__ float sq(float x) { return x * x; }
+
+__device__ __forceinline__ float3 ld3(const float* __restrict__ p, size_t row) {
+  const float* q = p + row * 3;
+  return make_float3(__ldg(q), __ldg(q + 1), __ldg(q + 2));
+}
+__device__ __forceinline__ float lerp_rn(float t, float a, float omt, float b) {
+  return __fadd_rn(__fmul_rn(t, a), __fmul_rn(omt, b));
+}
+
+// d(v/|v|)/dv applied to dv (auxiliary.h:132-142)
+__device__ __forceinline__ float3 dnormvdv(float3 v, float3 dv) {
+  float sum2 = v.x * v.x + v.y * v.y + v.z * v.z;
+  float invsum32 = 1.0f / sqrt(sum2 * sum2 * sum2);
+  float3 r;
+  r.x = ((+sum2 - v.x * v.x) * dv.x - v.y * v.x * dv.y - v.z * v.x * dv.z) * invsum32;
+  r.y = (-v.x * v.y * dv.x + (sum2 - v.y * v.y) * dv.y - v.z * v.y * dv.z) * invsum32;
+  r.z = (-v.x * v.z * dv.x - v.y * v.z * dv.y + (sum2 - v.z * v.z) * dv.z) * invsum32;
+  return r;
+}
+
+template <bool FUSED>
+__device__ __forceinline__ void put(float* base, size_t row, int width, int k, float v, size_t prow,
+                                    bool lerp, float t, float omt, float psign = 1.0f) {
+  if (base == nullptr) return;
+  if (!FUSED) {
+    base[row * width + k] = v;
+  } else {
+    if (!lerp) {
+      atomicAdd(base + row * width + k, v);
+    } else {
+      atomicAdd(base + row * width + k, t * v);
+      atomicAdd(base + prow * width + k, omt * psign * v);
+    }
+  }
+}
+
+template <bool FUSED>
+__global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdArgs b) {
+  const PreArgs& a = b.f;
+  const int t_idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t_idx >= a.P) return;
+  const H3dgsGrads& o = b.out;
+  const int M = a.M;
+  const bool visible = a.radii[t_idx] > 0;
+
+  if (!visible) {
+    if (o.dL_dmeans2D) {
+      o.dL_dmeans2D[(size_t)t_idx * 3] = 0.f;
+      o.dL_dmeans2D[(size_t)t_idx * 3 + 1] = 0.f;
+      o.dL_dmeans2D[(size_t)t_idx * 3 + 2] = 0.f;
+    }
+    if (!FUSED) {
+      const size_t r = (size_t)t_idx;
+      if (o.dL_dmeans3D) { o.dL_dmeans3D[r * 3] = 0.f; o.dL_dmeans3D[r * 3 + 1] = 0.f; o.dL_dmeans3D[r * 3 + 2] = 0.f; }
+      if (o.dL_dcolors) { o.dL_dcolors[r * 3] = 0.f; o.dL_dcolors[r * 3 + 1] = 0.f; o.dL_dcolors[r * 3 + 2] = 0.f; }
+      if (o.dL_dopacity) o.dL_dopacity[r] = 0.f;
+      if (o.dL_dscales) { o.dL_dscales[r * 3] = 0.f; o.dL_dscales[r * 3 + 1] = 0.f; o.dL_dscales[r * 3 + 2] = 0.f; }
+      if (o.dL_drotations) *reinterpret_cast<float4*>(o.dL_drotations + r * 4) = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (o.dL_dcov3D) for (int i = 0; i < 6; ++i) o.dL_dcov3D[r * 6 + i] = 0.f;
+      if (o.dL_dsh) {
+        float* d = o.dL_dsh + r * (size_t)M * 3;
+        if (((M * 3) & 3) == 0 && ((reinterpret_cast<size_t>(o.dL_dsh) & 15) == 0)) {
+          for (int i = 0; i < M * 3 / 4; ++i) reinterpret_cast<float4*>(d)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        } else {
+          for (int i = 0; i < M * 3; ++i) d[i] = 0.f;
+        }
+      }
+    }
+    return;
+  }
+
+  // ---- which rows? (same decode as the forward) ----
+  size_t r = (size_t)t_idx;
+  long long p = -1;
+  float t = 1.0f, omt = 0.0f;
+  bool lerp = false;
+  if (FUSED) {
+    const int K = a.P - a.skyboxnum;
+    if (t_idx >= K) {
+      r = (size_t)(a.rows - a.skyboxnum + (t_idx - K));
+    } else {
+      r = (size_t)__ldg(a.idx + t_idx);
+      if (a.pidx != nullptr) {
+        p = __ldg(a.pidx + t_idx);
+        if (p >= 0) {
+          t = __ldg(a.ts + t_idx);
+          omt = __fsub_rn(1.0f, t);
+          lerp = (omt != 0.0f);
+        }
+      }
+    }
+  }
+  const size_t pr = (size_t)(p < 0 ? 0 : p);
+
+  const GradRec gr = b.grad[t_idx];
+  const float dL_dmean2D_x = gr.v[0], dL_dmean2D_y = gr.v[1];
+  const float3 dL_dconic = {gr.v[2], gr.v[3], gr.v[4]};
+  const float dL_dopacity_v = gr.v[5];
+  float3 dL_dRGB = {gr.v[6], gr.v[7], gr.v[8]};
+  const float dL_dinvdepth = gr.v[9];
+
+  if (o.dL_dmeans2D) {
+    o.dL_dmeans2D[(size_t)t_idx * 3] = dL_dmean2D_x;
+    o.dL_dmeans2D[(size_t)t_idx * 3 + 1] = dL_dmean2D_y;
+    o.dL_dmeans2D[(size_t)t_idx * 3 + 2] = 0.f;
+  }
+
+  float3 mean = ld3(a.means, r);
+  if (FUSED && lerp) {
+    float3 q = ld3(a.means, pr);
+    mean = make_float3(lerp_rn(t, mean.x, omt, q.x), lerp_rn(t, mean.y, omt, q.y),
+                       lerp_rn(t, mean.z, omt, q.z));
+  }
+  const float* __restrict__ view = a.view;
+  const float* __restrict__ proj = a.proj;
+
+  // ---------------- 2D covariance / conic backward (backward.cu:147-326) ----------------
+  float c6[6];
+#pragma unroll
+  for (int i = 0; i < 6; ++i) c6[i] = a.ws.cov3D[(size_t)t_idx * 6 + i];
+  M3 T;
+  float3 tv;
+  float txtz, tytz;
+  float3 cov = cov2d_ewa(mean, a.focal_x, a.focal_y, a.tan_fovx, a.tan_fovy, c6, view, &T, &tv, &txtz,
+                         &tytz);
+  const float limx = 1.3f * a.tan_fovx, limy = 1.3f * a.tan_fovy;
+  const float x_grad_mul = txtz < -limx || txtz > limx ? 0 : 1;
+  const float y_grad_mul = tytz < -limy || tytz > limy ? 0 : 1;
+
+  float c_xx = cov.x, c_xy = cov.y, c_yy = cov.z;
+  constexpr float h_var = 0.3f;
+  const float det_cov = c_xx * c_yy - c_xy * c_xy;
+  c_xx += h_var;
+  c_yy += h_var;
+  const float det_cov_plus_h_cov = c_xx * c_yy - c_xy * c_xy;
+  const float h_convolution_scaling = sqrt(max(0.000025f, det_cov / det_cov_plus_h_cov));
+
+  float opacity = __ldg(a.opac + r);
+  if (FUSED && lerp) opacity = lerp_rn(t, opacity, omt, __ldg(a.opac + pr));
+  const float d_h_convolution_scaling = dL_dopacity_v * opacity;
+  const float dL_dopacity_out = dL_dopacity_v * h_convolution_scaling;
+  const float d_inside_root = (det_cov / det_cov_plus_h_cov) <= 0.000025f
+                                  ? 0.f
+                                  : d_h_convolution_scaling / (2 * h_convolution_scaling);
+
+  float dL_dc_xx = 0, dL_dc_xy = 0, dL_dc_yy = 0;
+  {
+    // gradient of sqrt(det/det') through the dilated entries, evaluated at the dilated values exactly
+    // as backward.cu:234-244 does
+    const float x = c_xx, y = c_yy, z = c_xy, w = h_var;
+    const float denom_f = d_inside_root / sq(w * w + w * (x + y) + x * y - z * z);
+    dL_dc_xx = w * (w * y + y * y + z * z) * denom_f;
+    dL_dc_yy = w * (w * x + x * x + z * z) * denom_f;
+    dL_dc_xy = -2.f * w * z * (w + x + y) * denom_f;
+  }
+
+  const float denom = c_xx * c_yy - c_xy * c_xy;
+  const float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
+  float dcov[6] = {0, 0, 0, 0, 0, 0};
+  if (denom2inv != 0) {
+    dL_dc_xx += denom2inv * (-c_yy * c_yy * dL_dconic.x + 2 * c_xy * c_yy * dL_dconic.y +
+                             (denom - c_xx * c_yy) * dL_dconic.z);
+    dL_dc_yy += denom2inv * (-c_xx * c_xx * dL_dconic.z + 2 * c_xx * c_xy * dL_dconic.y +
+                             (denom - c_xx * c_yy) * dL_dconic.x);
+    dL_dc_xy += denom2inv * 2 *
+                (c_xy * c_yy * dL_dconic.x - (denom + 2 * c_xy * c_xy) * dL_dconic.y +
+                 c_xx * c_xy * dL_dconic.z);
+    dcov[0] = (T.c[0][0] * T.c[0][0] * dL_dc_xx + T.c[0][0] * T.c[1][0] * dL_dc_xy + T.c[1][0] * T.c[1][0] * dL_dc_yy);
+    dcov[3] = (T.c[0][1] * T.c[0][1] * dL_dc_xx + T.c[0][1] * T.c[1][1] * dL_dc_xy + T.c[1][1] * T.c[1][1] * dL_dc_yy);
+    dcov[5] = (T.c[0][2] * T.c[0][2] * dL_dc_xx + T.c[0][2] * T.c[1][2] * dL_dc_xy + T.c[1][2] * T.c[1][2] * dL_dc_yy);
+    dcov[1] = 2 * T.c[0][0] * T.c[0][1] * dL_dc_xx + (T.c[0][0] * T.c[1][1] + T.c[0][1] * T.c[1][0]) * dL_dc_xy + 2 * T.c[1][0] * T.c[1][1] * dL_dc_yy;
+    dcov[2] = 2 * T.c[0][0] * T.c[0][2] * dL_dc_xx + (T.c[0][0] * T.c[1][2] + T.c[0][2] * T.c[1][0]) * dL_dc_xy + 2 * T.c[1][0] * T.c[1][2] * dL_dc_yy;
+    dcov[4] = 2 * T.c[0][2] * T.c[0][1] * dL_dc_xx + (T.c[0][1] * T.c[1][2] + T.c[0][2] * T.c[1][1]) * dL_dc_xy + 2 * T.c[1][1] * T.c[1][2] * dL_dc_yy;
+  }
+
+  // Vrk rows (symmetric)
+  const float V00 = c6[0], V01 = c6[1], V02 = c6[2], V11 = c6[3], V12 = c6[4], V22 = c6[5];
+  const float a0 = T.c[0][0] * V00 + T.c[0][1] * V01 + T.c[0][2] * V02;
+  const float a1 = T.c[0][0] * V01 + T.c[0][1] * V11 + T.c[0][2] * V12;
+  const float a2 = T.c[0][0] * V02 + T.c[0][1] * V12 + T.c[0][2] * V22;
+  const float b0 = T.c[1][0] * V00 + T.c[1][1] * V01 + T.c[1][2] * V02;
+  const float b1 = T.c[1][0] * V01 + T.c[1][1] * V11 + T.c[1][2] * V12;
+  const float b2 = T.c[1][0] * V02 + T.c[1][1] * V12 + T.c[1][2] * V22;
+  const float dL_dT00 = 2 * a0 * dL_dc_xx + b0 * dL_dc_xy;
+  const float dL_dT01 = 2 * a1 * dL_dc_xx + b1 * dL_dc_xy;
+  const float dL_dT02 = 2 * a2 * dL_dc_xx + b2 * dL_dc_xy;
+  const float dL_dT10 = 2 * b0 * dL_dc_yy + a0 * dL_dc_xy;
+  const float dL_dT11 = 2 * b1 * dL_dc_yy + a1 * dL_dc_xy;
+  const float dL_dT12 = 2 * b2 * dL_dc_yy + a2 * dL_dc_xy;
+
+  // W columns as in cov2d_ewa: W.c[j][i] = view[4*i + j]
+  const float W00 = view[0], W01 = view[4], W02 = view[8];
+  const float W10 = view[1], W11 = view[5], W12 = view[9];
+  const float W20 = view[2], W21 = view[6], W22 = view[10];
+  const float dL_dJ00 = W00 * dL_dT00 + W01 * dL_dT01 + W02 * dL_dT02;
+  const float dL_dJ02 = W20 * dL_dT00 + W21 * dL_dT01 + W22 * dL_dT02;
+  const float dL_dJ11 = W10 * dL_dT10 + W11 * dL_dT11 + W12 * dL_dT12;
+  const float dL_dJ12 = W20 * dL_dT10 + W21 * dL_dT11 + W22 * dL_dT12;
+
+  const float tz = 1.f / tv.z;
+  const float tz2 = tz * tz;
+  const float tz3 = tz2 * tz;
+  const float h_x = a.focal_x, h_y = a.focal_y;
+  const float dL_dtx = x_grad_mul * -h_x * tz2 * dL_dJ02;
+  const float dL_dty = y_grad_mul * -h_y * tz2 * dL_dJ12;
+  float dL_dtz = -h_x * tz2 * dL_dJ00 - h_y * tz2 * dL_dJ11 + (2 * h_x * tv.x) * tz3 * dL_dJ02 +
+                 (2 * h_y * tv.y) * tz3 * dL_dJ12;
+  if (b.has_invdepth) dL_dtz -= dL_dinvdepth / (tv.z * tv.z);
+  float3 dL_dmean = xform_vec4x3_t(make_float3(dL_dtx, dL_dty, dL_dtz), view);
+
+  // ---------------- projection of the mean (backward.cu:433-447) ----------------
+  {
+    float4 m_hom = xform4x4(mean, proj);
+    float m_w = 1.0f / (m_hom.w + 0.0000001f);
+    float mul1 = (proj[0] * mean.x + proj[4] * mean.y + proj[8] * mean.z + proj[12]) * m_w * m_w;
+    float mul2 = (proj[1] * mean.x + proj[5] * mean.y + proj[9] * mean.z + proj[13]) * m_w * m_w;
+    dL_dmean.x += (proj[0] * m_w - proj[3] * mul1) * dL_dmean2D_x + (proj[1] * m_w - proj[3] * mul2) * dL_dmean2D_y;
+    dL_dmean.y += (proj[4] * m_w - proj[7] * mul1) * dL_dmean2D_x + (proj[5] * m_w - proj[7] * mul2) * dL_dmean2D_y;
+    dL_dmean.z += (proj[8] * m_w - proj[11] * mul1) * dL_dmean2D_x + (proj[9] * m_w - proj[11] * mul2) * dL_dmean2D_y;
+  }
+
+  // ---------------- colour (backward.cu:23-142) ----------------
+  if (a.colors == nullptr) {
+    const unsigned cl = a.ws.clamped[t_idx];
+    dL_dRGB.x *= (cl & 1u) ? 0 : 1;
+    dL_dRGB.y *= (cl & 2u) ? 0 : 1;
+    dL_dRGB.z *= (cl & 4u) ? 0 : 1;
+    const float3 cam = make_float3(__ldg(a.campos), __ldg(a.campos + 1), __ldg(a.campos + 2));
+    const float3 dir_orig = make_float3(mean.x - cam.x, mean.y - cam.y, mean.z - cam.z);
+    const float len = sqrt(dir_orig.x * dir_orig.x + dir_orig.y * dir_orig.y + dir_orig.z * dir_orig.z);
+    const float x = dir_orig.x / len, y = dir_orig.y / len, z = dir_orig.z / len;
+    float bs[16];
+    sh_basis(a.D, x, y, z, bs);
+    const int n = sh_count(a.D);
+    const float* __restrict__ sh = a.shs + r * (size_t)M * 3;
+    const float* __restrict__ shp = a.shs + pr * (size_t)M * 3;
+
+    // dL/dsh rows
+    for (int k = 0; k < M; ++k) {
+      const float w = (k < n) ? bs[k] : 0.f;
+      put<FUSED>(o.dL_dsh, r, M * 3, 3 * k + 0, w * dL_dRGB.x, pr, lerp, t, omt);
+      put<FUSED>(o.dL_dsh, r, M * 3, 3 * k + 1, w * dL_dRGB.y, pr, lerp, t, omt);
+      put<FUSED>(o.dL_dsh, r, M * 3, 3 * k + 2, w * dL_dRGB.z, pr, lerp, t, omt);
+    }
+
+    // d colour / d direction
+    float3 dx3 = {0, 0, 0}, dy3 = {0, 0, 0}, dz3 = {0, 0, 0};
+    auto S = [&](int k) -> float3 {
+      float3 v = make_float3(__ldg(sh + 3 * k), __ldg(sh + 3 * k + 1), __ldg(sh + 3 * k + 2));
+      if (FUSED && lerp) {
+        v.x = lerp_rn(t, v.x, omt, __ldg(shp + 3 * k));
+        v.y = lerp_rn(t, v.y, omt, __ldg(shp + 3 * k + 1));
+        v.z = lerp_rn(t, v.z, omt, __ldg(shp + 3 * k + 2));
+      }
+      return v;
+    };
+    auto axpy = [](float3& acc, float s, const float3& v) {
+      acc.x += s * v.x; acc.y += s * v.y; acc.z += s * v.z;
+    };
+    if (a.D > 0) {
+      const float3 s1 = S(1), s2 = S(2), s3 = S(3);
+      axpy(dx3, -kSH1, s3);
+      axpy(dy3, -kSH1, s1);
+      axpy(dz3, kSH1, s2);
+      if (a.D > 1) {
+        const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+        const float3 s4 = S(4), s5 = S(5), s6 = S(6), s7 = S(7), s8 = S(8);
+        axpy(dx3, kSH2[0] * y, s4); axpy(dx3, kSH2[2] * 2.f * -x, s6); axpy(dx3, kSH2[3] * z, s7); axpy(dx3, kSH2[4] * 2.f * x, s8);
+        axpy(dy3, kSH2[0] * x, s4); axpy(dy3, kSH2[1] * z, s5); axpy(dy3, kSH2[2] * 2.f * -y, s6); axpy(dy3, kSH2[4] * 2.f * -y, s8);
+        axpy(dz3, kSH2[1] * y, s5); axpy(dz3, kSH2[2] * 2.f * 2.f * z, s6); axpy(dz3, kSH2[3] * x, s7);
+        if (a.D > 2) {
+          const float3 s9 = S(9), s10 = S(10), s11 = S(11), s12 = S(12), s13 = S(13), s14 = S(14), s15 = S(15);
+          axpy(dx3, kSH3[0] * 3.f * 2.f * xy, s9); axpy(dx3, kSH3[1] * yz, s10); axpy(dx3, kSH3[2] * -2.f * xy, s11);
+          axpy(dx3, kSH3[3] * -3.f * 2.f * xz, s12); axpy(dx3, kSH3[4] * (-3.f * xx + 4.f * zz - yy), s13);
+          axpy(dx3, kSH3[5] * 2.f * xz, s14); axpy(dx3, kSH3[6] * 3.f * (xx - yy), s15);
+          axpy(dy3, kSH3[0] * 3.f * (xx - yy), s9); axpy(dy3, kSH3[1] * xz, s10); axpy(dy3, kSH3[2] * (-3.f * yy + 4.f * zz - xx), s11);
+          axpy(dy3, kSH3[3] * -3.f * 2.f * yz, s12); axpy(dy3, kSH3[4] * -2.f * xy, s13);
+          axpy(dy3, kSH3[5] * -2.f * yz, s14); axpy(dy3, kSH3[6] * -3.f * 2.f * xy, s15);
+          axpy(dz3, kSH3[1] * xy, s10); axpy(dz3, kSH3[2] * 4.f * 2.f * yz, s11); axpy(dz3, kSH3[3] * 3.f * (2.f * zz - xx - yy), s12);
+          axpy(dz3, kSH3[4] * 4.f * 2.f * xz, s13); axpy(dz3, kSH3[5] * (xx - yy), s14);
+        }
+      }
+    }
+    const float3 dL_ddir = {dx3.x * dL_dRGB.x + dx3.y * dL_dRGB.y + dx3.z * dL_dRGB.z,
+                            dy3.x * dL_dRGB.x + dy3.y * dL_dRGB.y + dy3.z * dL_dRGB.z,
+                            dz3.x * dL_dRGB.x + dz3.y * dL_dRGB.y + dz3.z * dL_dRGB.z};
+    const float3 dm = dnormvdv(dir_orig, dL_ddir);
+    dL_dmean.x += dm.x; dL_dmean.y += dm.y; dL_dmean.z += dm.z;
+    if (!FUSED && o.dL_dcolors) {
+      o.dL_dcolors[r * 3] = 0.f; o.dL_dcolors[r * 3 + 1] = 0.f; o.dL_dcolors[r * 3 + 2] = 0.f;
+    }
+  } else {
+    put<FUSED>(o.dL_dcolors, r, 3, 0, dL_dRGB.x, pr, lerp, t, omt);
+    put<FUSED>(o.dL_dcolors, r, 3, 1, dL_dRGB.y, pr, lerp, t, omt);
+    put<FUSED>(o.dL_dcolors, r, 3, 2, dL_dRGB.z, pr, lerp, t, omt);
+    if (!FUSED && o.dL_dsh) for (int i = 0; i < M * 3; ++i) o.dL_dsh[r * (size_t)M * 3 + i] = 0.f;
+  }
+
+  put<FUSED>(o.dL_dmeans3D, r, 3, 0, dL_dmean.x, pr, lerp, t, omt);
+  put<FUSED>(o.dL_dmeans3D, r, 3, 1, dL_dmean.y, pr, lerp, t, omt);
+  put<FUSED>(o.dL_dmeans3D, r, 3, 2, dL_dmean.z, pr, lerp, t, omt);
+  put<FUSED>(o.dL_dopacity, r, 1, 0, dL_dopacity_out, pr, lerp, t, omt);
+
+  // ---------------- 3D covariance -> scale / rotation (backward.cu:330-393) ----------------
+  if (a.cov3D_pre == nullptr) {
+    float3 sc = ld3(a.scales, r);
+    const float4 q4 = __ldg(reinterpret_cast<const float4*>(a.rots) + r);
+    float qr = q4.x, qx = q4.y, qy = q4.z, qz = q4.w;
+    float psign = 1.0f;
+    if (FUSED && lerp) {
+      float3 s2 = ld3(a.scales, pr);
+      sc = make_float3(lerp_rn(t, sc.x, omt, s2.x), lerp_rn(t, sc.y, omt, s2.y), lerp_rn(t, sc.z, omt, s2.z));
+      float4 op = __ldg(reinterpret_cast<const float4*>(a.rots) + pr);
+      float dotp = (qr * op.x + qx * op.y) + (qy * op.z + qz * op.w);
+      if (dotp < 0.0f) { psign = -1.0f; op.x = -op.x; op.y = -op.y; op.z = -op.z; op.w = -op.w; }
+      qr = lerp_rn(t, qr, omt, op.x);
+      qx = lerp_rn(t, qx, omt, op.y);
+      qy = lerp_rn(t, qy, omt, op.z);
+      qz = lerp_rn(t, qz, omt, op.w);
+    }
+    const M3 R = quat_to_m3(qr, qx, qy, qz);
+    const float sx = a.scale_modifier * sc.x, sy = a.scale_modifier * sc.y, sz = a.scale_modifier * sc.z;
+    M3 S = m3(1.f, 0.f, 0.f, 0.f, 1.f, 0.f, 0.f, 0.f, 1.f);
+    S.c[0][0] = sx; S.c[1][1] = sy; S.c[2][2] = sz;
+    const M3 Mm = m3_mul(S, R);
+    const M3 dSig = m3(dcov[0], 0.5f * dcov[1], 0.5f * dcov[2], 0.5f * dcov[1], dcov[3], 0.5f * dcov[4],
+                       0.5f * dcov[2], 0.5f * dcov[4], dcov[5]);
+    M3 dM = m3_mul(Mm, dSig);
+#pragma unroll
+    for (int j = 0; j < 3; ++j)
+#pragma unroll
+      for (int i = 0; i < 3; ++i) dM.c[j][i] *= 2.0f;
+    const M3 Rt = m3_t(R);
+    M3 dMt = m3_t(dM);
+    // the reference stores the scale gradient without the scale_modifier factor
+    const float ds0 = Rt.c[0][0] * dMt.c[0][0] + Rt.c[0][1] * dMt.c[0][1] + Rt.c[0][2] * dMt.c[0][2];
+    const float ds1 = Rt.c[1][0] * dMt.c[1][0] + Rt.c[1][1] * dMt.c[1][1] + Rt.c[1][2] * dMt.c[1][2];
+    const float ds2 = Rt.c[2][0] * dMt.c[2][0] + Rt.c[2][1] * dMt.c[2][1] + Rt.c[2][2] * dMt.c[2][2];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) { dMt.c[0][i] *= sx; dMt.c[1][i] *= sy; dMt.c[2][i] *= sz; }
+    const float x = qx, y = qy, z = qz, rr = qr;
+    float4 dq;
+    dq.x = 2 * z * (dMt.c[0][1] - dMt.c[1][0]) + 2 * y * (dMt.c[2][0] - dMt.c[0][2]) + 2 * x * (dMt.c[1][2] - dMt.c[2][1]);
+    dq.y = 2 * y * (dMt.c[1][0] + dMt.c[0][1]) + 2 * z * (dMt.c[2][0] + dMt.c[0][2]) + 2 * rr * (dMt.c[1][2] - dMt.c[2][1]) - 4 * x * (dMt.c[2][2] + dMt.c[1][1]);
+    dq.z = 2 * x * (dMt.c[1][0] + dMt.c[0][1]) + 2 * rr * (dMt.c[2][0] - dMt.c[0][2]) + 2 * z * (dMt.c[1][2] + dMt.c[2][1]) - 4 * y * (dMt.c[2][2] + dMt.c[0][0]);
+    dq.w = 2 * rr * (dMt.c[0][1] - dMt.c[1][0]) + 2 * x * (dMt.c[2][0] + dMt.c[0][2]) + 2 * y * (dMt.c[1][2] + dMt.c[2][1]) - 4 * z * (dMt.c[1][1] + dMt.c[0][0]);
+
+    put<FUSED>(o.dL_dscales, r, 3, 0, ds0, pr, lerp, t, omt);
+    put<FUSED>(o.dL_dscales, r, 3, 1, ds1, pr, lerp, t, omt);
+    put<FUSED>(o.dL_dscales, r, 3, 2, ds2, pr, lerp, t, omt);
+    put<FUSED>(o.dL_drotations, r, 4, 0, dq.x, pr, lerp, t, omt, psign);
+    put<FUSED>(o.dL_drotations, r, 4, 1, dq.y, pr, lerp, t, omt, psign);
+    put<FUSED>(o.dL_drotations, r, 4, 2, dq.z, pr, lerp, t, omt, psign);
+    put<FUSED>(o.dL_drotations, r, 4, 3, dq.w, pr, lerp, t, omt, psign);
+    if (!FUSED && o.dL_dcov3D) for (int i = 0; i < 6; ++i) o.dL_dcov3D[r * 6 + i] = dcov[i];
+  } else {
+    for (int i = 0; i < 6; ++i) put<FUSED>(o.dL_dcov3D, r, 6, i, dcov[i], pr, lerp, t, omt);
+    if (!FUSED) {
+      if (o.dL_dscales) { o.dL_dscales[r * 3] = 0.f; o.dL_dscales[r * 3 + 1] = 0.f; o.dL_dscales[r * 3 + 2] = 0.f; }
+      if (o.dL_drotations) *reinterpret_cast<float4*>(o.dL_drotations + r * 4) = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+  }
+}
+
+}  // namespace
+
+cudaError_t launch_preprocess_bwd(const PreBwdArgs& b, cudaStream_t s) {
+  if (b.f.P <= 0) return cudaSuccess;
+  const int blocks = (b.f.P + 255) / 256;
+  if (b.f.idx != nullptr)
+    preprocess_bwd_kernel<true><<<blocks, 256, 0, s>>>(b);
+  else
+    preprocess_bwd_kernel<false><<<blocks, 256, 0, s>>>(b);
+  return cudaGetLastError();
+}
+
+}  // namespace h3dgs

@@ -1,0 +1,130 @@
+// Single-pass inclusive prefix sum (decoupled look-back) of the per-slot tile counts.
+// Replaces cub::DeviceScan::InclusiveSum at HR/cuda_rasterizer/rasterizer_impl.cu:316 and
+// GH/runtime_switching.cu:531-533.  8 bytes of HBM traffic per element, one launch.
+#include "common.cuh"
+
+namespace h3dgs {
+
+namespace {
+
+constexpr unsigned long long FLAG_AGG = 1ull << 62;
+constexpr unsigned long long FLAG_INC = 2ull << 62;
+constexpr unsigned long long VAL_MASK = (1ull << 62) - 1;
+
+__global__ void __launch_bounds__(SCAN_THREADS) scan_lookback_kernel(
+    const uint32_t* __restrict__ in, uint32_t* __restrict__ out, int n,
+    volatile unsigned long long* status, uint32_t* counters) {
+  __shared__ uint32_t s_tile;
+  __shared__ unsigned long long s_warp[SCAN_THREADS / 32];
+  __shared__ unsigned long long s_prefix;
+
+  if (threadIdx.x == 0) s_tile = atomicAdd(&counters[0], 1u);
+  __syncthreads();
+  const uint32_t tile = s_tile;
+  const size_t base = (size_t)tile * SCAN_TILE + (size_t)threadIdx.x * SCAN_ITEMS;
+
+  uint32_t v[SCAN_ITEMS];
+  if (base + SCAN_ITEMS <= (size_t)n) {
+    const uint4* p = reinterpret_cast<const uint4*>(in + base);
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS / 4; ++i) {
+      uint4 x = __ldg(p + i);
+      v[4 * i] = x.x; v[4 * i + 1] = x.y; v[4 * i + 2] = x.z; v[4 * i + 3] = x.w;
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; ++i) v[i] = (base + i < (size_t)n) ? in[base + i] : 0u;
+  }
+  unsigned long long tsum = 0;
+#pragma unroll
+  for (int i = 0; i < SCAN_ITEMS; ++i) tsum += v[i];
+
+  // block exclusive scan of per-thread sums
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  unsigned long long incl = tsum;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    unsigned long long o = __shfl_up_sync(0xffffffffu, incl, d);
+    if (lane >= d) incl += o;
+  }
+  if (lane == 31) s_warp[warp] = incl;
+  __syncthreads();
+  unsigned long long warp_off = 0, block_sum = 0;
+#pragma unroll
+  for (int w = 0; w < SCAN_THREADS / 32; ++w) {
+    unsigned long long x = s_warp[w];
+    if (w < warp) warp_off += x;
+    block_sum += x;
+  }
+  const unsigned long long thread_excl = warp_off + incl - tsum;
+
+  // publish aggregate, then look back for the exclusive prefix of this tile
+  if (warp == 0) {
+    if (lane == 0) status[tile] = (tile == 0 ? FLAG_INC : FLAG_AGG) | (block_sum & VAL_MASK);
+    unsigned long long prefix = 0;
+    if (tile > 0) {
+      long long look = (long long)tile - 1;
+      while (true) {
+        long long idx = look - lane;
+        unsigned long long w = FLAG_INC;  // out-of-range predecessors act as a zero inclusive prefix
+        if (idx >= 0) {
+          do { w = status[idx]; } while ((w >> 62) == 0);
+        }
+        const unsigned inc_mask = __ballot_sync(0xffffffffu, (w >> 62) == 2);
+        unsigned long long val = w & VAL_MASK;
+        if (inc_mask) {
+          const int first = __ffs(inc_mask) - 1;  // nearest predecessor holding an inclusive prefix
+          if (lane > first) val = 0;
+        }
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) val += __shfl_xor_sync(0xffffffffu, val, d);
+        prefix += val;
+        if (inc_mask) break;
+        look -= 32;
+      }
+      if (lane == 0) status[tile] = FLAG_INC | ((prefix + block_sum) & VAL_MASK);
+    }
+    if (lane == 0) s_prefix = prefix;
+  }
+  __syncthreads();
+  unsigned long long run = s_prefix + thread_excl;
+
+  if (base + SCAN_ITEMS <= (size_t)n) {
+    uint4* q = reinterpret_cast<uint4*>(out + base);
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS / 4; ++i) {
+      uint4 x;
+      run += v[4 * i]; x.x = (uint32_t)run;
+      run += v[4 * i + 1]; x.y = (uint32_t)run;
+      run += v[4 * i + 2]; x.z = (uint32_t)run;
+      run += v[4 * i + 3]; x.w = (uint32_t)run;
+      q[i] = x;
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; ++i) {
+      run += v[i];
+      if (base + i < (size_t)n) out[base + i] = (uint32_t)run;
+    }
+  }
+  // the tile holding element n-1 reports the grand total (as u64: the u32 outputs may have wrapped)
+  if ((size_t)tile == ((size_t)n - 1) / SCAN_TILE && threadIdx.x == SCAN_THREADS - 1) {
+    *reinterpret_cast<unsigned long long*>(counters + 2) = run;
+  }
+}
+
+}  // namespace
+
+cudaError_t launch_scan_inclusive(const uint32_t* in, uint32_t* out, int n, unsigned long long* status,
+                                  uint32_t* counters, cudaStream_t s) {
+  if (n <= 0) return cudaSuccess;
+  const int tiles = (n + SCAN_TILE - 1) / SCAN_TILE;
+  cudaError_t e = cudaMemsetAsync(status, 0, sizeof(unsigned long long) * (size_t)(tiles + 1), s);
+  if (e != cudaSuccess) return e;
+  e = cudaMemsetAsync(counters, 0, 8 * sizeof(uint32_t), s);
+  if (e != cudaSuccess) return e;
+  scan_lookback_kernel<<<tiles, SCAN_THREADS, 0, s>>>(in, out, n, status, counters);
+  return cudaGetLastError();
+}
+
+}  // namespace h3dgs

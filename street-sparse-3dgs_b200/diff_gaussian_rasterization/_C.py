@@ -1,0 +1,205 @@
+"""Drop-in for the reference's pybind module ``diff_gaussian_rasterization._C``
+(HR/ext.cpp:15-18, HR/rasterize_points.h:18-73): same function names, positional arguments, return
+tuples and error behaviour, implemented on top of the C ABI in include/h3dgs_b200.h.
+
+Differences that a caller can observe, all deliberate:
+  * kernels run on torch's current stream (the reference used the legacy default stream);
+  * ``mark_visible`` exists (the reference's Python calls it but its binding is missing);
+  * with ``indices`` given, the semantics are those of ``gaussian_renderer.render_post``'s Python
+    interpolation (complete gradients, ``dL_dmeans2D`` per slot) -- the reference's native index
+    path has an incomplete backward and is never reached from its own Python.
+"""
+import ctypes
+
+import torch
+
+import h3dgs_native as nat
+
+NUM_CHANNELS = 3
+
+
+def _null(t):
+    return t is None or t.numel() == 0
+
+
+def _scene(bg, indices, parent_indices, ts, kids, means3D, colors, opacity, scales, rotations,
+           scale_modifier, cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, H, W, sh, degree,
+           campos, skyboxnum):
+    """Build the two C structs; returns (view, gaussians, keepalive list)."""
+    if means3D.ndimension() != 2 or means3D.size(1) != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")
+    keep = []
+
+    def f32(t, name):
+        t = nat.as_f32(t, name)
+        keep.append(t)
+        return nat.ptr(t)
+
+    def i32(t, name):
+        t = nat.as_i32(t, name)
+        keep.append(t)
+        return nat.ptr(t)
+
+    rows = means3D.size(0)
+    fused = not _null(indices)
+    P = (indices.size(0) + skyboxnum) if fused else rows
+    view = nat.View(int(W), int(H), float(tan_fovx), float(tan_fovy), f32(viewmatrix, "viewmatrix"),
+                    f32(projmatrix, "projmatrix"), f32(campos, "campos"), f32(bg, "bg"))
+    M = 0 if _null(sh) else sh.size(1)
+    g = nat.Gaussians()
+    g.P = P
+    g.store_rows = rows
+    g.sh_degree = int(degree)
+    g.sh_coeffs = M
+    g.skyboxnum = int(skyboxnum)
+    g.scale_modifier = float(scale_modifier)
+    g.means3D = f32(means3D, "means3D")
+    g.shs = f32(sh, "sh")
+    g.colors_precomp = f32(colors, "colors_precomp")
+    g.opacities = f32(opacity, "opacities")
+    g.scales = f32(scales, "scales")
+    g.rotations = f32(rotations, "rotations")
+    g.cov3D_precomp = f32(cov3D_precomp, "cov3D_precomp")
+    g.render_indices = i32(indices, "render_indices") if fused else None
+    g.parent_indices = i32(parent_indices, "parent_indices") if fused else None
+    g.ts = f32(ts, "interpolation_weights")
+    g.kids = i32(kids, "num_node_kids")
+    if fused and not _null(parent_indices) and parent_indices.size(0) < indices.size(0):
+        raise RuntimeError("parent_indices is shorter than render_indices")
+    for name, t in (("interpolation_weights", ts), ("num_node_kids", kids)):
+        if not _null(t) and t.size(0) < P - skyboxnum:
+            raise RuntimeError(f"{name} must have at least one entry per rendered Gaussian")
+    return view, g, keep
+
+
+def rasterize_gaussians_ex(bg, indices, parent_indices, ts, kids, means3D, colors, opacity, scales,
+                           rotations, scale_modifier, cov3D_precomp, viewmatrix, projmatrix, tan_fovx,
+                           tan_fovy, image_height, image_width, sh, degree, campos, prefiltered, debug,
+                           do_depth, skyboxnum=0):
+    L = nat.lib()
+    dev = means3D.device
+    H, W = int(image_height), int(image_width)
+    view, g, keep = _scene(bg, indices, parent_indices, ts, kids, means3D, colors, opacity, scales,
+                           rotations, scale_modifier, cov3D_precomp, viewmatrix, projmatrix, tan_fovx,
+                           tan_fovy, H, W, sh, degree, campos, skyboxnum)
+    P = g.P
+    out_color = torch.empty((NUM_CHANNELS, H, W), dtype=torch.float32, device=dev)
+    out_invdepth = torch.empty((1 if do_depth else 0, H, W), dtype=torch.float32, device=dev)
+    radii = torch.empty((P,), dtype=torch.int32, device=dev)
+    geom = torch.empty((L.h3dgs_geom_bytes(P),), dtype=torch.uint8, device=dev)
+    img = torch.empty((L.h3dgs_image_bytes(W, H),), dtype=torch.uint8, device=dev)
+    stream = nat.stream_handle()
+    R = ctypes.c_int64(0)
+    nat.check(L.h3dgs_forward_preprocess(ctypes.byref(view), ctypes.byref(g), nat.ptr(radii), nat.ptr(geom),
+                                         geom.numel(), ctypes.byref(R), int(bool(debug)), stream),
+              "h3dgs_forward_preprocess")
+    R = int(R.value)
+    binning = torch.empty((L.h3dgs_binning_bytes(R, W, H) if R > 0 else 0,), dtype=torch.uint8, device=dev)
+    nat.check(L.h3dgs_forward_render(ctypes.byref(view), ctypes.byref(g), nat.ptr(geom), nat.ptr(binning),
+                                     binning.numel(), nat.ptr(img), R, nat.ptr(out_color),
+                                     nat.ptr(out_invdepth), int(bool(debug)), stream),
+              "h3dgs_forward_render")
+    return R, out_color, radii, geom, binning, img, out_invdepth
+
+
+def rasterize_gaussians(bg, indices, parent_indices, ts, kids, means3D, colors, opacity, scales, rotations,
+                        scale_modifier, cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy,
+                        image_height, image_width, sh, degree, campos, prefiltered, debug, do_depth):
+    """-> (num_rendered, color[3,H,W], radii[P], geomBuffer, binningBuffer, imgBuffer, invdepth)
+    (HR/rasterize_points.cu:35-136)."""
+    return rasterize_gaussians_ex(bg, indices, parent_indices, ts, kids, means3D, colors, opacity, scales,
+                                  rotations, scale_modifier, cov3D_precomp, viewmatrix, projmatrix,
+                                  tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos,
+                                  prefiltered, debug, do_depth, 0)
+
+
+def rasterize_gaussians_backward_ex(bg, indices, parent_indices, ts, kids, means3D, radii, colors,
+                                    opacities, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,
+                                    projmatrix, tan_fovx, tan_fovy, dL_dout_color, dL_dout_invdepth, sh,
+                                    degree, campos, geomBuffer, R, binningBuffer, imageBuffer, debug,
+                                    skyboxnum=0):
+    L = nat.lib()
+    dev = means3D.device
+    H, W = dL_dout_color.size(1), dL_dout_color.size(2)
+    view, g, keep = _scene(bg, indices, parent_indices, ts, kids, means3D, colors, opacities, scales,
+                           rotations, scale_modifier, cov3D_precomp, viewmatrix, projmatrix, tan_fovx,
+                           tan_fovy, H, W, sh, degree, campos, skyboxnum)
+    P, rows, M = g.P, g.store_rows, g.sh_coeffs
+    opts = dict(dtype=torch.float32, device=dev)
+    dL_dmeans2D = torch.empty((P, 3), **opts)
+    dL_dmeans3D = torch.empty((rows, 3), **opts)
+    dL_dopacity = torch.empty((rows, 1), **opts)
+    # only the gradients of inputs that exist are materialised; the others come back empty
+    dL_dsh = torch.empty((rows, M, 3), **opts) if not _null(sh) else torch.empty((0, 0, 3), **opts)
+    dL_dcolors = torch.empty((rows, NUM_CHANNELS), **opts) if not _null(colors) else torch.empty((0, 3), **opts)
+    dL_dscales = torch.empty((rows, 3), **opts) if not _null(scales) else torch.empty((0, 3), **opts)
+    dL_drot = torch.empty((rows, 4), **opts) if not _null(rotations) else torch.empty((0, 4), **opts)
+    dL_dcov3D = torch.empty((rows, 6), **opts) if not _null(cov3D_precomp) else torch.empty((0, 6), **opts)
+    grads = nat.Grads(nat.ptr(dL_dmeans2D), nat.ptr(dL_dmeans3D), nat.ptr(dL_dsh), nat.ptr(dL_dcolors),
+                      nat.ptr(dL_dopacity), nat.ptr(dL_dscales), nat.ptr(dL_drot), nat.ptr(dL_dcov3D))
+    ws = torch.empty((L.h3dgs_backward_workspace_bytes(P),), dtype=torch.uint8, device=dev)
+    dcol = nat.as_f32(dL_dout_color, "dL_dout_color")
+    ddep = nat.as_f32(dL_dout_invdepth, "dL_dout_invdepth")
+    nat.check(L.h3dgs_backward(ctypes.byref(view), ctypes.byref(g), nat.ptr(radii), nat.ptr(geomBuffer),
+                               nat.ptr(binningBuffer), nat.ptr(imageBuffer), int(R), nat.ptr(dcol),
+                               nat.ptr(ddep), ctypes.byref(grads), nat.ptr(ws), ws.numel(),
+                               int(bool(debug)), nat.stream_handle()),
+              "h3dgs_backward")
+    return dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drot
+
+
+def rasterize_gaussians_backward(bg, indices, parent_indices, ts, kids, means3D, radii, colors, opacities,
+                                 scales, rotations, scale_modifier, cov3D_precomp, viewmatrix, projmatrix,
+                                 tan_fovx, tan_fovy, dL_dout_color, dL_dout_invdepth, sh, degree, campos,
+                                 geomBuffer, R, binningBuffer, imageBuffer, debug):
+    """-> (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations)
+    (HR/rasterize_points.cu:138-242)."""
+    return rasterize_gaussians_backward_ex(bg, indices, parent_indices, ts, kids, means3D, radii, colors,
+                                           opacities, scales, rotations, scale_modifier, cov3D_precomp,
+                                           viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color,
+                                           dL_dout_invdepth, sh, degree, campos, geomBuffer, R,
+                                           binningBuffer, imageBuffer, debug, 0)
+
+
+def mark_visible(positions, viewmatrix, projmatrix):
+    """bool[P]: in front of the near plane (HR/cuda_rasterizer/rasterizer_impl.cu:54-66,145-157)."""
+    L = nat.lib()
+    positions = nat.as_f32(positions, "positions")
+    P = positions.size(0)
+    present = torch.zeros((P,), dtype=torch.bool, device=positions.device)
+    if P:
+        v = nat.as_f32(viewmatrix, "viewmatrix")
+        p = nat.as_f32(projmatrix, "projmatrix")
+        nat.check(L.h3dgs_mark_visible(P, nat.ptr(positions), nat.ptr(v), nat.ptr(p), nat.ptr(present),
+                                       nat.stream_handle()), "h3dgs_mark_visible")
+    return present
+
+
+def debug_view(P, W, H, R, geom, binning, img):
+    """Typed views into the opaque buffers (parity tests): dict of torch tensors aliasing them."""
+    L = nat.lib()
+    dv = nat.DebugView()
+    nat.check(L.h3dgs_debug_view(P, W, H, R, nat.ptr(geom), nat.ptr(binning), nat.ptr(img),
+                                 ctypes.byref(dv)), "h3dgs_debug_view")
+
+    def view_of(buf, address, count, dtype):
+        if not address or buf is None or buf.numel() == 0:
+            return None
+        off = address - buf.data_ptr()
+        nbytes = count * torch.empty((), dtype=dtype).element_size()
+        return buf[off:off + nbytes].view(dtype)
+
+    tiles = ((W + 15) // 16) * ((H + 15) // 16)
+    return {
+        "point_list_keys": view_of(binning, dv.point_list_keys, R, torch.int64),
+        "point_list": view_of(binning, dv.point_list, R, torch.int32),
+        "ranges": view_of(img, dv.ranges, tiles * 2, torch.int32),
+        "final_T": view_of(img, dv.final_T, W * H, torch.float32),
+        "n_contrib": view_of(img, dv.n_contrib, W * H, torch.int32),
+        "depths": view_of(geom, dv.depths, P, torch.float32),
+        "tiles_touched": view_of(geom, dv.tiles_touched, P, torch.int32),
+        "point_offsets": view_of(geom, dv.point_offsets, P, torch.int32),
+        "records": view_of(geom, dv.records, P * 16, torch.float32),
+        "cov3D": view_of(geom, dv.cov3D, P * 6, torch.float32),
+        "tile_rects": view_of(geom, dv.tile_rects, P * 4, torch.int16),
+    }

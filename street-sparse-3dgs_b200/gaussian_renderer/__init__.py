@@ -1,0 +1,246 @@
+"""Drop-in for the reference's ``gaussian_renderer`` (gaussian_renderer/__init__.py:20-417):
+``render``, ``render_post`` and ``render_coarse`` with the same signatures and returned dict keys.
+
+What changes underneath: where the reference gathers rows and interpolates child/parent attributes
+with a dozen torch kernels (and autograd scatters N-sized zero tensors back, :202-235), the cut
+indices and interpolation weights go straight into the rasterizer, whose preprocess kernels do the
+gather + lerp (forward) and the t / (1-t) scatter (backward).  Results follow the Python arithmetic
+(three separately rounded ops per lerp), so images match the reference path to the last bit of the
+projection.
+"""
+import math
+
+import torch
+
+from diff_gaussian_rasterization import (GaussianRasterizationSettings, GaussianRasterizer,
+                                         rasterize_gaussians_fused)
+
+
+def _eval_sh(deg, sh, dirs):
+    """utils/sh_utils.py:57-112 (used only for pipe.convert_SHs_python)."""
+    C0 = 0.28209479177387814
+    C1 = 0.4886025119029199
+    C2 = [1.0925484305920792, -1.0925484305920792, 0.31539156525252005, -1.0925484305920792, 0.5462742152960396]
+    C3 = [-0.5900435899266435, 2.890611442640554, -0.4570457994644658, 0.3731763325901154,
+          -0.4570457994644658, 1.445305721320277, -0.5900435899266435]
+    result = C0 * sh[..., 0]
+    if deg > 0:
+        x, y, z = dirs[..., 0:1], dirs[..., 1:2], dirs[..., 2:3]
+        result = result - C1 * y * sh[..., 1] + C1 * z * sh[..., 2] - C1 * x * sh[..., 3]
+        if deg > 1:
+            xx, yy, zz = x * x, y * y, z * z
+            xy, yz, xz = x * y, y * z, x * z
+            result = (result + C2[0] * xy * sh[..., 4] + C2[1] * yz * sh[..., 5] +
+                      C2[2] * (2.0 * zz - xx - yy) * sh[..., 6] + C2[3] * xz * sh[..., 7] +
+                      C2[4] * (xx - yy) * sh[..., 8])
+            if deg > 2:
+                result = (result + C3[0] * y * (3 * xx - yy) * sh[..., 9] + C3[1] * xy * z * sh[..., 10] +
+                          C3[2] * y * (4 * zz - xx - yy) * sh[..., 11] +
+                          C3[3] * z * (2 * zz - 3 * xx - 3 * yy) * sh[..., 12] +
+                          C3[4] * x * (4 * zz - xx - yy) * sh[..., 13] + C3[5] * z * (xx - yy) * sh[..., 14] +
+                          C3[6] * x * (xx - 3 * yy) * sh[..., 15])
+    return result
+
+
+def _screenspace_points(pc):
+    # zero tensor whose gradient is the 2D mean gradient (densification statistics)
+    pts = torch.zeros_like(pc.get_xyz, dtype=pc.get_xyz.dtype, requires_grad=True, device="cuda") + 0
+    try:
+        pts.retain_grad()
+    except Exception:
+        pass
+    return pts
+
+
+def _appearance(viewpoint_camera, pc, pipe, override_color):
+    shs, colors_precomp = None, None
+    if override_color is None:
+        if pipe.convert_SHs_python:
+            shs_view = pc.get_features.transpose(1, 2).view(-1, 3, (pc.max_sh_degree + 1) ** 2)
+            dir_pp = (pc.get_xyz - viewpoint_camera.camera_center.repeat(pc.get_features.shape[0], 1))
+            dir_pp_normalized = dir_pp / dir_pp.norm(dim=1, keepdim=True)
+            sh2rgb = _eval_sh(pc.active_sh_degree, shs_view, dir_pp_normalized)
+            colors_precomp = torch.clamp_min(sh2rgb + 0.5, 0.0)
+        else:
+            shs = pc.get_features
+    else:
+        colors_precomp = override_color
+    return shs, colors_precomp
+
+
+def _geometry(pc, pipe, scaling_modifier):
+    if pipe.compute_cov3D_python:
+        return None, None, pc.get_covariance(scaling_modifier)
+    return pc.get_scaling, pc.get_rotation, None
+
+
+def _settings(viewpoint_camera, pc, bg_color, scaling_modifier, debug, do_depth, render_indices,
+              parent_indices, interpolation_weights, num_node_kids):
+    return GaussianRasterizationSettings(
+        image_height=int(viewpoint_camera.image_height),
+        image_width=int(viewpoint_camera.image_width),
+        tanfovx=math.tan(viewpoint_camera.FoVx * 0.5),
+        tanfovy=math.tan(viewpoint_camera.FoVy * 0.5),
+        bg=bg_color,
+        scale_modifier=scaling_modifier,
+        viewmatrix=viewpoint_camera.world_view_transform,
+        projmatrix=viewpoint_camera.full_proj_transform,
+        sh_degree=pc.active_sh_degree,
+        campos=viewpoint_camera.camera_center,
+        prefiltered=False,
+        debug=debug,
+        render_indices=render_indices,
+        parent_indices=parent_indices,
+        interpolation_weights=interpolation_weights,
+        num_node_kids=num_node_kids,
+        do_depth=do_depth)
+
+
+def _empty(dtype):
+    return torch.empty(0, dtype=dtype, device="cuda")
+
+
+def _rasterize(settings, means3D, means2D, opacity, shs, colors_precomp, scales, rotations, cov3D_precomp,
+               skybox_points=None):
+    e = torch.Tensor([])
+    if skybox_points is None:
+        return GaussianRasterizer(raster_settings=settings)(
+            means3D=means3D, means2D=means2D, shs=shs, colors_precomp=colors_precomp, opacities=opacity,
+            scales=scales, rotations=rotations, cov3D_precomp=cov3D_precomp)
+    return rasterize_gaussians_fused(
+        means3D, means2D, e if shs is None else shs, e if colors_precomp is None else colors_precomp,
+        opacity, e if scales is None else scales, e if rotations is None else rotations,
+        e if cov3D_precomp is None else cov3D_precomp, settings, skybox_points)
+
+
+def _as_index(t):
+    return t.to(device="cuda", dtype=torch.int32).contiguous()
+
+
+def render(viewpoint_camera, pc, pipe, bg_color: torch.Tensor, scaling_modifier=1.0, override_color=None,
+           indices=None, use_trained_exp=False):
+    """Render the scene (gaussian_renderer/__init__.py:20-135).  Background tensor must be on GPU."""
+    screenspace_points = _screenspace_points(pc)
+    means3D, means2D, opacity = pc.get_xyz, screenspace_points, pc.get_opacity
+    scales, rotations, cov3D_precomp = _geometry(pc, pipe, scaling_modifier)
+    shs, colors_precomp = _appearance(viewpoint_camera, pc, pipe, override_color)
+
+    if indices is not None:
+        idx = _as_index(indices)
+        settings = _settings(viewpoint_camera, pc, bg_color, scaling_modifier, pipe.debug, True, idx,
+                             _empty(torch.int32), _empty(torch.float32), _empty(torch.int32))
+        rendered_image, radii, depth_image = _rasterize(settings, means3D, means2D[indices].contiguous(), opacity,
+                                                        shs, colors_precomp, scales, rotations, cov3D_precomp, 0)
+    else:
+        settings = _settings(viewpoint_camera, pc, bg_color, scaling_modifier, pipe.debug, True,
+                             _empty(torch.int32), _empty(torch.int32), _empty(torch.float32), _empty(torch.int32))
+        rendered_image, radii, depth_image = _rasterize(settings, means3D, means2D, opacity, shs, colors_precomp,
+                                                        scales, rotations, cov3D_precomp)
+
+    if use_trained_exp:
+        exposure = pc.get_exposure_from_name(viewpoint_camera.image_name)
+        rendered_image = torch.matmul(rendered_image.permute(1, 2, 0), exposure[:3, :3]).permute(2, 0, 1) + \
+            exposure[:3, 3, None, None]
+    rendered_image = rendered_image.clamp(0, 1)
+
+    subfilter = radii > 0
+    if indices is not None:
+        vis_filter = torch.zeros(pc._xyz.size(0), dtype=bool, device="cuda")
+        w = vis_filter[indices]
+        w[subfilter] = True
+        vis_filter[indices] = w
+    else:
+        vis_filter = subfilter
+    return {"render": rendered_image,
+            "depth": depth_image,
+            "viewspace_points": screenspace_points,
+            "visibility_filter": vis_filter.nonzero().flatten().long(),
+            "radii": radii[subfilter]}
+
+
+def render_post(viewpoint_camera, pc, pipe, bg_color: torch.Tensor, scaling_modifier=1.0, override_color=None,
+                render_indices=torch.Tensor([]).int(), parent_indices=torch.Tensor([]).int(),
+                interpolation_weights=torch.Tensor([]).float(), num_node_kids=torch.Tensor([]).int(),
+                interp_python=True, use_trained_exp=False, do_depth=False):
+    """Render the scene from a hierarchy cut (gaussian_renderer/__init__.py:138-304)."""
+    screenspace_points = _screenspace_points(pc)
+    means3D, means2D, opacity = pc.get_xyz, screenspace_points, pc.get_opacity
+    scales, rotations, cov3D_precomp = _geometry(pc, pipe, scaling_modifier)
+    shs, colors_precomp = _appearance(viewpoint_camera, pc, pipe, override_color)
+
+    skybox = None
+    if render_indices.size(0) != 0:
+        num_entries = render_indices.size(0)
+        idx = _as_index(render_indices)
+        if interp_python:
+            skybox = int(pc.skybox_points)
+            par = _as_index(parent_indices[:num_entries])
+            # the reference marks the appended skybox slots t = 1 / kids = 1, mutating the caller's kids
+            if skybox:
+                num_node_kids[num_entries:num_entries + skybox] = 1
+        else:
+            skybox = 0
+            par = _empty(torch.int32)
+        means2D = means2D[:(num_entries + skybox)].contiguous() if interp_python else means2D[render_indices.long()].contiguous()
+        render_indices, parent_indices = idx, par
+        if interpolation_weights.numel():
+            interpolation_weights = interpolation_weights.to("cuda")
+        if num_node_kids.numel():
+            num_node_kids = num_node_kids.to("cuda")
+
+    settings = _settings(viewpoint_camera, pc, bg_color, scaling_modifier, pipe.debug, do_depth, render_indices,
+                         parent_indices, interpolation_weights, num_node_kids)
+    rendered_image, radii, depth_image = _rasterize(settings, means3D, means2D, opacity, shs, colors_precomp,
+                                                    scales, rotations, cov3D_precomp, skybox)
+
+    if use_trained_exp and pc.pretrained_exposures:
+        try:
+            exposure = pc.pretrained_exposures[viewpoint_camera.image_name]
+            rendered_image = torch.matmul(rendered_image.permute(1, 2, 0), exposure[:3, :3]).permute(2, 0, 1) + \
+                exposure[:3, 3, None, None]
+        except Exception:
+            print(f"Exposures should be optimized in single. Missing exposure for image {viewpoint_camera.image_name}")
+    rendered_image = rendered_image.clamp(0, 1)
+
+    vis_filter = radii > 0
+    out = {"render": rendered_image,
+           "viewspace_points": screenspace_points,
+           "visibility_filter": vis_filter,
+           "radii": radii[vis_filter]}
+    if do_depth:
+        out["depth"] = depth_image
+    return out
+
+
+def render_coarse(viewpoint_camera, pc, pipe, bg_color: torch.Tensor, scaling_modifier=1.0, zfar=0.0,
+                  override_color=None, indices=None):
+    """Render for the coarse optimisation (gaussian_renderer/__init__.py:306-417): debug on, no depth."""
+    screenspace_points = _screenspace_points(pc)
+    means3D, means2D, opacity = pc.get_xyz, screenspace_points, pc.get_opacity
+    scales, rotations, cov3D_precomp = _geometry(pc, pipe, scaling_modifier)
+    shs, colors_precomp = _appearance(viewpoint_camera, pc, pipe, override_color)
+
+    if indices is not None:
+        idx = _as_index(indices)
+        settings = _settings(viewpoint_camera, pc, bg_color, scaling_modifier, True, False, idx,
+                             _empty(torch.int32), _empty(torch.float32), _empty(torch.int32))
+        rendered_image, radii, _ = _rasterize(settings, means3D, means2D[indices].contiguous(), opacity, shs,
+                                              colors_precomp, scales, rotations, cov3D_precomp, 0)
+    else:
+        settings = _settings(viewpoint_camera, pc, bg_color, scaling_modifier, True, False, _empty(torch.int32),
+                             _empty(torch.int32), _empty(torch.float32), _empty(torch.int32))
+        rendered_image, radii, _ = _rasterize(settings, means3D, means2D, opacity, shs, colors_precomp, scales,
+                                              rotations, cov3D_precomp)
+
+    subfilter = radii > 0
+    if indices is not None:
+        vis_filter = torch.zeros(pc._xyz.size(0), dtype=bool, device="cuda")
+        w = vis_filter[indices]
+        w[subfilter] = True
+        vis_filter[indices] = w
+    else:
+        vis_filter = subfilter
+    return {"render": rendered_image,
+            "viewspace_points": screenspace_points,
+            "visibility_filter": vis_filter,
+            "radii": radii[subfilter]}

@@ -1,0 +1,148 @@
+"""ctypes binding of libh3dgs_b200.so (include/h3dgs_b200.h).
+
+This is the only place that knows both torch and the C ABI: tensors go in as raw device pointers
+plus the current CUDA stream.  There is no fallback: if the library is missing or was not built for
+this machine, importing the op packages raises.
+"""
+import ctypes
+import os
+from ctypes import (POINTER, Structure, byref, c_char_p, c_float, c_int, c_int32, c_int64, c_size_t,
+                    c_void_p)
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libh3dgs_b200.so")
+
+
+class H3dgsError(RuntimeError):
+    pass
+
+
+class View(Structure):
+    _fields_ = [("image_width", c_int32), ("image_height", c_int32),
+                ("tan_fovx", c_float), ("tan_fovy", c_float),
+                ("viewmatrix", c_void_p), ("projmatrix", c_void_p),
+                ("campos", c_void_p), ("background", c_void_p)]
+
+
+class Gaussians(Structure):
+    _fields_ = [("P", c_int32), ("store_rows", c_int32), ("sh_degree", c_int32), ("sh_coeffs", c_int32),
+                ("skyboxnum", c_int32), ("scale_modifier", c_float),
+                ("means3D", c_void_p), ("shs", c_void_p), ("colors_precomp", c_void_p),
+                ("opacities", c_void_p), ("scales", c_void_p), ("rotations", c_void_p),
+                ("cov3D_precomp", c_void_p),
+                ("render_indices", c_void_p), ("parent_indices", c_void_p),
+                ("ts", c_void_p), ("kids", c_void_p)]
+
+
+class Grads(Structure):
+    _fields_ = [("dL_dmeans2D", c_void_p), ("dL_dmeans3D", c_void_p), ("dL_dsh", c_void_p),
+                ("dL_dcolors", c_void_p), ("dL_dopacity", c_void_p), ("dL_dscales", c_void_p),
+                ("dL_drotations", c_void_p), ("dL_dcov3D", c_void_p)]
+
+
+class DebugView(Structure):
+    _fields_ = [("point_list_keys", c_void_p), ("point_list", c_void_p), ("ranges", c_void_p),
+                ("final_T", c_void_p), ("n_contrib", c_void_p), ("depths", c_void_p),
+                ("tiles_touched", c_void_p), ("point_offsets", c_void_p), ("records", c_void_p),
+                ("cov3D", c_void_p), ("tile_rects", c_void_p)]
+
+
+class AdamTensor(Structure):
+    _fields_ = [("param", c_void_p), ("grad", c_void_p), ("exp_avg", c_void_p), ("exp_avg_sq", c_void_p),
+                ("width", c_int32), ("step_size", c_float), ("bias_correction2_sqrt", c_float),
+                ("beta1", c_float), ("beta2", c_float), ("eps", c_float)]
+
+
+ADAM_MAX_TENSORS = 8
+
+# name -> (restype, argtypes); every symbol include/h3dgs_b200.h declares
+SIGNATURES = {
+    "h3dgs_abi_version": (c_int, []),
+    "h3dgs_last_error": (c_char_p, []),
+    "h3dgs_geom_bytes": (c_size_t, [c_int32]),
+    "h3dgs_image_bytes": (c_size_t, [c_int32, c_int32]),
+    "h3dgs_binning_bytes": (c_size_t, [c_int64, c_int32, c_int32]),
+    "h3dgs_backward_workspace_bytes": (c_size_t, [c_int32]),
+    "h3dgs_forward_preprocess": (c_int, [POINTER(View), POINTER(Gaussians), c_void_p, c_void_p, c_size_t,
+                                          POINTER(c_int64), c_int, c_void_p]),
+    "h3dgs_forward_render": (c_int, [POINTER(View), POINTER(Gaussians), c_void_p, c_void_p, c_size_t,
+                                      c_void_p, c_int64, c_void_p, c_void_p, c_int, c_void_p]),
+    "h3dgs_backward": (c_int, [POINTER(View), POINTER(Gaussians), c_void_p, c_void_p, c_void_p, c_void_p,
+                                c_int64, c_void_p, c_void_p, POINTER(Grads), c_void_p, c_size_t, c_int,
+                                c_void_p]),
+    "h3dgs_mark_visible": (c_int, [c_int32, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "h3dgs_debug_view": (c_int, [c_int32, c_int32, c_int32, c_int64, c_void_p, c_void_p, c_void_p,
+                                  POINTER(DebugView)]),
+    "h3dgs_expand_workspace_bytes": (c_size_t, [c_int32]),
+    "h3dgs_expand_to_size": (c_int, [c_int32, c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                      c_void_p, c_void_p, c_size_t, POINTER(c_int32), c_void_p]),
+    "h3dgs_interpolation_weights": (c_int, [c_int32, c_void_p, c_float, c_void_p, c_void_p, c_float,
+                                             c_float, c_float, c_void_p, c_void_p, c_void_p]),
+    "h3dgs_expand_to_target": (c_int64, [c_int32, c_void_p, c_int32, c_void_p, c_int64]),
+    "h3dgs_hier_read_header": (c_int, [c_char_p, POINTER(c_int64), POINTER(c_int64), POINTER(c_int)]),
+    "h3dgs_hier_read": (c_int, [c_char_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                 c_void_p]),
+    "h3dgs_hier_write": (c_int, [c_char_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_void_p,
+                                  c_void_p, c_void_p, c_void_p, c_int]),
+    "h3dgs_sparse_adam": (c_int, [POINTER(AdamTensor), c_int32, c_void_p, c_int64, c_int64, c_void_p]),
+}
+
+_lib = None
+
+
+def lib():
+    """Load the shared library once; fail loudly when it is absent."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise H3dgsError(
+                f"{LIB_PATH} not found: build it with `python street-sparse-3dgs_b200/build.py` "
+                "(there is no CPU or PyTorch fallback)")
+        handle = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(handle, name)
+            fn.restype = res
+            fn.argtypes = args
+        if handle.h3dgs_abi_version() != 1:
+            raise H3dgsError("libh3dgs_b200.so ABI version mismatch")
+        _lib = handle
+    return _lib
+
+
+def check(rc, what=""):
+    if rc != 0:
+        msg = lib().h3dgs_last_error().decode("utf-8", "replace")
+        raise H3dgsError(f"{what} failed (code {rc}): {msg}")
+
+
+def ptr(t):
+    """Device (or host) pointer of a tensor; None (NULL) for an empty / absent tensor."""
+    if t is None or t.numel() == 0:
+        return None
+    return t.data_ptr()
+
+
+def stream_handle():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def as_f32(t, name):
+    if t is None or t.numel() == 0:
+        return t
+    if t.dtype != torch.float32:
+        raise TypeError(f"{name} must be float32, got {t.dtype}")
+    if not t.is_cuda:
+        raise ValueError(f"{name} must be a CUDA tensor")
+    return t.contiguous()
+
+
+def as_i32(t, name):
+    if t is None or t.numel() == 0:
+        return t
+    if t.dtype != torch.int32:
+        raise TypeError(f"{name} must be int32, got {t.dtype}")
+    if not t.is_cuda:
+        raise ValueError(f"{name} must be a CUDA tensor")
+    return t.contiguous()

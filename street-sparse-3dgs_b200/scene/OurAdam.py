@@ -1,0 +1,120 @@
+"""Drop-in for the reference's ``scene/OurAdam.py`` (class ``Adam``, :8-175): an Adam optimizer whose
+``step(relevant)`` only updates the rows listed in ``relevant`` (moments of other rows stay stale,
+no decay), and updates every row when ``relevant`` is empty.
+
+Same constructor, ``param_groups`` and ``state`` layout (``'step'`` CPU scalar tensor, ``'exp_avg'``,
+``'exp_avg_sq'``), so ``state_dict()`` checkpoints are interchangeable.  The arithmetic of
+``_single_tensor_adam`` / ``_single_tensor_adam2`` (:249-426) runs as one fused CUDA launch over all
+parameter tensors of the step (h3dgs_sparse_adam, include/h3dgs_b200.h) instead of ~10 torch kernels
+and three gathered temporaries per parameter group.
+"""
+import ctypes
+import math
+from typing import Optional
+
+import torch
+from torch.optim.optimizer import Optimizer
+
+import h3dgs_native as nat
+
+
+class Adam(Optimizer):
+    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0, amsgrad=False, *,
+                 foreach: Optional[bool] = None, maximize: bool = False, capturable: bool = False):
+        if not 0.0 <= lr:
+            raise ValueError("Invalid learning rate: {}".format(lr))
+        if not 0.0 <= eps:
+            raise ValueError("Invalid epsilon value: {}".format(eps))
+        if not 0.0 <= betas[0] < 1.0:
+            raise ValueError("Invalid beta parameter at index 0: {}".format(betas[0]))
+        if not 0.0 <= betas[1] < 1.0:
+            raise ValueError("Invalid beta parameter at index 1: {}".format(betas[1]))
+        if not 0.0 <= weight_decay:
+            raise ValueError("Invalid weight_decay value: {}".format(weight_decay))
+        defaults = dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay, amsgrad=amsgrad,
+                        maximize=maximize, foreach=foreach, capturable=capturable)
+        super(Adam, self).__init__(params, defaults)
+
+    def __setstate__(self, state):
+        super().__setstate__(state)
+        for group in self.param_groups:
+            group.setdefault('amsgrad', False)
+            group.setdefault('maximize', False)
+            group.setdefault('foreach', None)
+            group.setdefault('capturable', False)
+        state_values = list(self.state.values())
+        step_is_tensor = (len(state_values) != 0) and torch.is_tensor(state_values[0]['step'])
+        if not step_is_tensor:
+            for s in state_values:
+                s['step'] = torch.tensor(float(s['step']))
+
+    @torch.no_grad()
+    def step(self, relevant, closure=None):
+        """One optimisation step over the rows in ``relevant`` (1-D LongTensor of row indices; empty
+        means every row)."""
+        loss = None
+        if closure is not None:
+            with torch.enable_grad():
+                loss = closure()
+
+        batch = []  # (AdamTensor, rows) for one fused launch
+        dev = None
+        keep = []
+        for group in self.param_groups:
+            if group['amsgrad'] or group['maximize'] or group['weight_decay'] != 0 or group['capturable'] \
+                    or group['foreach']:
+                raise NotImplementedError(
+                    "the fused sparse Adam implements the options the reference training uses "
+                    "(amsgrad=False, maximize=False, weight_decay=0, capturable=False, foreach=None)")
+            beta1, beta2 = group['betas']
+            for p in group['params']:
+                if p.grad is None:
+                    continue
+                if p.grad.is_sparse:
+                    raise RuntimeError('Adam does not support sparse gradients, please consider SparseAdam instead')
+                if not p.is_cuda or p.dtype != torch.float32:
+                    raise RuntimeError("fused sparse Adam needs float32 CUDA parameters (no CPU fallback)")
+                dev = p.device
+                state = self.state[p]
+                if len(state) == 0:
+                    state['step'] = torch.tensor(0.)
+                    state['exp_avg'] = torch.zeros_like(p, memory_format=torch.preserve_format)
+                    state['exp_avg_sq'] = torch.zeros_like(p, memory_format=torch.preserve_format)
+                state['step'] += 1
+                step = state['step'].item()  # CPU tensor: no device sync
+                bias_correction1 = 1 - beta1 ** step
+                bias_correction2 = 1 - beta2 ** step
+                step_size = group['lr'] / bias_correction1
+                bias_correction2_sqrt = math.sqrt(bias_correction2)
+                if not (p.is_contiguous() and state['exp_avg'].is_contiguous() and state['exp_avg_sq'].is_contiguous()):
+                    raise RuntimeError("fused sparse Adam needs contiguous parameters and moments")
+                grad = p.grad.contiguous()
+                keep.append(grad)
+                rows = p.size(0) if p.dim() > 0 else 1
+                width = p.numel() // max(rows, 1)
+                batch.append((nat.AdamTensor(p.data_ptr(), grad.data_ptr(), state['exp_avg'].data_ptr(),
+                                             state['exp_avg_sq'].data_ptr(), width, step_size,
+                                             bias_correction2_sqrt, beta1, beta2, group['eps']), rows))
+        if not batch:
+            return loss
+
+        L = nat.lib()
+        if relevant is not None and relevant.numel() > 0:
+            if relevant.dim() != 1:
+                raise RuntimeError("relevant must be a 1-D tensor of row indices")
+            rel = relevant.to(device=dev, dtype=torch.int64).contiguous()
+            rel_ptr, K = rel.data_ptr(), rel.numel()
+        else:
+            rel, rel_ptr, K = None, None, 0
+
+        # tensors sharing a row count go out together, at most ADAM_MAX_TENSORS per launch
+        by_rows = {}
+        for t, rows in batch:
+            by_rows.setdefault(rows, []).append(t)
+        for rows, ts in by_rows.items():
+            for i in range(0, len(ts), nat.ADAM_MAX_TENSORS):
+                chunk = ts[i:i + nat.ADAM_MAX_TENSORS]
+                arr = (nat.AdamTensor * len(chunk))(*chunk)
+                nat.check(L.h3dgs_sparse_adam(arr, len(chunk), rel_ptr, K, rows, nat.stream_handle()),
+                          "h3dgs_sparse_adam")
+        return loss
