@@ -26,11 +26,12 @@ def main():
     ap.add_argument("--seed", type=int, default=0)
     ap.add_argument("--interp", action="store_true")
     ap.add_argument("--nodepth", action="store_true")
+    ap.add_argument("--yaw", type=float, default=None)
     args = ap.parse_args()
     import diff_gaussian_rasterization as dgr
     dev = "cuda"
     sc = scenes.street_gaussians(args.n, seed=args.seed, device=dev)
-    cam = scenes.street_camera(args.w, args.h, seed=args.seed, device=dev)
+    cam = scenes.street_camera(args.w, args.h, seed=args.seed, device=dev, yaw_deg=args.yaw)
     bg = torch.tensor([0.1, 0.2, 0.3], device=dev)
     ts = kids = None
     if args.interp:
@@ -100,9 +101,17 @@ def main():
     co, ro, do_, go, g2o = run(ours)
     cr, rr, dr, gr, g2r = run(ref)
     torch.cuda.synchronize()
+    cr2, rr2, dr2, gr2, g2r2 = run(ref)
+    torch.cuda.synchronize()
     for k in go:
-        print(f"grad {k:10s} relerr {relerr(go[k], gr[k]):.3e}  max|ref| {float(gr[k].abs().max()):.3e}")
-    print(f"grad means2D   relerr {relerr(g2o, g2r):.3e}")
+        print(f"grad {k:10s} relerr {relerr(go[k], gr[k]):.3e}  ref-vs-ref {relerr(gr2[k], gr[k]):.3e}  max|ref| {float(gr[k].abs().max()):.3e}")
+    print(f"grad means2D   relerr {relerr(g2o, g2r):.3e}  ref-vs-ref {relerr(g2r2, g2r):.3e}")
+    d = (go["scales"] - gr["scales"]).abs().max(dim=1).values
+    top = d.topk(6).indices
+    for i in top.tolist():
+        print("worst scales idx", i, "ours", go["scales"][i].tolist(), "ref", gr["scales"][i].tolist(), "ref2", gr2["scales"][i].tolist(),
+              "radius", int(ro[i]), "t", float(ts[i]) if ts is not None else None, "kids", int(kids[i]) if kids is not None else None,
+              "opac", float(sc["opacities"][i]), "scale", sc["scales"][i].tolist())
     return 0
 
 

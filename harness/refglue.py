@@ -14,9 +14,32 @@ import importlib.util
 import math
 import os
 
+from typing import NamedTuple
+
 import torch
 
 from . import ROOT
+
+
+class RefSettings(NamedTuple):
+    """Field-for-field GaussianRasterizationSettings (HR/diff_gaussian_rasterization/__init__.py:146-163)."""
+    image_height: int
+    image_width: int
+    tanfovx: float
+    tanfovy: float
+    bg: torch.Tensor
+    scale_modifier: float
+    viewmatrix: torch.Tensor
+    projmatrix: torch.Tensor
+    sh_degree: int
+    campos: torch.Tensor
+    prefiltered: bool
+    debug: bool
+    render_indices: torch.Tensor
+    parent_indices: torch.Tensor
+    interpolation_weights: torch.Tensor
+    num_node_kids: torch.Tensor
+    do_depth: bool
 
 REF_DIR = os.path.join(ROOT, "oracle", "_ref")
 

@@ -245,6 +245,18 @@ H3DGS_API int h3dgs_sparse_adam(const H3dgsAdamTensor* tensors, int32_t num_tens
                       const int64_t* relevant, int64_t num_relevant, int64_t num_rows,
                       h3dgs_stream_t stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * Instrumentation (no reference counterpart).  Launch counting is always on; per-kernel timing wraps
+ * every kernel in a pair of CUDA events on the launching stream while enabled.
+ * ------------------------------------------------------------------------------------------------ */
+#define H3DGS_PROF_KERNELS 16
+H3DGS_API int64_t h3dgs_launch_count(void);          /* kernels launched by this library so far (process-wide) */
+H3DGS_API int h3dgs_profile_enable(int enable);      /* returns the previous setting */
+/* Synchronises pending events and adds their durations; ms[i] / launches[i] are per kernel id
+ * 0..H3DGS_PROF_KERNELS-1 (see h3dgs_profile_name).  reset != 0 clears the accumulators afterwards. */
+H3DGS_API int h3dgs_profile_read(double* ms, int64_t* launches, int reset);
+H3DGS_API const char* h3dgs_profile_name(int kernel_id);
+
 #ifdef __cplusplus
 }
 #endif

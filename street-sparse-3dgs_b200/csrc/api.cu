@@ -3,6 +3,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <vector>
 
 #include "common.cuh"
 
@@ -17,6 +18,42 @@ int fail(int code, const char* what) {
 int cuda_fail(cudaError_t e, const char* what) {
   std::snprintf(g_err, sizeof(g_err), "CUDA error %d (%s) in %s", (int)e, cudaGetErrorString(e), what);
   return (int)e;
+}
+
+// ---- instrumentation ----
+namespace {
+struct Prof {
+  bool on = false;
+  long long launches_total = 0;
+  double ms[K_COUNT] = {0};
+  long long count[K_COUNT] = {0};
+  struct Pair { int id; cudaEvent_t a, b; };
+  std::vector<Pair> pending;
+  std::vector<cudaEvent_t> pool;
+  cudaEvent_t cur[K_COUNT] = {nullptr};
+  cudaEvent_t get() {
+    if (!pool.empty()) { cudaEvent_t e = pool.back(); pool.pop_back(); return e; }
+    cudaEvent_t e; cudaEventCreate(&e); return e;
+  }
+} g_prof;
+const char* const kKernelNames[K_COUNT] = {
+  "preprocess_fwd", "scan", "emit_instances", "sort_histogram", "sort_scan", "sort_onesweep_pass",
+  "tile_ranges", "blend_fwd", "blend_bwd", "preprocess_bwd", "cut_mark_nodes", "cut_put_indices",
+  "cut_interp_weights", "sparse_adam", "mark_visible", "memset"};
+}  // namespace
+
+void prof_begin(int id, cudaStream_t s) {
+  if (id != K_MEMSET) g_prof.launches_total++;
+  if (!g_prof.on) return;
+  g_prof.cur[id] = g_prof.get();
+  cudaEventRecord(g_prof.cur[id], s);
+}
+void prof_end(int id, cudaStream_t s) {
+  if (!g_prof.on || !g_prof.cur[id]) return;
+  cudaEvent_t b = g_prof.get();
+  cudaEventRecord(b, s);
+  g_prof.pending.push_back({id, g_prof.cur[id], b});
+  g_prof.cur[id] = nullptr;
 }
 
 // H3DGS_STAGE=tma|ldgsts selects how the blend kernels stage records into shared memory.
@@ -203,6 +240,7 @@ int h3dgs_backward(const H3dgsView* view, const H3dgsGaussians* g, const int32_t
     return p ? cudaMemsetAsync(p, 0, n * sizeof(float), s) : cudaSuccess;
   };
   if (P == 0 || R <= 0 || fused) {
+    ProfScope ps(K_MEMSET, s);
     // fused-cut mode scatters into store rows; empty renders produce all-zero gradients
     H3_CUDA(zero(grads->dL_dmeans3D, rows * 3));
     H3_CUDA(zero(grads->dL_dsh, rows * (size_t)M * 3));
@@ -224,7 +262,7 @@ int h3dgs_backward(const H3dgsView* view, const H3dgsGaussians* g, const int32_t
   BinWs bw = BinWs::make(const_cast<void*>(binning), R, W, H);
   ImageWs iw = ImageWs::make(const_cast<void*>(image), W, H);
   BwdWs ww = BwdWs::make(workspace, P);
-  H3_CUDA(cudaMemsetAsync(ww.grad, 0, sizeof(GradRec) * (size_t)P, s));
+  { ProfScope ps(K_MEMSET, s); H3_CUDA(cudaMemsetAsync(ww.grad, 0, sizeof(GradRec) * (size_t)P, s)); }
 
   BlendArgs b;
   std::memset(&b, 0, sizeof(b));
@@ -325,5 +363,31 @@ int h3dgs_sparse_adam(const H3dgsAdamTensor* tensors, int32_t num_tensors, const
                           num_rows, (cudaStream_t)stream));
   return 0;
 }
+
+int64_t h3dgs_launch_count(void) { return g_prof.launches_total; }
+int h3dgs_profile_enable(int enable) {
+  const int prev = g_prof.on ? 1 : 0;
+  g_prof.on = enable != 0;
+  return prev;
+}
+int h3dgs_profile_read(double* ms, int64_t* launches, int reset) {
+  for (auto& p : g_prof.pending) {
+    H3_CUDA(cudaEventSynchronize(p.b));
+    float t = 0.f;
+    H3_CUDA(cudaEventElapsedTime(&t, p.a, p.b));
+    g_prof.ms[p.id] += t;
+    g_prof.count[p.id] += 1;
+    g_prof.pool.push_back(p.a);
+    g_prof.pool.push_back(p.b);
+  }
+  g_prof.pending.clear();
+  for (int i = 0; i < K_COUNT; ++i) {
+    if (ms) ms[i] = g_prof.ms[i];
+    if (launches) launches[i] = g_prof.count[i];
+    if (reset) { g_prof.ms[i] = 0; g_prof.count[i] = 0; }
+  }
+  return 0;
+}
+const char* h3dgs_profile_name(int id) { return (id >= 0 && id < K_COUNT) ? kKernelNames[id] : ""; }
 
 }  // extern "C"

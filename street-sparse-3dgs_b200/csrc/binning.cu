@@ -84,6 +84,7 @@ __global__ void __launch_bounds__(256) tile_ranges_kernel(long long L,
 cudaError_t launch_emit_instances(int P, const int* radii, const GeomWs& g, int grid_x,
                                   unsigned long long* keys, uint32_t* vals, cudaStream_t s) {
   if (P <= 0) return cudaSuccess;
+  ProfScope ps(K_EMIT, s);
   emit_instances_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, radii, g.depth, g.tile_rect, g.offsets,
                                                         grid_x, keys, vals);
   return cudaGetLastError();
@@ -94,6 +95,7 @@ cudaError_t launch_tile_ranges(int64_t R, const unsigned long long* keys, uint2*
   cudaError_t e = cudaMemsetAsync(ranges, 0, sizeof(uint2) * (size_t)tiles, s);
   if (e != cudaSuccess || R <= 0) return e;
   const long long blocks = (R + 255) / 256;
+  ProfScope ps(K_TILE_RANGES, s);
   tile_ranges_kernel<<<(unsigned)blocks, 256, 0, s>>>(R, keys, ranges);
   return cudaGetLastError();
 }

@@ -1,11 +1,13 @@
 // Backward tile alpha blend.  Replaces renderCUDA of HR/cuda_rasterizer/backward.cu:498-721.
 //
-// Same tiling, staging and per-warp culling as the forward kernel, walking each pixel's list front to
-// back so that T and alpha are recomputed by the very operations the forward used.  The reference's
-// back-to-front recursion  dL/dalpha_i = T_i (c_i - A_i).g - T_final/(1-alpha_i) bg.g  is evaluated
-// in the equivalent prefix form
-//     dL/dalpha_i = T_i u_i - (U_total + T_final bg.g - sum_{j<=i} w_j u_j) / (1 - alpha_i),
-// with u_j = c_j.g + invdepth_j gD and U_total taken from the per-pixel sums the forward stored.
+// Same tiling, staging and per-warp culling as the forward kernel.  Each pixel walks its list back to
+// front from its last contributor, rebuilding T by division from the stored final transmittance and
+// re-evaluating alpha with the reference's backward arithmetic (expf, and precise powf on interpolated
+// slots -- the forward used __powf; that asymmetry is the reference's and is part of its gradients).
+// The per-channel recursion "colour accumulated behind me" is carried as one scalar,
+//     u_i = c_i.g + invdepth_i gD,   A_i = alpha_{i+1} u_{i+1} + (1 - alpha_{i+1}) A_{i+1},
+//     dL/dalpha_i = (u_i - A_i) T_i - T_final/(1-alpha_i) bg.g ,
+// which is the same linear recursion as backward.cu:657-691 contracted with the pixel gradient.
 //
 // Gradient reduction: per (warp, Gaussian) the ten partial sums are reduced with warp shuffles, added
 // into a per-CTA shared-memory accumulator, and flushed once per (tile, Gaussian) with three vector
@@ -48,17 +50,15 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_bwd_kernel(const BlendArg
 
   // per-pixel constants
   int last = 0;
-  float g0 = 0.f, g1 = 0.f, g2 = 0.f, gD = 0.f, Urest = 0.f;
+  float g0 = 0.f, g1 = 0.f, g2 = 0.f, gD = 0.f, T_final = 0.f, bgdot = 0.f;
   if (inside) {
     last = (int)a.n_contrib[pix];
     g0 = a.dL_dcolor[pix];
     g1 = a.dL_dcolor[plane + pix];
     g2 = a.dL_dcolor[2 * plane + pix];
     if (DEPTH) gD = a.dL_dinvdepth[pix];
-    const float4 acc = a.accum[pix];
-    const float Tf = a.final_T[pix];
-    const float bgdot = a.bg[0] * g0 + a.bg[1] * g1 + a.bg[2] * g2;
-    Urest = acc.x * g0 + acc.y * g1 + acc.z * g2 + (DEPTH ? acc.w * gD : 0.f) + Tf * bgdot;
+    T_final = a.final_T[pix];
+    bgdot = a.bg[0] * g0 + a.bg[1] * g1 + a.bg[2] * g2;
   }
   // how far does this warp / this CTA have to walk?
   int wlast = last;
@@ -101,12 +101,13 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_bwd_kernel(const BlendArg
     }
   };
 
-  float T = 1.0f, Upre = 0.f;
+  float T = T_final, accum_u = 0.f, last_alpha = 0.f, last_u = 0.f;
   const float half_w = 0.5f * (float)a.W, half_h = 0.5f * (float)a.H;
 
-  uint32_t id_cur = (tid < nn) ? __ldg(list + tid) : 0u;
+  // staging slot k of round b holds list position nn - 1 - (b * BATCH + k): back to front
+  uint32_t id_cur = (tid < nn) ? __ldg(list + (nn - 1 - tid)) : 0u;
   issue(0, id_cur);
-  uint32_t id_next = (BLEND_BATCH + tid < nn) ? __ldg(list + BLEND_BATCH + tid) : 0u;
+  uint32_t id_next = (BLEND_BATCH + tid < nn) ? __ldg(list + (nn - 1 - BLEND_BATCH - tid)) : 0u;
 
   for (int b = 0; b < rounds; ++b) {
     const int s = b & 1;
@@ -114,7 +115,7 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_bwd_kernel(const BlendArg
     if (b + 1 < rounds) {
       issue(b + 1, id_next);
       const int j2 = (b + 2) * BLEND_BATCH + tid;
-      id_after = (j2 < nn) ? __ldg(list + j2) : 0u;
+      id_after = (j2 < nn) ? __ldg(list + (nn - 1 - j2)) : 0u;
       if (!TMA) cp_async_wait<1>();
     } else {
       if (!TMA) cp_async_wait<0>();
@@ -124,12 +125,13 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_bwd_kernel(const BlendArg
 
     const int base = b * BLEND_BATCH;
     const int cnt = min(BLEND_BATCH, nn - base);
-    const int wcnt = min(cnt, wlast - base);  // entries this warp still cares about
+    // slots whose list position is >= this warp's last contributor come first; skip them
+    const int first = max(0, nn - wlast - base);
     const Rec* __restrict__ recs = sm.rec[s];
-    for (int c = 0; c < wcnt; c += 32) {
+    for (int c = first & ~31; c < cnt; c += 32) {
       const int j = c + lane;
       bool hit = false;
-      if (j < wcnt) hit = block_hit(recs[j].q0, fx0, fy0);
+      if (j >= first && j < cnt) hit = block_hit(recs[j].q0, fx0, fy0);
       unsigned m = __ballot_sync(0xffffffffu, hit);
       while (m) {
         const int jj = c + __ffs(m) - 1;
@@ -137,7 +139,7 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_bwd_kernel(const BlendArg
         float v0 = 0.f, v1 = 0.f, v2 = 0.f, v3 = 0.f, v4 = 0.f, v5 = 0.f, v6 = 0.f, v7 = 0.f,
               v8 = 0.f, v9 = 0.f;
         bool contrib = false;
-        if (base + jj < last) {
+        if (nn - 1 - (base + jj) < last) {
           const float4 q0 = recs[jj].q0;
           const float4 con_o = recs[jj].q1;
           const float dx = q0.x - pixx, dy = q0.y - pixy;
@@ -152,22 +154,24 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_bwd_kernel(const BlendArg
               const float4 q3 = recs[jj].q3;
               if (q3.x != 1.0f) {
                 const float om = 1.0f - my_alpha;
-                const float root = __powf(om, q3.y);  // (1-a)^(1/k), as the forward evaluated it
-                alpha = q3.x * my_alpha + (1.0f - q3.x) * (1.0f - root);
-                // d alpha / d a = t + (1-t) (1/k) (1-a)^(1/k - 1)      (backward.cu:714)
-                opac_mult = q3.x - __fdividef(root, om) * (q3.x - 1.0f) * q3.y;
+                const float kidsqrt_alpha = 1.0f - powf(om, q3.y);   // backward.cu:631
+                alpha = q3.x * my_alpha + (1.0f - q3.x) * kidsqrt_alpha;
+                // d alpha / d a = t - (1-a)^(1/k - 1) (t-1) / k            (backward.cu:714)
+                opac_mult = q3.x - __powf(om, q3.y - 1.0f) * (q3.x - 1.0f) * q3.y;
               }
             }
             if (!(alpha < 1.0f / 255.0f)) {
               contrib = true;
               const float4 q2 = recs[jj].q2;
-              const float one_m = 1 - alpha;
+              T = T / (1.f - alpha);
               const float w = alpha * T;
               float u = q2.x * g0 + q2.y * g1 + q2.z * g2;
               if (DEPTH) u += q2.w * gD;
-              Upre += w * u;
-              float dL_dalpha = T * u - __fdividef(Urest - Upre, one_m);
-              T = T * one_m;
+              accum_u = last_alpha * last_u + (1.f - last_alpha) * accum_u;
+              last_u = u;
+              float dL_dalpha = (u - accum_u) * T;
+              last_alpha = alpha;
+              dL_dalpha += (-T_final / (1.f - alpha)) * bgdot;
               if (test_alpha > 0.99f) dL_dalpha = 0.f;  // clamped alpha passes no gradient (backward.cu:619,693)
               const float dL_dG = con_o.w * dL_dalpha;
               const float gdx = G * dx, gdy = G * dy;
@@ -246,6 +250,7 @@ cudaError_t launch2(const BlendArgs& a, bool tma, cudaStream_t s) {
   const int tiles = a.grid_x * a.grid_y;
   const size_t smem = sizeof(BwdSmem);
   cudaError_t e;
+  ProfScope ps(K_BLEND_BWD, s);
   if (tma) {
     auto k = blend_bwd_kernel<INTERP, DEPTH, true>;
     e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

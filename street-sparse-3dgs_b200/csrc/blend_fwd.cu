@@ -161,6 +161,7 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_fwd_kernel(const BlendArg
 template <bool INTERP, bool DEPTH>
 cudaError_t launch2(const BlendArgs& a, bool tma, cudaStream_t s) {
   const int tiles = a.grid_x * a.grid_y;
+  ProfScope ps(K_BLEND_FWD, s);
   if (tma)
     blend_fwd_kernel<INTERP, DEPTH, true><<<tiles, BLEND_THREADS, 0, s>>>(a);
   else

@@ -192,6 +192,21 @@ int cuda_fail(cudaError_t e, const char* what);
     if (e__ != cudaSuccess) return ::h3dgs::cuda_fail(e__, #expr); \
   } while (0)
 
+// ---- instrumentation (api.cu) ----
+enum KernelId {
+  K_PREPROCESS_FWD = 0, K_SCAN, K_EMIT, K_SORT_HIST, K_SORT_SCAN, K_SORT_PASS, K_TILE_RANGES, K_BLEND_FWD,
+  K_BLEND_BWD, K_PREPROCESS_BWD, K_CUT_MARK, K_CUT_PUT, K_CUT_WEIGHTS, K_ADAM, K_MARK_VISIBLE, K_MEMSET,
+  K_COUNT
+};
+static_assert(K_COUNT == H3DGS_PROF_KERNELS, "kernel id table out of sync with the header");
+void prof_begin(int id, cudaStream_t s);
+void prof_end(int id, cudaStream_t s);
+struct ProfScope {
+  int id; cudaStream_t s;
+  ProfScope(int id_, cudaStream_t s_) : id(id_), s(s_) { prof_begin(id, s); }
+  ~ProfScope() { prof_end(id, s); }
+};
+
 // ---- kernel launchers (one per .cu) ----
 struct PreArgs {
   int P, rows, D, M, skyboxnum;

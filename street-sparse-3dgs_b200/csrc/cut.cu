@@ -137,11 +137,13 @@ cudaError_t run_expand_to_size(int N, float target_size, const int* nodes, const
   if (N <= 0) return cudaSuccess;
   ExpandWs w = ExpandWs::make(workspace, N);
   const int blocks = (N + 255) / 256;
-  mark_nodes_for_size_kernel<<<blocks, 256, 0, s>>>(N, nodes, boxes, viewpoint, target_size, w.counts);
+  { ProfScope ps(K_CUT_MARK, s);
+  mark_nodes_for_size_kernel<<<blocks, 256, 0, s>>>(N, nodes, boxes, viewpoint, target_size, w.counts); }
   cudaError_t e = launch_scan_inclusive(w.counts, w.offsets, N, w.status, w.counters, s);
   if (e != cudaSuccess) return e;
+  { ProfScope ps(K_CUT_PUT, s);
   put_render_indices_kernel<<<blocks, 256, 0, s>>>(N, nodes, w.counts, w.offsets, render_indices,
-                                                   parent_indices, nodes_for_render_indices);
+                                                   parent_indices, nodes_for_render_indices); }
   unsigned long long total = 0;
   e = cudaMemcpyAsync(&total, w.counters + 2, sizeof(total), cudaMemcpyDeviceToHost, s);
   if (e != cudaSuccess) return e;
@@ -155,6 +157,7 @@ cudaError_t run_interpolation_weights(int K, const int* indices, float target_si
                                       const float* boxes, float vx, float vy, float vz, float* ts,
                                       int* kids, cudaStream_t s) {
   if (K <= 0) return cudaSuccess;
+  ProfScope ps(K_CUT_WEIGHTS, s);
   interpolation_weights_kernel<<<(K + 255) / 256, 256, 0, s>>>(K, indices, nodes, boxes, vx, vy, vz,
                                                                target_size, ts, kids);
   return cudaGetLastError();

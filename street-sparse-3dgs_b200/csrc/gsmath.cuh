@@ -79,11 +79,20 @@ __device__ __forceinline__ float3 xform_vec4x3_t(const float3& p, const float* _
 __device__ __forceinline__ float ndc_to_pix(float v, int S) { return ((v + 1.0) * S - 1.0) * 0.5; }
 
 // Rotation matrix of an (un-normalised) quaternion (w,x,y,z), listed column by column
-// (forward.cu:190-201).
+// (forward.cu:190-201).  Which of two products nvcc folds into an FMA depends on use counts inside
+// the optimiser, not on the source, so the contraction pattern is pinned here with intrinsics to the
+// one the reference build has in its sm_100a SASS: r*x, x*z, r*z, y*y, z*z are rounded products; the
+// products involving y (y*z, r*y, x*y) and x*x are fused.
 __device__ __forceinline__ M3 quat_to_m3(float r, float x, float y, float z) {
-  return m3(1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y),
-            2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x),
-            2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y));
+  const float rx = __fmul_rn(r, x), xz = __fmul_rn(x, z), rz = __fmul_rn(r, z);
+  const float yy = __fmul_rn(y, y), zz = __fmul_rn(z, z);
+  const float yz_m_rx = __fmaf_rn(y, z, -rx), yz_p_rx = __fmaf_rn(y, z, rx);
+  const float xz_p_ry = __fmaf_rn(r, y, xz), xz_m_ry = __fmaf_rn(-r, y, xz);
+  const float xy_m_rz = __fmaf_rn(x, y, -rz), xy_p_rz = __fmaf_rn(x, y, rz);
+  const float yy_zz = __fadd_rn(yy, zz), xx_zz = __fmaf_rn(x, x, zz), xx_yy = __fmaf_rn(x, x, yy);
+  return m3(__fsub_rn(1.f, __fmul_rn(2.f, yy_zz)), __fmul_rn(2.f, xy_m_rz), __fmul_rn(2.f, xz_p_ry),
+            __fmul_rn(2.f, xy_p_rz), __fsub_rn(1.f, __fmul_rn(2.f, xx_zz)), __fmul_rn(2.f, yz_m_rx),
+            __fmul_rn(2.f, xz_m_ry), __fmul_rn(2.f, yz_p_rx), __fsub_rn(1.f, __fmul_rn(2.f, xx_yy)));
 }
 
 // World-space covariance from scale and rotation: Sigma = (S R)^T (S R); upper triangle out.

@@ -384,6 +384,7 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdArgs b)
 cudaError_t launch_preprocess_bwd(const PreBwdArgs& b, cudaStream_t s) {
   if (b.f.P <= 0) return cudaSuccess;
   const int blocks = (b.f.P + 255) / 256;
+  ProfScope ps(K_PREPROCESS_BWD, s);
   if (b.f.idx != nullptr)
     preprocess_bwd_kernel<true><<<blocks, 256, 0, s>>>(b);
   else

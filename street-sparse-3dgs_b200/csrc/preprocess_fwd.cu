@@ -268,6 +268,7 @@ __global__ void mark_visible_kernel(int P, const float* __restrict__ means,
 cudaError_t launch_preprocess_fwd(const PreArgs& a, cudaStream_t s) {
   if (a.P <= 0) return cudaSuccess;
   const int blocks = (a.P + 255) / 256;
+  ProfScope ps(K_PREPROCESS_FWD, s);
   if (a.idx != nullptr)
     preprocess_fwd_kernel<true><<<blocks, 256, 0, s>>>(a);
   else
@@ -278,6 +279,7 @@ cudaError_t launch_preprocess_fwd(const PreArgs& a, cudaStream_t s) {
 cudaError_t launch_mark_visible(int P, const float* means, const float* view, const float* proj,
                                 uint8_t* present, cudaStream_t s) {
   if (P <= 0) return cudaSuccess;
+  ProfScope ps(K_MARK_VISIBLE, s);
   mark_visible_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, means, view, proj, present);
   return cudaGetLastError();
 }

@@ -198,7 +198,8 @@ cudaError_t launch_radix_sort(BinWs& b, int64_t R, const SortPlan& plan, cudaStr
     if (e != cudaSuccess) return e;
     attr_done = true;
   }
-  cudaError_t e = cudaMemsetAsync(b.zero_base, 0, b.zero_bytes, s);
+  cudaError_t e;
+  { ProfScope ps(K_MEMSET, s); e = cudaMemsetAsync(b.zero_base, 0, b.zero_bytes, s); }
   if (e != cudaSuccess) return e;
 
   PlanDev pd;
@@ -211,10 +212,13 @@ cudaError_t launch_radix_sort(BinWs& b, int64_t R, const SortPlan& plan, cudaStr
   int hist_blocks = (int)((R + 512 * 16 - 1) / (512 * 16));
   if (hist_blocks > 148 * 4) hist_blocks = 148 * 4;
   if (hist_blocks < 1) hist_blocks = 1;
-  radix_hist_kernel<<<hist_blocks, 512, 0, s>>>(b.keys[0], R, pd, b.hist);
-  radix_scan_hist_kernel<<<plan.num_passes, RADIX, 0, s>>>(b.hist);
+  { ProfScope ps(K_SORT_HIST, s);
+  radix_hist_kernel<<<hist_blocks, 512, 0, s>>>(b.keys[0], R, pd, b.hist); }
+  { ProfScope ps(K_SORT_SCAN, s);
+  radix_scan_hist_kernel<<<plan.num_passes, RADIX, 0, s>>>(b.hist); }
   for (int p = 0; p < plan.num_passes; ++p) {
     const int src = p & 1, dst = src ^ 1;
+    ProfScope ps(K_SORT_PASS, s);
     onesweep_kernel<<<(unsigned)tiles, SORT_THREADS, smem, s>>>(
         b.keys[src], b.keys[dst], b.vals[src], b.vals[dst], R, pd.shift[p], pd.mask[p],
         b.hist + (size_t)p * RADIX, b.status + (size_t)p * tiles * RADIX, b.counters + p);

@@ -123,6 +123,7 @@ cudaError_t launch_scan_inclusive(const uint32_t* in, uint32_t* out, int n, unsi
   if (e != cudaSuccess) return e;
   e = cudaMemsetAsync(counters, 0, 8 * sizeof(uint32_t), s);
   if (e != cudaSuccess) return e;
+  ProfScope ps(K_SCAN, s);
   scan_lookback_kernel<<<tiles, SCAN_THREADS, 0, s>>>(in, out, n, status, counters);
   return cudaGetLastError();
 }

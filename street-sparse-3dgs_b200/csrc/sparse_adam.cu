@@ -69,6 +69,7 @@ cudaError_t run_sparse_adam(const H3dgsAdamTensor* tensors, int n, const long lo
   const long long work = K * acc;
   if (work <= 0) return cudaSuccess;
   const long long blocks = (work + 255) / 256;
+  ProfScope ps(K_ADAM, s);
   sparse_adam_kernel<<<(unsigned)blocks, 256, 0, s>>>(pk, relevant, K);
   return cudaGetLastError();
 }

@@ -87,7 +87,21 @@ SIGNATURES = {
     "h3dgs_hier_write": (c_int, [c_char_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_void_p,
                                   c_void_p, c_void_p, c_void_p, c_int]),
     "h3dgs_sparse_adam": (c_int, [POINTER(AdamTensor), c_int32, c_void_p, c_int64, c_int64, c_void_p]),
+    "h3dgs_launch_count": (c_int64, []),
+    "h3dgs_profile_enable": (c_int, [c_int]),
+    "h3dgs_profile_read": (c_int, [POINTER(ctypes.c_double), POINTER(c_int64), c_int]),
+    "h3dgs_profile_name": (c_char_p, [c_int]),
 }
+PROF_KERNELS = 16
+
+
+def profile_read(reset=True):
+    """{kernel name: (total ms, launches)} accumulated while profiling was enabled."""
+    L = lib()
+    ms = (ctypes.c_double * PROF_KERNELS)()
+    n = (c_int64 * PROF_KERNELS)()
+    check(L.h3dgs_profile_read(ms, n, 1 if reset else 0), "h3dgs_profile_read")
+    return {L.h3dgs_profile_name(i).decode(): (ms[i], int(n[i])) for i in range(PROF_KERNELS)}
 
 _lib = None
 
