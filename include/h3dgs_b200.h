@@ -237,6 +237,7 @@ typedef struct H3dgsAdamTensor {
   float step_size;
   float bias_correction2_sqrt;
   float beta1, beta2, eps;
+  float one_minus_beta1, one_minus_beta2; /* (1 - beta) rounded from the host's double, as torch passes it */
 } H3dgsAdamTensor;
 
 #define H3DGS_ADAM_MAX_TENSORS 8

@@ -38,8 +38,8 @@ __global__ void __launch_bounds__(256) sparse_adam_kernel(const AdamPack pk,
   float v = T.exp_avg_sq[off];
   float p = T.param[off];
 
-  const float omb1 = (float)(1.0 - (double)T.beta1);
-  const float omb2 = (float)(1.0 - (double)T.beta2);
+  const float omb1 = T.one_minus_beta1;
+  const float omb2 = T.one_minus_beta2;
   m = __fmaf_rn(omb1, g, __fmul_rn(m, T.beta1));
   v = __fmaf_rn(__fmul_rn(omb2, g), g, __fmul_rn(v, T.beta2));
   const float inv_bc2 = 1.0f / T.bias_correction2_sqrt;

@@ -52,7 +52,8 @@ class DebugView(Structure):
 class AdamTensor(Structure):
     _fields_ = [("param", c_void_p), ("grad", c_void_p), ("exp_avg", c_void_p), ("exp_avg_sq", c_void_p),
                 ("width", c_int32), ("step_size", c_float), ("bias_correction2_sqrt", c_float),
-                ("beta1", c_float), ("beta2", c_float), ("eps", c_float)]
+                ("beta1", c_float), ("beta2", c_float), ("eps", c_float),
+                ("one_minus_beta1", c_float), ("one_minus_beta2", c_float)]
 
 
 ADAM_MAX_TENSORS = 8

@@ -94,7 +94,8 @@ class Adam(Optimizer):
                 width = p.numel() // max(rows, 1)
                 batch.append((nat.AdamTensor(p.data_ptr(), grad.data_ptr(), state['exp_avg'].data_ptr(),
                                              state['exp_avg_sq'].data_ptr(), width, step_size,
-                                             bias_correction2_sqrt, beta1, beta2, group['eps']), rows))
+                                             bias_correction2_sqrt, beta1, beta2, group['eps'],
+                                             1 - beta1, 1 - beta2), rows))
         if not batch:
             return loss
 
