@@ -35,7 +35,7 @@ OUT = os.environ.get("H3DGS_GOLDEN_OUT", HERE)
 
 
 def _np(t):
-    return t.detach().cpu().contiguous().numpy()
+    return t.detach().cpu().contiguous().numpy().copy()   # copy: CPU tensors share memory with numpy
 
 
 def _save(name, d):
