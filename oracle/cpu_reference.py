@@ -228,3 +228,42 @@ def sparse_adam(param, grad, exp_avg, exp_avg_sq, relevant, lr, step, betas=(0.9
     lib().orc_sparse_adam(_p(param), _p(_f32(grad)), _p(exp_avg), _p(exp_avg_sq), C.c_int64(rows), C.c_int(width),
                           _p(rel), C.c_int64(0 if rel is None else rel.shape[0]), C.c_double(lr),
                           C.c_double(betas[0]), C.c_double(betas[1]), C.c_double(eps), C.c_double(step))
+
+
+# ---------------------------------------------------------------------------------------------------
+# one-call checker used by __graft_entry__.smoke() and the GPU tests
+# ---------------------------------------------------------------------------------------------------
+def render_post_reference(cam, attrs, skybox, limit, dL_dcolor=None, dL_dinvdepth=None, bg=None, do_depth=True):
+    """Whole hot path on the host for torch inputs (any device): cut at `limit` for camera `cam`, gather +
+    lerp, rasterize forward (+ backward when dL_dcolor is given).  Returns numpy arrays:
+    dict(count, render_indices, parent_indices, ts, kids, render (clamped), depth, radii, grads{...})."""
+    import math
+
+    def n(t):
+        return t.detach().cpu().numpy() if hasattr(t, "detach") else np.asarray(t)
+
+    a = {k: n(v) for k, v in attrs.items()}
+    vp = n(cam.camera_center)
+    W, H = int(cam.image_width), int(cam.image_height)
+    K, ri, pi, ni = expand_to_size(a["nodes"], a["boxes"], float(limit), vp)
+    ts, kids = get_interpolation_weights(ni, float(limit), a["nodes"], a["boxes"], vp)
+    at, w, sign = render_post_gather(a["means3D"], a["shs"], a["opacities"], a["scales"], a["rotations"], ri, pi, ts,
+                                     skybox)
+    kids_full = np.concatenate([kids, np.ones(skybox, np.int32)])
+    bgv = np.zeros(3, np.float32) if bg is None else n(bg)
+    o = rasterize_forward(at["means3D"], at["opacities"], at["scales"], at["rotations"],
+                          n(cam.world_view_transform).ravel(), n(cam.full_proj_transform).ravel(), vp, bgv, W, H,
+                          math.tan(cam.FoVx * 0.5), math.tan(cam.FoVy * 0.5), shs=at["shs"], ts=w, kids=kids_full,
+                          do_depth=do_depth)
+    out = dict(count=K, render_indices=ri, parent_indices=pi, ts=ts, kids=kids_full,
+               render=np.clip(o["color"], 0, 1), depth=o["invdepth"], radii=o["radii"],
+               num_rendered=o["num_rendered"])
+    if dL_dcolor is not None:
+        dcol = n(dL_dcolor) * ((o["color"] >= 0) & (o["color"] <= 1))     # clamp(0,1) backward
+        gr = rasterize_backward(o, dcol, None if dL_dinvdepth is None else n(dL_dinvdepth))
+        store = render_post_scatter(dict(means3D=gr["dL_dmeans3D"], shs=gr["dL_dsh"], opacities=gr["dL_dopacity"],
+                                         scales=gr["dL_dscales"], rotations=gr["dL_drotations"]),
+                                    a["means3D"].shape[0], ri, pi, ts, sign, skybox)
+        store["means2D"] = gr["dL_dmeans2D"]
+        out["grads"] = store
+    return out

@@ -66,6 +66,36 @@ int blend_stage_mode() {
   return mode;
 }
 
+// Zero fill with plain 16-byte stores (H3DGS_ZERO=kernel) instead of cudaMemsetAsync (default).
+__global__ void fill_zero_kernel(float* __restrict__ p, size_t n) {
+  const size_t head = (16 - (reinterpret_cast<size_t>(p) & 15)) / 4 % 4;   // floats up to 16-byte alignment
+  const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  if (tid < head && tid < n) p[tid] = 0.f;
+  if (n <= head) return;
+  float4* q = reinterpret_cast<float4*>(p + head);
+  const size_t n4 = (n - head) / 4;
+  for (size_t i = tid; i < n4; i += stride) q[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  const size_t tail = head + n4 * 4;
+  if (tid < n - tail) p[tail + tid] = 0.f;
+}
+int zero_mode() {
+  static int mode = -1;
+  if (mode < 0) {
+    const char* e = std::getenv("H3DGS_ZERO");
+    mode = (e && std::strcmp(e, "kernel") == 0) ? 1 : 0;
+  }
+  return mode;
+}
+cudaError_t zero_fill(float* p, size_t n, cudaStream_t s) {
+  if (!p || n == 0) return cudaSuccess;
+  if (zero_mode() == 0) return cudaMemsetAsync(p, 0, n * sizeof(float), s);
+  const size_t want = (n / 4 + 255) / 256;
+  const int blocks = (int)(want < 148 * 16 ? (want ? want : 1) : 148 * 16);
+  fill_zero_kernel<<<blocks, 256, 0, s>>>(p, n);
+  return cudaGetLastError();
+}
+
 size_t expand_ws_bytes(int N);
 cudaError_t run_expand_to_size(int N, float target_size, const int* nodes, const float* boxes,
                                const float* viewpoint, int* render_indices, int* parent_indices,
@@ -237,7 +267,7 @@ int h3dgs_backward(const H3dgsView* view, const H3dgsGaussians* g, const int32_t
   const bool fused = g->render_indices != nullptr;
 
   auto zero = [&](float* p, size_t n) -> cudaError_t {
-    return p ? cudaMemsetAsync(p, 0, n * sizeof(float), s) : cudaSuccess;
+    return zero_fill(p, n, s);
   };
   if (P == 0 || R <= 0 || fused) {
     ProfScope ps(K_MEMSET, s);

@@ -72,7 +72,7 @@ def _fused_vs_glue(levels, sky, w, h, target, seed, depth=True):
     attrs = workload.build_scene(levels, sky, seed, DEV)
     cam = scenes.street_camera(w, h, seed=seed, device=DEV, yaw_deg=4.0, x=-10.0)
     bg = torch.tensor([0.05, 0.1, 0.15], device=DEV)
-    m_o, m_r, m_r2 = (workload.ActivatedModel(attrs, sky) for _ in range(3))
+    m_o, m_r, m_r2, m_r3, m_r4 = (workload.ActivatedModel(attrs, sky) for _ in range(5))
     limit = workload.find_limit(gaussian_hierarchy._C, m_o, cam, target, DEV)
     n = attrs["means3D"].size(0)
     g = torch.Generator().manual_seed(11)
@@ -92,6 +92,8 @@ def _fused_vs_glue(levels, sky, w, h, target, seed, depth=True):
     out_o, cut_o = run(m_o, workload.ours_render_post, gaussian_hierarchy._C)
     out_r, cut_r = run(m_r, workload.ref_render_post, refglue.ref_gh())
     out_r2, _ = run(m_r2, workload.ref_render_post, refglue.ref_gh())
+    out_r3, _ = run(m_r3, workload.ref_render_post, refglue.ref_gh())
+    out_r4, _ = run(m_r4, workload.ref_render_post, refglue.ref_gh())
     torch.cuda.synchronize()
     assert cut_o.count == cut_r.count and cut_o.count > 0
     # the appended skybox slots get kids = 1 in the caller's tensor, as the reference glue does
@@ -102,12 +104,14 @@ def _fused_vs_glue(levels, sky, w, h, target, seed, depth=True):
     assert torch.equal(out_o["visibility_filter"], out_r["visibility_filter"])
     assert torch.equal(out_o["radii"], out_r["radii"])
     names = ["xyz", "features", "opacity", "scaling", "rotation"]
-    for name, po, pr, pr2 in zip(names, m_o.parameters(), m_r.parameters(), m_r2.parameters()):
-        util.assert_grad_close(po.grad, pr.grad, pr2.grad, name)
+    for name, po, pr, pr2, pr3, pr4 in zip(names, m_o.parameters(), m_r.parameters(), m_r2.parameters(),
+                                           m_r3.parameters(), m_r4.parameters()):
+        util.assert_grad_close(po.grad, pr.grad, pr2.grad, name, more_refs=(pr3.grad, pr4.grad))
     go = out_o["viewspace_points"].grad
     gr = out_r["viewspace_points"].grad
     gr2 = out_r2["viewspace_points"].grad
-    util.assert_grad_close(go, gr, gr2, "viewspace_points")
+    util.assert_grad_close(go, gr, gr2, "viewspace_points",
+                           more_refs=(out_r3["viewspace_points"].grad, out_r4["viewspace_points"].grad))
 
 
 @pytest.mark.parametrize("levels,sky,w,h,target,depth", [
