@@ -86,7 +86,9 @@ def test_rasterizer_against_reference_golden(name):
     checked = 0
     for k, ours in zip(GRADS, grads):
         ref, ref2 = g[k], g[k + "_run2"]
-        if ref.size == 0 or not np.any(ref):
+        if ref.size == 0 or not np.any(ref) or ours.numel() == 0:
+            # gradients of inputs that were not given come back empty here (the reference materialises the
+            # intermediate dL_dcolors / dL_dcov3D even then; Python never reads them, __init__.py:132-142)
             continue
         den = np.abs(ref).max()
         noise = np.abs(ref2 - ref).max() / den
