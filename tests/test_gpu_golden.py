@@ -192,8 +192,17 @@ def test_rasterizer_against_cpu_oracle(n, w, h, interp, seed):
                              c(cam.camera_center), c(bg), w, h, rs.tanfovx, rs.tanfovy, shs=c(sc["shs"]),
                              ts=None if ts is None else c(ts), kids=None if kids is None else c(kids))
     assert np.array_equal(c(radii), o["radii"])
-    assert np.abs(c(color) - o["color"]).max() <= 2e-6
-    assert np.abs(c(depth) - o["invdepth"]).max() <= 2e-6 * max(1.0, np.abs(o["invdepth"]).max())
+    # Without interpolation weights the CUDA path and the oracle differ only by device vs host expf.
+    # With them the forward uses the hardware __powf (MUFU lg2/ex2, forward.cu:543), which the host
+    # cannot reproduce: a pixel whose alpha lands within an ulp of the 1/255 or T < 1e-4 threshold may
+    # keep or drop one contribution (<= alpha*T*c ~ 4e-3).  Such pixels must stay rare and small.
+    dcolor = np.abs(c(color) - o["color"]).max(axis=0)
+    ddepth = np.abs(c(depth) - o["invdepth"])[0] / max(1.0, np.abs(o["invdepth"]).max())
+    if not interp:
+        assert dcolor.max() <= 2e-6 and ddepth.max() <= 2e-6
+    else:
+        assert (dcolor > 2e-6).mean() <= 1e-3 and dcolor.max() <= 5e-3, (float((dcolor > 2e-6).mean()), float(dcolor.max()))
+        assert (ddepth > 2e-6).mean() <= 1e-3 and ddepth.max() <= 5e-3
     gr = cr.rasterize_backward(o, c(dcol), c(ddep))
     for key, ours in (("dL_dmeans3D", p["means3D"].grad), ("dL_dsh", p["shs"].grad),
                       ("dL_dopacity", p["opacities"].grad), ("dL_dscales", p["scales"].grad),
