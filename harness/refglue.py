@@ -133,7 +133,10 @@ def ref_render_post(Settings, cam, pc, bg, render_indices, parent_indices, inter
                     do_depth=True, debug=False):
     """gaussian_renderer/__init__.py:138-304 with interp_python=True, restated on the reference rasterizer."""
     screenspace_points = torch.zeros_like(pc.get_xyz, requires_grad=True) + 0
-    screenspace_points.retain_grad()
+    try:
+        screenspace_points.retain_grad()
+    except Exception:
+        pass
     means3D, means2D, opacity = pc.get_xyz, screenspace_points, pc.get_opacity
     scales, rotations, shs = pc.get_scaling, pc.get_rotation, pc.get_features
     render_inds = render_indices.long()

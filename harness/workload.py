@@ -31,11 +31,15 @@ class HierModel:
         self.active_sh_degree = 3
         self.max_sh_degree = 3
         self.pretrained_exposures = None
+        # scene/gaussian_model.py:40-48 (setup_functions) and :411-412 (hierarchy mode: abs opacity)
+        self.scaling_activation = torch.exp
+        self.rotation_activation = torch.nn.functional.normalize
+        self.opacity_activation = torch.abs
 
     get_xyz = property(lambda self: self._xyz)
-    get_scaling = property(lambda self: torch.exp(self._scaling))
-    get_rotation = property(lambda self: torch.nn.functional.normalize(self._rotation))
-    get_opacity = property(lambda self: torch.abs(self._opacity))
+    get_scaling = property(lambda self: self.scaling_activation(self._scaling))
+    get_rotation = property(lambda self: self.rotation_activation(self._rotation))
+    get_opacity = property(lambda self: self.opacity_activation(self._opacity))
     get_features = property(lambda self: torch.cat((self._features_dc, self._features_rest), dim=1))
 
     def param_groups(self, lr=1e-4):

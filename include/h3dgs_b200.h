@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define H3DGS_ABI_VERSION 1
+#define H3DGS_ABI_VERSION 2
 
 #if defined(__GNUC__)
 #define H3DGS_API __attribute__((visibility("default")))
@@ -98,7 +98,23 @@ typedef struct H3dgsGaussians {
   const int32_t* parent_indices; /* [K] or NULL */
   const float* ts;               /* [>=P] or NULL */
   const int32_t* kids;           /* [>=P] or NULL */
+  /* Raw parameter store (ABI 2).  The reference activates the WHOLE store on every render
+   * (scene/gaussian_model.py:121-145: exp of _scaling, normalize of _rotation, sigmoid/abs of _opacity,
+   * torch.cat of _features_dc/_features_rest) before render_post gathers the cut rows from it
+   * (gaussian_renderer/__init__.py:202-235).  With these fields the kernels read the raw parameters and
+   * apply the same activations to the rows they gather; the backward then returns gradients of the RAW
+   * parameters.  All zero / NULL = the arrays above are already activated (ABI 1 behaviour). */
+  const float* shs_rest;        /* NULL, or [rows,M-1,3]: then shs is [rows,1,3] (_features_dc/_features_rest) */
+  int32_t scale_activation;     /* H3DGS_ACT_NONE | H3DGS_ACT_EXP */
+  int32_t rotation_activation;  /* H3DGS_ACT_NONE | H3DGS_ACT_NORMALIZE  (x / max(||x||_2, 1e-12)) */
+  int32_t opacity_activation;   /* H3DGS_ACT_NONE | H3DGS_ACT_SIGMOID | H3DGS_ACT_ABS */
 } H3dgsGaussians;
+
+#define H3DGS_ACT_NONE      0
+#define H3DGS_ACT_EXP       1
+#define H3DGS_ACT_NORMALIZE 2
+#define H3DGS_ACT_SIGMOID   3
+#define H3DGS_ACT_ABS       4
 
 /* Workspace sizes.  geom: per-slot state (GeometryState, rasterizer_impl.cu:159-175);
  * image: per-pixel + per-tile state (ImageState, :177-184);
@@ -141,6 +157,7 @@ typedef struct H3dgsGrads {
   float* dL_dscales;    /* [rows,3] */
   float* dL_drotations; /* [rows,4] */
   float* dL_dcov3D;     /* [rows,6]   (gradient of cov3D_precomp) */
+  float* dL_dsh_rest;   /* [rows,M-1,3] when g->shs_rest is given (then dL_dsh is [rows,1,3]); else NULL */
 } H3dgsGrads;
 
 H3DGS_API size_t h3dgs_backward_workspace_bytes(int32_t P);

@@ -66,6 +66,18 @@ int blend_stage_mode() {
   return mode;
 }
 
+// H3DGS_NORM_VARIANT=0..3 selects the summation order of ||q||^2 in the fused F.normalize (parity diagnostic;
+// 2, the default, is the order torch's CUDA reduction uses, see gsmath.cuh).
+int norm_variant() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = std::getenv("H3DGS_NORM_VARIANT");
+    v = e ? std::atoi(e) : 2;
+    if (v < 0 || v > 3) v = 2;
+  }
+  return v;
+}
+
 // Zero fill with plain 16-byte stores (H3DGS_ZERO=kernel) instead of cudaMemsetAsync (default).
 __global__ void fill_zero_kernel(float* __restrict__ p, size_t n) {
   const size_t head = (16 - (reinterpret_cast<size_t>(p) & 15)) / 4 % 4;   // floats up to 16-byte alignment
@@ -125,6 +137,14 @@ int check_scene(const H3dgsView* v, const H3dgsGaussians* g) {
                 "Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!");
   if (g->shs && (g->sh_degree < 0 || g->sh_degree > 3 || (g->sh_degree + 1) * (g->sh_degree + 1) > g->sh_coeffs))
     return fail(H3DGS_EINVAL, "sh_degree must be 0..3 and fit in sh_coeffs");
+  if (g->shs_rest && (!g->shs || g->sh_coeffs < 2)) return fail(H3DGS_EINVAL, "shs_rest needs shs (dc) and sh_coeffs >= 2");
+  if ((g->scale_activation != H3DGS_ACT_NONE && g->scale_activation != H3DGS_ACT_EXP) ||
+      (g->rotation_activation != H3DGS_ACT_NONE && g->rotation_activation != H3DGS_ACT_NORMALIZE) ||
+      (g->opacity_activation != H3DGS_ACT_NONE && g->opacity_activation != H3DGS_ACT_SIGMOID &&
+       g->opacity_activation != H3DGS_ACT_ABS))
+    return fail(H3DGS_EINVAL, "unsupported activation code");
+  if ((g->scale_activation || g->rotation_activation) && g->cov3D_precomp)
+    return fail(H3DGS_EINVAL, "scale / rotation activations need scales + rotations");
   if (g->skyboxnum < 0 || g->skyboxnum > g->P) return fail(H3DGS_EINVAL, "skyboxnum out of range");
   if (g->render_indices == nullptr) {
     if (g->P != g->store_rows) return fail(H3DGS_EINVAL, "plain mode needs P == store_rows");
@@ -149,6 +169,9 @@ PreArgs make_pre(const H3dgsView* v, const H3dgsGaussians* g, int* radii, void* 
   a.focal_x = a.W / (2.0f * a.tan_fovx);
   a.means = g->means3D; a.shs = g->shs; a.colors = g->colors_precomp; a.opac = g->opacities;
   a.scales = g->scales; a.rots = g->rotations; a.cov3D_pre = g->cov3D_precomp;
+  a.shs_rest = g->shs ? g->shs_rest : nullptr;
+  a.act_scale = g->scale_activation; a.act_rot = g->rotation_activation; a.act_opac = g->opacity_activation;
+  a.norm_variant = norm_variant();
   a.idx = g->render_indices; a.pidx = g->render_indices ? g->parent_indices : nullptr;
   a.ts = g->ts; a.kids = g->kids;
   a.view = v->viewmatrix; a.proj = v->projmatrix; a.campos = v->campos;
@@ -273,7 +296,9 @@ int h3dgs_backward(const H3dgsView* view, const H3dgsGaussians* g, const int32_t
     ProfScope ps(K_MEMSET, s);
     // fused-cut mode scatters into store rows; empty renders produce all-zero gradients
     H3_CUDA(zero(grads->dL_dmeans3D, rows * 3));
-    H3_CUDA(zero(grads->dL_dsh, rows * (size_t)M * 3));
+    const bool split = g->shs && g->shs_rest;
+    H3_CUDA(zero(grads->dL_dsh, rows * (size_t)(split ? 1 : M) * 3));
+    if (split) H3_CUDA(zero(grads->dL_dsh_rest, rows * (size_t)(M - 1) * 3));
     H3_CUDA(zero(grads->dL_dcolors, rows * 3));
     H3_CUDA(zero(grads->dL_dopacity, rows));
     H3_CUDA(zero(grads->dL_dscales, rows * 3));

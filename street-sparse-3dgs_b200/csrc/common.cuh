@@ -214,6 +214,9 @@ struct PreArgs {
   float scale_modifier, tan_fovx, tan_fovy, focal_x, focal_y;
   const float* means; const float* shs; const float* colors; const float* opac;
   const float* scales; const float* rots; const float* cov3D_pre;
+  const float* shs_rest;                 // raw store: shs = [rows,1,3], shs_rest = [rows,M-1,3]
+  int act_scale, act_rot, act_opac;      // H3DGS_ACT_*
+  int norm_variant;                      // summation order of ||q||^2, see gsmath.cuh act_rotation
   const int* idx; const int* pidx; const float* ts; const int* kids;
   const float* view; const float* proj; const float* campos;
   int* radii;

@@ -8,6 +8,7 @@
 // floating-point flags as the reference (-fmad=true, IEEE div/sqrt, no fast-math).
 #pragma once
 #include <cuda_runtime.h>
+#include "../../include/h3dgs_b200.h"
 
 namespace h3dgs {
 
@@ -178,5 +179,58 @@ __device__ __forceinline__ void sh_basis(int deg, float x, float y, float z, flo
 }
 
 __device__ __forceinline__ int sh_count(int deg) { return (deg + 1) * (deg + 1); }
+
+// ---- parameter activations of scene/gaussian_model.py:40-48,411-412, applied to gathered rows ----
+// Each one restates the arithmetic of the torch CUDA kernel the reference runs over the whole store, so
+// that the activated values (and with them radii, tile counts and sort keys) come out bit-identical:
+//   torch.exp      -> expf
+//   torch.sigmoid  -> 1 / (1 + expf(-x))
+//   torch.abs      -> fabsf
+//   F.normalize    -> x / max(sqrt(sum x_i^2), 1e-12); the sum is torch's block-x reduction over the four
+//                     components: each lane squares its own element, then shuffle-down by 2 and by 1,
+//                     i.e. (q0^2 + q2^2) + (q1^2 + q3^2)  (variant 2, the default: measured bit-identical to
+//                     F.normalize on B200 with harness/diag_raw.py; variants 0, 1, 3 are not).  Other orders
+//                     stay selectable for that diagnostic (H3DGS_NORM_VARIANT).
+__device__ __forceinline__ float act_scalar(int act, float x) {
+  if (act == H3DGS_ACT_EXP) return expf(x);
+  if (act == H3DGS_ACT_SIGMOID) return __fdiv_rn(1.0f, __fadd_rn(1.0f, expf(-x)));
+  if (act == H3DGS_ACT_ABS) return fabsf(x);
+  return x;
+}
+// d act(x) / dx given the raw x and the activated y
+__device__ __forceinline__ float act_scalar_grad(int act, float x, float y) {
+  if (act == H3DGS_ACT_EXP) return y;
+  if (act == H3DGS_ACT_SIGMOID) return (1.0f - y) * y;
+  if (act == H3DGS_ACT_ABS) return x > 0.f ? 1.f : (x < 0.f ? -1.f : 0.f);
+  return 1.0f;
+}
+__device__ __forceinline__ float quat_norm(int variant, const float4& q) {
+  const float a = __fmul_rn(q.x, q.x), b = __fmul_rn(q.y, q.y), c = __fmul_rn(q.z, q.z), d = __fmul_rn(q.w, q.w);
+  float s;
+  if (variant == 1) s = __fadd_rn(__fadd_rn(__fadd_rn(a, b), c), d);
+  else if (variant == 2) s = __fadd_rn(__fadd_rn(a, c), __fadd_rn(b, d));
+  else if (variant == 3) s = __fmaf_rn(q.w, q.w, __fmaf_rn(q.z, q.z, __fmaf_rn(q.y, q.y, a)));
+  else s = __fadd_rn(__fadd_rn(a, b), __fadd_rn(c, d));
+  return sqrtf(s);
+}
+__device__ __forceinline__ float4 act_rotation(int act, int variant, const float4& q) {
+  if (act != H3DGS_ACT_NORMALIZE) return q;
+  const float d = fmaxf(quat_norm(variant, q), 1e-12f);
+  return make_float4(__fdiv_rn(q.x, d), __fdiv_rn(q.y, d), __fdiv_rn(q.z, d), __fdiv_rn(q.w, d));
+}
+// gradient of y = q / max(||q||, eps) contracted with g (autograd of F.normalize: div, clamp_min, norm)
+__device__ __forceinline__ float4 act_rotation_grad(int act, int variant, const float4& q, const float4& g) {
+  if (act != H3DGS_ACT_NORMALIZE) return g;
+  const float n = quat_norm(variant, q);
+  const float d = fmaxf(n, 1e-12f);
+  const float inv = 1.0f / d;
+  float4 r = make_float4(g.x * inv, g.y * inv, g.z * inv, g.w * inv);
+  if (n > 1e-12f) {
+    const float dot = g.x * q.x + g.y * q.y + g.z * q.z + g.w * q.w;
+    const float k = dot * inv * inv / n;
+    r.x -= q.x * k; r.y -= q.y * k; r.z -= q.z * k; r.w -= q.w * k;
+  }
+  return r;
+}
 
 }  // namespace h3dgs

@@ -51,6 +51,19 @@ __device__ __forceinline__ void put(float* base, size_t row, int width, int k, f
   }
 }
 
+// child / parent values already carry their t, (1-t) and activation-derivative factors
+template <bool FUSED>
+__device__ __forceinline__ void put2(float* base, size_t row, int width, int k, float vc, size_t prow,
+                                     bool lerp, float vp) {
+  if (base == nullptr) return;
+  if (!FUSED) {
+    base[row * width + k] = vc;
+  } else {
+    atomicAdd(base + row * width + k, vc);
+    if (lerp) atomicAdd(base + prow * width + k, vp);
+  }
+}
+
 template <bool FUSED>
 __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdArgs b) {
   const PreArgs& a = b.f;
@@ -74,7 +87,10 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdArgs b)
       if (o.dL_dscales) { o.dL_dscales[r * 3] = 0.f; o.dL_dscales[r * 3 + 1] = 0.f; o.dL_dscales[r * 3 + 2] = 0.f; }
       if (o.dL_drotations) *reinterpret_cast<float4*>(o.dL_drotations + r * 4) = make_float4(0.f, 0.f, 0.f, 0.f);
       if (o.dL_dcov3D) for (int i = 0; i < 6; ++i) o.dL_dcov3D[r * 6 + i] = 0.f;
-      if (o.dL_dsh) {
+      if (o.dL_dsh && o.dL_dsh_rest) {
+        for (int i = 0; i < 3; ++i) o.dL_dsh[r * 3 + i] = 0.f;
+        for (int i = 0; i < (M - 1) * 3; ++i) o.dL_dsh_rest[r * (size_t)(M - 1) * 3 + i] = 0.f;
+      } else if (o.dL_dsh) {
         float* d = o.dL_dsh + r * (size_t)M * 3;
         if (((M * 3) & 3) == 0 && ((reinterpret_cast<size_t>(o.dL_dsh) & 15) == 0)) {
           for (int i = 0; i < M * 3 / 4; ++i) reinterpret_cast<float4*>(d)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -152,8 +168,16 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdArgs b)
   const float det_cov_plus_h_cov = c_xx * c_yy - c_xy * c_xy;
   const float h_convolution_scaling = sqrt(max(0.000025f, det_cov / det_cov_plus_h_cov));
 
-  float opacity = __ldg(a.opac + r);
-  if (FUSED && lerp) opacity = lerp_rn(t, opacity, omt, __ldg(a.opac + pr));
+  const float tc = lerp ? t : 1.0f;   // weight of the child row
+  const float o_raw = __ldg(a.opac + r);
+  const float o_act = act_scalar(a.act_opac, o_raw);
+  float op_raw = 0.f, op_act = 0.f;
+  float opacity = o_act;
+  if (FUSED && lerp) {
+    op_raw = __ldg(a.opac + pr);
+    op_act = act_scalar(a.act_opac, op_raw);
+    opacity = lerp_rn(t, o_act, omt, op_act);
+  }
   const float d_h_convolution_scaling = dL_dopacity_v * opacity;
   const float dL_dopacity_out = dL_dopacity_v * h_convolution_scaling;
   const float d_inside_root = (det_cov / det_cov_plus_h_cov) <= 0.000025f
@@ -249,20 +273,38 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdArgs b)
     float bs[16];
     sh_basis(a.D, x, y, z, bs);
     const int n = sh_count(a.D);
-    const float* __restrict__ sh = a.shs + r * (size_t)M * 3;
-    const float* __restrict__ shp = a.shs + pr * (size_t)M * 3;
+    const bool split = a.shs_rest != nullptr;   // raw store: coefficient 0 in shs [rows,1,3], rest in shs_rest
+    const float* __restrict__ sh = split ? a.shs_rest + r * (size_t)(M - 1) * 3 - 3 : a.shs + r * (size_t)M * 3;
+    const float* __restrict__ shp = split ? a.shs_rest + pr * (size_t)(M - 1) * 3 - 3 : a.shs + pr * (size_t)M * 3;
 
     // dL/dsh rows
-    for (int k = 0; k < M; ++k) {
-      const float w = (k < n) ? bs[k] : 0.f;
-      put<FUSED>(o.dL_dsh, r, M * 3, 3 * k + 0, w * dL_dRGB.x, pr, lerp, t, omt);
-      put<FUSED>(o.dL_dsh, r, M * 3, 3 * k + 1, w * dL_dRGB.y, pr, lerp, t, omt);
-      put<FUSED>(o.dL_dsh, r, M * 3, 3 * k + 2, w * dL_dRGB.z, pr, lerp, t, omt);
+    if (split) {
+      put<FUSED>(o.dL_dsh, r, 3, 0, bs[0] * dL_dRGB.x, pr, lerp, t, omt);
+      put<FUSED>(o.dL_dsh, r, 3, 1, bs[0] * dL_dRGB.y, pr, lerp, t, omt);
+      put<FUSED>(o.dL_dsh, r, 3, 2, bs[0] * dL_dRGB.z, pr, lerp, t, omt);
+      const int Wd = (M - 1) * 3;
+      for (int k = 1; k < M; ++k) {
+        const float w = (k < n) ? bs[k] : 0.f;
+        if (!FUSED || k < n) {   // in fused mode the rows are pre-zeroed: skip the zero atomics
+          put<FUSED>(o.dL_dsh_rest, r, Wd, 3 * k - 3, w * dL_dRGB.x, pr, lerp, t, omt);
+          put<FUSED>(o.dL_dsh_rest, r, Wd, 3 * k - 2, w * dL_dRGB.y, pr, lerp, t, omt);
+          put<FUSED>(o.dL_dsh_rest, r, Wd, 3 * k - 1, w * dL_dRGB.z, pr, lerp, t, omt);
+        }
+      }
+    } else {
+      for (int k = 0; k < M; ++k) {
+        const float w = (k < n) ? bs[k] : 0.f;
+        if (!FUSED || k < n) {
+          put<FUSED>(o.dL_dsh, r, M * 3, 3 * k + 0, w * dL_dRGB.x, pr, lerp, t, omt);
+          put<FUSED>(o.dL_dsh, r, M * 3, 3 * k + 1, w * dL_dRGB.y, pr, lerp, t, omt);
+          put<FUSED>(o.dL_dsh, r, M * 3, 3 * k + 2, w * dL_dRGB.z, pr, lerp, t, omt);
+        }
+      }
     }
 
     // d colour / d direction
     float3 dx3 = {0, 0, 0}, dy3 = {0, 0, 0}, dz3 = {0, 0, 0};
-    auto S = [&](int k) -> float3 {
+    auto S = [&](int k) -> float3 {   // k >= 1 only: `sh` is biased by one coefficient in split mode
       float3 v = make_float3(__ldg(sh + 3 * k), __ldg(sh + 3 * k + 1), __ldg(sh + 3 * k + 2));
       if (FUSED && lerp) {
         v.x = lerp_rn(t, v.x, omt, __ldg(shp + 3 * k));
@@ -310,24 +352,35 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdArgs b)
     put<FUSED>(o.dL_dcolors, r, 3, 0, dL_dRGB.x, pr, lerp, t, omt);
     put<FUSED>(o.dL_dcolors, r, 3, 1, dL_dRGB.y, pr, lerp, t, omt);
     put<FUSED>(o.dL_dcolors, r, 3, 2, dL_dRGB.z, pr, lerp, t, omt);
-    if (!FUSED && o.dL_dsh) for (int i = 0; i < M * 3; ++i) o.dL_dsh[r * (size_t)M * 3 + i] = 0.f;
+    if (!FUSED && o.dL_dsh && !o.dL_dsh_rest) for (int i = 0; i < M * 3; ++i) o.dL_dsh[r * (size_t)M * 3 + i] = 0.f;
   }
 
   put<FUSED>(o.dL_dmeans3D, r, 3, 0, dL_dmean.x, pr, lerp, t, omt);
   put<FUSED>(o.dL_dmeans3D, r, 3, 1, dL_dmean.y, pr, lerp, t, omt);
   put<FUSED>(o.dL_dmeans3D, r, 3, 2, dL_dmean.z, pr, lerp, t, omt);
-  put<FUSED>(o.dL_dopacity, r, 1, 0, dL_dopacity_out, pr, lerp, t, omt);
+  put2<FUSED>(o.dL_dopacity, r, 1, 0, tc * dL_dopacity_out * act_scalar_grad(a.act_opac, o_raw, o_act), pr,
+              lerp, omt * dL_dopacity_out * act_scalar_grad(a.act_opac, op_raw, op_act));
 
   // ---------------- 3D covariance -> scale / rotation (backward.cu:330-393) ----------------
   if (a.cov3D_pre == nullptr) {
-    float3 sc = ld3(a.scales, r);
-    const float4 q4 = __ldg(reinterpret_cast<const float4*>(a.rots) + r);
+    const float3 s_raw = ld3(a.scales, r);
+    const float3 s_act = make_float3(act_scalar(a.act_scale, s_raw.x), act_scalar(a.act_scale, s_raw.y),
+                                     act_scalar(a.act_scale, s_raw.z));
+    float3 sc = s_act;
+    const float4 q_raw = __ldg(reinterpret_cast<const float4*>(a.rots) + r);
+    const float4 q4 = act_rotation(a.act_rot, a.norm_variant, q_raw);
     float qr = q4.x, qx = q4.y, qy = q4.z, qz = q4.w;
     float psign = 1.0f;
+    float3 sp_raw = {0.f, 0.f, 0.f}, sp_act = {0.f, 0.f, 0.f};
+    float4 qp_raw = {0.f, 0.f, 0.f, 0.f};
     if (FUSED && lerp) {
-      float3 s2 = ld3(a.scales, pr);
+      sp_raw = ld3(a.scales, pr);
+      sp_act = make_float3(act_scalar(a.act_scale, sp_raw.x), act_scalar(a.act_scale, sp_raw.y),
+                           act_scalar(a.act_scale, sp_raw.z));
+      const float3 s2 = sp_act;
       sc = make_float3(lerp_rn(t, sc.x, omt, s2.x), lerp_rn(t, sc.y, omt, s2.y), lerp_rn(t, sc.z, omt, s2.z));
-      float4 op = __ldg(reinterpret_cast<const float4*>(a.rots) + pr);
+      qp_raw = __ldg(reinterpret_cast<const float4*>(a.rots) + pr);
+      float4 op = act_rotation(a.act_rot, a.norm_variant, qp_raw);
       float dotp = (qr * op.x + qx * op.y) + (qy * op.z + qz * op.w);
       if (dotp < 0.0f) { psign = -1.0f; op.x = -op.x; op.y = -op.y; op.z = -op.z; op.w = -op.w; }
       qr = lerp_rn(t, qr, omt, op.x);
@@ -362,13 +415,24 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdArgs b)
     dq.z = 2 * x * (dMt.c[1][0] + dMt.c[0][1]) + 2 * rr * (dMt.c[2][0] - dMt.c[0][2]) + 2 * z * (dMt.c[1][2] + dMt.c[2][1]) - 4 * y * (dMt.c[2][2] + dMt.c[0][0]);
     dq.w = 2 * rr * (dMt.c[0][1] - dMt.c[1][0]) + 2 * x * (dMt.c[2][0] + dMt.c[0][2]) + 2 * y * (dMt.c[1][2] + dMt.c[2][1]) - 4 * z * (dMt.c[1][1] + dMt.c[0][0]);
 
-    put<FUSED>(o.dL_dscales, r, 3, 0, ds0, pr, lerp, t, omt);
-    put<FUSED>(o.dL_dscales, r, 3, 1, ds1, pr, lerp, t, omt);
-    put<FUSED>(o.dL_dscales, r, 3, 2, ds2, pr, lerp, t, omt);
-    put<FUSED>(o.dL_drotations, r, 4, 0, dq.x, pr, lerp, t, omt, psign);
-    put<FUSED>(o.dL_drotations, r, 4, 1, dq.y, pr, lerp, t, omt, psign);
-    put<FUSED>(o.dL_drotations, r, 4, 2, dq.z, pr, lerp, t, omt, psign);
-    put<FUSED>(o.dL_drotations, r, 4, 3, dq.w, pr, lerp, t, omt, psign);
+    put2<FUSED>(o.dL_dscales, r, 3, 0, tc * ds0 * act_scalar_grad(a.act_scale, s_raw.x, s_act.x), pr, lerp,
+                omt * ds0 * act_scalar_grad(a.act_scale, sp_raw.x, sp_act.x));
+    put2<FUSED>(o.dL_dscales, r, 3, 1, tc * ds1 * act_scalar_grad(a.act_scale, s_raw.y, s_act.y), pr, lerp,
+                omt * ds1 * act_scalar_grad(a.act_scale, sp_raw.y, sp_act.y));
+    put2<FUSED>(o.dL_dscales, r, 3, 2, tc * ds2 * act_scalar_grad(a.act_scale, s_raw.z, s_act.z), pr, lerp,
+                omt * ds2 * act_scalar_grad(a.act_scale, sp_raw.z, sp_act.z));
+    // dq is in (r, x, y, z) = float4 (x, y, z, w) component order, like the stored quaternion
+    const float4 gc = act_rotation_grad(a.act_rot, a.norm_variant, q_raw,
+                                        make_float4(tc * dq.x, tc * dq.y, tc * dq.z, tc * dq.w));
+    float4 gp = {0.f, 0.f, 0.f, 0.f};
+    if (FUSED && lerp) {
+      const float w = omt * psign;
+      gp = act_rotation_grad(a.act_rot, a.norm_variant, qp_raw, make_float4(w * dq.x, w * dq.y, w * dq.z, w * dq.w));
+    }
+    put2<FUSED>(o.dL_drotations, r, 4, 0, gc.x, pr, lerp, gp.x);
+    put2<FUSED>(o.dL_drotations, r, 4, 1, gc.y, pr, lerp, gp.y);
+    put2<FUSED>(o.dL_drotations, r, 4, 2, gc.z, pr, lerp, gp.z);
+    put2<FUSED>(o.dL_drotations, r, 4, 3, gc.w, pr, lerp, gp.w);
     if (!FUSED && o.dL_dcov3D) for (int i = 0; i < 6; ++i) o.dL_dcov3D[r * 6 + i] = dcov[i];
   } else {
     for (int i = 0; i < 6; ++i) put<FUSED>(o.dL_dcov3D, r, 6, i, dcov[i], pr, lerp, t, omt);

@@ -83,13 +83,15 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreArgs a) {
   float c6[6];
   if (a.cov3D_pre == nullptr) {
     float3 sc = ld3(a.scales, r);
-    const float4 q4 = __ldg(reinterpret_cast<const float4*>(a.rots) + r);
+    sc = make_float3(act_scalar(a.act_scale, sc.x), act_scalar(a.act_scale, sc.y), act_scalar(a.act_scale, sc.z));
+    const float4 q4 = act_rotation(a.act_rot, a.norm_variant, __ldg(reinterpret_cast<const float4*>(a.rots) + r));
     float qr = q4.x, qx = q4.y, qy = q4.z, qz = q4.w;
     if (FUSED && lerp) {
       float3 s2 = ld3(a.scales, pr);
+      s2 = make_float3(act_scalar(a.act_scale, s2.x), act_scalar(a.act_scale, s2.y), act_scalar(a.act_scale, s2.z));
       sc = make_float3(lerp_rn(t, sc.x, omt, s2.x), lerp_rn(t, sc.y, omt, s2.y),
                        lerp_rn(t, sc.z, omt, s2.z));
-      float4 o = __ldg(reinterpret_cast<const float4*>(a.rots) + pr);
+      float4 o = act_rotation(a.act_rot, a.norm_variant, __ldg(reinterpret_cast<const float4*>(a.rots) + pr));
       float dotp = (qr * o.x + qx * o.y) + (qy * o.z + qz * o.w);
       if (dotp < 0.0f) { o.x = -o.x; o.y = -o.y; o.z = -o.z; o.w = -o.w; }
       qr = lerp_rn(t, qr, omt, o.x);
@@ -156,7 +158,35 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreArgs a) {
     const float* __restrict__ shp = a.shs + pr * (size_t)a.M * 3;
     float cr = 0.f, cg = 0.f, cb = 0.f;
     const bool vec = (a.M == 16) && ((reinterpret_cast<size_t>(a.shs) & 15) == 0);
-    if (vec) {
+    if (a.shs_rest != nullptr) {
+      // raw store: coefficient 0 lives in _features_dc [rows,1,3], the others in _features_rest [rows,M-1,3]
+      const float* __restrict__ dc = a.shs + r * 3;
+      const float* __restrict__ dcp = a.shs + pr * 3;
+      const float* __restrict__ rs = a.shs_rest + r * (size_t)(a.M - 1) * 3;
+      const float* __restrict__ rsp = a.shs_rest + pr * (size_t)(a.M - 1) * 3;
+      float v[48];
+#pragma unroll
+      for (int i = 0; i < 3; ++i) v[i] = __ldg(dc + i);
+#pragma unroll
+      for (int i = 3; i < 48; ++i)
+        if (i < n * 3) v[i] = __ldg(rs + (i - 3));
+      if (FUSED && lerp) {
+#pragma unroll
+        for (int i = 0; i < 3; ++i) v[i] = lerp_rn(t, v[i], omt, __ldg(dcp + i));
+#pragma unroll
+        for (int i = 3; i < 48; ++i)
+          if (i < n * 3) v[i] = lerp_rn(t, v[i], omt, __ldg(rsp + (i - 3)));
+      }
+      cr = b[0] * v[0]; cg = b[0] * v[1]; cb = b[0] * v[2];
+#pragma unroll
+      for (int k = 1; k < 16; ++k) {
+        if (k < n) {
+          cr = cr + b[k] * v[3 * k];
+          cg = cg + b[k] * v[3 * k + 1];
+          cb = cb + b[k] * v[3 * k + 2];
+        }
+      }
+    } else if (vec) {
       // 48 floats = 12 float4 per row
       const float4* s4 = reinterpret_cast<const float4*>(sh);
       const float4* p4 = reinterpret_cast<const float4*>(shp);
@@ -213,8 +243,8 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreArgs a) {
     }
   }
 
-  float opacity = __ldg(a.opac + r);
-  if (FUSED && lerp) opacity = lerp_rn(t, opacity, omt, __ldg(a.opac + pr));
+  float opacity = act_scalar(a.act_opac, __ldg(a.opac + r));
+  if (FUSED && lerp) opacity = lerp_rn(t, opacity, omt, act_scalar(a.act_opac, __ldg(a.opac + pr)));
   const float op = opacity * h_convolution_scaling;
 
   // Conservative half-extents of the region where this Gaussian can reach alpha >= 1/255:

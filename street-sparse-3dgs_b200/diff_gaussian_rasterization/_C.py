@@ -24,8 +24,10 @@ def _null(t):
 
 def _scene(bg, indices, parent_indices, ts, kids, means3D, colors, opacity, scales, rotations,
            scale_modifier, cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, H, W, sh, degree,
-           campos, skyboxnum):
-    """Build the two C structs; returns (view, gaussians, keepalive list)."""
+           campos, skyboxnum, sh_rest=None, acts=None):
+    """Build the two C structs; returns (view, gaussians, keepalive list).  With ``sh_rest`` / ``acts`` the
+    attribute tensors are the RAW parameter store (``sh`` = _features_dc, ``sh_rest`` = _features_rest,
+    ``acts`` = (scale, rotation, opacity) activation codes applied inside the kernels)."""
     if means3D.ndimension() != 2 or means3D.size(1) != 3:
         raise RuntimeError("means3D must have dimensions (num_points, 3)")
     keep = []
@@ -46,6 +48,10 @@ def _scene(bg, indices, parent_indices, ts, kids, means3D, colors, opacity, scal
     view = nat.View(int(W), int(H), float(tan_fovx), float(tan_fovy), f32(viewmatrix, "viewmatrix"),
                     f32(projmatrix, "projmatrix"), f32(campos, "campos"), f32(bg, "bg"))
     M = 0 if _null(sh) else sh.size(1)
+    if not _null(sh_rest):
+        if _null(sh) or sh.size(1) != 1 or sh_rest.size(0) != sh.size(0):
+            raise RuntimeError("sh_rest needs sh of shape (rows, 1, 3) with the same number of rows")
+        M = 1 + sh_rest.size(1)
     g = nat.Gaussians()
     g.P = P
     g.store_rows = rows
@@ -64,6 +70,8 @@ def _scene(bg, indices, parent_indices, ts, kids, means3D, colors, opacity, scal
     g.parent_indices = i32(parent_indices, "parent_indices") if fused else None
     g.ts = f32(ts, "interpolation_weights")
     g.kids = i32(kids, "num_node_kids")
+    g.shs_rest = f32(sh_rest, "sh_rest") if not _null(sh_rest) else None
+    g.scale_activation, g.rotation_activation, g.opacity_activation = acts if acts is not None else (0, 0, 0)
     if fused and not _null(parent_indices) and parent_indices.size(0) < indices.size(0):
         raise RuntimeError("parent_indices is shorter than render_indices")
     for name, t in (("interpolation_weights", ts), ("num_node_kids", kids)):
@@ -75,13 +83,13 @@ def _scene(bg, indices, parent_indices, ts, kids, means3D, colors, opacity, scal
 def rasterize_gaussians_ex(bg, indices, parent_indices, ts, kids, means3D, colors, opacity, scales,
                            rotations, scale_modifier, cov3D_precomp, viewmatrix, projmatrix, tan_fovx,
                            tan_fovy, image_height, image_width, sh, degree, campos, prefiltered, debug,
-                           do_depth, skyboxnum=0):
+                           do_depth, skyboxnum=0, sh_rest=None, acts=None):
     L = nat.lib()
     dev = means3D.device
     H, W = int(image_height), int(image_width)
     view, g, keep = _scene(bg, indices, parent_indices, ts, kids, means3D, colors, opacity, scales,
                            rotations, scale_modifier, cov3D_precomp, viewmatrix, projmatrix, tan_fovx,
-                           tan_fovy, H, W, sh, degree, campos, skyboxnum)
+                           tan_fovy, H, W, sh, degree, campos, skyboxnum, sh_rest, acts)
     P = g.P
     out_color = torch.empty((NUM_CHANNELS, H, W), dtype=torch.float32, device=dev)
     out_invdepth = torch.empty((1 if do_depth else 0, H, W), dtype=torch.float32, device=dev)
@@ -117,26 +125,30 @@ def rasterize_gaussians_backward_ex(bg, indices, parent_indices, ts, kids, means
                                     opacities, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,
                                     projmatrix, tan_fovx, tan_fovy, dL_dout_color, dL_dout_invdepth, sh,
                                     degree, campos, geomBuffer, R, binningBuffer, imageBuffer, debug,
-                                    skyboxnum=0):
+                                    skyboxnum=0, sh_rest=None, acts=None):
+    """With ``sh_rest`` the returned dL_dsh is the pair (dL_dfeatures_dc, dL_dfeatures_rest)."""
     L = nat.lib()
     dev = means3D.device
     H, W = dL_dout_color.size(1), dL_dout_color.size(2)
     view, g, keep = _scene(bg, indices, parent_indices, ts, kids, means3D, colors, opacities, scales,
                            rotations, scale_modifier, cov3D_precomp, viewmatrix, projmatrix, tan_fovx,
-                           tan_fovy, H, W, sh, degree, campos, skyboxnum)
+                           tan_fovy, H, W, sh, degree, campos, skyboxnum, sh_rest, acts)
     P, rows, M = g.P, g.store_rows, g.sh_coeffs
+    split = not _null(sh_rest)
     opts = dict(dtype=torch.float32, device=dev)
     dL_dmeans2D = torch.empty((P, 3), **opts)
     dL_dmeans3D = torch.empty((rows, 3), **opts)
     dL_dopacity = torch.empty((rows, 1), **opts)
     # only the gradients of inputs that exist are materialised; the others come back empty
-    dL_dsh = torch.empty((rows, M, 3), **opts) if not _null(sh) else torch.empty((0, 0, 3), **opts)
+    dL_dsh = torch.empty((rows, 1 if split else M, 3), **opts) if not _null(sh) else torch.empty((0, 0, 3), **opts)
+    dL_dsh_rest = torch.empty((rows, M - 1, 3), **opts) if split else None
     dL_dcolors = torch.empty((rows, NUM_CHANNELS), **opts) if not _null(colors) else torch.empty((0, 3), **opts)
     dL_dscales = torch.empty((rows, 3), **opts) if not _null(scales) else torch.empty((0, 3), **opts)
     dL_drot = torch.empty((rows, 4), **opts) if not _null(rotations) else torch.empty((0, 4), **opts)
     dL_dcov3D = torch.empty((rows, 6), **opts) if not _null(cov3D_precomp) else torch.empty((0, 6), **opts)
     grads = nat.Grads(nat.ptr(dL_dmeans2D), nat.ptr(dL_dmeans3D), nat.ptr(dL_dsh), nat.ptr(dL_dcolors),
-                      nat.ptr(dL_dopacity), nat.ptr(dL_dscales), nat.ptr(dL_drot), nat.ptr(dL_dcov3D))
+                      nat.ptr(dL_dopacity), nat.ptr(dL_dscales), nat.ptr(dL_drot), nat.ptr(dL_dcov3D),
+                      nat.ptr(dL_dsh_rest))
     ws = torch.empty((L.h3dgs_backward_workspace_bytes(P),), dtype=torch.uint8, device=dev)
     dcol = nat.as_f32(dL_dout_color, "dL_dout_color")
     ddep = nat.as_f32(dL_dout_invdepth, "dL_dout_invdepth")
@@ -145,6 +157,8 @@ def rasterize_gaussians_backward_ex(bg, indices, parent_indices, ts, kids, means
                                nat.ptr(ddep), ctypes.byref(grads), nat.ptr(ws), ws.numel(),
                                int(bool(debug)), nat.stream_handle()),
               "h3dgs_backward")
+    if split:
+        dL_dsh = (dL_dsh, dL_dsh_rest)
     return dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drot
 
 

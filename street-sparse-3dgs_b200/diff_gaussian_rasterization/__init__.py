@@ -27,6 +27,60 @@ def rasterize_gaussians_fused(means3D, means2D, sh, colors_precomp, opacities, s
                                      cov3Ds_precomp, raster_settings, int(skybox_points))
 
 
+def rasterize_gaussians_raw(xyz, means2D, features_dc, features_rest, opacity_raw, scaling_raw, rotation_raw,
+                            raster_settings, skybox_points, activations):
+    """``rasterize_gaussians_fused`` on the RAW parameter store of a reference ``GaussianModel``
+    (scene/gaussian_model.py:121-145): the kernels apply ``activations`` = (scale, rotation, opacity) codes
+    (``h3dgs_native.ACT_*``) and the dc/rest concatenation to the rows they gather instead of torch
+    activating all N rows per render; gradients come back for the raw parameters."""
+    return _RasterizeGaussiansRaw.apply(xyz, means2D, features_dc, features_rest, opacity_raw, scaling_raw,
+                                        rotation_raw, raster_settings, int(skybox_points), tuple(activations))
+
+
+class _RasterizeGaussiansRaw(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, xyz, means2D, f_dc, f_rest, opacity, scaling, rotation, raster_settings, skyboxnum, acts):
+        rs = raster_settings
+        e = torch.Tensor([])
+        args = (rs.bg, rs.render_indices, rs.parent_indices, rs.interpolation_weights, rs.num_node_kids,
+                xyz, e, opacity, scaling, rotation, rs.scale_modifier, e, rs.viewmatrix, rs.projmatrix,
+                rs.tanfovx, rs.tanfovy, rs.image_height, rs.image_width, f_dc, rs.sh_degree, rs.campos,
+                rs.prefiltered, rs.debug, rs.do_depth)
+        num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer, invdepths = \
+            _C.rasterize_gaussians_ex(*args, skyboxnum, f_rest, acts)
+        ctx.raster_settings = rs
+        ctx.num_rendered = num_rendered
+        ctx.skyboxnum = skyboxnum
+        ctx.acts = acts
+        ctx.means2D_rows = means2D.size(0)
+        ctx.save_for_backward(xyz, f_dc, f_rest, opacity, scaling, rotation, radii, geomBuffer, binningBuffer,
+                              imgBuffer)
+        ctx.mark_non_differentiable(radii)
+        return color, radii, invdepths
+
+    @staticmethod
+    def backward(ctx, grad_out_color, _, grad_out_depth):
+        rs = ctx.raster_settings
+        xyz, f_dc, f_rest, opacity, scaling, rotation, radii, geomBuffer, binningBuffer, imgBuffer = ctx.saved_tensors
+        if grad_out_depth is None:
+            grad_out_depth = torch.empty(0, device=grad_out_color.device)
+        e = torch.Tensor([])
+        args = (rs.bg, rs.render_indices, rs.parent_indices, rs.interpolation_weights, rs.num_node_kids,
+                xyz, radii, e, opacity, scaling, rotation, rs.scale_modifier, e, rs.viewmatrix, rs.projmatrix,
+                rs.tanfovx, rs.tanfovy, grad_out_color, grad_out_depth, f_dc, rs.sh_degree, rs.campos,
+                geomBuffer, ctx.num_rendered, binningBuffer, imgBuffer, rs.debug)
+        (grad_means2D, _gc, grad_opacity, grad_xyz, _gcov, grad_sh, grad_scaling, grad_rotation) = \
+            _C.rasterize_gaussians_backward_ex(*args, ctx.skyboxnum, f_rest, ctx.acts)
+        grad_dc, grad_rest = grad_sh
+        if grad_means2D.size(0) != ctx.means2D_rows:
+            full = torch.zeros((ctx.means2D_rows, 3), dtype=grad_means2D.dtype, device=grad_means2D.device)
+            n = min(ctx.means2D_rows, grad_means2D.size(0))
+            full[:n] = grad_means2D[:n]
+            grad_means2D = full
+        return (grad_xyz, grad_means2D, grad_dc, grad_rest, grad_opacity, grad_scaling, grad_rotation,
+                None, None, None)
+
+
 class _RasterizeGaussians(torch.autograd.Function):
     @staticmethod
     def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,

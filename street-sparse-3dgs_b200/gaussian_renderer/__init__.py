@@ -12,8 +12,39 @@ import math
 
 import torch
 
+import os
+
+import h3dgs_native as nat
 from diff_gaussian_rasterization import (GaussianRasterizationSettings, GaussianRasterizer,
-                                         rasterize_gaussians_fused)
+                                         rasterize_gaussians_fused, rasterize_gaussians_raw)
+
+
+def _raw_store(pc, pipe, override_color):
+    """The raw parameter tensors + activation codes of a reference-style ``GaussianModel``
+    (scene/gaussian_model.py:40-48,121-145,411-412) when the kernels can apply its activations themselves;
+    None for any other model object (then its activated ``get_*`` properties are used, as in the reference)."""
+    if override_color is not None or pipe.convert_SHs_python or pipe.compute_cov3D_python:
+        return None
+    if os.environ.get("H3DGS_RAW_STORE", "1") == "0":
+        return None
+    try:
+        t = (pc._xyz, pc._features_dc, pc._features_rest, pc._opacity, pc._scaling, pc._rotation)
+        sa, ra, oa = pc.scaling_activation, pc.rotation_activation, pc.opacity_activation
+    except AttributeError:
+        return None
+    if sa is not torch.exp or ra is not torch.nn.functional.normalize:
+        return None
+    if oa is torch.sigmoid:
+        oc = nat.ACT_SIGMOID
+    elif oa is torch.abs:
+        oc = nat.ACT_ABS
+    else:
+        return None
+    if any((not x.is_cuda) or x.dtype != torch.float32 or not x.is_contiguous() for x in t):
+        return None
+    if t[1].dim() != 3 or t[1].size(1) != 1 or t[2].dim() != 3 or t[2].size(1) < 1:
+        return None
+    return t, (nat.ACT_EXP, nat.ACT_NORMALIZE, oc)
 
 
 def _eval_sh(deg, sh, dirs):
@@ -164,9 +195,14 @@ def render_post(viewpoint_camera, pc, pipe, bg_color: torch.Tensor, scaling_modi
                 interp_python=True, use_trained_exp=False, do_depth=False):
     """Render the scene from a hierarchy cut (gaussian_renderer/__init__.py:138-304)."""
     screenspace_points = _screenspace_points(pc)
-    means3D, means2D, opacity = pc.get_xyz, screenspace_points, pc.get_opacity
-    scales, rotations, cov3D_precomp = _geometry(pc, pipe, scaling_modifier)
-    shs, colors_precomp = _appearance(viewpoint_camera, pc, pipe, override_color)
+    means2D = screenspace_points
+    # Hierarchy cut with Python-style interpolation on a reference GaussianModel: hand the RAW parameters to
+    # the kernels, which activate only the rows of the cut (the reference activates all N rows per render).
+    raw = _raw_store(pc, pipe, override_color) if (render_indices.size(0) != 0 and interp_python) else None
+    if raw is None:
+        means3D, opacity = pc.get_xyz, pc.get_opacity
+        scales, rotations, cov3D_precomp = _geometry(pc, pipe, scaling_modifier)
+        shs, colors_precomp = _appearance(viewpoint_camera, pc, pipe, override_color)
 
     skybox = None
     if render_indices.size(0) != 0:
@@ -190,8 +226,13 @@ def render_post(viewpoint_camera, pc, pipe, bg_color: torch.Tensor, scaling_modi
 
     settings = _settings(viewpoint_camera, pc, bg_color, scaling_modifier, pipe.debug, do_depth, render_indices,
                          parent_indices, interpolation_weights, num_node_kids)
-    rendered_image, radii, depth_image = _rasterize(settings, means3D, means2D, opacity, shs, colors_precomp,
-                                                    scales, rotations, cov3D_precomp, skybox)
+    if raw is not None:
+        (xyz, f_dc, f_rest, op_raw, sc_raw, rot_raw), acts = raw
+        rendered_image, radii, depth_image = rasterize_gaussians_raw(xyz, means2D, f_dc, f_rest, op_raw, sc_raw,
+                                                                     rot_raw, settings, skybox, acts)
+    else:
+        rendered_image, radii, depth_image = _rasterize(settings, means3D, means2D, opacity, shs, colors_precomp,
+                                                        scales, rotations, cov3D_precomp, skybox)
 
     if use_trained_exp and pc.pretrained_exposures:
         try:

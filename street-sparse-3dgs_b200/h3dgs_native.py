@@ -33,13 +33,18 @@ class Gaussians(Structure):
                 ("opacities", c_void_p), ("scales", c_void_p), ("rotations", c_void_p),
                 ("cov3D_precomp", c_void_p),
                 ("render_indices", c_void_p), ("parent_indices", c_void_p),
-                ("ts", c_void_p), ("kids", c_void_p)]
+                ("ts", c_void_p), ("kids", c_void_p),
+                ("shs_rest", c_void_p), ("scale_activation", c_int32), ("rotation_activation", c_int32),
+                ("opacity_activation", c_int32)]
+
+
+ACT_NONE, ACT_EXP, ACT_NORMALIZE, ACT_SIGMOID, ACT_ABS = 0, 1, 2, 3, 4
 
 
 class Grads(Structure):
     _fields_ = [("dL_dmeans2D", c_void_p), ("dL_dmeans3D", c_void_p), ("dL_dsh", c_void_p),
                 ("dL_dcolors", c_void_p), ("dL_dopacity", c_void_p), ("dL_dscales", c_void_p),
-                ("dL_drotations", c_void_p), ("dL_dcov3D", c_void_p)]
+                ("dL_drotations", c_void_p), ("dL_dcov3D", c_void_p), ("dL_dsh_rest", c_void_p)]
 
 
 class DebugView(Structure):
@@ -120,7 +125,7 @@ def lib():
             fn = getattr(handle, name)
             fn.restype = res
             fn.argtypes = args
-        if handle.h3dgs_abi_version() != 1:
+        if handle.h3dgs_abi_version() != 2:
             raise H3dgsError("libh3dgs_b200.so ABI version mismatch")
         _lib = handle
     return _lib

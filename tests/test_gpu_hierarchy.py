@@ -67,12 +67,31 @@ def test_expand_to_target_matches_reference():
         assert torch.equal(ours, ref)
 
 
-def _fused_vs_glue(levels, sky, w, h, target, seed, depth=True):
+def _raw_model(attrs, sky, opacity_activation):
+    """Reference-style GaussianModel on RAW parameters: un-normalised rotations, log scales, signed
+    (abs activation) or logit-like (sigmoid activation) opacities."""
+    m = workload.HierModel(attrs, sky)
+    g = torch.Generator().manual_seed(5)
+    n = m._xyz.size(0)
+    with torch.no_grad():
+        m._rotation.mul_((0.25 + 3.0 * torch.rand(n, 1, generator=g)).to(DEV))
+        if opacity_activation is torch.abs:
+            m._opacity.mul_((torch.rand(n, 1, generator=g) < 0.5).to(DEV) * 2.0 - 1.0)
+        else:
+            m._opacity.copy_(torch.logit(m._opacity.clamp(1e-3, 1 - 1e-3)))
+    m.opacity_activation = opacity_activation
+    return m
+
+
+def _fused_vs_glue(levels, sky, w, h, target, seed, depth=True, raw=None):
     import gaussian_hierarchy
     attrs = workload.build_scene(levels, sky, seed, DEV)
     cam = scenes.street_camera(w, h, seed=seed, device=DEV, yaw_deg=4.0, x=-10.0)
     bg = torch.tensor([0.05, 0.1, 0.15], device=DEV)
-    m_o, m_r, m_r2, m_r3, m_r4 = (workload.ActivatedModel(attrs, sky) for _ in range(5))
+    if raw is None:
+        m_o, m_r, m_r2, m_r3, m_r4 = (workload.ActivatedModel(attrs, sky) for _ in range(5))
+    else:
+        m_o, m_r, m_r2, m_r3, m_r4 = (_raw_model(attrs, sky, raw) for _ in range(5))
     limit = workload.find_limit(gaussian_hierarchy._C, m_o, cam, target, DEV)
     n = attrs["means3D"].size(0)
     g = torch.Generator().manual_seed(11)
@@ -103,7 +122,8 @@ def _fused_vs_glue(levels, sky, w, h, target, seed, depth=True):
         assert torch.equal(bits(out_o["depth"]), bits(out_r["depth"]))
     assert torch.equal(out_o["visibility_filter"], out_r["visibility_filter"])
     assert torch.equal(out_o["radii"], out_r["radii"])
-    names = ["xyz", "features", "opacity", "scaling", "rotation"]
+    names = ["xyz", "features", "opacity", "scaling", "rotation"] if raw is None else \
+        ["xyz", "features_dc", "features_rest", "opacity", "scaling", "rotation"]
     for name, po, pr, pr2, pr3, pr4 in zip(names, m_o.parameters(), m_r.parameters(), m_r2.parameters(),
                                            m_r3.parameters(), m_r4.parameters()):
         util.assert_grad_close(po.grad, pr.grad, pr2.grad, name, more_refs=(pr3.grad, pr4.grad))
@@ -112,6 +132,21 @@ def _fused_vs_glue(levels, sky, w, h, target, seed, depth=True):
     gr2 = out_r2["viewspace_points"].grad
     util.assert_grad_close(go, gr, gr2, "viewspace_points",
                            more_refs=(out_r3["viewspace_points"].grad, out_r4["viewspace_points"].grad))
+
+
+@pytest.mark.parametrize("act", [torch.abs, torch.sigmoid])
+def test_raw_store_render_post_matches_python_glue(act, monkeypatch):
+    """render_post on a reference-style GaussianModel: the kernels activate the gathered rows themselves
+    (exp / normalize / abs|sigmoid / dc+rest) and return raw-parameter gradients; the reference activates
+    the whole store with torch and lets autograd chain back."""
+    util.need_ref()
+    import diff_gaussian_rasterization as dgr
+    calls = []
+    orig = dgr._RasterizeGaussiansRaw.forward
+    monkeypatch.setattr(dgr._RasterizeGaussiansRaw, "forward",
+                        staticmethod(lambda *a, **k: (calls.append(1), orig(*a, **k))[1]))
+    _fused_vs_glue(15, 1000, 800, 600, 15000, seed=7, depth=True, raw=act)
+    assert calls, "the raw-store path was not taken"
 
 
 @pytest.mark.parametrize("levels,sky,w,h,target,depth", [
