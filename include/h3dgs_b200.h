@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define H3DGS_ABI_VERSION 2
+#define H3DGS_ABI_VERSION 3
 
 #if defined(__GNUC__)
 #define H3DGS_API __attribute__((visibility("default")))
@@ -121,27 +121,31 @@ typedef struct H3dgsGaussians {
  * binning: instance keys/values + sort workspace (BinningState, :186-199). */
 H3DGS_API size_t h3dgs_geom_bytes(int32_t P);
 H3DGS_API size_t h3dgs_image_bytes(int32_t image_width, int32_t image_height);
-H3DGS_API size_t h3dgs_binning_bytes(int64_t num_rendered, int32_t image_width, int32_t image_height);
+H3DGS_API size_t h3dgs_binning_bytes(int64_t num_rendered, int64_t num_visible, int32_t image_width,
+                                     int32_t image_height);
 
 /*
  * Forward, stage 1: preprocess (EWA projection, SH, culling, fused interpolation) + tile-count scan.
  * Replaces FORWARD::preprocess + cub::DeviceScan::InclusiveSum + the num_rendered read-back
  * (rasterizer_impl.cu:275-325).  Writes radii[P] (0 = culled) and, after synchronising `stream`,
- * *num_rendered_host.
+ * *num_rendered_host (tile instances, the reference's num_rendered) and *num_visible_host (slots with
+ * radii > 0); both size the binning workspace and go to h3dgs_forward_render.
  */
 H3DGS_API int h3dgs_forward_preprocess(const H3dgsView* view, const H3dgsGaussians* g,
                              int32_t* radii, void* geom, size_t geom_bytes,
-                             int64_t* num_rendered_host, int debug, h3dgs_stream_t stream);
+                             int64_t* num_rendered_host, int64_t* num_visible_host, int debug,
+                             h3dgs_stream_t stream);
 
 /*
- * Forward, stage 2: instance emission, onesweep radix sort by (tile, depth), tile ranges, alpha blend.
+ * Forward, stage 2: depth sort of the visible slots, ordered instance emission, stable onesweep partition
+ * by tile (together: the reference's sort by (tile, depth), bit-identical lists), tile ranges, alpha blend.
  * Replaces duplicateWithKeys + cub::DeviceRadixSort::SortPairs + identifyTileRanges + FORWARD::render
  * (rasterizer_impl.cu:336-390).  out_color is [3,H,W]; out_invdepth is [1,H,W] or NULL.
  * num_rendered == 0 only fills out_color with the background.
  */
 H3DGS_API int h3dgs_forward_render(const H3dgsView* view, const H3dgsGaussians* g,
                          void* geom, void* binning, size_t binning_bytes, void* image,
-                         int64_t num_rendered, float* out_color, float* out_invdepth,
+                         int64_t num_rendered, int64_t num_visible, float* out_color, float* out_invdepth,
                          int debug, h3dgs_stream_t stream);
 
 /* Gradient outputs of the backward pass; any pointer may be NULL (that gradient is not produced).
@@ -190,7 +194,7 @@ typedef struct H3dgsDebugView {
   const uint32_t* n_contrib;     /* [H*W] */
   const float* depths;           /* [P] */
   const uint32_t* tiles_touched; /* [P] */
-  const uint32_t* point_offsets; /* [P] inclusive scan */
+  const uint32_t* point_offsets; /* [P] inclusive rank of the slot among the visible slots */
   const float* records;          /* [P,16] packed per-slot record, see DESIGN.md */
   const float* cov3D;            /* [P,6] */
   const uint16_t* tile_rects;    /* [P,4] x0,y0,x1,y1 in tiles */

@@ -200,17 +200,19 @@ const char* h3dgs_last_error(void) { return g_err; }
 
 size_t h3dgs_geom_bytes(int32_t P) { return GeomWs::make(nullptr, P).bytes; }
 size_t h3dgs_image_bytes(int32_t W, int32_t H) { return ImageWs::make(nullptr, W, H).bytes; }
-size_t h3dgs_binning_bytes(int64_t R, int32_t W, int32_t H) { return BinWs::make(nullptr, R, W, H).bytes; }
+size_t h3dgs_binning_bytes(int64_t R, int64_t V, int32_t W, int32_t H) { return BinWs::make(nullptr, R, V, W, H).bytes; }
 size_t h3dgs_backward_workspace_bytes(int32_t P) { return BwdWs::make(nullptr, P).bytes; }
 size_t h3dgs_expand_workspace_bytes(int32_t N) { return expand_ws_bytes(N); }
 
 int h3dgs_forward_preprocess(const H3dgsView* view, const H3dgsGaussians* g, int32_t* radii, void* geom,
-                             size_t geom_bytes, int64_t* num_rendered_host, int debug,
+                             size_t geom_bytes, int64_t* num_rendered_host, int64_t* num_visible_host, int debug,
                              h3dgs_stream_t stream) {
   int rc = check_scene(view, g);
   if (rc) return rc;
-  if (!num_rendered_host) return fail(H3DGS_EINVAL, "num_rendered_host is required");
+  if (!num_rendered_host || !num_visible_host)
+    return fail(H3DGS_EINVAL, "num_rendered_host and num_visible_host are required");
   *num_rendered_host = 0;
+  *num_visible_host = 0;
   if (g->P == 0) return 0;
   if (!radii || !geom) return fail(H3DGS_EINVAL, "radii and geom are required");
   if (geom_bytes < h3dgs_geom_bytes(g->P)) return fail(H3DGS_ENOSPACE, "geom workspace too small");
@@ -219,17 +221,18 @@ int h3dgs_forward_preprocess(const H3dgsView* view, const H3dgsGaussians* g, int
   PreArgs a = make_pre(view, g, radii, geom);
   H3_CUDA(launch_preprocess_fwd(a, s));
   if ((rc = debug_sync(debug, s, "preprocess_fwd"))) return rc;
-  H3_CUDA(launch_scan_inclusive(a.ws.tiles_touched, a.ws.offsets, g->P, a.ws.scan_status, a.ws.counters, s));
-  unsigned long long total = 0;
-  H3_CUDA(cudaMemcpyAsync(&total, a.ws.counters + 2, sizeof(total), cudaMemcpyDeviceToHost, s));
+  H3_CUDA(launch_scan_visible(a.ws.tiles_touched, a.ws.offsets, g->P, a.ws.scan_status, a.ws.counters, s));
+  unsigned long long totals[2] = {0, 0};   // V, R
+  H3_CUDA(cudaMemcpyAsync(totals, a.ws.counters + 2, sizeof(totals), cudaMemcpyDeviceToHost, s));
   H3_CUDA(cudaStreamSynchronize(s));
-  if (total >= (1ull << 30)) return fail(H3DGS_EINVAL, "more than 2^30 tile instances");
-  *num_rendered_host = (int64_t)total;
+  if (totals[1] >= (1ull << 30)) return fail(H3DGS_EINVAL, "more than 2^30 tile instances");
+  *num_visible_host = (int64_t)totals[0];
+  *num_rendered_host = (int64_t)totals[1];
   return 0;
 }
 
 int h3dgs_forward_render(const H3dgsView* view, const H3dgsGaussians* g, void* geom, void* binning,
-                         size_t binning_bytes, void* image, int64_t R, float* out_color,
+                         size_t binning_bytes, void* image, int64_t R, int64_t V, float* out_color,
                          float* out_invdepth, int debug, h3dgs_stream_t stream) {
   int rc = check_scene(view, g);
   if (rc) return rc;
@@ -248,27 +251,33 @@ int h3dgs_forward_render(const H3dgsView* view, const H3dgsGaussians* g, void* g
     return 0;
   }
   if (!geom || !binning || !image) return fail(H3DGS_EINVAL, "geom, binning and image are required");
-  if (binning_bytes < h3dgs_binning_bytes(R, W, H)) return fail(H3DGS_ENOSPACE, "binning workspace too small");
+  if (V <= 0 || V > R || V > g->P) return fail(H3DGS_EINVAL, "num_visible must be in [1, min(P, num_rendered)]");
+  if (binning_bytes < h3dgs_binning_bytes(R, V, W, H)) return fail(H3DGS_ENOSPACE, "binning workspace too small");
   GeomWs gw = GeomWs::make(geom, g->P);
-  BinWs bw = BinWs::make(binning, R, W, H);
+  BinWs bw = BinWs::make(binning, R, V, W, H);
   ImageWs iw = ImageWs::make(image, W, H);
   const int grid_x = (W + TILE_X - 1) / TILE_X, grid_y = (H + TILE_Y - 1) / TILE_Y;
   const SortPlan plan = make_sort_plan(W, H);
 
-  // radii > 0 <=> tiles_touched > 0; use the workspace copy so that radii need not be passed again
-  H3_CUDA(launch_emit_instances(g->P, reinterpret_cast<const int*>(gw.tiles_touched), gw, grid_x,
-                                bw.keys[0], bw.vals[0], s));
+  // visible slots -> (depth, slot) order -> ordered emission -> stable partition by tile
+  { ProfScope ps(K_MEMSET, s); H3_CUDA(cudaMemsetAsync(bw.zero_base, 0, bw.zero_bytes, s)); }
+  H3_CUDA(launch_compact_visible(g->P, gw, bw, s));
+  if ((rc = debug_sync(debug, s, "compact_visible"))) return rc;
+  H3_CUDA(launch_depth_sort(bw, V, s));
+  if ((rc = debug_sync(debug, s, "depth_sort"))) return rc;
+  H3_CUDA(launch_scan_gather(gw.tiles_touched, bw.dvals[0], bw.soffs, (int)V, bw.scan_status, bw.scan_counters, s));
+  H3_CUDA(launch_emit_instances(V, gw, bw, grid_x, plan.tile_key_bytes, s));
   if ((rc = debug_sync(debug, s, "emit_instances"))) return rc;
-  H3_CUDA(launch_radix_sort(bw, R, plan, s));
-  if ((rc = debug_sync(debug, s, "radix_sort"))) return rc;
-  H3_CUDA(launch_tile_ranges(R, bw.keys[bw.sorted], iw.ranges, grid_x * grid_y, s));
+  H3_CUDA(launch_tile_sort(bw, R, plan, gw.depth, s));
+  if ((rc = debug_sync(debug, s, "tile_sort"))) return rc;
+  H3_CUDA(launch_tile_ranges(R, bw.keys64, iw.ranges, grid_x * grid_y, s));
   if ((rc = debug_sync(debug, s, "tile_ranges"))) return rc;
 
   BlendArgs b;
   std::memset(&b, 0, sizeof(b));
   b.W = W; b.H = H; b.grid_x = grid_x; b.grid_y = grid_y; b.P = g->P; b.skyboxnum = g->skyboxnum;
   b.interp = (g->ts != nullptr && g->kids != nullptr) ? 1 : 0;
-  b.ranges = iw.ranges; b.point_list = bw.vals[bw.sorted]; b.rec = gw.rec; b.bg = view->background;
+  b.ranges = iw.ranges; b.point_list = bw.tvals[bw.sorted]; b.rec = gw.rec; b.bg = view->background;
   b.final_T = iw.final_T; b.n_contrib = iw.n_contrib; b.accum = iw.accum;
   b.out_color = out_color; b.out_invdepth = out_invdepth;
   H3_CUDA(launch_blend_fwd(b, s));
@@ -314,7 +323,7 @@ int h3dgs_backward(const H3dgsView* view, const H3dgsGaussians* g, const int32_t
   if (workspace_bytes < h3dgs_backward_workspace_bytes(P)) return fail(H3DGS_ENOSPACE, "backward workspace too small");
 
   GeomWs gw = GeomWs::make(const_cast<void*>(geom), P);
-  BinWs bw = BinWs::make(const_cast<void*>(binning), R, W, H);
+  BinWs bw = BinWs::make(const_cast<void*>(binning), R, 1, W, H);   // the R-sized arrays do not depend on V
   ImageWs iw = ImageWs::make(const_cast<void*>(image), W, H);
   BwdWs ww = BwdWs::make(workspace, P);
   { ProfScope ps(K_MEMSET, s); H3_CUDA(cudaMemsetAsync(ww.grad, 0, sizeof(GradRec) * (size_t)P, s)); }
@@ -324,7 +333,7 @@ int h3dgs_backward(const H3dgsView* view, const H3dgsGaussians* g, const int32_t
   b.W = W; b.H = H; b.grid_x = (W + TILE_X - 1) / TILE_X; b.grid_y = (H + TILE_Y - 1) / TILE_Y;
   b.P = P; b.skyboxnum = g->skyboxnum;
   b.interp = (g->ts != nullptr && g->kids != nullptr) ? 1 : 0;
-  b.ranges = iw.ranges; b.point_list = bw.vals[bw.sorted]; b.rec = gw.rec; b.bg = view->background;
+  b.ranges = iw.ranges; b.point_list = bw.tvals[bw.sorted]; b.rec = gw.rec; b.bg = view->background;
   b.final_T = iw.final_T; b.n_contrib = iw.n_contrib; b.accum = iw.accum;
   b.dL_dcolor = dL_dout_color; b.dL_dinvdepth = dL_dout_invdepth; b.grad = ww.grad;
   H3_CUDA(launch_blend_bwd(b, s));
@@ -363,9 +372,9 @@ int h3dgs_debug_view(int32_t P, int32_t W, int32_t H, int64_t R, const void* geo
     out->tile_rects = reinterpret_cast<const uint16_t*>(gw.tile_rect);
   }
   if (binning && R > 0) {
-    BinWs bw = BinWs::make(const_cast<void*>(binning), R, W, H);
-    out->point_list_keys = reinterpret_cast<const uint64_t*>(bw.keys[bw.sorted]);
-    out->point_list = bw.vals[bw.sorted];
+    BinWs bw = BinWs::make(const_cast<void*>(binning), R, 1, W, H);
+    out->point_list_keys = reinterpret_cast<const uint64_t*>(bw.keys64);
+    out->point_list = bw.tvals[bw.sorted];
   }
   if (image) {
     ImageWs iw = ImageWs::make(const_cast<void*>(image), W, H);

@@ -1,8 +1,11 @@
-// Instance emission ((tile, depth) keys + slot values) and per-tile range detection.
+// Binning: visible-slot compaction, ordered instance emission and per-tile range detection.
 // Replaces duplicateWithKeys and identifyTileRanges (HR/cuda_rasterizer/rasterizer_impl.cu:70-142).
-// Emission order within a slot is row-major over its tile rectangle and slots are laid out by the
-// inclusive scan, so the unsorted arrays are element-for-element those of the reference; the stable
-// sort that follows therefore yields identical sorted lists.
+//
+// The reference emits (tile << 32 | depth, slot) pairs in slot order and sorts all R of them on 45 bits.
+// Here the V visible slots are first put in (depth, slot) order (a 32-bit sort over V << R items,
+// radix_sort.cu), instances are emitted in THAT order -- row-major over each slot's tile rectangle, as
+// the reference does -- and then stably partitioned by tile id only.  Within a tile the list is therefore
+// ordered by (depth bits, slot), which is exactly what the reference's stable sort of the full keys yields.
 #include "common.cuh"
 
 namespace h3dgs {
@@ -11,29 +14,53 @@ namespace {
 
 constexpr int EMIT_SERIAL_MAX = 8;  // rectangles up to this many tiles are written by their own thread
 
+// slot -> compact position rank-1; also the four 8-bit digit histograms of the depth keys
+__global__ void __launch_bounds__(256) compact_visible_kernel(
+    int P, const uint32_t* __restrict__ tiles_touched, const uint32_t* __restrict__ rank,
+    const float* __restrict__ depth, uint32_t* __restrict__ dkeys, uint32_t* __restrict__ dvals,
+    uint32_t* __restrict__ hist) {
+  __shared__ uint32_t h[SORT_DEPTH_PASSES * SORT_RADIX];
+  for (int i = threadIdx.x; i < SORT_DEPTH_PASSES * SORT_RADIX; i += blockDim.x) h[i] = 0;
+  __syncthreads();
+  const int stride = gridDim.x * blockDim.x;
+  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < P; idx += stride) {
+    if (tiles_touched[idx] == 0) continue;
+    const uint32_t pos = rank[idx] - 1u;
+    const uint32_t k = __float_as_uint(depth[idx]);
+    dkeys[pos] = k;
+    dvals[pos] = (uint32_t)idx;
+#pragma unroll
+    for (int p = 0; p < SORT_DEPTH_PASSES; ++p) atomicAdd(&h[p * SORT_RADIX + ((k >> (8 * p)) & 0xffu)], 1u);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < SORT_DEPTH_PASSES * SORT_RADIX; i += blockDim.x) {
+    const uint32_t c = h[i];
+    if (c) atomicAdd(&hist[i], c);
+  }
+}
+
+// one thread per visible slot, in (depth, slot) order
+template <typename K>
 __global__ void __launch_bounds__(256) emit_instances_kernel(
-    int P, const int* __restrict__ radii, const float* __restrict__ depth,
-    const ushort4* __restrict__ rect, const uint32_t* __restrict__ offsets, int grid_x,
-    unsigned long long* __restrict__ keys, uint32_t* __restrict__ vals) {
-  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    long long V, const uint32_t* __restrict__ order, const uint32_t* __restrict__ soffs,
+    const ushort4* __restrict__ rect, int grid_x, K* __restrict__ keys, uint32_t* __restrict__ vals) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const int lane = threadIdx.x & 31;
-  uint32_t off = 0, dbits = 0;
+  uint32_t off = 0, slot = 0;
   int x0 = 0, y0 = 0, w = 0, n = 0;
-  if (idx < P && radii[idx] > 0) {
-    off = (idx == 0) ? 0u : offsets[idx - 1];
-    const ushort4 r = rect[idx];
+  if (i < V) {
+    slot = order[i];
+    off = (i == 0) ? 0u : soffs[i - 1];
+    const ushort4 r = rect[slot];
     x0 = r.x; y0 = r.y;
     w = (int)r.z - (int)r.x;
     n = w * ((int)r.w - (int)r.y);
-    dbits = __float_as_uint(depth[idx]);
   }
   if (n > 0 && n <= EMIT_SERIAL_MAX) {
     int x = 0, y = 0;
-    for (int i = 0; i < n; ++i) {
-      unsigned long long key = (unsigned long long)(uint32_t)((y0 + y) * grid_x + (x0 + x));
-      key = (key << 32) | dbits;
-      keys[off + i] = key;
-      vals[off + i] = (uint32_t)idx;
+    for (int j = 0; j < n; ++j) {
+      keys[off + j] = (K)((y0 + y) * grid_x + (x0 + x));
+      vals[off + j] = slot;
       if (++x == w) { x = 0; ++y; }
     }
   }
@@ -43,18 +70,15 @@ __global__ void __launch_bounds__(256) emit_instances_kernel(
     const int src = __ffs(big) - 1;
     big &= big - 1;
     const uint32_t o = __shfl_sync(0xffffffffu, off, src);
-    const uint32_t db = __shfl_sync(0xffffffffu, dbits, src);
+    const uint32_t id = __shfl_sync(0xffffffffu, slot, src);
     const int bx0 = __shfl_sync(0xffffffffu, x0, src);
     const int by0 = __shfl_sync(0xffffffffu, y0, src);
     const int bw = __shfl_sync(0xffffffffu, w, src);
     const int bn = __shfl_sync(0xffffffffu, n, src);
-    const uint32_t id = (uint32_t)(idx - lane + src);
-    for (int i = lane; i < bn; i += 32) {
-      const int y = i / bw, x = i - y * bw;
-      unsigned long long key = (unsigned long long)(uint32_t)((by0 + y) * grid_x + (bx0 + x));
-      key = (key << 32) | db;
-      keys[o + i] = key;
-      vals[o + i] = id;
+    for (int j = lane; j < bn; j += 32) {
+      const int y = j / bw, x = j - y * bw;
+      keys[o + j] = (K)((by0 + y) * grid_x + (bx0 + x));
+      vals[o + j] = id;
     }
   }
 }
@@ -81,12 +105,27 @@ __global__ void __launch_bounds__(256) tile_ranges_kernel(long long L,
 
 }  // namespace
 
-cudaError_t launch_emit_instances(int P, const int* radii, const GeomWs& g, int grid_x,
-                                  unsigned long long* keys, uint32_t* vals, cudaStream_t s) {
+cudaError_t launch_compact_visible(int P, const GeomWs& g, BinWs& b, cudaStream_t s) {
   if (P <= 0) return cudaSuccess;
+  int blocks = (P + 256 * 8 - 1) / (256 * 8);
+  if (blocks > 148 * 8) blocks = 148 * 8;
   ProfScope ps(K_EMIT, s);
-  emit_instances_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, radii, g.depth, g.tile_rect, g.offsets,
-                                                        grid_x, keys, vals);
+  compact_visible_kernel<<<blocks, 256, 0, s>>>(P, g.tiles_touched, g.offsets, g.depth, b.dkeys[0], b.dvals[0],
+                                                b.depth_hist);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_emit_instances(int64_t V, const GeomWs& g, BinWs& b, int grid_x, int key_bytes,
+                                  cudaStream_t s) {
+  if (V <= 0) return cudaSuccess;
+  const unsigned blocks = (unsigned)((V + 255) / 256);
+  ProfScope ps(K_EMIT, s);
+  if (key_bytes == 2)
+    emit_instances_kernel<uint16_t><<<blocks, 256, 0, s>>>(V, b.dvals[0], b.soffs, g.tile_rect, grid_x,
+                                                           reinterpret_cast<uint16_t*>(b.tkeys[0]), b.tvals[0]);
+  else
+    emit_instances_kernel<uint32_t><<<blocks, 256, 0, s>>>(V, b.dvals[0], b.soffs, g.tile_rect, grid_x,
+                                                           reinterpret_cast<uint32_t*>(b.tkeys[0]), b.tvals[0]);
   return cudaGetLastError();
 }
 

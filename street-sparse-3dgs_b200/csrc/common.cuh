@@ -50,10 +50,10 @@ struct GeomWs {
   float* cov3D;
   ushort4* tile_rect;
   uint32_t* tiles_touched;
-  uint32_t* offsets;
+  uint32_t* offsets;                // inclusive rank of the slot among the visible slots
   uint8_t* clamped;
   unsigned long long* scan_status;  // one per scan tile
-  uint32_t* counters;               // [0] dynamic tile id, [1] unused, [2..3] total (u64)
+  uint32_t* counters;               // [0] dynamic tile id, [2..3] V (u64), [4..5] R (u64)
   size_t bytes;
   static GeomWs make(void* base, int P) {
     GeomWs w;
@@ -95,22 +95,30 @@ struct ImageWs {
   }
 };
 
-// ---- onesweep radix sort geometry ----
-constexpr int SORT_RADIX_BITS_MAX = 9;
-constexpr int SORT_RADIX_MAX = 1 << SORT_RADIX_BITS_MAX;
+// ---- two-level instance sort geometry (radix_sort.cu / binning.cu) ----
+constexpr int SORT_RADIX_BITS = 8;
+constexpr int SORT_RADIX = 1 << SORT_RADIX_BITS;
 constexpr int SORT_THREADS = 512;
 constexpr int SORT_ITEMS = 12;
 constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;
-constexpr int SORT_MAX_PASSES = 8;
+constexpr int SORT_MAX_PASSES = 4;
+constexpr int SORT_DEPTH_PASSES = 4;   // 32 depth bits, 8 per pass
 
-struct SortPlan {
-  int num_passes;
+struct SortShifts {
   int shift[SORT_MAX_PASSES];
-  int bits[SORT_MAX_PASSES];
+  uint32_t mask[SORT_MAX_PASSES];
 };
 
-// Number of key bits that matter: 32 depth bits + ceil-ish log2 of the tile count, exactly as the
-// reference computes it (getHigherMsb, HR/cuda_rasterizer/rasterizer_impl.cu:35-50,349).
+struct SortPlan {
+  int tile_bits_total;             // bits of a tile id, as the reference counts them
+  int tile_passes;                 // ceil(tile_bits_total / 8)
+  int tile_shift[SORT_MAX_PASSES];
+  int tile_bits[SORT_MAX_PASSES];
+  int tile_key_bytes;              // 2 (tile ids fit 16 bits) or 4
+};
+
+// Number of key bits that matter above the 32 depth bits: the reference's getHigherMsb
+// (HR/cuda_rasterizer/rasterizer_impl.cu:35-50,349) of the tile count.
 inline uint32_t higher_msb(uint32_t n) {
   uint32_t msb = sizeof(n) * 4;
   uint32_t step = msb;
@@ -124,47 +132,72 @@ inline uint32_t higher_msb(uint32_t n) {
 
 inline SortPlan make_sort_plan(int W, int H) {
   uint32_t tiles = (uint32_t)((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
-  int total = 32 + (int)higher_msb(tiles);
   SortPlan pl;
-  pl.num_passes = (total + SORT_RADIX_BITS_MAX - 1) / SORT_RADIX_BITS_MAX;
-  int base = total / pl.num_passes, extra = total % pl.num_passes, s = 0;
-  for (int i = 0; i < pl.num_passes; ++i) {
-    pl.bits[i] = base + (i < extra ? 1 : 0);
-    pl.shift[i] = s;
-    s += pl.bits[i];
+  int total = (int)higher_msb(tiles);
+  if (total < 1) total = 1;
+  pl.tile_bits_total = total;
+  pl.tile_passes = (total + SORT_RADIX_BITS - 1) / SORT_RADIX_BITS;
+  const int base = total / pl.tile_passes, extra = total % pl.tile_passes;
+  int sft = 0;
+  for (int i = 0; i < SORT_MAX_PASSES; ++i) {
+    pl.tile_bits[i] = i < pl.tile_passes ? base + (i < extra ? 1 : 0) : 0;
+    pl.tile_shift[i] = sft;
+    sft += pl.tile_bits[i];
   }
+  pl.tile_key_bytes = total <= 16 ? 2 : 4;
   return pl;
 }
 
+// Binning workspace.  Everything sized by R (instances) comes first so that the backward pass can find the
+// sorted list knowing R alone; the depth-sort arrays sized by V (visible slots, V <= R) follow.
 struct BinWs {
-  unsigned long long* keys[2];
-  uint32_t* vals[2];
-  uint32_t* hist;     // [SORT_MAX_PASSES][SORT_RADIX_MAX] exclusive-scanned digit bases
-  uint32_t* status;   // [num_passes][tiles][SORT_RADIX_MAX] look-back words
-  uint32_t* counters; // [SORT_MAX_PASSES] dynamic tile ids
-  size_t status_words;
-  size_t zero_bytes;  // hist..counters are contiguous: one memset
-  char* zero_base;
-  int sorted;         // index (0/1) of the buffer holding the sorted result
+  void* tkeys[2];               // tile ids of the emitted instances (u16 or u32), double buffered
+  uint32_t* tvals[2];           // slot of each instance, double buffered; tvals[sorted] is point_list
+  unsigned long long* keys64;   // point_list_keys: (tile << 32) | depth bits, sorted
+  uint32_t* dkeys[2];           // depth bits of the visible slots, double buffered
+  uint32_t* dvals[2];           // visible slots; dvals[0] ends up in (depth, slot) order
+  uint32_t* soffs;              // inclusive scan of tiles_touched in that order
+  unsigned long long* scan_status;
+  uint32_t* scan_counters;
+  char* zero_base;              // depth_hist .. counters are contiguous: one memset
+  size_t zero_bytes;
+  uint32_t* depth_hist;         // [SORT_DEPTH_PASSES][SORT_RADIX]
+  uint32_t* tile_hist;          // [SORT_MAX_PASSES][SORT_RADIX]
+  uint32_t* depth_status;       // [SORT_DEPTH_PASSES][tiles(V)][SORT_RADIX] look-back words
+  uint32_t* tile_status;        // [tile_passes][tiles(R)][SORT_RADIX]
+  uint32_t* counters;           // [0..3] depth passes, [8..11] tile passes: dynamic tile ids
+  int sorted;                   // index (0/1) of the tvals buffer holding point_list
   size_t bytes;
-  static BinWs make(void* base, int64_t R, int W, int H) {
+  static BinWs make(void* base, int64_t R, int64_t V, int W, int H) {
     BinWs w;
     SortPlan pl = make_sort_plan(W, H);
     char* p = reinterpret_cast<char*>(base);
     char* p0 = p;
-    size_t n = (size_t)(R > 0 ? R : 1);
-    size_t tiles = (n + SORT_TILE - 1) / SORT_TILE;
-    carve(p, w.keys[0], n);
-    carve(p, w.keys[1], n);
-    carve(p, w.vals[0], n);
-    carve(p, w.vals[1], n);
-    carve(p, w.hist, (size_t)SORT_MAX_PASSES * SORT_RADIX_MAX);
-    w.zero_base = reinterpret_cast<char*>(w.hist);
-    w.status_words = (size_t)pl.num_passes * tiles * SORT_RADIX_MAX;
-    carve(p, w.status, w.status_words);
-    carve(p, w.counters, 64);
+    const size_t n = (size_t)(R > 0 ? R : 1);
+    const size_t v = (size_t)(V > 0 ? V : 1);
+    const size_t tiles_r = (n + SORT_TILE - 1) / SORT_TILE, tiles_v = (v + SORT_TILE - 1) / SORT_TILE;
+    char* tk;
+    carve(p, tk, n * pl.tile_key_bytes); w.tkeys[0] = tk;
+    carve(p, tk, n * pl.tile_key_bytes); w.tkeys[1] = tk;
+    carve(p, w.tvals[0], n);
+    carve(p, w.tvals[1], n);
+    carve(p, w.keys64, n);
+    w.sorted = pl.tile_passes & 1;
+    // ---- V-sized part ----
+    carve(p, w.dkeys[0], v);
+    carve(p, w.dkeys[1], v);
+    carve(p, w.dvals[0], v);
+    carve(p, w.dvals[1], v);
+    carve(p, w.soffs, v);
+    carve(p, w.scan_status, (v + SCAN_TILE - 1) / SCAN_TILE + 1);
+    carve(p, w.scan_counters, 8);
+    carve(p, w.depth_hist, (size_t)SORT_DEPTH_PASSES * SORT_RADIX);
+    w.zero_base = reinterpret_cast<char*>(w.depth_hist);
+    carve(p, w.tile_hist, (size_t)SORT_MAX_PASSES * SORT_RADIX);
+    carve(p, w.depth_status, (size_t)SORT_DEPTH_PASSES * tiles_v * SORT_RADIX);
+    carve(p, w.tile_status, (size_t)pl.tile_passes * tiles_r * SORT_RADIX);
+    carve(p, w.counters, 16);
     w.zero_bytes = (size_t)(p - w.zero_base);
-    w.sorted = pl.num_passes & 1;
     w.bytes = (size_t)(p - p0) + 256;
     return w;
   }
@@ -230,11 +263,22 @@ cudaError_t launch_mark_visible(int P, const float* means, const float* view, co
 cudaError_t launch_scan_inclusive(const uint32_t* in, uint32_t* out, int n, unsigned long long* status,
                                   uint32_t* counters, cudaStream_t s);
 
-cudaError_t launch_emit_instances(int P, const int* radii, const GeomWs& g, int grid_x,
-                                  unsigned long long* keys, uint32_t* vals, cudaStream_t s);
+// rank (inclusive) of every visible slot among the visible ones; totals: counters[2..3] = V, counters[4..5] = R
+cudaError_t launch_scan_visible(const uint32_t* tiles_touched, uint32_t* rank, int n,
+                                unsigned long long* status, uint32_t* counters, cudaStream_t s);
+// inclusive scan of tiles_touched[order[i]], i < n
+cudaError_t launch_scan_gather(const uint32_t* tiles_touched, const uint32_t* order, uint32_t* out, int n,
+                               unsigned long long* status, uint32_t* counters, cudaStream_t s);
+
+// binning.cu: visible slots -> (depth bits, slot) pairs + depth digit histograms; ordered emission
+cudaError_t launch_compact_visible(int P, const GeomWs& g, BinWs& b, cudaStream_t s);
+cudaError_t launch_emit_instances(int64_t V, const GeomWs& g, BinWs& b, int grid_x, int key_bytes,
+                                  cudaStream_t s);
 cudaError_t launch_tile_ranges(int64_t R, const unsigned long long* keys, uint2* ranges, int tiles,
                                cudaStream_t s);
-cudaError_t launch_radix_sort(BinWs& b, int64_t R, const SortPlan& plan, cudaStream_t s);
+// radix_sort.cu
+cudaError_t launch_depth_sort(BinWs& b, int64_t V, cudaStream_t s);
+cudaError_t launch_tile_sort(BinWs& b, int64_t R, const SortPlan& plan, const float* depth, cudaStream_t s);
 
 struct BlendArgs {
   int W, H, grid_x, grid_y, P, skyboxnum;

@@ -1,53 +1,51 @@
-// Onesweep least-significant-digit radix sort of (u64 key, u32 value) pairs on the low `total` bits.
-// Replaces cub::DeviceRadixSort::SortPairs at HR/cuda_rasterizer/rasterizer_impl.cu:352-357.
+// Onesweep least-significant-digit radix sort passes used by the two-level instance sort.
 //
-// One global histogram pass (all digits at once), then one kernel per digit that ranks a 6144-pair
-// tile in shared memory, resolves its global offsets with a decoupled look-back over the previous
-// tiles' per-digit counts and scatters -- every pair is read and written exactly once per digit.
-// Digits are 9 bits wide (45 key bits at 1920x1080 -> 5 passes instead of the 6 an 8-bit digit
-// needs).  The sort is stable, so equal (tile, depth) keys keep emission order exactly as with CUB.
+// The reference sorts R (tile << 32 | depth) keys with cub::DeviceRadixSort::SortPairs
+// (HR/cuda_rasterizer/rasterizer_impl.cu:352-357): 45 key bits at 1920x1080, i.e. 6 (CUB, 8-bit digits)
+// sweeps over 12-byte pairs.  The same ordered list is produced here in two levels (see binning.cu):
+//   1. the V visible slots are sorted by depth (32-bit keys, 4 sweeps over V 8-byte pairs, V << R);
+//   2. instances are emitted in that order and stably partitioned by tile id alone: ceil(tile bits / 8)
+//      sweeps (2 at 1080p) over R 6-byte pairs; the last sweep writes the 64-bit key next to the slot id.
+// Equal (tile, depth) keys keep slot order in both levels, exactly as the stable CUB sort leaves them.
+//
+// One kernel per digit: a CTA ranks a 6144-element tile in shared memory, resolves its global offsets with a
+// decoupled look-back over the preceding tiles' per-digit counts and scatters; every element is read and
+// written once per digit.
 #include "common.cuh"
 
 namespace h3dgs {
 
 namespace {
 
-constexpr int RADIX = SORT_RADIX_MAX;
+constexpr int RADIX = SORT_RADIX;       // 256
 constexpr int WARPS = SORT_THREADS / 32;
 constexpr uint32_t ST_AGG = 1u << 30;
 constexpr uint32_t ST_INC = 2u << 30;
 constexpr uint32_t ST_VAL = (1u << 30) - 1;
 
-struct PlanDev {
-  int num_passes;
-  int shift[SORT_MAX_PASSES];
-  uint32_t mask[SORT_MAX_PASSES];
-};
-
-__global__ void __launch_bounds__(512) radix_hist_kernel(const unsigned long long* __restrict__ keys,
-                                                         long long n, PlanDev plan,
-                                                         uint32_t* __restrict__ hist) {
+// per-pass digit histograms of n keys: hist[p][d]
+template <typename K>
+__global__ void __launch_bounds__(512) digit_hist_kernel(const K* __restrict__ keys, long long n, int passes,
+                                                         SortShifts sh, uint32_t* __restrict__ hist) {
   __shared__ uint32_t h[SORT_MAX_PASSES * RADIX];
-  for (int i = threadIdx.x; i < plan.num_passes * RADIX; i += blockDim.x) h[i] = 0;
+  for (int i = threadIdx.x; i < passes * RADIX; i += blockDim.x) h[i] = 0;
   __syncthreads();
   const long long stride = (long long)gridDim.x * blockDim.x;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-    const unsigned long long k = keys[i];
+    const uint32_t k = (uint32_t)keys[i];
 #pragma unroll
-    for (int p = 0; p < SORT_MAX_PASSES; ++p) {
-      if (p < plan.num_passes)
-        atomicAdd(&h[p * RADIX + (uint32_t)((k >> plan.shift[p]) & plan.mask[p])], 1u);
-    }
+    for (int p = 0; p < SORT_MAX_PASSES; ++p)
+      if (p < passes) atomicAdd(&h[p * RADIX + ((k >> sh.shift[p]) & sh.mask[p])], 1u);
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < plan.num_passes * RADIX; i += blockDim.x) {
+  for (int i = threadIdx.x; i < passes * RADIX; i += blockDim.x) {
     const uint32_t c = h[i];
     if (c) atomicAdd(&hist[i], c);
   }
 }
 
-// exclusive scan of each pass' 512-bin histogram, in place (one block per pass)
-__global__ void __launch_bounds__(RADIX) radix_scan_hist_kernel(uint32_t* __restrict__ hist) {
+// exclusive scan of each pass' histogram, in place (one block of RADIX threads per pass)
+__global__ void __launch_bounds__(RADIX) scan_hist_kernel(uint32_t* __restrict__ hist) {
   __shared__ uint32_t s_w[RADIX / 32];
   uint32_t* h = hist + (size_t)blockIdx.x * RADIX;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -65,23 +63,27 @@ __global__ void __launch_bounds__(RADIX) radix_scan_hist_kernel(uint32_t* __rest
   h[threadIdx.x] = off + incl - c;
 }
 
+template <typename K>
 struct SweepSmem {
-  uint32_t cnt[WARPS][RADIX];           // per-warp digit counters -> exclusive warp offsets
-  unsigned long long keys[SORT_TILE];
+  uint32_t cnt[WARPS][RADIX];   // per-warp digit counters -> exclusive warp offsets
   uint32_t vals[SORT_TILE];
-  uint32_t bin_start[RADIX];            // start of each digit inside the tile
-  uint32_t gbase[RADIX];                // global position of tile-local slot p with digit d: gbase[d] + p
-  uint32_t warp_sums[WARPS];
+  K keys[SORT_TILE];
+  uint32_t bin_start[RADIX];    // start of each digit inside the tile
+  uint32_t gbase[RADIX];        // global position of tile-local slot p with digit d: gbase[d] + p
+  uint32_t warp_sums[RADIX / 32];
   uint32_t tile;
 };
 
+// OUT 0: write (key, value).  OUT 1: write value only (last depth pass: only the order is needed).
+// OUT 2: write value and the 64-bit key (key << 32 | depth bits of the slot) -- last tile pass.
+template <typename K, int OUT>
 __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(
-    const unsigned long long* __restrict__ kin, unsigned long long* __restrict__ kout,
-    const uint32_t* __restrict__ vin, uint32_t* __restrict__ vout, long long n, int shift,
-    uint32_t mask, const uint32_t* __restrict__ digit_base, volatile uint32_t* status,
-    uint32_t* counter) {
+    const K* __restrict__ kin, K* __restrict__ kout, const uint32_t* __restrict__ vin,
+    uint32_t* __restrict__ vout, unsigned long long* __restrict__ kout64,
+    const uint32_t* __restrict__ depth_bits, long long n, int shift, uint32_t mask,
+    const uint32_t* __restrict__ digit_base, volatile uint32_t* status, uint32_t* counter) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  SweepSmem& sm = *reinterpret_cast<SweepSmem*>(smem_raw);
+  SweepSmem<K>& sm = *reinterpret_cast<SweepSmem<K>*>(smem_raw);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
   if (tid == 0) sm.tile = atomicAdd(counter, 1u);
@@ -93,19 +95,19 @@ __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(
   const int tile_valid = (int)(remaining < SORT_TILE ? remaining : SORT_TILE);
 
   // warp-striped load: element order in memory == (warp, item, lane) order == ranking order
-  unsigned long long key[SORT_ITEMS];
+  K key[SORT_ITEMS];
   const int wbase = warp * (32 * SORT_ITEMS) + lane;
 #pragma unroll
   for (int i = 0; i < SORT_ITEMS; ++i) {
     const int local = wbase + i * 32;
-    key[i] = (local < tile_valid) ? kin[tile_base + local] : ~0ull;
+    key[i] = (local < tile_valid) ? kin[tile_base + local] : (K)~(K)0;
   }
 
   uint32_t rank[SORT_ITEMS];
   const uint32_t lt = (1u << lane) - 1u;
 #pragma unroll
   for (int i = 0; i < SORT_ITEMS; ++i) {
-    const uint32_t d = (uint32_t)((key[i] >> shift) & mask);
+    const uint32_t d = ((uint32_t)key[i] >> shift) & mask;
     const uint32_t peers = __match_any_sync(0xffffffffu, d);
     const int leader = __ffs(peers) - 1;
     uint32_t prior = 0;
@@ -119,48 +121,47 @@ __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(
   }
   __syncthreads();
 
-  // one thread per digit: warp counts -> exclusive warp offsets, tile total, look-back
-  {
-    const int d = tid;  // SORT_THREADS == RADIX
+  // one thread per digit: warp counts -> exclusive warp offsets and the tile total
+  uint32_t total = 0, incl = 0;
+  if (tid < RADIX) {
     uint32_t run = 0;
 #pragma unroll
     for (int w = 0; w < WARPS; ++w) {
-      const uint32_t c = sm.cnt[w][d];
-      sm.cnt[w][d] = run;
+      const uint32_t c = sm.cnt[w][tid];
+      sm.cnt[w][tid] = run;
       run += c;
     }
-    const uint32_t total = run;
-    volatile uint32_t* my_status = status + (size_t)tile * RADIX;
-    my_status[d] = (tile == 0 ? ST_INC : ST_AGG) | total;
-
-    // exclusive scan of totals over digits -> position of each digit inside the tile
-    uint32_t incl = total;
+    total = run;
+    status[(size_t)tile * RADIX + tid] = (tile == 0 ? ST_INC : ST_AGG) | total;
+    incl = total;
 #pragma unroll
     for (int k = 1; k < 32; k <<= 1) {
       uint32_t o = __shfl_up_sync(0xffffffffu, incl, k);
       if (lane >= k) incl += o;
     }
     if (lane == 31) sm.warp_sums[warp] = incl;
-    __syncthreads();
+  }
+  __syncthreads();
+  if (tid < RADIX) {
     uint32_t off = 0;
     for (int w = 0; w < warp; ++w) off += sm.warp_sums[w];
     const uint32_t start = off + incl - total;
-    sm.bin_start[d] = start;
-
+    sm.bin_start[tid] = start;
+    // decoupled look-back over the preceding tiles
     uint32_t excl = 0;
     if (tile > 0) {
       long long t = (long long)tile - 1;
       while (true) {
         volatile uint32_t* ps = status + (size_t)t * RADIX;
         uint32_t w;
-        do { w = ps[d]; } while ((w >> 30) == 0);
+        do { w = ps[tid]; } while ((w >> 30) == 0);
         excl += w & ST_VAL;
         if ((w >> 30) == 2 || t == 0) break;
         --t;
       }
-      my_status[d] = ST_INC | ((excl + total) & ST_VAL);
+      status[(size_t)tile * RADIX + tid] = ST_INC | ((excl + total) & ST_VAL);
     }
-    sm.gbase[d] = digit_base[d] + excl - start;
+    sm.gbase[tid] = digit_base[tid] + excl - start;
   }
   __syncthreads();
 
@@ -168,7 +169,7 @@ __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(
 #pragma unroll
   for (int i = 0; i < SORT_ITEMS; ++i) {
     const int local = wbase + i * 32;
-    const uint32_t d = (uint32_t)((key[i] >> shift) & mask);
+    const uint32_t d = ((uint32_t)key[i] >> shift) & mask;
     const uint32_t pos = sm.bin_start[d] + sm.cnt[warp][d] + rank[i];
     sm.keys[pos] = key[i];
     sm.vals[pos] = (local < tile_valid) ? vin[tile_base + local] : 0u;
@@ -177,53 +178,109 @@ __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(
 
   // coalesced write-out; padding keys (all ones) sort to the very end of the tile
   for (int p = tid; p < tile_valid; p += SORT_THREADS) {
-    const unsigned long long k = sm.keys[p];
-    const uint32_t d = (uint32_t)((k >> shift) & mask);
+    const K k = sm.keys[p];
+    const uint32_t d = ((uint32_t)k >> shift) & mask;
     const uint32_t g = sm.gbase[d] + (uint32_t)p;
-    kout[g] = k;
-    vout[g] = sm.vals[p];
+    const uint32_t v = sm.vals[p];
+    if (OUT == 0) kout[g] = k;
+    vout[g] = v;
+    if (OUT == 2) kout64[g] = ((unsigned long long)k << 32) | (unsigned long long)__ldg(depth_bits + v);
   }
+}
+
+template <typename K, int OUT>
+cudaError_t launch_pass(const K* kin, K* kout, const uint32_t* vin, uint32_t* vout, unsigned long long* kout64,
+                        const uint32_t* depth_bits, long long n, int shift, uint32_t mask,
+                        const uint32_t* digit_base, uint32_t* status, uint32_t* counter, cudaStream_t s) {
+  auto k = onesweep_kernel<K, OUT>;
+  const size_t smem = sizeof(SweepSmem<K>);
+  static bool attr_done = false;   // one flag per template instantiation
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    attr_done = true;
+  }
+  const long long tiles = (n + SORT_TILE - 1) / SORT_TILE;
+  ProfScope ps(K_SORT_PASS, s);
+  k<<<(unsigned)tiles, SORT_THREADS, smem, s>>>(kin, kout, vin, vout, kout64, depth_bits, n, shift, mask,
+                                                digit_base, status, counter);
+  return cudaGetLastError();
+}
+
+template <typename K>
+cudaError_t launch_hist(const K* keys, long long n, int passes, const SortShifts& sh, uint32_t* hist,
+                        cudaStream_t s) {
+  int blocks = (int)((n + 512 * 16 - 1) / (512 * 16));
+  if (blocks > 148 * 4) blocks = 148 * 4;
+  if (blocks < 1) blocks = 1;
+  { ProfScope ps(K_SORT_HIST, s);
+    digit_hist_kernel<K><<<blocks, 512, 0, s>>>(keys, n, passes, sh, hist); }
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
+  { ProfScope ps(K_SORT_SCAN, s);
+    scan_hist_kernel<<<passes, RADIX, 0, s>>>(hist); }
+  return cudaGetLastError();
+}
+
+template <typename K>
+cudaError_t tile_sort(BinWs& b, int64_t R, const SortPlan& plan, const uint32_t* depth_bits, cudaStream_t s) {
+  K* keys[2] = {reinterpret_cast<K*>(b.tkeys[0]), reinterpret_cast<K*>(b.tkeys[1])};
+  SortShifts sh;
+  for (int p = 0; p < SORT_MAX_PASSES; ++p) {
+    sh.shift[p] = p < plan.tile_passes ? plan.tile_shift[p] : 0;
+    sh.mask[p] = p < plan.tile_passes ? ((1u << plan.tile_bits[p]) - 1u) : 0u;
+  }
+  cudaError_t e = launch_hist<K>(keys[0], R, plan.tile_passes, sh, b.tile_hist, s);
+  if (e != cudaSuccess) return e;
+  const size_t tiles = (size_t)((R + SORT_TILE - 1) / SORT_TILE);
+  for (int p = 0; p < plan.tile_passes; ++p) {
+    const int src = p & 1, dst = src ^ 1;
+    uint32_t* status = b.tile_status + (size_t)p * tiles * RADIX;
+    if (p + 1 < plan.tile_passes)
+      e = launch_pass<K, 0>(keys[src], keys[dst], b.tvals[src], b.tvals[dst], nullptr, nullptr, R, sh.shift[p],
+                            sh.mask[p], b.tile_hist + (size_t)p * RADIX, status, b.counters + 8 + p, s);
+    else
+      e = launch_pass<K, 2>(keys[src], keys[dst], b.tvals[src], b.tvals[dst], b.keys64, depth_bits, R,
+                            sh.shift[p], sh.mask[p], b.tile_hist + (size_t)p * RADIX, status,
+                            b.counters + 8 + p, s);
+    if (e != cudaSuccess) return e;
+  }
+  return cudaSuccess;
 }
 
 }  // namespace
 
-cudaError_t launch_radix_sort(BinWs& b, int64_t R, const SortPlan& plan, cudaStream_t s) {
-  if (R <= 0) return cudaSuccess;
-  static_assert(SORT_THREADS == RADIX, "one thread per digit");
-  static bool attr_done = false;
-  const size_t smem = sizeof(SweepSmem);
-  if (!attr_done) {
-    cudaError_t e = cudaFuncSetAttribute(onesweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int)smem);
-    if (e != cudaSuccess) return e;
-    attr_done = true;
-  }
-  cudaError_t e;
-  { ProfScope ps(K_MEMSET, s); e = cudaMemsetAsync(b.zero_base, 0, b.zero_bytes, s); }
-  if (e != cudaSuccess) return e;
-
-  PlanDev pd;
-  pd.num_passes = plan.num_passes;
-  for (int i = 0; i < SORT_MAX_PASSES; ++i) {
-    pd.shift[i] = i < plan.num_passes ? plan.shift[i] : 0;
-    pd.mask[i] = i < plan.num_passes ? ((1u << plan.bits[i]) - 1u) : 0u;
-  }
-  const long long tiles = (R + SORT_TILE - 1) / SORT_TILE;
-  int hist_blocks = (int)((R + 512 * 16 - 1) / (512 * 16));
-  if (hist_blocks > 148 * 4) hist_blocks = 148 * 4;
-  if (hist_blocks < 1) hist_blocks = 1;
-  { ProfScope ps(K_SORT_HIST, s);
-  radix_hist_kernel<<<hist_blocks, 512, 0, s>>>(b.keys[0], R, pd, b.hist); }
+// Sort the V compacted (depth bits, slot) pairs in b.dkeys[0] / b.dvals[0]; the digit histograms were
+// accumulated by the compaction kernel.  The sorted slot order ends up in b.dvals[0] (4 passes).
+cudaError_t launch_depth_sort(BinWs& b, int64_t V, cudaStream_t s) {
+  if (V <= 0) return cudaSuccess;
   { ProfScope ps(K_SORT_SCAN, s);
-  radix_scan_hist_kernel<<<plan.num_passes, RADIX, 0, s>>>(b.hist); }
-  for (int p = 0; p < plan.num_passes; ++p) {
+    scan_hist_kernel<<<SORT_DEPTH_PASSES, RADIX, 0, s>>>(b.depth_hist); }
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
+  const size_t tiles = (size_t)((V + SORT_TILE - 1) / SORT_TILE);
+  for (int p = 0; p < SORT_DEPTH_PASSES; ++p) {
     const int src = p & 1, dst = src ^ 1;
-    ProfScope ps(K_SORT_PASS, s);
-    onesweep_kernel<<<(unsigned)tiles, SORT_THREADS, smem, s>>>(
-        b.keys[src], b.keys[dst], b.vals[src], b.vals[dst], R, pd.shift[p], pd.mask[p],
-        b.hist + (size_t)p * RADIX, b.status + (size_t)p * tiles * RADIX, b.counters + p);
+    uint32_t* status = b.depth_status + (size_t)p * tiles * RADIX;
+    if (p + 1 < SORT_DEPTH_PASSES)
+      e = launch_pass<uint32_t, 0>(b.dkeys[src], b.dkeys[dst], b.dvals[src], b.dvals[dst], nullptr, nullptr, V,
+                                   8 * p, 0xffu, b.depth_hist + (size_t)p * RADIX, status, b.counters + p, s);
+    else
+      e = launch_pass<uint32_t, 1>(b.dkeys[src], b.dkeys[dst], b.dvals[src], b.dvals[dst], nullptr, nullptr, V,
+                                   8 * p, 0xffu, b.depth_hist + (size_t)p * RADIX, status, b.counters + p, s);
+    if (e != cudaSuccess) return e;
   }
-  return cudaGetLastError();
+  static_assert((SORT_DEPTH_PASSES & 1) == 0, "sorted order must land in dvals[0]");
+  return cudaSuccess;
+}
+
+// Stable partition of the R emitted (tile id, slot) pairs by tile id; writes point_list (b.tvals[b.sorted])
+// and point_list_keys (b.keys64).
+cudaError_t launch_tile_sort(BinWs& b, int64_t R, const SortPlan& plan, const float* depth, cudaStream_t s) {
+  if (R <= 0) return cudaSuccess;
+  const uint32_t* dbits = reinterpret_cast<const uint32_t*>(depth);
+  if (plan.tile_key_bytes == 2) return tile_sort<uint16_t>(b, R, plan, dbits, s);
+  return tile_sort<uint32_t>(b, R, plan, dbits, s);
 }
 
 }  // namespace h3dgs

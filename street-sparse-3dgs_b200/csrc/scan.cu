@@ -11,8 +11,11 @@ constexpr unsigned long long FLAG_AGG = 1ull << 62;
 constexpr unsigned long long FLAG_INC = 2ull << 62;
 constexpr unsigned long long VAL_MASK = (1ull << 62) - 1;
 
+// MODE 0: scan in[i].   MODE 1: scan (in[i] != 0) -- the rank of every visible slot -- and also add up in[i]
+// itself into counters[4..5] (the instance total).   MODE 2: scan in[idx[i]] (tile counts in depth order).
+template <int MODE>
 __global__ void __launch_bounds__(SCAN_THREADS) scan_lookback_kernel(
-    const uint32_t* __restrict__ in, uint32_t* __restrict__ out, int n,
+    const uint32_t* __restrict__ in, const uint32_t* __restrict__ idx, uint32_t* __restrict__ out, int n,
     volatile unsigned long long* status, uint32_t* counters) {
   __shared__ uint32_t s_tile;
   __shared__ unsigned long long s_warp[SCAN_THREADS / 32];
@@ -24,8 +27,9 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_lookback_kernel(
   const size_t base = (size_t)tile * SCAN_TILE + (size_t)threadIdx.x * SCAN_ITEMS;
 
   uint32_t v[SCAN_ITEMS];
+  const uint32_t* __restrict__ src = (MODE == 2) ? idx : in;
   if (base + SCAN_ITEMS <= (size_t)n) {
-    const uint4* p = reinterpret_cast<const uint4*>(in + base);
+    const uint4* p = reinterpret_cast<const uint4*>(src + base);
 #pragma unroll
     for (int i = 0; i < SCAN_ITEMS / 4; ++i) {
       uint4 x = __ldg(p + i);
@@ -33,7 +37,19 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_lookback_kernel(
     }
   } else {
 #pragma unroll
-    for (int i = 0; i < SCAN_ITEMS; ++i) v[i] = (base + i < (size_t)n) ? in[base + i] : 0u;
+    for (int i = 0; i < SCAN_ITEMS; ++i) v[i] = (base + i < (size_t)n) ? src[base + i] : 0u;
+  }
+  if (MODE == 2) {
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; ++i) v[i] = (base + i < (size_t)n) ? __ldg(in + v[i]) : 0u;
+  }
+  if (MODE == 1) {
+    unsigned long long raw = 0;
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; ++i) { raw += v[i]; v[i] = v[i] != 0u ? 1u : 0u; }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) raw += __shfl_xor_sync(0xffffffffu, raw, d);
+    if ((threadIdx.x & 31) == 0 && raw) atomicAdd(reinterpret_cast<unsigned long long*>(counters + 4), raw);
   }
   unsigned long long tsum = 0;
 #pragma unroll
@@ -115,8 +131,9 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_lookback_kernel(
 
 }  // namespace
 
-cudaError_t launch_scan_inclusive(const uint32_t* in, uint32_t* out, int n, unsigned long long* status,
-                                  uint32_t* counters, cudaStream_t s) {
+template <int MODE>
+static cudaError_t launch_scan(const uint32_t* in, const uint32_t* idx, uint32_t* out, int n,
+                               unsigned long long* status, uint32_t* counters, cudaStream_t s) {
   if (n <= 0) return cudaSuccess;
   const int tiles = (n + SCAN_TILE - 1) / SCAN_TILE;
   cudaError_t e = cudaMemsetAsync(status, 0, sizeof(unsigned long long) * (size_t)(tiles + 1), s);
@@ -124,8 +141,21 @@ cudaError_t launch_scan_inclusive(const uint32_t* in, uint32_t* out, int n, unsi
   e = cudaMemsetAsync(counters, 0, 8 * sizeof(uint32_t), s);
   if (e != cudaSuccess) return e;
   ProfScope ps(K_SCAN, s);
-  scan_lookback_kernel<<<tiles, SCAN_THREADS, 0, s>>>(in, out, n, status, counters);
+  scan_lookback_kernel<MODE><<<tiles, SCAN_THREADS, 0, s>>>(in, idx, out, n, status, counters);
   return cudaGetLastError();
+}
+
+cudaError_t launch_scan_inclusive(const uint32_t* in, uint32_t* out, int n, unsigned long long* status,
+                                  uint32_t* counters, cudaStream_t s) {
+  return launch_scan<0>(in, nullptr, out, n, status, counters, s);
+}
+cudaError_t launch_scan_visible(const uint32_t* tiles_touched, uint32_t* rank, int n,
+                                unsigned long long* status, uint32_t* counters, cudaStream_t s) {
+  return launch_scan<1>(tiles_touched, nullptr, rank, n, status, counters, s);
+}
+cudaError_t launch_scan_gather(const uint32_t* tiles_touched, const uint32_t* order, uint32_t* out, int n,
+                               unsigned long long* status, uint32_t* counters, cudaStream_t s) {
+  return launch_scan<2>(tiles_touched, order, out, n, status, counters, s);
 }
 
 }  // namespace h3dgs

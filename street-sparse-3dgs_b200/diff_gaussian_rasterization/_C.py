@@ -97,14 +97,14 @@ def rasterize_gaussians_ex(bg, indices, parent_indices, ts, kids, means3D, color
     geom = torch.empty((L.h3dgs_geom_bytes(P),), dtype=torch.uint8, device=dev)
     img = torch.empty((L.h3dgs_image_bytes(W, H),), dtype=torch.uint8, device=dev)
     stream = nat.stream_handle()
-    R = ctypes.c_int64(0)
+    R, V = ctypes.c_int64(0), ctypes.c_int64(0)
     nat.check(L.h3dgs_forward_preprocess(ctypes.byref(view), ctypes.byref(g), nat.ptr(radii), nat.ptr(geom),
-                                         geom.numel(), ctypes.byref(R), int(bool(debug)), stream),
+                                         geom.numel(), ctypes.byref(R), ctypes.byref(V), int(bool(debug)), stream),
               "h3dgs_forward_preprocess")
-    R = int(R.value)
-    binning = torch.empty((L.h3dgs_binning_bytes(R, W, H) if R > 0 else 0,), dtype=torch.uint8, device=dev)
+    R, V = int(R.value), int(V.value)
+    binning = torch.empty((L.h3dgs_binning_bytes(R, V, W, H) if R > 0 else 0,), dtype=torch.uint8, device=dev)
     nat.check(L.h3dgs_forward_render(ctypes.byref(view), ctypes.byref(g), nat.ptr(geom), nat.ptr(binning),
-                                     binning.numel(), nat.ptr(img), R, nat.ptr(out_color),
+                                     binning.numel(), nat.ptr(img), R, V, nat.ptr(out_color),
                                      nat.ptr(out_invdepth), int(bool(debug)), stream),
               "h3dgs_forward_render")
     return R, out_color, radii, geom, binning, img, out_invdepth

@@ -69,12 +69,12 @@ SIGNATURES = {
     "h3dgs_last_error": (c_char_p, []),
     "h3dgs_geom_bytes": (c_size_t, [c_int32]),
     "h3dgs_image_bytes": (c_size_t, [c_int32, c_int32]),
-    "h3dgs_binning_bytes": (c_size_t, [c_int64, c_int32, c_int32]),
+    "h3dgs_binning_bytes": (c_size_t, [c_int64, c_int64, c_int32, c_int32]),
     "h3dgs_backward_workspace_bytes": (c_size_t, [c_int32]),
     "h3dgs_forward_preprocess": (c_int, [POINTER(View), POINTER(Gaussians), c_void_p, c_void_p, c_size_t,
-                                          POINTER(c_int64), c_int, c_void_p]),
+                                          POINTER(c_int64), POINTER(c_int64), c_int, c_void_p]),
     "h3dgs_forward_render": (c_int, [POINTER(View), POINTER(Gaussians), c_void_p, c_void_p, c_size_t,
-                                      c_void_p, c_int64, c_void_p, c_void_p, c_int, c_void_p]),
+                                      c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_int, c_void_p]),
     "h3dgs_backward": (c_int, [POINTER(View), POINTER(Gaussians), c_void_p, c_void_p, c_void_p, c_void_p,
                                 c_int64, c_void_p, c_void_p, POINTER(Grads), c_void_p, c_size_t, c_int,
                                 c_void_p]),
@@ -125,7 +125,7 @@ def lib():
             fn = getattr(handle, name)
             fn.restype = res
             fn.argtypes = args
-        if handle.h3dgs_abi_version() != 2:
+        if handle.h3dgs_abi_version() != 3:
             raise H3dgsError("libh3dgs_b200.so ABI version mismatch")
         _lib = handle
     return _lib
