@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define H3DGS_ABI_VERSION 3
+#define H3DGS_ABI_VERSION 4
 
 #if defined(__GNUC__)
 #define H3DGS_API __attribute__((visibility("default")))
@@ -162,9 +162,25 @@ typedef struct H3dgsGrads {
   float* dL_drotations; /* [rows,4] */
   float* dL_dcov3D;     /* [rows,6]   (gradient of cov3D_precomp) */
   float* dL_dsh_rest;   /* [rows,M-1,3] when g->shs_rest is given (then dL_dsh is [rows,1,3]); else NULL */
+  /* Fused-cut mode only (ABI 4), both optional.  The per-store-row outputs are N-row tensors of which a
+   * render touches only the rows of its cut; zero-filling all N rows (4 GB at 17 M rows) costs more than
+   * the gradient kernel itself.  A caller that recycles its gradient tensors can instead
+   *   - set rows_prezeroed = 1: the per-row outputs already hold zeros, skip the zero fill, and
+   *   - pass dirty_rows (device int32 [1 + 2*P]): [0] receives the number n of store rows this call added
+   *     into, [1..n] their ids (duplicates possible) -- feed it to h3dgs_zero_rows before the next reuse. */
+  int32_t* dirty_rows;
+  int32_t rows_prezeroed;
 } H3dgsGrads;
 
 H3DGS_API size_t h3dgs_backward_workspace_bytes(int32_t P);
+
+/* Zero the rows listed in dirty_rows (layout above) of up to 8 row-major fp32 tensors [rows,width]. */
+typedef struct H3dgsRowTensor {
+  float* data;
+  int32_t width;
+} H3dgsRowTensor;
+H3DGS_API int h3dgs_zero_rows(const int32_t* dirty_rows, int64_t max_entries, const H3dgsRowTensor* tensors,
+                    int32_t num_tensors, h3dgs_stream_t stream);
 
 /*
  * Backward.  Replaces BACKWARD::render + computeCov2DCUDA + BACKWARD::preprocess

@@ -108,6 +108,32 @@ cudaError_t zero_fill(float* p, size_t n, cudaStream_t s) {
   return cudaGetLastError();
 }
 
+// side stream for work that overlaps the caller's stream (one per device, created on first use)
+struct SideStream {
+  cudaStream_t stream = nullptr;
+  cudaEvent_t fork = nullptr, join = nullptr;
+};
+SideStream* side_stream() {
+  static SideStream per_device[64];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+  SideStream& ss = per_device[dev];
+  if (!ss.stream) {
+    if (cudaStreamCreateWithFlags(&ss.stream, cudaStreamNonBlocking) != cudaSuccess) { ss.stream = nullptr; return nullptr; }
+    cudaEventCreateWithFlags(&ss.fork, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&ss.join, cudaEventDisableTiming);
+  }
+  return &ss;
+}
+bool overlap_zero() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = std::getenv("H3DGS_OVERLAP_ZERO");
+    v = (e && std::strcmp(e, "0") == 0) ? 0 : 1;
+  }
+  return v == 1;
+}
+
 size_t expand_ws_bytes(int N);
 cudaError_t run_expand_to_size(int N, float target_size, const int* nodes, const float* boxes,
                                const float* viewpoint, int* render_indices, int* parent_indices,
@@ -265,8 +291,9 @@ int h3dgs_forward_render(const H3dgsView* view, const H3dgsGaussians* g, void* g
   if ((rc = debug_sync(debug, s, "compact_visible"))) return rc;
   H3_CUDA(launch_depth_sort(bw, V, s));
   if ((rc = debug_sync(debug, s, "depth_sort"))) return rc;
-  H3_CUDA(launch_scan_gather(gw.tiles_touched, bw.dvals[0], bw.soffs, (int)V, bw.scan_status, bw.scan_counters, s));
-  H3_CUDA(launch_emit_instances(V, gw, bw, grid_x, plan.tile_key_bytes, s));
+  H3_CUDA(launch_scan_gather(gw.tiles_touched, bw.dvals[0], bw.soffs, (int)V, bw.chunk_first, bw.scan_status,
+                             bw.scan_counters, s));
+  H3_CUDA(launch_emit_instances(R, V, gw, bw, grid_x, plan.tile_key_bytes, s));
   if ((rc = debug_sync(debug, s, "emit_instances"))) return rc;
   H3_CUDA(launch_tile_sort(bw, R, plan, gw.depth, s));
   if ((rc = debug_sync(debug, s, "tile_sort"))) return rc;
@@ -298,11 +325,23 @@ int h3dgs_backward(const H3dgsView* view, const H3dgsGaussians* g, const int32_t
   const int M = g->sh_coeffs;
   const bool fused = g->render_indices != nullptr;
 
+  // The N-row zero fill of fused-cut mode is pure HBM write bandwidth (4 GB at 17 M rows) while the blend
+  // kernel that follows is issue-bound with ~1 % DRAM utilisation: run the fill on a side stream, forked
+  // here and joined before the scatter kernel, so that the two overlap (H3DGS_OVERLAP_ZERO=0 disables).
+  const bool busy = !(P == 0 || R <= 0);
+  SideStream* side = (busy && fused && !grads->rows_prezeroed && overlap_zero()) ? side_stream() : nullptr;
+  cudaStream_t zs = s;
+  if (side) {
+    H3_CUDA(cudaEventRecord(side->fork, s));
+    H3_CUDA(cudaStreamWaitEvent(side->stream, side->fork, 0));
+    zs = side->stream;
+  }
   auto zero = [&](float* p, size_t n) -> cudaError_t {
-    return zero_fill(p, n, s);
+    return zero_fill(p, n, zs);
   };
-  if (P == 0 || R <= 0 || fused) {
-    ProfScope ps(K_MEMSET, s);
+  if (grads->dirty_rows) H3_CUDA(cudaMemsetAsync(grads->dirty_rows, 0, sizeof(int32_t), s));
+  if (P == 0 || R <= 0 || (fused && !grads->rows_prezeroed)) {
+    ProfScope ps(K_MEMSET, zs);
     // fused-cut mode scatters into store rows; empty renders produce all-zero gradients
     H3_CUDA(zero(grads->dL_dmeans3D, rows * 3));
     const bool split = g->shs && g->shs_rest;
@@ -314,6 +353,7 @@ int h3dgs_backward(const H3dgsView* view, const H3dgsGaussians* g, const int32_t
     H3_CUDA(zero(grads->dL_drotations, rows * 4));
     H3_CUDA(zero(grads->dL_dcov3D, rows * 6));
   }
+  if (side) H3_CUDA(cudaEventRecord(side->join, side->stream));
   if (P == 0 || R <= 0) {
     H3_CUDA(zero(grads->dL_dmeans2D, (size_t)P * 3));
     return 0;
@@ -339,6 +379,7 @@ int h3dgs_backward(const H3dgsView* view, const H3dgsGaussians* g, const int32_t
   H3_CUDA(launch_blend_bwd(b, s));
   if ((rc = debug_sync(debug, s, "blend_bwd"))) return rc;
 
+  if (side) H3_CUDA(cudaStreamWaitEvent(s, side->join, 0));
   PreBwdArgs pb;
   pb.f = make_pre(view, g, const_cast<int*>(radii), const_cast<void*>(geom));
   pb.grad = ww.grad;
@@ -346,6 +387,48 @@ int h3dgs_backward(const H3dgsView* view, const H3dgsGaussians* g, const int32_t
   pb.out = *grads;
   H3_CUDA(launch_preprocess_bwd(pb, s));
   if ((rc = debug_sync(debug, s, "preprocess_bwd"))) return rc;
+  return 0;
+}
+
+// one warp per listed row
+__global__ void __launch_bounds__(256) zero_rows_kernel(const int32_t* __restrict__ dirty, long long max_entries,
+                                                        H3dgsRowTensor t0, H3dgsRowTensor t1, H3dgsRowTensor t2,
+                                                        H3dgsRowTensor t3, H3dgsRowTensor t4, H3dgsRowTensor t5,
+                                                        H3dgsRowTensor t6, H3dgsRowTensor t7) {
+  long long n = dirty[0];
+  if (n > max_entries) n = max_entries;
+  const int lane = threadIdx.x & 31;
+  const long long warps = (long long)gridDim.x * (blockDim.x >> 5);
+  const H3dgsRowTensor ts[8] = {t0, t1, t2, t3, t4, t5, t6, t7};
+  for (long long w = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); w < n; w += warps) {
+    const size_t row = (size_t)dirty[1 + w];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      if (ts[k].data == nullptr) continue;
+      float* p = ts[k].data + row * (size_t)ts[k].width;
+      for (int i = lane; i < ts[k].width; i += 32) p[i] = 0.f;
+    }
+  }
+}
+
+int h3dgs_zero_rows(const int32_t* dirty_rows, int64_t max_entries, const H3dgsRowTensor* tensors,
+                    int32_t num_tensors, h3dgs_stream_t stream) {
+  if (!dirty_rows || !tensors || num_tensors < 0 || num_tensors > 8 || max_entries < 0)
+    return fail(H3DGS_EINVAL, "h3dgs_zero_rows: bad arguments");
+  if (max_entries == 0 || num_tensors == 0) return 0;
+  H3dgsRowTensor t[8];
+  std::memset(t, 0, sizeof(t));
+  for (int i = 0; i < num_tensors; ++i) {
+    if (tensors[i].data && tensors[i].width <= 0) return fail(H3DGS_EINVAL, "h3dgs_zero_rows: width must be positive");
+    t[i] = tensors[i];
+  }
+  cudaStream_t s = (cudaStream_t)stream;
+  long long blocks = (max_entries + 7) / 8;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  ProfScope ps(K_MEMSET, s);
+  zero_rows_kernel<<<(unsigned)blocks, 256, 0, s>>>(dirty_rows, max_entries, t[0], t[1], t[2], t[3], t[4], t[5],
+                                                    t[6], t[7]);
+  H3_CUDA(cudaGetLastError());
   return 0;
 }
 

@@ -12,8 +12,6 @@ namespace h3dgs {
 
 namespace {
 
-constexpr int EMIT_SERIAL_MAX = 8;  // rectangles up to this many tiles are written by their own thread
-
 // slot -> compact position rank-1; also the four 8-bit digit histograms of the depth keys
 __global__ void __launch_bounds__(256) compact_visible_kernel(
     int P, const uint32_t* __restrict__ tiles_touched, const uint32_t* __restrict__ rank,
@@ -39,47 +37,41 @@ __global__ void __launch_bounds__(256) compact_visible_kernel(
   }
 }
 
-// one thread per visible slot, in (depth, slot) order
+// Ordered emission, load balanced over OUTPUT positions: CTA c writes instances [c*EMIT_CHUNK, (c+1)*EMIT_CHUNK).
+// The gathered scan (scan.cu, MODE 2) recorded for every chunk the first visible slot (in (depth, slot)
+// order) that reaches into it; the CTA stages the end offsets of its slots in shared memory and every thread
+// locates the slot of its output position by binary search there.  A slot covering 8000 tiles and 8000 slots
+// covering one tile each cost the same, and all stores are coalesced.
 template <typename K>
 __global__ void __launch_bounds__(256) emit_instances_kernel(
-    long long V, const uint32_t* __restrict__ order, const uint32_t* __restrict__ soffs,
-    const ushort4* __restrict__ rect, int grid_x, K* __restrict__ keys, uint32_t* __restrict__ vals) {
-  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  const int lane = threadIdx.x & 31;
-  uint32_t off = 0, slot = 0;
-  int x0 = 0, y0 = 0, w = 0, n = 0;
-  if (i < V) {
-    slot = order[i];
-    off = (i == 0) ? 0u : soffs[i - 1];
+    long long R, long long V, const uint32_t* __restrict__ order, const uint32_t* __restrict__ soffs,
+    const uint32_t* __restrict__ chunk_first, const ushort4* __restrict__ rect, int grid_x,
+    K* __restrict__ keys, uint32_t* __restrict__ vals) {
+  __shared__ uint32_t ends[EMIT_CHUNK + 1];
+  const long long c = blockIdx.x;
+  const long long cs = c * EMIT_CHUNK;
+  const long long ce = (cs + EMIT_CHUNK < R) ? cs + EMIT_CHUNK : R;
+  const uint32_t lo = chunk_first[c];
+  const uint32_t hi = (c + 1 < (long long)gridDim.x) ? chunk_first[c + 1] : (uint32_t)(V - 1);
+  const int ns = (int)(hi - lo + 1);   // <= EMIT_CHUNK + 1: every slot has at least one instance
+  for (int k = threadIdx.x; k < ns; k += blockDim.x) ends[k] = soffs[lo + k];
+  const uint32_t first_start = (lo == 0) ? 0u : soffs[lo - 1];
+  __syncthreads();
+  for (long long o = cs + threadIdx.x; o < ce; o += blockDim.x) {
+    const uint32_t pos = (uint32_t)o;
+    int a = 0, b = ns - 1;   // smallest k with ends[k] > pos
+    while (a < b) {
+      const int m = (a + b) >> 1;
+      if (ends[m] > pos) b = m; else a = m + 1;
+    }
+    const uint32_t start = (a == 0) ? first_start : ends[a - 1];
+    const uint32_t slot = __ldg(order + lo + a);
     const ushort4 r = rect[slot];
-    x0 = r.x; y0 = r.y;
-    w = (int)r.z - (int)r.x;
-    n = w * ((int)r.w - (int)r.y);
-  }
-  if (n > 0 && n <= EMIT_SERIAL_MAX) {
-    int x = 0, y = 0;
-    for (int j = 0; j < n; ++j) {
-      keys[off + j] = (K)((y0 + y) * grid_x + (x0 + x));
-      vals[off + j] = slot;
-      if (++x == w) { x = 0; ++y; }
-    }
-  }
-  // wide rectangles: the whole warp writes one rectangle at a time (coalesced, balanced)
-  unsigned big = __ballot_sync(0xffffffffu, n > EMIT_SERIAL_MAX);
-  while (big) {
-    const int src = __ffs(big) - 1;
-    big &= big - 1;
-    const uint32_t o = __shfl_sync(0xffffffffu, off, src);
-    const uint32_t id = __shfl_sync(0xffffffffu, slot, src);
-    const int bx0 = __shfl_sync(0xffffffffu, x0, src);
-    const int by0 = __shfl_sync(0xffffffffu, y0, src);
-    const int bw = __shfl_sync(0xffffffffu, w, src);
-    const int bn = __shfl_sync(0xffffffffu, n, src);
-    for (int j = lane; j < bn; j += 32) {
-      const int y = j / bw, x = j - y * bw;
-      keys[o + j] = (K)((by0 + y) * grid_x + (bx0 + x));
-      vals[o + j] = id;
-    }
+    const int w = (int)r.z - (int)r.x;
+    const int j = (int)(pos - start);
+    const int y = j / w, x = j - y * w;
+    keys[o] = (K)(((int)r.y + y) * grid_x + ((int)r.x + x));
+    vals[o] = slot;
   }
 }
 
@@ -115,17 +107,19 @@ cudaError_t launch_compact_visible(int P, const GeomWs& g, BinWs& b, cudaStream_
   return cudaGetLastError();
 }
 
-cudaError_t launch_emit_instances(int64_t V, const GeomWs& g, BinWs& b, int grid_x, int key_bytes,
+cudaError_t launch_emit_instances(int64_t R, int64_t V, const GeomWs& g, BinWs& b, int grid_x, int key_bytes,
                                   cudaStream_t s) {
-  if (V <= 0) return cudaSuccess;
-  const unsigned blocks = (unsigned)((V + 255) / 256);
+  if (V <= 0 || R <= 0) return cudaSuccess;
+  const unsigned blocks = (unsigned)((R + EMIT_CHUNK - 1) / EMIT_CHUNK);
   ProfScope ps(K_EMIT, s);
   if (key_bytes == 2)
-    emit_instances_kernel<uint16_t><<<blocks, 256, 0, s>>>(V, b.dvals[0], b.soffs, g.tile_rect, grid_x,
-                                                           reinterpret_cast<uint16_t*>(b.tkeys[0]), b.tvals[0]);
+    emit_instances_kernel<uint16_t><<<blocks, 256, 0, s>>>(R, V, b.dvals[0], b.soffs, b.chunk_first, g.tile_rect,
+                                                           grid_x, reinterpret_cast<uint16_t*>(b.tkeys[0]),
+                                                           b.tvals[0]);
   else
-    emit_instances_kernel<uint32_t><<<blocks, 256, 0, s>>>(V, b.dvals[0], b.soffs, g.tile_rect, grid_x,
-                                                           reinterpret_cast<uint32_t*>(b.tkeys[0]), b.tvals[0]);
+    emit_instances_kernel<uint32_t><<<blocks, 256, 0, s>>>(R, V, b.dvals[0], b.soffs, b.chunk_first, g.tile_rect,
+                                                           grid_x, reinterpret_cast<uint32_t*>(b.tkeys[0]),
+                                                           b.tvals[0]);
   return cudaGetLastError();
 }
 

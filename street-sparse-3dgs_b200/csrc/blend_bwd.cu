@@ -101,6 +101,18 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_bwd_kernel(const BlendArg
     }
   };
 
+  // which of the ten sums ends up complete in this lane after the transposed butterfly:
+  // group (lane bit 4) * 5 + (bit1 ? 2 : bit2 ? (bit3 ? 4 : 1) : (bit3 ? 3 : 0)); one depositor per sum
+  int red_dst = -1;
+  if ((lane & 1) == 0) {
+    const int b4 = (lane >> 4) & 1, b3 = (lane >> 3) & 1, b2 = (lane >> 2) & 1, b1 = (lane >> 1) & 1;
+    if (b1) {
+      if (!b2 && !b3) red_dst = b4 * 5 + 2;
+    } else {
+      red_dst = b4 * 5 + (b2 ? (b3 ? 4 : 1) : (b3 ? 3 : 0));
+    }
+    if (!DEPTH && red_dst == 9) red_dst = -1;
+  }
   float T = T_final, accum_u = 0.f, last_alpha = 0.f, last_u = 0.f;
   const float half_w = 0.5f * (float)a.W, half_h = 0.5f * (float)a.H;
 
@@ -153,11 +165,20 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_bwd_kernel(const BlendArg
             if (INTERP) {
               const float4 q3 = recs[jj].q3;
               if (q3.x != 1.0f) {
+                // (1-a)^(1/k) as the reference's backward evaluates it with precise pow (backward.cu:631),
+                // here exp2f(y log2f(x)) with the full-precision library functions: same value to a few ulp
+                // without the ~45-instruction slow path; (1-a)^(1/k - 1) = that / (1-a)   (backward.cu:714)
                 const float om = 1.0f - my_alpha;
-                const float kidsqrt_alpha = 1.0f - powf(om, q3.y);   // backward.cu:631
-                alpha = q3.x * my_alpha + (1.0f - q3.x) * kidsqrt_alpha;
-                // d alpha / d a = t - (1-a)^(1/k - 1) (t-1) / k            (backward.cu:714)
-                opac_mult = q3.x - __powf(om, q3.y - 1.0f) * (q3.x - 1.0f) * q3.y;
+                float pw = exp2f(q3.y * log2f(om));
+                alpha = q3.x * my_alpha + (1.0f - q3.x) * (1.0f - pw);
+                // the keep / skip decision below must be the reference's: within reach of the 1/255
+                // threshold (the two evaluations differ by < 1e-6) redo it with powf itself
+                if (fabsf(alpha - 1.0f / 255.0f) < 2e-5f) {
+                  pw = powf(om, q3.y);
+                  alpha = q3.x * my_alpha + (1.0f - q3.x) * (1.0f - pw);
+                }
+                // d alpha / d a = t - (1-a)^(1/k - 1) (t-1) / k
+                opac_mult = q3.x - __fdividef(pw, om) * (q3.x - 1.0f) * q3.y;
               }
             }
             if (!(alpha < 1.0f / 255.0f)) {
@@ -189,31 +210,23 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_bwd_kernel(const BlendArg
           }
         }
         if (__any_sync(0xffffffffu, contrib)) {
-#pragma unroll
-          for (int d = 16; d > 0; d >>= 1) {
-            v0 += __shfl_xor_sync(0xffffffffu, v0, d);
-            v1 += __shfl_xor_sync(0xffffffffu, v1, d);
-            v2 += __shfl_xor_sync(0xffffffffu, v2, d);
-            v3 += __shfl_xor_sync(0xffffffffu, v3, d);
-            v4 += __shfl_xor_sync(0xffffffffu, v4, d);
-            v5 += __shfl_xor_sync(0xffffffffu, v5, d);
-            v6 += __shfl_xor_sync(0xffffffffu, v6, d);
-            v7 += __shfl_xor_sync(0xffffffffu, v7, d);
-            v8 += __shfl_xor_sync(0xffffffffu, v8, d);
-            if (DEPTH) v9 += __shfl_xor_sync(0xffffffffu, v9, d);
-          }
-          // lane k deposits sum k: ten lanes, ten different banks
-          float mine = v0;
-          mine = lane == 1 ? v1 : mine;
-          mine = lane == 2 ? v2 : mine;
-          mine = lane == 3 ? v3 : mine;
-          mine = lane == 4 ? v4 : mine;
-          mine = lane == 5 ? v5 : mine;
-          mine = lane == 6 ? v6 : mine;
-          mine = lane == 7 ? v7 : mine;
-          mine = lane == 8 ? v8 : mine;
-          mine = lane == 9 ? v9 : mine;
-          if (lane < (DEPTH ? 10 : 9)) atomicAdd(&sm.acc[jj][lane], mine);
+          // Transposed butterfly: at every level a lane keeps half of its values and hands the other half
+          // to its partner, so the ten sums cost 5+3+2+1+1 = 12 shuffles instead of 10 x 5.
+          const bool h16 = lane & 16, h8 = lane & 8, h4 = lane & 4, h2 = lane & 2;
+          float r0 = (h16 ? v5 : v0) + __shfl_xor_sync(0xffffffffu, h16 ? v0 : v5, 16);
+          float r1 = (h16 ? v6 : v1) + __shfl_xor_sync(0xffffffffu, h16 ? v1 : v6, 16);
+          float r2 = (h16 ? v7 : v2) + __shfl_xor_sync(0xffffffffu, h16 ? v2 : v7, 16);
+          float r3 = (h16 ? v8 : v3) + __shfl_xor_sync(0xffffffffu, h16 ? v3 : v8, 16);
+          float r4 = (h16 ? v9 : v4) + __shfl_xor_sync(0xffffffffu, h16 ? v4 : v9, 16);
+          float s0 = (h8 ? r3 : r0) + __shfl_xor_sync(0xffffffffu, h8 ? r0 : r3, 8);
+          float s1 = (h8 ? r4 : r1) + __shfl_xor_sync(0xffffffffu, h8 ? r1 : r4, 8);
+          float s2 = r2 + __shfl_xor_sync(0xffffffffu, r2, 8);
+          float t0 = (h4 ? s1 : s0) + __shfl_xor_sync(0xffffffffu, h4 ? s0 : s1, 4);
+          float t1 = s2 + __shfl_xor_sync(0xffffffffu, s2, 4);
+          float u = (h2 ? t1 : t0) + __shfl_xor_sync(0xffffffffu, h2 ? t0 : t1, 2);
+          u += __shfl_xor_sync(0xffffffffu, u, 1);
+          // lane (b4 b3 b2 b1 0) now holds the complete sum number red_dst (see below); ten lanes deposit
+          if (red_dst >= 0) atomicAdd(&sm.acc[jj][red_dst], u);
         }
       }
     }

@@ -103,6 +103,7 @@ constexpr int SORT_ITEMS = 12;
 constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;
 constexpr int SORT_MAX_PASSES = 4;
 constexpr int SORT_DEPTH_PASSES = 4;   // 32 depth bits, 8 per pass
+constexpr int EMIT_CHUNK = 2048;       // instances written per CTA of the emission kernel
 
 struct SortShifts {
   int shift[SORT_MAX_PASSES];
@@ -157,6 +158,7 @@ struct BinWs {
   uint32_t* dkeys[2];           // depth bits of the visible slots, double buffered
   uint32_t* dvals[2];           // visible slots; dvals[0] ends up in (depth, slot) order
   uint32_t* soffs;              // inclusive scan of tiles_touched in that order
+  uint32_t* chunk_first;        // [ceil(R / EMIT_CHUNK)] first position (in that order) reaching into each chunk
   unsigned long long* scan_status;
   uint32_t* scan_counters;
   char* zero_base;              // depth_hist .. counters are contiguous: one memset
@@ -189,6 +191,7 @@ struct BinWs {
     carve(p, w.dvals[0], v);
     carve(p, w.dvals[1], v);
     carve(p, w.soffs, v);
+    carve(p, w.chunk_first, n / EMIT_CHUNK + 2);
     carve(p, w.scan_status, (v + SCAN_TILE - 1) / SCAN_TILE + 1);
     carve(p, w.scan_counters, 8);
     carve(p, w.depth_hist, (size_t)SORT_DEPTH_PASSES * SORT_RADIX);
@@ -268,11 +271,12 @@ cudaError_t launch_scan_visible(const uint32_t* tiles_touched, uint32_t* rank, i
                                 unsigned long long* status, uint32_t* counters, cudaStream_t s);
 // inclusive scan of tiles_touched[order[i]], i < n
 cudaError_t launch_scan_gather(const uint32_t* tiles_touched, const uint32_t* order, uint32_t* out, int n,
-                               unsigned long long* status, uint32_t* counters, cudaStream_t s);
+                               uint32_t* chunk_first, unsigned long long* status, uint32_t* counters,
+                               cudaStream_t s);
 
 // binning.cu: visible slots -> (depth bits, slot) pairs + depth digit histograms; ordered emission
 cudaError_t launch_compact_visible(int P, const GeomWs& g, BinWs& b, cudaStream_t s);
-cudaError_t launch_emit_instances(int64_t V, const GeomWs& g, BinWs& b, int grid_x, int key_bytes,
+cudaError_t launch_emit_instances(int64_t R, int64_t V, const GeomWs& g, BinWs& b, int grid_x, int key_bytes,
                                   cudaStream_t s);
 cudaError_t launch_tile_ranges(int64_t R, const unsigned long long* keys, uint2* ranges, int tiles,
                                cudaStream_t s);

@@ -125,6 +125,20 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdArgs b)
   }
   const size_t pr = (size_t)(p < 0 ? 0 : p);
 
+  if (FUSED && o.dirty_rows != nullptr) {
+    // remember which store rows this render adds into (child, and parent when interpolating)
+    // (two entries per visible slot, one warp-aggregated atomic; without a parent the child is listed twice)
+    const unsigned m = __activemask();
+    const int lane_id = threadIdx.x & 31;
+    const int leader = __ffs(m) - 1;
+    int base = 0;
+    if (lane_id == leader) base = atomicAdd(o.dirty_rows, 2 * __popc(m));
+    base = __shfl_sync(m, base, leader);
+    const int at = 1 + base + 2 * __popc(m & ((1u << lane_id) - 1u));
+    o.dirty_rows[at] = (int32_t)r;
+    o.dirty_rows[at + 1] = (int32_t)(lerp ? pr : r);
+  }
+
   const GradRec gr = b.grad[t_idx];
   const float dL_dmean2D_x = gr.v[0], dL_dmean2D_y = gr.v[1];
   const float3 dL_dconic = {gr.v[2], gr.v[3], gr.v[4]};

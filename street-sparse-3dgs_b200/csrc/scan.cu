@@ -11,12 +11,19 @@ constexpr unsigned long long FLAG_AGG = 1ull << 62;
 constexpr unsigned long long FLAG_INC = 2ull << 62;
 constexpr unsigned long long VAL_MASK = (1ull << 62) - 1;
 
+// element `index` owns outputs [prev, cur): it is the first one reaching into every chunk that starts there
+__device__ __forceinline__ void mark_chunks(uint32_t* __restrict__ chunk_first, unsigned long long prev,
+                                            unsigned long long cur, uint32_t index) {
+  for (unsigned long long c = (prev + EMIT_CHUNK - 1) / EMIT_CHUNK; c * EMIT_CHUNK < cur; ++c)
+    chunk_first[c] = index;
+}
+
 // MODE 0: scan in[i].   MODE 1: scan (in[i] != 0) -- the rank of every visible slot -- and also add up in[i]
 // itself into counters[4..5] (the instance total).   MODE 2: scan in[idx[i]] (tile counts in depth order).
 template <int MODE>
 __global__ void __launch_bounds__(SCAN_THREADS) scan_lookback_kernel(
     const uint32_t* __restrict__ in, const uint32_t* __restrict__ idx, uint32_t* __restrict__ out, int n,
-    volatile unsigned long long* status, uint32_t* counters) {
+    uint32_t* __restrict__ chunk_first, volatile unsigned long long* status, uint32_t* counters) {
   __shared__ uint32_t s_tile;
   __shared__ unsigned long long s_warp[SCAN_THREADS / 32];
   __shared__ unsigned long long s_prefix;
@@ -110,15 +117,25 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_lookback_kernel(
 #pragma unroll
     for (int i = 0; i < SCAN_ITEMS / 4; ++i) {
       uint4 x;
-      run += v[4 * i]; x.x = (uint32_t)run;
-      run += v[4 * i + 1]; x.y = (uint32_t)run;
-      run += v[4 * i + 2]; x.z = (uint32_t)run;
-      run += v[4 * i + 3]; x.w = (uint32_t)run;
+      if (MODE == 2) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          mark_chunks(chunk_first, run, run + v[4 * i + k], (uint32_t)(base + 4 * i + k));
+          run += v[4 * i + k];
+          (&x.x)[k] = (uint32_t)run;
+        }
+      } else {
+        run += v[4 * i]; x.x = (uint32_t)run;
+        run += v[4 * i + 1]; x.y = (uint32_t)run;
+        run += v[4 * i + 2]; x.z = (uint32_t)run;
+        run += v[4 * i + 3]; x.w = (uint32_t)run;
+      }
       q[i] = x;
     }
   } else {
 #pragma unroll
     for (int i = 0; i < SCAN_ITEMS; ++i) {
+      if (MODE == 2 && base + i < (size_t)n) mark_chunks(chunk_first, run, run + v[i], (uint32_t)(base + i));
       run += v[i];
       if (base + i < (size_t)n) out[base + i] = (uint32_t)run;
     }
@@ -133,7 +150,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_lookback_kernel(
 
 template <int MODE>
 static cudaError_t launch_scan(const uint32_t* in, const uint32_t* idx, uint32_t* out, int n,
-                               unsigned long long* status, uint32_t* counters, cudaStream_t s) {
+                               uint32_t* chunk_first, unsigned long long* status, uint32_t* counters, cudaStream_t s) {
   if (n <= 0) return cudaSuccess;
   const int tiles = (n + SCAN_TILE - 1) / SCAN_TILE;
   cudaError_t e = cudaMemsetAsync(status, 0, sizeof(unsigned long long) * (size_t)(tiles + 1), s);
@@ -141,21 +158,22 @@ static cudaError_t launch_scan(const uint32_t* in, const uint32_t* idx, uint32_t
   e = cudaMemsetAsync(counters, 0, 8 * sizeof(uint32_t), s);
   if (e != cudaSuccess) return e;
   ProfScope ps(K_SCAN, s);
-  scan_lookback_kernel<MODE><<<tiles, SCAN_THREADS, 0, s>>>(in, idx, out, n, status, counters);
+  scan_lookback_kernel<MODE><<<tiles, SCAN_THREADS, 0, s>>>(in, idx, out, n, chunk_first, status, counters);
   return cudaGetLastError();
 }
 
 cudaError_t launch_scan_inclusive(const uint32_t* in, uint32_t* out, int n, unsigned long long* status,
                                   uint32_t* counters, cudaStream_t s) {
-  return launch_scan<0>(in, nullptr, out, n, status, counters, s);
+  return launch_scan<0>(in, nullptr, out, n, nullptr, status, counters, s);
 }
 cudaError_t launch_scan_visible(const uint32_t* tiles_touched, uint32_t* rank, int n,
                                 unsigned long long* status, uint32_t* counters, cudaStream_t s) {
-  return launch_scan<1>(tiles_touched, nullptr, rank, n, status, counters, s);
+  return launch_scan<1>(tiles_touched, nullptr, rank, n, nullptr, status, counters, s);
 }
 cudaError_t launch_scan_gather(const uint32_t* tiles_touched, const uint32_t* order, uint32_t* out, int n,
-                               unsigned long long* status, uint32_t* counters, cudaStream_t s) {
-  return launch_scan<2>(tiles_touched, order, out, n, status, counters, s);
+                               uint32_t* chunk_first, unsigned long long* status, uint32_t* counters,
+                               cudaStream_t s) {
+  return launch_scan<2>(tiles_touched, order, out, n, chunk_first, status, counters, s);
 }
 
 }  // namespace h3dgs

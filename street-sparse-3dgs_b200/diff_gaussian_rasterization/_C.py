@@ -121,6 +121,93 @@ def rasterize_gaussians(bg, indices, parent_indices, ts, kids, means3D, colors, 
                                   prefiltered, debug, do_depth, 0)
 
 
+class _Lease:
+    """Per-row gradient tensors handed to one backward call; ``release`` turns them back into bare storages
+    so that autograd can take the tensors over without a copy."""
+
+    def __init__(self, entry, tensors, dirty):
+        self.entry, self.tensors, self.dirty = entry, tensors, dirty
+
+    def release(self):
+        e = self.entry
+        e["storages"] = {k: v.untyped_storage() for k, v in self.tensors.items()}
+        e["dirty"] = self.dirty
+        self.tensors = None
+
+
+class _GradArena:
+    """Recycles the N-row gradient tensors of fused-cut renders (render_post).
+
+    A render adds into the rows of its cut only (a few % of a 17 M-row store), but autograd needs dense
+    [N, ...] tensors: the reference zero-fills 4 GB per backward for them (HR/rasterize_points.cu:168-198 plus
+    the index_put scatters of its Python glue).  Here a gradient set is allocated and zero-filled once; the
+    backward kernels record which rows they added into (``H3dgsGrads.dirty_rows``); when every tensor of the
+    set has been dropped by its users (``optimizer.zero_grad(set_to_none=True)``, ``p.grad = None``) the set is
+    handed out again after ``h3dgs_zero_rows`` cleared just those rows.
+
+    Contract: while they hold such a gradient, callers may scale it or zero parts of it (train_post.py:171-182
+    zeroes skybox and anchor rows), but must not write non-zero values into rows the render did not touch.
+    Off by default: clearing scattered rows is partial-sector read-modify-write traffic, and at the density of
+    the benchmark cut (15 % of the store rows touched per render) it costs as much as the streaming 4 GB
+    fill, which the library now overlaps with the blend kernel instead.  It pays when a render touches a few
+    % of the rows or less.  ``H3DGS_GRAD_ARENA=1`` enables recycling; ``H3DGS_GRAD_ARENA=check`` additionally
+    verifies on every reuse that the recycled set is all zero."""
+
+    MAX_SETS = 4
+
+    def __init__(self):
+        self.entries = []
+
+    @staticmethod
+    def enabled():
+        import os
+        return os.environ.get("H3DGS_GRAD_ARENA", "0") in ("1", "check") and hasattr(torch._C, "_storage_Use_Count")
+
+    def release_all(self):
+        self.entries.clear()
+
+    def lease(self, dev, shapes, P):
+        import os
+        L = nat.lib()
+        key = (dev.index, tuple(sorted((k, v) for k, v in shapes.items() if v is not None)))
+        opts = dict(dtype=torch.float32, device=dev)
+        dirty = torch.empty((1 + 2 * P,), dtype=torch.int32, device=dev)
+        for e in self.entries:
+            if e["key"] != key or e["storages"] is None:
+                continue
+            if any(torch._C._storage_Use_Count(st._cdata) != 1 for st in e["storages"].values()):
+                continue   # somebody still holds (a view of) one of these gradients
+            tensors = {k: torch.empty(0, **opts).set_(st, 0, shapes[k]) for k, st in e["storages"].items()}
+            e["storages"] = None
+            names = list(tensors)
+            arr = (nat.RowTensor * len(names))()
+            for i, k in enumerate(names):
+                arr[i].data = tensors[k].data_ptr()
+                arr[i].width = tensors[k][0].numel()
+            nat.check(L.h3dgs_zero_rows(nat.ptr(e["dirty"]), e["dirty"].numel() - 1, arr, len(names),
+                                        nat.stream_handle()), "h3dgs_zero_rows")
+            if os.environ.get("H3DGS_GRAD_ARENA") == "check":
+                for k, v in tensors.items():
+                    if bool(v.any()):
+                        raise nat.H3dgsError(f"gradient arena: recycled '{k}' gradient is not all zero -- a caller "
+                                             "wrote into rows outside the render's cut")
+            return _Lease(e, tensors, dirty)
+        tensors = {k: torch.zeros(v, **opts) for k, v in shapes.items() if v is not None}
+        e = {"key": key, "storages": None, "dirty": None}
+        self.entries.append(e)
+        if len(self.entries) > self.MAX_SETS:
+            self.entries.pop(0)
+        return _Lease(e, tensors, dirty)
+
+
+_arena = _GradArena()
+
+
+def release_gradient_arena():
+    """Drop the recycled gradient sets (frees their device memory once the caller's references are gone)."""
+    _arena.release_all()
+
+
 def rasterize_gaussians_backward_ex(bg, indices, parent_indices, ts, kids, means3D, radii, colors,
                                     opacities, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,
                                     projmatrix, tan_fovx, tan_fovy, dL_dout_color, dL_dout_invdepth, sh,
@@ -137,18 +224,32 @@ def rasterize_gaussians_backward_ex(bg, indices, parent_indices, ts, kids, means
     split = not _null(sh_rest)
     opts = dict(dtype=torch.float32, device=dev)
     dL_dmeans2D = torch.empty((P, 3), **opts)
-    dL_dmeans3D = torch.empty((rows, 3), **opts)
-    dL_dopacity = torch.empty((rows, 1), **opts)
-    # only the gradients of inputs that exist are materialised; the others come back empty
-    dL_dsh = torch.empty((rows, 1 if split else M, 3), **opts) if not _null(sh) else torch.empty((0, 0, 3), **opts)
-    dL_dsh_rest = torch.empty((rows, M - 1, 3), **opts) if split else None
-    dL_dcolors = torch.empty((rows, NUM_CHANNELS), **opts) if not _null(colors) else torch.empty((0, 3), **opts)
-    dL_dscales = torch.empty((rows, 3), **opts) if not _null(scales) else torch.empty((0, 3), **opts)
-    dL_drot = torch.empty((rows, 4), **opts) if not _null(rotations) else torch.empty((0, 4), **opts)
-    dL_dcov3D = torch.empty((rows, 6), **opts) if not _null(cov3D_precomp) else torch.empty((0, 6), **opts)
+    # per-store-row gradients; only those of inputs that exist are materialised, the others come back empty
+    shapes = {"means3D": (rows, 3), "opacity": (rows, 1),
+              "sh": (rows, 1 if split else M, 3) if not _null(sh) else None,
+              "sh_rest": (rows, M - 1, 3) if split else None,
+              "colors": (rows, NUM_CHANNELS) if not _null(colors) else None,
+              "scales": (rows, 3) if not _null(scales) else None,
+              "rot": (rows, 4) if not _null(rotations) else None,
+              "cov3D": (rows, 6) if not _null(cov3D_precomp) else None}
+    fused = not _null(indices)
+    lease = _arena.lease(dev, shapes, P) if (fused and P > 0 and R > 0 and _arena.enabled()) else None
+    if lease is not None:
+        t = lease.tensors
+    else:
+        t = {k: torch.empty(v, **opts) for k, v in shapes.items() if v is not None}
+    empty = {"sh": (0, 0, 3), "colors": (0, 3), "scales": (0, 3), "rot": (0, 4), "cov3D": (0, 6)}
+    dL_dmeans3D, dL_dopacity = t["means3D"], t["opacity"]
+    dL_dsh = t["sh"] if "sh" in t else torch.empty(empty["sh"], **opts)
+    dL_dsh_rest = t.get("sh_rest")
+    dL_dcolors = t["colors"] if "colors" in t else torch.empty(empty["colors"], **opts)
+    dL_dscales = t["scales"] if "scales" in t else torch.empty(empty["scales"], **opts)
+    dL_drot = t["rot"] if "rot" in t else torch.empty(empty["rot"], **opts)
+    dL_dcov3D = t["cov3D"] if "cov3D" in t else torch.empty(empty["cov3D"], **opts)
     grads = nat.Grads(nat.ptr(dL_dmeans2D), nat.ptr(dL_dmeans3D), nat.ptr(dL_dsh), nat.ptr(dL_dcolors),
                       nat.ptr(dL_dopacity), nat.ptr(dL_dscales), nat.ptr(dL_drot), nat.ptr(dL_dcov3D),
-                      nat.ptr(dL_dsh_rest))
+                      nat.ptr(dL_dsh_rest), nat.ptr(lease.dirty) if lease is not None else None,
+                      1 if lease is not None else 0)
     ws = torch.empty((L.h3dgs_backward_workspace_bytes(P),), dtype=torch.uint8, device=dev)
     dcol = nat.as_f32(dL_dout_color, "dL_dout_color")
     ddep = nat.as_f32(dL_dout_invdepth, "dL_dout_invdepth")
@@ -157,6 +258,9 @@ def rasterize_gaussians_backward_ex(bg, indices, parent_indices, ts, kids, means
                                nat.ptr(ddep), ctypes.byref(grads), nat.ptr(ws), ws.numel(),
                                int(bool(debug)), nat.stream_handle()),
               "h3dgs_backward")
+    if lease is not None:
+        lease.release()
+        del lease, t
     if split:
         dL_dsh = (dL_dsh, dL_dsh_rest)
     return dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drot

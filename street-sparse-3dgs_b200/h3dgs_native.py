@@ -44,7 +44,12 @@ ACT_NONE, ACT_EXP, ACT_NORMALIZE, ACT_SIGMOID, ACT_ABS = 0, 1, 2, 3, 4
 class Grads(Structure):
     _fields_ = [("dL_dmeans2D", c_void_p), ("dL_dmeans3D", c_void_p), ("dL_dsh", c_void_p),
                 ("dL_dcolors", c_void_p), ("dL_dopacity", c_void_p), ("dL_dscales", c_void_p),
-                ("dL_drotations", c_void_p), ("dL_dcov3D", c_void_p), ("dL_dsh_rest", c_void_p)]
+                ("dL_drotations", c_void_p), ("dL_dcov3D", c_void_p), ("dL_dsh_rest", c_void_p),
+                ("dirty_rows", c_void_p), ("rows_prezeroed", c_int32)]
+
+
+class RowTensor(Structure):
+    _fields_ = [("data", c_void_p), ("width", c_int32)]
 
 
 class DebugView(Structure):
@@ -78,6 +83,7 @@ SIGNATURES = {
     "h3dgs_backward": (c_int, [POINTER(View), POINTER(Gaussians), c_void_p, c_void_p, c_void_p, c_void_p,
                                 c_int64, c_void_p, c_void_p, POINTER(Grads), c_void_p, c_size_t, c_int,
                                 c_void_p]),
+    "h3dgs_zero_rows": (c_int, [c_void_p, c_int64, POINTER(RowTensor), c_int32, c_void_p]),
     "h3dgs_mark_visible": (c_int, [c_int32, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "h3dgs_debug_view": (c_int, [c_int32, c_int32, c_int32, c_int64, c_void_p, c_void_p, c_void_p,
                                   POINTER(DebugView)]),
@@ -125,7 +131,7 @@ def lib():
             fn = getattr(handle, name)
             fn.restype = res
             fn.argtypes = args
-        if handle.h3dgs_abi_version() != 3:
+        if handle.h3dgs_abi_version() != 4:
             raise H3dgsError("libh3dgs_b200.so ABI version mismatch")
         _lib = handle
     return _lib

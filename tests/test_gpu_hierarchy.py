@@ -289,3 +289,56 @@ def test_hier_file_bytes_equal_reference_writer(tmp_path):
     if "WROTE" not in r.stdout:
         pytest.skip("reference write_hierarchy binding crashed: " + r.stderr[-300:])
     assert open(tmp_path / "ours.hier", "rb").read() == open(tmp_path / "ref.hier", "rb").read()
+
+
+def test_gradient_arena_recycles(monkeypatch):
+    """Fused-cut backward hands out recycled N-row gradient tensors: same storage on the next step once the
+    previous gradients were dropped, only the rows of the current cut non-zero, values equal to a fresh
+    zero-filled run; a gradient still held by the caller is never recycled."""
+    import gaussian_hierarchy
+    import diff_gaussian_rasterization as dgr
+    monkeypatch.setenv("H3DGS_GRAD_ARENA", "check")
+    dgr._C.release_gradient_arena()
+    attrs = workload.build_scene(14, 300, 4, DEV)
+    n = attrs["means3D"].size(0)
+    model = workload.HierModel(attrs, 300)
+    bg = torch.zeros(3, device=DEV)
+    cams = [scenes.street_camera(640, 480, seed=i, device=DEV, yaw_deg=90.0 * i, x=-10.0 + 7 * i) for i in range(3)]
+    limit = workload.find_limit(gaussian_hierarchy._C, model, cams[0], 6000, DEV)
+
+    def step(cam):
+        cut = workload.Cut(n, DEV)
+        cut.compute(gaussian_hierarchy._C, model, cam, limit)
+        out = workload.ours_render_post(cam, model, bg, cut, do_depth=True)
+        (out["render"].sum() + out["depth"].sum()).backward()
+        touched = torch.zeros(n, dtype=torch.bool, device=DEV)
+        K = cut.count
+        touched[cut.render_indices[:K].long()] = True
+        touched[cut.parent_indices[:K][cut.parent_indices[:K] >= 0].long()] = True
+        touched[n - 300:] = True
+        return touched
+
+    ptrs, grads = [], []
+    for cam in cams:
+        for p in model.parameters():
+            p.grad = None
+        touched = step(cam)
+        ptrs.append([p.grad.data_ptr() for p in model.parameters()])
+        for p in model.parameters():
+            assert not bool(p.grad[~touched].any()), "stale rows in a recycled gradient"
+        grads.append([p.grad.clone() for p in model.parameters()])
+    assert ptrs[0] == ptrs[1] == ptrs[2], "gradient storage was not recycled"
+    # a gradient that is still referenced must not be reused
+    held = model._xyz.grad
+    for p in model.parameters():
+        p.grad = None
+    step(cams[0])
+    assert model._xyz.grad.data_ptr() != held.data_ptr()
+    # same numbers as with recycling switched off
+    monkeypatch.setenv("H3DGS_GRAD_ARENA", "0")
+    for p in model.parameters():
+        p.grad = None
+    step(cams[2])
+    for p, ref in zip(model.parameters(), grads[2]):
+        assert util.relerr(p.grad, ref) <= 1e-5
+    dgr._C.release_gradient_arena()
