@@ -329,7 +329,8 @@ int h3dgs_backward(const H3dgsView* view, const H3dgsGaussians* g, const int32_t
   // kernel that follows is issue-bound with ~1 % DRAM utilisation: run the fill on a side stream, forked
   // here and joined before the scatter kernel, so that the two overlap (H3DGS_OVERLAP_ZERO=0 disables).
   const bool busy = !(P == 0 || R <= 0);
-  SideStream* side = (busy && fused && !grads->rows_prezeroed && overlap_zero()) ? side_stream() : nullptr;
+  // (not while per-kernel timing is on: overlapped kernels would be charged each other's time)
+  SideStream* side = (busy && fused && !grads->rows_prezeroed && overlap_zero() && !g_prof.on) ? side_stream() : nullptr;
   cudaStream_t zs = s;
   if (side) {
     H3_CUDA(cudaEventRecord(side->fork, s));

@@ -143,7 +143,7 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_bwd_kernel(const BlendArg
     for (int c = first & ~31; c < cnt; c += 32) {
       const int j = c + lane;
       bool hit = false;
-      if (j >= first && j < cnt) hit = block_hit(recs[j].q0, fx0, fy0);
+      if (j >= first && j < cnt) hit = block_hit(recs[j].q0, recs[j].q1, fx0, fy0);
       unsigned m = __ballot_sync(0xffffffffu, hit);
       while (m) {
         const int jj = c + __ffs(m) - 1;
@@ -184,7 +184,8 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_bwd_kernel(const BlendArg
             if (!(alpha < 1.0f / 255.0f)) {
               contrib = true;
               const float4 q2 = recs[jj].q2;
-              T = T / (1.f - alpha);
+              const float rcp_om = __frcp_rn(1.f - alpha);   // one reciprocal serves both divisions below
+              T = T * rcp_om;
               const float w = alpha * T;
               float u = q2.x * g0 + q2.y * g1 + q2.z * g2;
               if (DEPTH) u += q2.w * gD;
@@ -192,7 +193,7 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_bwd_kernel(const BlendArg
               last_u = u;
               float dL_dalpha = (u - accum_u) * T;
               last_alpha = alpha;
-              dL_dalpha += (-T_final / (1.f - alpha)) * bgdot;
+              dL_dalpha += (-T_final * rcp_om) * bgdot;
               if (test_alpha > 0.99f) dL_dalpha = 0.f;  // clamped alpha passes no gradient (backward.cu:619,693)
               const float dL_dG = con_o.w * dL_dalpha;
               const float gdx = G * dx, gdy = G * dy;

@@ -72,11 +72,24 @@ __device__ __forceinline__ void red_add_v2(float* addr, float a, float b) {
   asm volatile("red.global.add.v2.f32 [%0], {%1, %2};\n" ::"l"(addr), "f"(a), "f"(b) : "memory");
 }
 
-// Does the region where a Gaussian can reach alpha >= 1/255 (centre q0.xy, half extents q0.zw) touch the
-// pixel block [x0, x0+SUB_W-1] x [y0, y0+SUB_H-1]?
-__device__ __forceinline__ bool block_hit(const float4& q0, float x0, float y0) {
-  return (q0.x + q0.z >= x0) && (q0.x - q0.z <= x0 + (float)(SUB_W - 1)) && (q0.y + q0.w >= y0) &&
-         (q0.y - q0.w <= y0 + (float)(SUB_H - 1));
+// Can the Gaussian of record (q0, q1) reach alpha >= 1/255 anywhere in the pixel block
+// [x0, x0+SUB_W-1] x [y0, y0+SUB_H-1]?  alpha >= 1/255  <=>  a dx^2 + 2 b dx dy + c dy^2 <= 2 ln(255 o) = q0.z
+// (preprocess stores that bound with a small safety margin, +inf for "never cull", negative for "never
+// visible").  The left side is minimised over the block exactly: the minimiser of a convex quadratic over a
+// rectangle that does not contain its centre lies on an edge facing the centre, so it is the smaller of the
+// two one-dimensional minima on the vertical line x = nearest x and on the horizontal line y = nearest y.
+// One lane runs this for one list entry on behalf of its whole warp, so it costs ~1 instruction per pair.
+__device__ __forceinline__ bool block_hit(const float4& q0, const float4& q1, float x0, float y0) {
+  const float X0 = x0 - q0.x, X1 = X0 + (float)(SUB_W - 1);
+  const float Y0 = y0 - q0.y, Y1 = Y0 + (float)(SUB_H - 1);
+  const float dxn = fmaxf(X0, fminf(0.0f, X1));   // nearest block point, per axis (0 when the centre is inside)
+  const float dyn = fmaxf(Y0, fminf(0.0f, Y1));
+  const float a = q1.x, b = q1.y, c = q1.z;
+  const float dys = fmaxf(Y0, fminf(__fdividef(-b * dxn, c), Y1));   // best dy on the line dx = dxn
+  const float dxs = fmaxf(X0, fminf(__fdividef(-b * dyn, a), X1));   // best dx on the line dy = dyn
+  const float qa = a * dxn * dxn + 2.0f * b * dxn * dys + c * dys * dys;
+  const float qb = a * dxs * dxs + 2.0f * b * dxs * dyn + c * dyn * dyn;
+  return !(fminf(qa, qb) > q0.z);   // NaN anywhere -> keep the entry, the blend itself decides
 }
 
 }  // namespace h3dgs

@@ -100,7 +100,7 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_fwd_kernel(const BlendArg
       for (int c = 0; c < cnt; c += 32) {
         const int j = c + lane;
         bool hit = false;
-        if (j < cnt) hit = block_hit(recs[j].q0, fx0, fy0);
+        if (j < cnt) hit = block_hit(recs[j].q0, recs[j].q1, fx0, fy0);
         unsigned m = __ballot_sync(0xffffffffu, hit);
         while (m) {
           const int jj = c + __ffs(m) - 1;

@@ -12,7 +12,7 @@ constexpr int TILE_Y = 16;
 constexpr int TILE_PIX = TILE_X * TILE_Y;
 
 // Per-slot record written by preprocess and staged into shared memory by the blend kernels.
-//   q0 = (pixel x, pixel y, cull half-extent x, cull half-extent y)
+//   q0 = (pixel x, pixel y, 2 ln(255 opacity) with margin: bound of the conic form for alpha >= 1/255, 0)
 //   q1 = (conic a, conic b, conic c, opacity * AA-compensation)
 //   q2 = (r, g, b, 1/depth)
 //   q3 = (t, 1/kids, depth, h_convolution_scaling)

@@ -247,18 +247,15 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreArgs a) {
   if (FUSED && lerp) opacity = lerp_rn(t, opacity, omt, act_scalar(a.act_opac, __ldg(a.opac + pr)));
   const float op = opacity * h_convolution_scaling;
 
-  // Conservative half-extents of the region where this Gaussian can reach alpha >= 1/255:
-  // a dx^2 + 2b dx dy + c dy^2 <= 2 ln(255 op)  =>  |dx| <= sqrt(2 ln(255 op) cov_xx), same for y.
-  float cex = -1e30f, cey = -1e30f;
+  // Bound of the quadratic form inside which this Gaussian can reach alpha >= 1/255:
+  // o exp(-q/2) >= 1/255  <=>  q = a dx^2 + 2 b dx dy + c dy^2 <= 2 ln(255 o); kept with a safety margin far
+  // above the rounding of either side, so the blend kernels' block test (blend_common.cuh) only ever drops
+  // pairs the reference would reject at its alpha < 1/255 test.
+  float qmax = -1.0f;                       // opacity below 1/255: contributes nowhere
   {
-    float l = 2.0f * logf(255.0f * op);
-    if (l > 0.0f) {
-      l = l * 1.002f + 0.002f;
-      cex = sqrtf(l * cov.x) * 1.001f + 0.02f;
-      cey = sqrtf(l * cov.z) * 1.001f + 0.02f;
-    } else if (!(op < 1.0f / 255.0f)) {
-      cex = 1e30f; cey = 1e30f;  // NaN / inf opacity: never cull, let the blend decide
-    }
+    const float l = 2.0f * logf(255.0f * op);
+    if (l > 0.0f) qmax = l * 1.002f + 0.002f;
+    else if (!(op < 1.0f / 255.0f)) qmax = __int_as_float(0x7f800000);   // NaN / inf opacity: never cull
   }
 
   // per-slot interpolation terms of the blend (forward.cu:510-511); slot-indexed arrays
@@ -269,7 +266,7 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreArgs a) {
   }
 
   Rec rec;
-  rec.q0 = make_float4(point_image.x, point_image.y, cex, cey);
+  rec.q0 = make_float4(point_image.x, point_image.y, qmax, 0.0f);
   rec.q1 = make_float4(conic.x, conic.y, conic.z, op);
   rec.q2 = make_float4(rgb.x, rgb.y, rgb.z, 1 / p_view.z);
   rec.q3 = make_float4(bt, binvk, p_view.z, h_convolution_scaling);

