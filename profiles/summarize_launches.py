@@ -16,7 +16,12 @@ def main(path):
     if len(starts) < 2:
         print("fewer than two steps in the launch list")
         return
-    s, e = starts[-2], starts[-1]
+    # the last segment that holds a whole step (forward AND backward): the bench ends with forward-only passes
+    segs = [(a, b) for a, b in zip(starts[:-1], starts[1:]) if any("blend_bwd_kernel" in n for n in names[a:b])]
+    if not segs:
+        print("no forward+backward step in the launch list")
+        return
+    s, e = segs[-1]
     agg = collections.OrderedDict()
     total = 0.0
     for r in rows[s:e]:
