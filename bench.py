@@ -140,7 +140,7 @@ def main():
 
     W, H = args.width, args.height
     seed = rank if args.mode == "chunks" else 0
-    attrs = workload.build_scene(args.levels, args.skybox, seed, dev)
+    attrs = workload.build_scene(args.levels, args.skybox, seed, dev, free_corridor=True)
     n_store = attrs["means3D"].size(0)
     cams = workload.cameras(W, H, args.cameras, dev, seed=seed * 100)
     bg = torch.zeros(3, device=dev)
@@ -177,6 +177,7 @@ def main():
         if collect:
             stats.setdefault("P", []).append(cut.count + args.skybox)
             stats.setdefault("V", []).append(int(out["visibility_filter"].sum()))
+            stats.setdefault("grad_rows", []).append(int((model.parameters()[2].grad.flatten() != 0).sum()))
 
     def barrier():
         if world > 1:
@@ -231,9 +232,11 @@ def main():
         R_list = []
         import diff_gaussian_rasterization as dgr
         n_prof = len(cams)
+        prezero_was, dgr._C.PREZERO = dgr._C.PREZERO, False   # no side-stream overlap while timing kernels one by one
         for i in range(n_prof):
             resident_step(i)
         torch.cuda.synchronize()
+        dgr._C.PREZERO = prezero_was
         prof = nat.profile_read(reset=True)
         nat.lib().h3dgs_profile_enable(0)
         kernels = {k: {"ms_per_step": v[0] / n_prof, "launches_per_step": v[1] / n_prof}
@@ -246,7 +249,7 @@ def main():
         except Exception:
             pass
         peak_gbs = float(peaks.get("hbm_gbs", 6650.0))
-        stats["R"] = workload_R(cams, cuts, model, bg, args, render_post)
+        stats["R"], stats["n_contrib"] = workload_R(cams, cuts, model, bg, args, render_post)
         Rm = sum(stats["R"]) / len(stats["R"])
         Pm = sum(stats["P"]) / len(stats["P"])
         Vm = sum(stats["V"]) / len(stats["V"])
@@ -339,6 +342,10 @@ def main():
                        "image": [W, H], "hierarchy_leaves": 1 << args.levels, "store_rows": n_store,
                        "cut_target": args.target, "skybox": args.skybox, "cameras": len(cams),
                        "P_mean": avg(stats.get("P")), "V_mean": avg(stats.get("V")), "R_mean": avg(stats.get("R")),
+                       "mean_tile_list_length": (avg(stats["R"]) / (((W + 15) // 16) * ((H + 15) // 16))) if stats.get("R") else None,
+                       "mean_last_contributor_per_pixel": avg(stats.get("n_contrib")),
+                       "rows_with_gradient_mean": avg(stats.get("grad_rows")),
+                       "scene": "street corridor, drivable space free of Gaussians (harness/scenes.py free_corridor)",
                        "l2": "inputs larger than L2 (parameter store %.1f GB, cut cycles over %d cameras)" %
                              (n_store * 236 / 1e9, len(cams)),
                        "multi_gpu": "independent chunk per rank, no collective" if args.mode == "chunks" else "dp + NCCL allreduce"},
@@ -354,15 +361,18 @@ def main():
 
 
 def workload_R(cams, cuts, model, bg, args, render_post):
-    """num_rendered per camera, read from the forward pass (untimed)."""
+    """num_rendered and the mean per-pixel depth of blending (position of the last contributing list entry)
+    per camera, read from the forward pass (untimed)."""
     import torch
     import diff_gaussian_rasterization as dgr
-    Rs = []
+    Rs, nc = [], []
     orig = dgr._C.rasterize_gaussians_ex
 
     def spy(*a, **k):
         out = orig(*a, **k)
         Rs.append(int(out[0]))
+        dv = dgr._C.debug_view(out[2].numel(), args.width, args.height, int(out[0]), out[3], out[4], out[5])
+        nc.append(float(dv["n_contrib"].float().mean()))
         return out
 
     dgr._C.rasterize_gaussians_ex = spy
@@ -372,7 +382,7 @@ def workload_R(cams, cuts, model, bg, args, render_post):
                 render_post(c, model, bg, cut, do_depth=True)
     finally:
         dgr._C.rasterize_gaussians_ex = orig
-    return Rs
+    return Rs, nc
 
 
 if __name__ == "__main__":

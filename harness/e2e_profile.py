@@ -30,7 +30,7 @@ def main():
     else:
         gh = refglue.ref_gh()
         render_post = workload.ref_render_post
-    attrs = workload.build_scene(args.levels, args.skybox, 0, dev)
+    attrs = workload.build_scene(args.levels, args.skybox, 0, dev, free_corridor=True)
     n_store = attrs["means3D"].size(0)
     cams = workload.cameras(W, H, 4, dev, seed=0)
     bg = torch.zeros(3, device=dev)

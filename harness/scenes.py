@@ -13,7 +13,12 @@ import numpy as np
 import torch
 
 
-def street_gaussians(n, seed=0, device="cpu", extent=(100.0, 12.0, 15.0), sh_coeffs=16):
+def street_gaussians(n, seed=0, device="cpu", extent=(100.0, 12.0, 15.0), sh_coeffs=16, free_corridor=False):
+    """``free_corridor``: keep the drivable space empty, as a captured street is.  The 40 % of the points that
+    are not snapped to a surface would otherwise fill the air around the cameras with up-to-0.4 m blobs, and a
+    few thousand of them right in front of the lens occlude the whole scene (a render then back-propagates
+    into < 1 % of its visible Gaussians).  With the flag those that fall between the facades are moved into
+    the building slabs behind them (9.7 m <= |y| <= ``extent[1]``); x and z are kept."""
     g = torch.Generator(device="cpu").manual_seed(seed)
     ex, ey, ez = extent
     pos = torch.rand((n, 3), generator=g) * torch.tensor([2 * ex, 2 * ey, ez]) - torch.tensor([ex, ey, 0.0])
@@ -25,6 +30,11 @@ def street_gaussians(n, seed=0, device="cpu", extent=(100.0, 12.0, 15.0), sh_coe
     pos[left, 1] = -10.0 + jitter[left]
     pos[right, 1] = 10.0 + jitter[right]
     pos[road, 2] = jitter[road].abs()
+    if free_corridor:
+        air = (u >= 0.6) & (pos[:, 1].abs() < 9.7)
+        side = torch.where(pos[:, 1] < 0, -1.0, 1.0)
+        depth = (pos[:, 1].abs() / 9.7) * (ey - 9.7)          # uniform again inside the slab
+        pos[air, 1] = (side * (9.7 + depth))[air]
     log_scales = torch.rand((n, 3), generator=g) * (math.log(0.4) - math.log(0.01)) + math.log(0.01)
     rot = torch.randn((n, 4), generator=g)
     rot = rot / rot.norm(dim=1, keepdim=True)
@@ -118,7 +128,7 @@ def _preorder_index(level, j, levels):
     return idx
 
 
-def build_hierarchy(levels, seed=0, device="cpu", extent=(100.0, 12.0, 15.0), leaf=None):
+def build_hierarchy(levels, seed=0, device="cpu", extent=(100.0, 12.0, 15.0), leaf=None, free_corridor=False):
     """Balanced KD hierarchy over 2**levels leaves.
 
     Returns dict(means3D, log_scales, scales, rotations, opacities, shs) for all 2**(levels+1)-1
@@ -126,7 +136,7 @@ def build_hierarchy(levels, seed=0, device="cpu", extent=(100.0, 12.0, 15.0), le
     """
     n = 1 << levels
     if leaf is None:
-        leaf = street_gaussians(n, seed=seed, device=device, extent=extent)
+        leaf = street_gaussians(n, seed=seed, device=device, extent=extent, free_corridor=free_corridor)
     pos = leaf["means3D"]
     # median splits along the longest axis, level by level (one global sort per level)
     order = torch.arange(n, device=device)

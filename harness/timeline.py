@@ -31,7 +31,7 @@ def main():
     W, H = 1920, 1080
     import gaussian_hierarchy
     gh = gaussian_hierarchy._C
-    attrs = workload.build_scene(args.levels, args.skybox, 0, dev)
+    attrs = workload.build_scene(args.levels, args.skybox, 0, dev, free_corridor=True)
     n_store = attrs["means3D"].size(0)
     cams = workload.cameras(W, H, 4, dev, seed=0)
     bg = torch.zeros(3, device=dev)

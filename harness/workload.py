@@ -80,10 +80,11 @@ class ActivatedModel:
         return [self._xyz, self._f, self._o, self._s, self._r]
 
 
-def build_scene(levels, skybox, seed, device):
+def build_scene(levels, skybox, seed, device, free_corridor=False):
     """Hierarchy of 2**levels leaves with `skybox` skybox Gaussians appended at the END
-    (scene/gaussian_model.py:389-401)."""
-    h = scenes.build_hierarchy(levels, seed=seed, device=device)
+    (scene/gaussian_model.py:389-401).  ``free_corridor`` (the benchmark scene): no Gaussians floating in the
+    drivable space, see scenes.street_gaussians."""
+    h = scenes.build_hierarchy(levels, seed=seed, device=device, free_corridor=free_corridor)
     if skybox:
         sky = scenes.skybox_gaussians(skybox, seed=seed + 1, device=device)
         for k in ("means3D", "log_scales", "scales", "rotations", "opacities", "shs"):

@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define H3DGS_ABI_VERSION 4
+#define H3DGS_ABI_VERSION 5
 
 #if defined(__GNUC__)
 #define H3DGS_API __attribute__((visibility("default")))
@@ -142,11 +142,14 @@ H3DGS_API int h3dgs_forward_preprocess(const H3dgsView* view, const H3dgsGaussia
  * Replaces duplicateWithKeys + cub::DeviceRadixSort::SortPairs + identifyTileRanges + FORWARD::render
  * (rasterizer_impl.cu:336-390).  out_color is [3,H,W]; out_invdepth is [1,H,W] or NULL.
  * num_rendered == 0 only fills out_color with the background.
+ * pre_blend_event (a cudaEvent_t, or NULL) is recorded on `stream` right before the blend kernel: the point
+ * after which the forward stops using HBM bandwidth, where a caller can fork bandwidth-only side work
+ * (h3dgs_zero_fill of the gradient tensors the backward will add into) onto another stream.
  */
 H3DGS_API int h3dgs_forward_render(const H3dgsView* view, const H3dgsGaussians* g,
                          void* geom, void* binning, size_t binning_bytes, void* image,
                          int64_t num_rendered, int64_t num_visible, float* out_color, float* out_invdepth,
-                         int debug, h3dgs_stream_t stream);
+                         int debug, h3dgs_stream_t stream, void* pre_blend_event);
 
 /* Gradient outputs of the backward pass; any pointer may be NULL (that gradient is not produced).
  * Row counts: dL_dmeans2D is per slot [P,3]; every other tensor is per store row [store_rows, ...]
@@ -181,6 +184,18 @@ typedef struct H3dgsRowTensor {
 } H3dgsRowTensor;
 H3DGS_API int h3dgs_zero_rows(const int32_t* dirty_rows, int64_t max_entries, const H3dgsRowTensor* tensors,
                     int32_t num_tensors, h3dgs_stream_t stream);
+
+/* Zero-fill up to 8 fp32 arrays (data, count floats) with ONE launch of a deliberately small grid
+ * (ctas_per_sm resident CTAs per SM, 1..8; 0 = 2), so that the fill can share the SMs with an issue-bound
+ * kernel running on another stream (the blend kernels use ~1 % of the HBM bandwidth).  This is the zero
+ * fill of the reference's backward (torch::zeros x 9, rasterize_points.cu:168-198) taken off the critical
+ * path; pass the filled tensors to h3dgs_backward with rows_prezeroed = 1. */
+typedef struct H3dgsSpan {
+  float* data;
+  int64_t count;
+} H3dgsSpan;
+H3DGS_API int h3dgs_zero_fill(const H3dgsSpan* spans, int32_t num_spans, int32_t ctas_per_sm,
+                    h3dgs_stream_t stream);
 
 /*
  * Backward.  Replaces BACKWARD::render + computeCov2DCUDA + BACKWARD::preprocess

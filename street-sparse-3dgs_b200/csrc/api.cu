@@ -259,7 +259,7 @@ int h3dgs_forward_preprocess(const H3dgsView* view, const H3dgsGaussians* g, int
 
 int h3dgs_forward_render(const H3dgsView* view, const H3dgsGaussians* g, void* geom, void* binning,
                          size_t binning_bytes, void* image, int64_t R, int64_t V, float* out_color,
-                         float* out_invdepth, int debug, h3dgs_stream_t stream) {
+                         float* out_invdepth, int debug, h3dgs_stream_t stream, void* pre_blend_event) {
   int rc = check_scene(view, g);
   if (rc) return rc;
   if (!out_color) return fail(H3DGS_EINVAL, "out_color is required");
@@ -274,6 +274,7 @@ int h3dgs_forward_render(const H3dgsView* view, const H3dgsGaussians* g, void* g
       ImageWs iw = ImageWs::make(image, W, H);
       H3_CUDA(cudaMemsetAsync(iw.n_contrib, 0, plane * sizeof(uint32_t), s));
     }
+    if (pre_blend_event) H3_CUDA(cudaEventRecord((cudaEvent_t)pre_blend_event, s));
     return 0;
   }
   if (!geom || !binning || !image) return fail(H3DGS_EINVAL, "geom, binning and image are required");
@@ -307,6 +308,7 @@ int h3dgs_forward_render(const H3dgsView* view, const H3dgsGaussians* g, void* g
   b.ranges = iw.ranges; b.point_list = bw.tvals[bw.sorted]; b.rec = gw.rec; b.bg = view->background;
   b.final_T = iw.final_T; b.n_contrib = iw.n_contrib; b.accum = iw.accum;
   b.out_color = out_color; b.out_invdepth = out_invdepth;
+  if (pre_blend_event) H3_CUDA(cudaEventRecord((cudaEvent_t)pre_blend_event, s));
   H3_CUDA(launch_blend_fwd(b, s));
   if ((rc = debug_sync(debug, s, "blend_fwd"))) return rc;
   return 0;
@@ -429,6 +431,55 @@ int h3dgs_zero_rows(const int32_t* dirty_rows, int64_t max_entries, const H3dgsR
   ProfScope ps(K_MEMSET, s);
   zero_rows_kernel<<<(unsigned)blocks, 256, 0, s>>>(dirty_rows, max_entries, t[0], t[1], t[2], t[3], t[4], t[5],
                                                     t[6], t[7]);
+  H3_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// One launch zero-fills every span: grid-stride over 16-byte stores, spans walked one after the other.
+struct SpanPack {
+  H3dgsSpan sp[8];
+  int n;
+};
+__global__ void __launch_bounds__(256) fill_spans_kernel(const SpanPack pk) {
+  const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (int k = 0; k < pk.n; ++k) {
+    float* p = pk.sp[k].data;
+    const size_t n = (size_t)pk.sp[k].count;
+    const size_t head = ((16 - (reinterpret_cast<size_t>(p) & 15)) / 4) % 4;   // floats up to 16-byte alignment
+    if (tid < head && tid < n) p[tid] = 0.f;
+    if (n <= head) continue;
+    float4* q = reinterpret_cast<float4*>(p + head);
+    const size_t n4 = (n - head) / 4;
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    size_t i = tid;
+    for (; i + 3 * stride < n4; i += 4 * stride) {
+      q[i] = z; q[i + stride] = z; q[i + 2 * stride] = z; q[i + 3 * stride] = z;
+    }
+    for (; i < n4; i += stride) q[i] = z;
+    const size_t tail = head + n4 * 4;
+    if (tid < n - tail) p[tail + tid] = 0.f;
+  }
+}
+
+int h3dgs_zero_fill(const H3dgsSpan* spans, int32_t num_spans, int32_t ctas_per_sm, h3dgs_stream_t stream) {
+  if (num_spans < 0 || num_spans > 8 || (num_spans > 0 && !spans)) return fail(H3DGS_EINVAL, "h3dgs_zero_fill: 0..8 spans");
+  if (ctas_per_sm < 0 || ctas_per_sm > 8) return fail(H3DGS_EINVAL, "h3dgs_zero_fill: ctas_per_sm must be 0..8");
+  SpanPack pk;
+  pk.n = 0;
+  for (int i = 0; i < num_spans; ++i) {
+    if (spans[i].count < 0) return fail(H3DGS_EINVAL, "h3dgs_zero_fill: negative count");
+    if (!spans[i].data || spans[i].count == 0) continue;
+    if (reinterpret_cast<size_t>(spans[i].data) & 3) return fail(H3DGS_EINVAL, "h3dgs_zero_fill: unaligned span");
+    pk.sp[pk.n++] = spans[i];
+  }
+  if (pk.n == 0) return 0;
+  int dev = 0, sms = 148;
+  if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  cudaStream_t s = (cudaStream_t)stream;
+  g_prof.launches_total++;
+  ProfScope ps(K_MEMSET, s);
+  fill_spans_kernel<<<sms * (ctas_per_sm ? ctas_per_sm : 2), 256, 0, s>>>(pk);
   H3_CUDA(cudaGetLastError());
   return 0;
 }

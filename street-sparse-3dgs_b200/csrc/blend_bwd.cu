@@ -148,69 +148,74 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_bwd_kernel(const BlendArg
       while (m) {
         const int jj = c + __ffs(m) - 1;
         m &= m - 1;
-        float v0 = 0.f, v1 = 0.f, v2 = 0.f, v3 = 0.f, v4 = 0.f, v5 = 0.f, v6 = 0.f, v7 = 0.f,
-              v8 = 0.f, v9 = 0.f;
-        bool contrib = false;
-        if (nn - 1 - (base + jj) < last) {
-          const float4 q0 = recs[jj].q0;
-          const float4 con_o = recs[jj].q1;
-          const float dx = q0.x - pixx, dy = q0.y - pixy;
-          const float power = -0.5f * (con_o.x * dx * dx + con_o.z * dy * dy) - con_o.y * dx * dy;
-          if (!(power > 0.0f)) {
-            const float G = exp(power);
-            const float test_alpha = con_o.w * G;
-            const float my_alpha = min(0.99f, test_alpha);
-            float alpha = my_alpha;
-            float opac_mult = 1.0f;
-            if (INTERP) {
-              const float4 q3 = recs[jj].q3;
-              if (q3.x != 1.0f) {
-                // (1-a)^(1/k) as the reference's backward evaluates it with precise pow (backward.cu:631),
-                // here exp2f(y log2f(x)) with the full-precision library functions: same value to a few ulp
-                // without the ~45-instruction slow path; (1-a)^(1/k - 1) = that / (1-a)   (backward.cu:714)
-                const float om = 1.0f - my_alpha;
-                float pw = exp2f(q3.y * log2f(om));
-                alpha = q3.x * my_alpha + (1.0f - q3.x) * (1.0f - pw);
-                // the keep / skip decision below must be the reference's: within reach of the 1/255
-                // threshold (the two evaluations differ by < 1e-6) redo it with powf itself
-                if (fabsf(alpha - 1.0f / 255.0f) < 2e-5f) {
-                  pw = powf(om, q3.y);
-                  alpha = q3.x * my_alpha + (1.0f - q3.x) * (1.0f - pw);
-                }
-                // d alpha / d a = t - (1-a)^(1/k - 1) (t-1) / k
-                opac_mult = q3.x - __fdividef(pw, om) * (q3.x - 1.0f) * q3.y;
-              }
+        // Straight-line evaluation with the decisions folded into one predicate: lanes that do not contribute
+        // (behind their last contributor, power > 0, alpha < 1/255) run the same arithmetic on values nobody
+        // reads and deposit exact zeros (G, w and dL_dalpha are forced to 0 for them).
+        const float2 xy = *reinterpret_cast<const float2*>(&recs[jj].q0);
+        const float4 con_o = recs[jj].q1;
+        const float dx = xy.x - pixx, dy = xy.y - pixy;
+        const float power = -0.5f * (con_o.x * dx * dx + con_o.z * dy * dy) - con_o.y * dx * dy;
+        const float G = exp(power);
+        const float test_alpha = con_o.w * G;
+        const float my_alpha = min(0.99f, test_alpha);
+        float alpha = my_alpha;
+        float opac_mult = 1.0f;
+        if (INTERP) {
+          const float2 tk = *reinterpret_cast<const float2*>(&recs[jj].q3);
+          if (tk.x != 1.0f) {
+            // (1-a)^(1/k) as the reference's backward evaluates it with precise pow (backward.cu:631),
+            // here exp2f(y log2f(x)) with the full-precision library functions: same value to a few ulp
+            // without the ~45-instruction slow path; (1-a)^(1/k - 1) = that / (1-a)   (backward.cu:714)
+            const float om = 1.0f - my_alpha;
+            float pw = exp2f(tk.y * log2f(om));
+            alpha = tk.x * my_alpha + (1.0f - tk.x) * (1.0f - pw);
+            // the keep / skip decision below must be the reference's: within reach of the 1/255
+            // threshold (the two evaluations differ by < 1e-6) redo it with powf itself
+            if (fabsf(alpha - 1.0f / 255.0f) < 2e-5f) {
+              pw = powf(om, tk.y);
+              alpha = tk.x * my_alpha + (1.0f - tk.x) * (1.0f - pw);
             }
-            if (!(alpha < 1.0f / 255.0f)) {
-              contrib = true;
-              const float4 q2 = recs[jj].q2;
-              const float rcp_om = __frcp_rn(1.f - alpha);   // one reciprocal serves both divisions below
-              T = T * rcp_om;
-              const float w = alpha * T;
-              float u = q2.x * g0 + q2.y * g1 + q2.z * g2;
-              if (DEPTH) u += q2.w * gD;
-              accum_u = last_alpha * last_u + (1.f - last_alpha) * accum_u;
-              last_u = u;
-              float dL_dalpha = (u - accum_u) * T;
-              last_alpha = alpha;
-              dL_dalpha += (-T_final * rcp_om) * bgdot;
-              if (test_alpha > 0.99f) dL_dalpha = 0.f;  // clamped alpha passes no gradient (backward.cu:619,693)
-              const float dL_dG = con_o.w * dL_dalpha;
-              const float gdx = G * dx, gdy = G * dy;
-              v0 = dL_dG * gdx;
-              v1 = dL_dG * gdy;
-              v2 = v0 * dx;
-              v3 = v0 * dy;
-              v4 = v1 * dy;
-              v5 = opac_mult * G * dL_dalpha;
-              v6 = w * g0;
-              v7 = w * g1;
-              v8 = w * g2;
-              if (DEPTH) v9 = w * gD;
-            }
+            // d alpha / d a = t - (1-a)^(1/k - 1) (t-1) / k
+            opac_mult = tk.x - __fdividef(pw, om) * (tk.x - 1.0f) * tk.y;
           }
         }
-        if (__any_sync(0xffffffffu, contrib)) {
+        const bool contrib = (nn - 1 - (base + jj) < last) & !(power > 0.0f) & !(alpha < 1.0f / 255.0f);
+        if (!__any_sync(0xffffffffu, contrib)) continue;
+        const float4 q2 = recs[jj].q2;
+        // 1 - alpha is in [0.01, 1]: the approximate reciprocal plus one Newton step is exact to an ulp there
+        // and needs none of the range checks of a full-range division
+        const float om_a = 1.f - alpha;
+        float rcp_om = __frcp_approx(om_a);
+        rcp_om = fmaf(fmaf(-om_a, rcp_om, 1.0f), rcp_om, rcp_om);
+        const float Tn = T * rcp_om;
+        float u = q2.x * g0 + q2.y * g1 + q2.z * g2;
+        if (DEPTH) u += q2.w * gD;
+        const float acc_n = last_alpha * last_u + (1.f - last_alpha) * accum_u;
+        float dL_dalpha = (u - acc_n) * Tn + (-T_final * rcp_om) * bgdot;
+        // clamped alpha passes no gradient (backward.cu:619,693)
+        if (!contrib | (test_alpha > 0.99f)) dL_dalpha = 0.f;
+        const float Gc = contrib ? G : 0.f;
+        const float w = contrib ? alpha * Tn : 0.f;
+        if (contrib) {
+          T = Tn;
+          accum_u = acc_n;
+          last_u = u;
+          last_alpha = alpha;
+        }
+        const float dL_dG = con_o.w * dL_dalpha;
+        const float gdx = Gc * dx, gdy = Gc * dy;
+        const float v0 = dL_dG * gdx;
+        const float v1 = dL_dG * gdy;
+        const float v2 = v0 * dx;
+        const float v3 = v0 * dy;
+        const float v4 = v1 * dy;
+        const float v5 = opac_mult * Gc * dL_dalpha;
+        const float v6 = w * g0;
+        const float v7 = w * g1;
+        const float v8 = w * g2;
+        const float v9 = DEPTH ? w * gD : 0.f;
+        {
+
           // Transposed butterfly: at every level a lane keeps half of its values and hands the other half
           // to its partner, so the ten sums cost 5+3+2+1+1 = 12 shuffles instead of 10 x 5.
           const bool h16 = lane & 16, h8 = lane & 8, h4 = lane & 4, h2 = lane & 2;

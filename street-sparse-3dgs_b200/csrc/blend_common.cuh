@@ -72,6 +72,13 @@ __device__ __forceinline__ void red_add_v2(float* addr, float a, float b) {
   asm volatile("red.global.add.v2.f32 [%0], {%1, %2};\n" ::"l"(addr), "f"(a), "f"(b) : "memory");
 }
 
+// MUFU.RCP without the range handling of a full division (callers refine with a Newton step)
+__device__ __forceinline__ float __frcp_approx(float x) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+
 // Can the Gaussian of record (q0, q1) reach alpha >= 1/255 anywhere in the pixel block
 // [x0, x0+SUB_W-1] x [y0, y0+SUB_H-1]?  alpha >= 1/255  <=>  a dx^2 + 2 b dx dy + c dy^2 <= 2 ln(255 o) = q0.z
 // (preprocess stores that bound with a small safety margin, +inf for "never cull", negative for "never

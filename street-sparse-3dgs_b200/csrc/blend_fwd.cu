@@ -67,10 +67,9 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_fwd_kernel(const BlendArg
     }
   };
 
-  float T = 1.0f;
+  float T = inside ? 1.0f : -1.0f;   // sign bit = "done" (saturated, or outside the image)
   float C0 = 0.f, C1 = 0.f, C2 = 0.f, D = 0.f;
   uint32_t last_contributor = 0;
-  bool done = !inside;
 
   // software pipeline: ids two rounds ahead, records one round ahead
   uint32_t id_next = 0;
@@ -93,7 +92,7 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_fwd_kernel(const BlendArg
     if (TMA) mbar_wait(&sm.bar[s], (unsigned)((b >> 1) & 1));
     else __syncthreads();
 
-    const bool warp_live = __any_sync(0xffffffffu, !done);
+    const bool warp_live = __any_sync(0xffffffffu, T > 0.0f);
     if (warp_live) {
       const int cnt = min(BLEND_BATCH, n - b * BLEND_BATCH);
       const Rec* __restrict__ recs = sm.rec[s];
@@ -105,49 +104,48 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_fwd_kernel(const BlendArg
         while (m) {
           const int jj = c + __ffs(m) - 1;
           m &= m - 1;
-          if (!done) {
-            const float4 q0 = recs[jj].q0;
-            const float4 con_o = recs[jj].q1;
-            const float dx = q0.x - pixx, dy = q0.y - pixy;
-            const float power = -0.5f * (con_o.x * dx * dx + con_o.z * dy * dy) - con_o.y * dx * dy;
-            if (!(power > 0.0f)) {
-              const float my_alpha = min(0.99f, con_o.w * exp(power));
-              float alpha = my_alpha;
-              if (INTERP) {
-                const float4 q3 = recs[jj].q3;
-                if (q3.x != 1.0f) {  // t == 1 gives alpha == my_alpha exactly
-                  // slot gate (forward.cu:537): skybox slots carry t = 1 in their record already
-                  const float kidsqrt_alpha = 1.0f - __powf(1.0f - my_alpha, q3.y);
-                  alpha = q3.x * my_alpha + (1.0f - q3.x) * kidsqrt_alpha;
-                }
-              }
-              if (!(alpha < 1.0f / 255.0f)) {
-                const float test_T = T * (1 - alpha);
-                if (test_T < 0.0001f) {
-                  done = true;
-                } else {
-                  const float4 q2 = recs[jj].q2;
-                  C0 += q2.x * alpha * T;
-                  C1 += q2.y * alpha * T;
-                  C2 += q2.z * alpha * T;
-                  if (DEPTH) D += q2.w * alpha * T;
-                  T = test_T;
-                  last_contributor = (uint32_t)(b * BLEND_BATCH + jj + 1);
-                }
-              }
+          // Straight-line evaluation, decisions folded into predicates: the arithmetic of every lane that
+          // blends is the reference's, lanes that do not blend compute values nobody reads.
+          const float2 xy = *reinterpret_cast<const float2*>(&recs[jj].q0);
+          const float4 con_o = recs[jj].q1;
+          const float dx = xy.x - pixx, dy = xy.y - pixy;
+          const float power = -0.5f * (con_o.x * dx * dx + con_o.z * dy * dy) - con_o.y * dx * dy;
+          const float my_alpha = min(0.99f, con_o.w * exp(power));
+          float alpha = my_alpha;
+          if (INTERP) {
+            const float2 tk = *reinterpret_cast<const float2*>(&recs[jj].q3);
+            if (tk.x != 1.0f) {  // t == 1 gives alpha == my_alpha exactly
+              // slot gate (forward.cu:537): skybox slots carry t = 1 in their record already
+              const float kidsqrt_alpha = 1.0f - __powf(1.0f - my_alpha, tk.y);
+              alpha = tk.x * my_alpha + (1.0f - tk.x) * kidsqrt_alpha;
             }
           }
+          // a saturated pixel carries -T: its test_T is negative, so it can never take another entry
+          const float test_T = T * (1 - alpha);
+          const bool ok = !(power > 0.0f) & !(alpha < 1.0f / 255.0f);
+          const bool take = ok & !(test_T < 0.0001f);
+          if (ok & !take) T = -fabsf(T);
+          const float4 q2 = recs[jj].q2;
+          if (take) {
+            C0 += q2.x * alpha * T;
+            C1 += q2.y * alpha * T;
+            C2 += q2.z * alpha * T;
+            if (DEPTH) D += q2.w * alpha * T;
+            T = test_T;
+            last_contributor = (uint32_t)(b * BLEND_BATCH + jj + 1);
+          }
         }
-        if (!__any_sync(0xffffffffu, !done)) break;
+        if (!__any_sync(0xffffffffu, T > 0.0f)) break;
       }
     }
     // all warps saturated -> stop; the barrier also frees stage s for the copy issued next round
-    if (__syncthreads_and(done ? 1 : 0)) break;
+    if (__syncthreads_and(T < 0.0f ? 1 : 0)) break;
   }
 
   if (inside) {
     const size_t pix = (size_t)py * a.W + px;
     const size_t plane = (size_t)a.W * a.H;
+    T = fabsf(T);
     a.final_T[pix] = T;
     a.n_contrib[pix] = last_contributor;
     a.accum[pix] = make_float4(C0, C1, C2, D);

@@ -10,6 +10,7 @@ Differences that a caller can observe, all deliberate:
     path has an incomplete backward and is never reached from its own Python.
 """
 import ctypes
+import os
 
 import torch
 
@@ -80,10 +81,74 @@ def _scene(bg, indices, parent_indices, ts, kids, means3D, colors, opacity, scal
     return view, g, keep
 
 
+def _grad_shapes(rows, M, sh, sh_rest, colors, scales, rotations, cov3D_precomp):
+    """Per-store-row gradient tensors of one backward call; None = that input is absent."""
+    split = not _null(sh_rest)
+    return {"means3D": (rows, 3), "opacity": (rows, 1),
+            "sh": (rows, 1 if split else M, 3) if not _null(sh) else None,
+            "sh_rest": (rows, M - 1, 3) if split else None,
+            "colors": (rows, NUM_CHANNELS) if not _null(colors) else None,
+            "scales": (rows, 3) if not _null(scales) else None,
+            "rot": (rows, 4) if not _null(rotations) else None,
+            "cov3D": (rows, 6) if not _null(cov3D_precomp) else None}
+
+
+class _Prezero:
+    """Gradient tensors of a fused-cut render, allocated by the FORWARD and zero-filled on a side stream
+    forked right before the blend kernel.  The 4 GB fill of a 17 M-row store (0.6 ms of pure HBM writes) then
+    runs under the issue-bound forward blend and in the host-side gap between forward and backward instead of
+    in front of the backward kernels.  ``H3DGS_PREZERO=0`` (or ``_C.PREZERO = False``) disables."""
+
+    _streams = {}
+
+    def __init__(self, tensors, means2D):
+        self.tensors, self.means2D, self.done = tensors, means2D, None
+
+    @classmethod
+    def side_stream(cls, dev):
+        s = cls._streams.get(dev.index)
+        if s is None:
+            s = cls._streams[dev.index] = torch.cuda.Stream(device=dev)
+        return s
+
+    @classmethod
+    def allocate(cls, dev, shapes, means2D_rows, P):
+        opts = dict(dtype=torch.float32, device=dev)
+        tensors = {k: torch.empty(v, **opts) for k, v in shapes.items() if v is not None}
+        return cls(tensors, torch.empty((max(means2D_rows, P), 3), **opts))
+
+    def fill(self, dev, fork_event, P):
+        """Enqueue the zero fill on the side stream, ordered after ``fork_event``."""
+        L = nat.lib()
+        side = self.side_stream(dev)
+        side.wait_event(fork_event)
+        spans = [(t.data_ptr(), t.numel()) for t in self.tensors.values()]
+        m2 = self.means2D
+        if m2.size(0) > P:   # rows of a store-sized means2D beyond the rendered slots get no gradient
+            spans.append((m2.data_ptr() + P * 3 * 4, (m2.size(0) - P) * 3))
+        for i in range(0, len(spans), 8):
+            chunk = spans[i:i + 8]
+            arr = (nat.Span * len(chunk))(*[nat.Span(a, n) for a, n in chunk])
+            nat.check(L.h3dgs_zero_fill(arr, len(chunk), 0, side.cuda_stream), "h3dgs_zero_fill")
+        for t in list(self.tensors.values()) + [m2]:
+            t.record_stream(side)
+        self.done = torch.cuda.Event()
+        self.done.record(side)
+
+
+PREZERO = os.environ.get("H3DGS_PREZERO", "1") != "0"
+
+# sizes of the most recent forward (slots, visible slots, tile instances): the glue packages use the visible
+# count to compact per-slot results without a device->host round trip
+last_forward = {"P": 0, "V": 0, "R": 0}
+
+
 def rasterize_gaussians_ex(bg, indices, parent_indices, ts, kids, means3D, colors, opacity, scales,
                            rotations, scale_modifier, cov3D_precomp, viewmatrix, projmatrix, tan_fovx,
                            tan_fovy, image_height, image_width, sh, degree, campos, prefiltered, debug,
-                           do_depth, skyboxnum=0, sh_rest=None, acts=None):
+                           do_depth, skyboxnum=0, sh_rest=None, acts=None, prezero_means2D_rows=None):
+    """``prezero_means2D_rows`` (fused-cut mode, set by the autograd wrapper when a backward will follow):
+    also allocate the backward's gradient tensors and start their zero fill; an 8th return value carries them."""
     L = nat.lib()
     dev = means3D.device
     H, W = int(image_height), int(image_width)
@@ -102,11 +167,25 @@ def rasterize_gaussians_ex(bg, indices, parent_indices, ts, kids, means3D, color
                                          geom.numel(), ctypes.byref(R), ctypes.byref(V), int(bool(debug)), stream),
               "h3dgs_forward_preprocess")
     R, V = int(R.value), int(V.value)
+    last_forward.update(P=P, V=V, R=R)
     binning = torch.empty((L.h3dgs_binning_bytes(R, V, W, H) if R > 0 else 0,), dtype=torch.uint8, device=dev)
+    pre, fork = None, None
+    if prezero_means2D_rows is not None and prezero_means2D_rows >= 0 and PREZERO and not _null(indices) \
+            and R > 0 and P > 0 and not _arena.enabled():
+        # allocated BEFORE the fork point is recorded: whatever used these blocks last was enqueued earlier
+        pre = _Prezero.allocate(dev, _grad_shapes(g.store_rows, g.sh_coeffs, sh, sh_rest, colors, scales,
+                                                  rotations, cov3D_precomp), prezero_means2D_rows, P)
+        fork = torch.cuda.Event()
+        fork.record()   # creates the CUDA event; the library re-records it in front of the blend kernel
     nat.check(L.h3dgs_forward_render(ctypes.byref(view), ctypes.byref(g), nat.ptr(geom), nat.ptr(binning),
                                      binning.numel(), nat.ptr(img), R, V, nat.ptr(out_color),
-                                     nat.ptr(out_invdepth), int(bool(debug)), stream),
+                                     nat.ptr(out_invdepth), int(bool(debug)), stream,
+                                     fork.cuda_event if fork is not None else None),
               "h3dgs_forward_render")
+    if pre is not None:
+        pre.fill(dev, fork, P)
+    if prezero_means2D_rows is not None:
+        return R, out_color, radii, geom, binning, img, out_invdepth, pre
     return R, out_color, radii, geom, binning, img, out_invdepth
 
 
@@ -212,8 +291,9 @@ def rasterize_gaussians_backward_ex(bg, indices, parent_indices, ts, kids, means
                                     opacities, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,
                                     projmatrix, tan_fovx, tan_fovy, dL_dout_color, dL_dout_invdepth, sh,
                                     degree, campos, geomBuffer, R, binningBuffer, imageBuffer, debug,
-                                    skyboxnum=0, sh_rest=None, acts=None):
-    """With ``sh_rest`` the returned dL_dsh is the pair (dL_dfeatures_dc, dL_dfeatures_rest)."""
+                                    skyboxnum=0, sh_rest=None, acts=None, prezero=None):
+    """With ``sh_rest`` the returned dL_dsh is the pair (dL_dfeatures_dc, dL_dfeatures_rest).  ``prezero``: the
+    gradient tensors the forward allocated and zero-filled (``_Prezero``); dL_dmeans2D then has its rows."""
     L = nat.lib()
     dev = means3D.device
     H, W = dL_dout_color.size(1), dL_dout_color.size(2)
@@ -223,18 +303,17 @@ def rasterize_gaussians_backward_ex(bg, indices, parent_indices, ts, kids, means
     P, rows, M = g.P, g.store_rows, g.sh_coeffs
     split = not _null(sh_rest)
     opts = dict(dtype=torch.float32, device=dev)
-    dL_dmeans2D = torch.empty((P, 3), **opts)
     # per-store-row gradients; only those of inputs that exist are materialised, the others come back empty
-    shapes = {"means3D": (rows, 3), "opacity": (rows, 1),
-              "sh": (rows, 1 if split else M, 3) if not _null(sh) else None,
-              "sh_rest": (rows, M - 1, 3) if split else None,
-              "colors": (rows, NUM_CHANNELS) if not _null(colors) else None,
-              "scales": (rows, 3) if not _null(scales) else None,
-              "rot": (rows, 4) if not _null(rotations) else None,
-              "cov3D": (rows, 6) if not _null(cov3D_precomp) else None}
+    shapes = _grad_shapes(rows, M, sh, sh_rest, colors, scales, rotations, cov3D_precomp)
     fused = not _null(indices)
-    lease = _arena.lease(dev, shapes, P) if (fused and P > 0 and R > 0 and _arena.enabled()) else None
-    if lease is not None:
+    if prezero is not None and not (fused and P > 0 and R > 0 and prezero.done is not None):
+        prezero = None
+    dL_dmeans2D = prezero.means2D if prezero is not None else torch.empty((P, 3), **opts)
+    lease = _arena.lease(dev, shapes, P) if (prezero is None and fused and P > 0 and R > 0 and _arena.enabled()) else None
+    if prezero is not None:
+        torch.cuda.current_stream().wait_event(prezero.done)
+        t = prezero.tensors
+    elif lease is not None:
         t = lease.tensors
     else:
         t = {k: torch.empty(v, **opts) for k, v in shapes.items() if v is not None}
@@ -249,7 +328,7 @@ def rasterize_gaussians_backward_ex(bg, indices, parent_indices, ts, kids, means
     grads = nat.Grads(nat.ptr(dL_dmeans2D), nat.ptr(dL_dmeans3D), nat.ptr(dL_dsh), nat.ptr(dL_dcolors),
                       nat.ptr(dL_dopacity), nat.ptr(dL_dscales), nat.ptr(dL_drot), nat.ptr(dL_dcov3D),
                       nat.ptr(dL_dsh_rest), nat.ptr(lease.dirty) if lease is not None else None,
-                      1 if lease is not None else 0)
+                      1 if (lease is not None or prezero is not None) else 0)
     ws = torch.empty((L.h3dgs_backward_workspace_bytes(P),), dtype=torch.uint8, device=dev)
     dcol = nat.as_f32(dL_dout_color, "dL_dout_color")
     ddep = nat.as_f32(dL_dout_invdepth, "dL_dout_invdepth")

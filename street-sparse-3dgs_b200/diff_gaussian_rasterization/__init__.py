@@ -46,8 +46,9 @@ class _RasterizeGaussiansRaw(torch.autograd.Function):
                 xyz, e, opacity, scaling, rotation, rs.scale_modifier, e, rs.viewmatrix, rs.projmatrix,
                 rs.tanfovx, rs.tanfovy, rs.image_height, rs.image_width, f_dc, rs.sh_degree, rs.campos,
                 rs.prefiltered, rs.debug, rs.do_depth)
-        num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer, invdepths = \
-            _C.rasterize_gaussians_ex(*args, skyboxnum, f_rest, acts)
+        num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer, invdepths, ctx.prezero = \
+            _C.rasterize_gaussians_ex(*args, skyboxnum, f_rest, acts,
+                                      means2D.size(0) if any(ctx.needs_input_grad) else -1)
         ctx.raster_settings = rs
         ctx.num_rendered = num_rendered
         ctx.skyboxnum = skyboxnum
@@ -69,8 +70,9 @@ class _RasterizeGaussiansRaw(torch.autograd.Function):
                 xyz, radii, e, opacity, scaling, rotation, rs.scale_modifier, e, rs.viewmatrix, rs.projmatrix,
                 rs.tanfovx, rs.tanfovy, grad_out_color, grad_out_depth, f_dc, rs.sh_degree, rs.campos,
                 geomBuffer, ctx.num_rendered, binningBuffer, imgBuffer, rs.debug)
+        prezero, ctx.prezero = ctx.prezero, None   # a second backward through this node allocates afresh
         (grad_means2D, _gc, grad_opacity, grad_xyz, _gcov, grad_sh, grad_scaling, grad_rotation) = \
-            _C.rasterize_gaussians_backward_ex(*args, ctx.skyboxnum, f_rest, ctx.acts)
+            _C.rasterize_gaussians_backward_ex(*args, ctx.skyboxnum, f_rest, ctx.acts, prezero)
         grad_dc, grad_rest = grad_sh
         if grad_means2D.size(0) != ctx.means2D_rows:
             full = torch.zeros((ctx.means2D_rows, 3), dtype=grad_means2D.dtype, device=grad_means2D.device)
@@ -91,8 +93,9 @@ class _RasterizeGaussians(torch.autograd.Function):
                 means3D, colors_precomp, opacities, scales, rotations, rs.scale_modifier, cov3Ds_precomp,
                 rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, rs.image_height, rs.image_width, sh,
                 rs.sh_degree, rs.campos, rs.prefiltered, rs.debug, rs.do_depth)
-        num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer, invdepths = \
-            _C.rasterize_gaussians_ex(*args, skyboxnum)
+        num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer, invdepths, ctx.prezero = \
+            _C.rasterize_gaussians_ex(*args, skyboxnum, None, None,
+                                      means2D.size(0) if any(ctx.needs_input_grad) else -1)
         ctx.raster_settings = rs
         ctx.num_rendered = num_rendered
         ctx.skyboxnum = skyboxnum
@@ -114,8 +117,10 @@ class _RasterizeGaussians(torch.autograd.Function):
                 cov3Ds_precomp, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, grad_out_color,
                 grad_out_depth, sh, rs.sh_degree, rs.campos, geomBuffer, ctx.num_rendered, binningBuffer,
                 imgBuffer, rs.debug)
+        prezero, ctx.prezero = ctx.prezero, None   # a second backward through this node allocates afresh
         (grad_means2D, grad_colors_precomp, grad_opacities, grad_means3D, grad_cov3Ds_precomp, grad_sh,
-         grad_scales, grad_rotations) = _C.rasterize_gaussians_backward_ex(*args, ctx.skyboxnum)
+         grad_scales, grad_rotations) = _C.rasterize_gaussians_backward_ex(*args, ctx.skyboxnum, None, None,
+                                                                           prezero)
 
         if grad_means2D.size(0) != ctx.means2D_rows:
             # index mode called with a store-sized means2D: slots map to its leading rows

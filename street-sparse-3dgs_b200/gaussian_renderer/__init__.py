@@ -74,13 +74,11 @@ def _eval_sh(deg, sh, dirs):
 
 
 def _screenspace_points(pc):
-    # zero tensor whose gradient is the 2D mean gradient (densification statistics)
-    pts = torch.zeros_like(pc.get_xyz, dtype=pc.get_xyz.dtype, requires_grad=True, device="cuda") + 0
-    try:
-        pts.retain_grad()
-    except Exception:
-        pass
-    return pts
+    # zero tensor whose gradient is the 2D mean gradient (densification statistics).  The reference builds
+    # it as ``zeros(requires_grad=True) + 0`` with retain_grad(); a leaf gives callers the same ``.grad``
+    # without the N-row add (and without autograd cloning the gradient into the retained copy).
+    xyz = pc.get_xyz
+    return torch.zeros(xyz.shape, dtype=xyz.dtype, requires_grad=True, device="cuda")
 
 
 def _appearance(viewpoint_camera, pc, pipe, override_color):
@@ -125,6 +123,18 @@ def _settings(viewpoint_camera, pc, bg_color, scaling_modifier, debug, do_depth,
         interpolation_weights=interpolation_weights,
         num_node_kids=num_node_kids,
         do_depth=do_depth)
+
+
+def _visible(radii):
+    """(mask, indices) of the slots with radii > 0.  The forward already knows how many there are, so the
+    indices come from ``nonzero_static`` -- no device->host sync, the host keeps queueing the loss and the
+    backward while the blend kernel runs (the reference's ``radii[radii > 0]`` blocks on the GPU)."""
+    from diff_gaussian_rasterization import _C
+    mask = radii > 0
+    info = _C.last_forward
+    if info["P"] == radii.numel():
+        return mask, torch.nonzero_static(mask, size=info["V"]).flatten()
+    return mask, mask.nonzero().flatten()
 
 
 def _empty(dtype):
@@ -174,19 +184,20 @@ def render(viewpoint_camera, pc, pipe, bg_color: torch.Tensor, scaling_modifier=
             exposure[:3, 3, None, None]
     rendered_image = rendered_image.clamp(0, 1)
 
-    subfilter = radii > 0
+    subfilter, visible = _visible(radii)
     if indices is not None:
         vis_filter = torch.zeros(pc._xyz.size(0), dtype=bool, device="cuda")
         w = vis_filter[indices]
         w[subfilter] = True
         vis_filter[indices] = w
+        vis_ids = vis_filter.nonzero().flatten().long()
     else:
-        vis_filter = subfilter
+        vis_ids = visible.long()
     return {"render": rendered_image,
             "depth": depth_image,
             "viewspace_points": screenspace_points,
-            "visibility_filter": vis_filter.nonzero().flatten().long(),
-            "radii": radii[subfilter]}
+            "visibility_filter": vis_ids,
+            "radii": radii[visible]}
 
 
 def render_post(viewpoint_camera, pc, pipe, bg_color: torch.Tensor, scaling_modifier=1.0, override_color=None,
@@ -217,7 +228,10 @@ def render_post(viewpoint_camera, pc, pipe, bg_color: torch.Tensor, scaling_modi
         else:
             skybox = 0
             par = _empty(torch.int32)
-        means2D = means2D[:(num_entries + skybox)].contiguous() if interp_python else means2D[render_indices.long()].contiguous()
+        # interp_python: slots map to the leading rows of the store-sized tensor (the reference slices it,
+        # :239); the rasterizer writes those rows of a full-size gradient itself
+        if not interp_python:
+            means2D = means2D[render_indices.long()].contiguous()
         render_indices, parent_indices = idx, par
         if interpolation_weights.numel():
             interpolation_weights = interpolation_weights.to("cuda")
@@ -243,11 +257,11 @@ def render_post(viewpoint_camera, pc, pipe, bg_color: torch.Tensor, scaling_modi
             print(f"Exposures should be optimized in single. Missing exposure for image {viewpoint_camera.image_name}")
     rendered_image = rendered_image.clamp(0, 1)
 
-    vis_filter = radii > 0
+    vis_filter, visible = _visible(radii)
     out = {"render": rendered_image,
            "viewspace_points": screenspace_points,
            "visibility_filter": vis_filter,
-           "radii": radii[vis_filter]}
+           "radii": radii[visible]}
     if do_depth:
         out["depth"] = depth_image
     return out
@@ -273,7 +287,7 @@ def render_coarse(viewpoint_camera, pc, pipe, bg_color: torch.Tensor, scaling_mo
         rendered_image, radii, _ = _rasterize(settings, means3D, means2D, opacity, shs, colors_precomp, scales,
                                               rotations, cov3D_precomp)
 
-    subfilter = radii > 0
+    subfilter, visible = _visible(radii)
     if indices is not None:
         vis_filter = torch.zeros(pc._xyz.size(0), dtype=bool, device="cuda")
         w = vis_filter[indices]
@@ -284,4 +298,4 @@ def render_coarse(viewpoint_camera, pc, pipe, bg_color: torch.Tensor, scaling_mo
     return {"render": rendered_image,
             "viewspace_points": screenspace_points,
             "visibility_filter": vis_filter,
-            "radii": radii[subfilter]}
+            "radii": radii[visible]}

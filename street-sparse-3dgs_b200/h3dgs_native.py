@@ -52,6 +52,10 @@ class RowTensor(Structure):
     _fields_ = [("data", c_void_p), ("width", c_int32)]
 
 
+class Span(Structure):
+    _fields_ = [("data", c_void_p), ("count", c_int64)]
+
+
 class DebugView(Structure):
     _fields_ = [("point_list_keys", c_void_p), ("point_list", c_void_p), ("ranges", c_void_p),
                 ("final_T", c_void_p), ("n_contrib", c_void_p), ("depths", c_void_p),
@@ -79,11 +83,12 @@ SIGNATURES = {
     "h3dgs_forward_preprocess": (c_int, [POINTER(View), POINTER(Gaussians), c_void_p, c_void_p, c_size_t,
                                           POINTER(c_int64), POINTER(c_int64), c_int, c_void_p]),
     "h3dgs_forward_render": (c_int, [POINTER(View), POINTER(Gaussians), c_void_p, c_void_p, c_size_t,
-                                      c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_int, c_void_p]),
+                                      c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
     "h3dgs_backward": (c_int, [POINTER(View), POINTER(Gaussians), c_void_p, c_void_p, c_void_p, c_void_p,
                                 c_int64, c_void_p, c_void_p, POINTER(Grads), c_void_p, c_size_t, c_int,
                                 c_void_p]),
     "h3dgs_zero_rows": (c_int, [c_void_p, c_int64, POINTER(RowTensor), c_int32, c_void_p]),
+    "h3dgs_zero_fill": (c_int, [POINTER(Span), c_int32, c_int32, c_void_p]),
     "h3dgs_mark_visible": (c_int, [c_int32, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "h3dgs_debug_view": (c_int, [c_int32, c_int32, c_int32, c_int64, c_void_p, c_void_p, c_void_p,
                                   POINTER(DebugView)]),
@@ -131,7 +136,7 @@ def lib():
             fn = getattr(handle, name)
             fn.restype = res
             fn.argtypes = args
-        if handle.h3dgs_abi_version() != 4:
+        if handle.h3dgs_abi_version() != 5:
             raise H3dgsError("libh3dgs_b200.so ABI version mismatch")
         _lib = handle
     return _lib
