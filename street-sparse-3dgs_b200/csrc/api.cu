@@ -300,6 +300,8 @@ int h3dgs_forward_render(const H3dgsView* view, const H3dgsGaussians* g, void* g
   if ((rc = debug_sync(debug, s, "tile_sort"))) return rc;
   H3_CUDA(launch_tile_ranges(R, bw.keys64, iw.ranges, grid_x * grid_y, s));
   if ((rc = debug_sync(debug, s, "tile_ranges"))) return rc;
+  H3_CUDA(launch_tile_order(iw.ranges, nullptr, grid_x * grid_y, iw.order_fwd, s));
+  H3_CUDA(cudaMemsetAsync(iw.tile_last, 0, sizeof(uint32_t) * (size_t)(grid_x * grid_y), s));
 
   BlendArgs b;
   std::memset(&b, 0, sizeof(b));
@@ -308,6 +310,7 @@ int h3dgs_forward_render(const H3dgsView* view, const H3dgsGaussians* g, void* g
   b.ranges = iw.ranges; b.point_list = bw.tvals[bw.sorted]; b.rec = gw.rec; b.bg = view->background;
   b.final_T = iw.final_T; b.n_contrib = iw.n_contrib; b.accum = iw.accum;
   b.out_color = out_color; b.out_invdepth = out_invdepth;
+  b.order = iw.order_fwd; b.tile_last = iw.tile_last;
   if (pre_blend_event) H3_CUDA(cudaEventRecord((cudaEvent_t)pre_blend_event, s));
   H3_CUDA(launch_blend_fwd(b, s));
   if ((rc = debug_sync(debug, s, "blend_fwd"))) return rc;
@@ -379,6 +382,8 @@ int h3dgs_backward(const H3dgsView* view, const H3dgsGaussians* g, const int32_t
   b.ranges = iw.ranges; b.point_list = bw.tvals[bw.sorted]; b.rec = gw.rec; b.bg = view->background;
   b.final_T = iw.final_T; b.n_contrib = iw.n_contrib; b.accum = iw.accum;
   b.dL_dcolor = dL_dout_color; b.dL_dinvdepth = dL_dout_invdepth; b.grad = ww.grad;
+  H3_CUDA(launch_tile_order(nullptr, iw.tile_last, b.grid_x * b.grid_y, iw.order_bwd, s));
+  b.order = iw.order_bwd;
   H3_CUDA(launch_blend_bwd(b, s));
   if ((rc = debug_sync(debug, s, "blend_bwd"))) return rc;
 

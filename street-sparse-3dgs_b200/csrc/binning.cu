@@ -95,7 +95,56 @@ __global__ void __launch_bounds__(256) tile_ranges_kernel(long long L,
   }
 }
 
+// Heavy-first launch order for the blend kernels.  Tile work is wildly uneven in street views (median list
+// ~1.7 k entries, horizon tiles 25 k): in blockIdx order the few longest tiles start late and the SMs idle
+// 40 % of the kernel waiting for them.  One CTA counting-sorts the tiles into 64 logarithmic buckets
+// (4 per octave of the length), longest first; the order inside a bucket does not matter.
+__device__ __forceinline__ int work_bucket(uint32_t len) {
+  if (len < 4u) return 63;
+  const int msb = 31 - __clz(len);
+  const int sub = (int)((len >> (msb - 2)) & 3u);
+  const int b = msb * 4 + sub - 8;          // len 4..7 -> 0..3, doubling every 4
+  return 63 - (b > 63 ? 63 : b);
+}
+__global__ void __launch_bounds__(1024) tile_order_kernel(const uint2* __restrict__ ranges,
+                                                          const uint32_t* __restrict__ lengths, int tiles,
+                                                          uint32_t* __restrict__ order) {
+  __shared__ uint32_t cnt[64];
+  if (threadIdx.x < 64) cnt[threadIdx.x] = 0;
+  __syncthreads();
+  for (int t = threadIdx.x; t < tiles; t += blockDim.x) {
+    const uint32_t len = ranges ? (ranges[t].y - ranges[t].x) : lengths[t];
+    atomicAdd(&cnt[work_bucket(len)], 1u);
+  }
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    // exclusive scan of the 64 counters by one warp (two per lane)
+    const uint32_t a = cnt[2 * threadIdx.x], b = cnt[2 * threadIdx.x + 1];
+    uint32_t incl = a + b;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t o = __shfl_up_sync(0xffffffffu, incl, d);
+      if ((int)threadIdx.x >= d) incl += o;
+    }
+    cnt[2 * threadIdx.x] = incl - a - b;
+    cnt[2 * threadIdx.x + 1] = incl - b;
+  }
+  __syncthreads();
+  for (int t = threadIdx.x; t < tiles; t += blockDim.x) {
+    const uint32_t len = ranges ? (ranges[t].y - ranges[t].x) : lengths[t];
+    order[atomicAdd(&cnt[work_bucket(len)], 1u)] = (uint32_t)t;
+  }
+}
+
 }  // namespace
+
+cudaError_t launch_tile_order(const uint2* ranges, const uint32_t* lengths, int tiles, uint32_t* order,
+                              cudaStream_t s) {
+  if (tiles <= 0) return cudaSuccess;
+  ProfScope ps(K_TILE_RANGES, s);
+  tile_order_kernel<<<1, 1024, 0, s>>>(ranges, lengths, tiles, order);
+  return cudaGetLastError();
+}
 
 cudaError_t launch_compact_visible(int P, const GeomWs& g, BinWs& b, cudaStream_t s) {
   if (P <= 0) return cudaSuccess;

@@ -32,7 +32,7 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_bwd_kernel(const BlendArg
   extern __shared__ __align__(16) unsigned char smem_raw[];
   BwdSmem& sm = *reinterpret_cast<BwdSmem*>(smem_raw);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int tile = blockIdx.x;
+  const int tile = a.order ? (int)a.order[blockIdx.x] : (int)blockIdx.x;
   const int tx = tile % a.grid_x, ty = tile / a.grid_x;
   const int bx0 = tx * TILE_X + (warp & 1) * SUB_W;
   const int by0 = ty * TILE_Y + (warp >> 1) * SUB_H;

@@ -21,7 +21,7 @@ template <bool INTERP, bool DEPTH, bool TMA>
 __global__ void __launch_bounds__(BLEND_THREADS) blend_fwd_kernel(const BlendArgs a) {
   __shared__ FwdSmem sm;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int tile = blockIdx.x;
+  const int tile = a.order ? (int)a.order[blockIdx.x] : (int)blockIdx.x;
   const int tx = tile % a.grid_x, ty = tile / a.grid_x;
   const int bx0 = tx * TILE_X + (warp & 1) * SUB_W;
   const int by0 = ty * TILE_Y + (warp >> 1) * SUB_H;
@@ -101,17 +101,18 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_fwd_kernel(const BlendArg
         bool hit = false;
         if (j < cnt) hit = block_hit(recs[j].q0, recs[j].q1, fx0, fy0);
         unsigned m = __ballot_sync(0xffffffffu, hit);
-        while (m) {
-          const int jj = c + __ffs(m) - 1;
-          m &= m - 1;
-          // Straight-line evaluation, decisions folded into predicates: the arithmetic of every lane that
-          // blends is the reference's, lanes that do not blend compute values nobody reads.
+        // Straight-line evaluation, decisions folded into predicates: the arithmetic of every lane that
+        // blends is the reference's, lanes that do not blend compute values nobody reads.  `eval` is the part
+        // that does not depend on the running transmittance; survivors are taken two at a time so that two
+        // such chains (LDS -> power -> exp -> alpha) are in flight per warp -- what bounds the long horizon
+        // tiles that end up alone on their SM.  `apply` then blends in list order.
+        auto eval = [&](int jj, float& alpha, bool& ok) {
           const float2 xy = *reinterpret_cast<const float2*>(&recs[jj].q0);
           const float4 con_o = recs[jj].q1;
           const float dx = xy.x - pixx, dy = xy.y - pixy;
           const float power = -0.5f * (con_o.x * dx * dx + con_o.z * dy * dy) - con_o.y * dx * dy;
           const float my_alpha = min(0.99f, con_o.w * exp(power));
-          float alpha = my_alpha;
+          alpha = my_alpha;
           if (INTERP) {
             const float2 tk = *reinterpret_cast<const float2*>(&recs[jj].q3);
             if (tk.x != 1.0f) {  // t == 1 gives alpha == my_alpha exactly
@@ -120,9 +121,11 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_fwd_kernel(const BlendArg
               alpha = tk.x * my_alpha + (1.0f - tk.x) * kidsqrt_alpha;
             }
           }
+          ok = !(power > 0.0f) & !(alpha < 1.0f / 255.0f);
+        };
+        auto apply = [&](int jj, float alpha, bool ok) {
           // a saturated pixel carries -T: its test_T is negative, so it can never take another entry
           const float test_T = T * (1 - alpha);
-          const bool ok = !(power > 0.0f) & !(alpha < 1.0f / 255.0f);
           const bool take = ok & !(test_T < 0.0001f);
           if (ok & !take) T = -fabsf(T);
           const float4 q2 = recs[jj].q2;
@@ -134,6 +137,23 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_fwd_kernel(const BlendArg
             T = test_T;
             last_contributor = (uint32_t)(b * BLEND_BATCH + jj + 1);
           }
+        };
+        while (m) {
+          const int j0 = c + __ffs(m) - 1;
+          m &= m - 1;
+          float a0, a1;
+          bool k0, k1;
+          if (m) {
+            const int j1 = c + __ffs(m) - 1;
+            m &= m - 1;
+            eval(j0, a0, k0);
+            eval(j1, a1, k1);
+            apply(j0, a0, k0);
+            apply(j1, a1, k1);
+          } else {
+            eval(j0, a0, k0);
+            apply(j0, a0, k0);
+          }
         }
         if (!__any_sync(0xffffffffu, T > 0.0f)) break;
       }
@@ -142,6 +162,10 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_fwd_kernel(const BlendArg
     if (__syncthreads_and(T < 0.0f ? 1 : 0)) break;
   }
 
+  if (a.tile_last) {
+    const uint32_t wl = __reduce_max_sync(0xffffffffu, last_contributor);
+    if (lane == 0 && wl) atomicMax(a.tile_last + tile, wl);
+  }
   if (inside) {
     const size_t pix = (size_t)py * a.W + px;
     const size_t plane = (size_t)a.W * a.H;

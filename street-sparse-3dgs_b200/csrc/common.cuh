@@ -79,6 +79,9 @@ struct ImageWs {
   float* final_T;     // per pixel
   uint32_t* n_contrib;
   float4* accum;      // (C.r, C.g, C.b, D) without background, per pixel
+  uint32_t* order_fwd;  // per tile: launch order of the forward blend, longest list first
+  uint32_t* order_bwd;  // per tile: launch order of the backward blend, deepest last contributor first
+  uint32_t* tile_last;  // per tile: max over its pixels of n_contrib (how far the backward walks)
   size_t bytes;
   static ImageWs make(void* base, int W, int H) {
     ImageWs w;
@@ -90,6 +93,9 @@ struct ImageWs {
     carve(p, w.final_T, npix);
     carve(p, w.n_contrib, npix);
     carve(p, w.accum, npix);
+    carve(p, w.order_fwd, tiles);
+    carve(p, w.order_bwd, tiles);
+    carve(p, w.tile_last, tiles);
     w.bytes = (size_t)(p - p0) + 256;
     return w;
   }
@@ -278,6 +284,9 @@ cudaError_t launch_scan_gather(const uint32_t* tiles_touched, const uint32_t* or
 cudaError_t launch_compact_visible(int P, const GeomWs& g, BinWs& b, cudaStream_t s);
 cudaError_t launch_emit_instances(int64_t R, int64_t V, const GeomWs& g, BinWs& b, int grid_x, int key_bytes,
                                   cudaStream_t s);
+// order[] = tile ids sorted by descending work (ranges given: list length; else lengths[] itself), 64 log buckets
+cudaError_t launch_tile_order(const uint2* ranges, const uint32_t* lengths, int tiles, uint32_t* order,
+                              cudaStream_t s);
 cudaError_t launch_tile_ranges(int64_t R, const unsigned long long* keys, uint2* ranges, int tiles,
                                cudaStream_t s);
 // radix_sort.cu
@@ -292,6 +301,8 @@ struct BlendArgs {
   float* final_T; uint32_t* n_contrib; float4* accum;
   float* out_color; float* out_invdepth;   // fwd
   const float* dL_dcolor; const float* dL_dinvdepth; GradRec* grad;  // bwd
+  const uint32_t* order;   // CTA i processes tile order[i] (heavy tiles first); NULL = identity
+  uint32_t* tile_last;     // fwd: per-tile max of n_contrib (pre-zeroed)
 };
 cudaError_t launch_blend_fwd(const BlendArgs& a, cudaStream_t s);
 cudaError_t launch_blend_bwd(const BlendArgs& a, cudaStream_t s);
