@@ -292,6 +292,14 @@ typedef struct H3dgsAdamTensor {
   float one_minus_beta1, one_minus_beta2; /* (1 - beta) rounded from the host's double, as torch passes it */
 } H3dgsAdamTensor;
 
+/* Gradient exchange of camera-batch data parallelism (mode B): gather the listed rows of up to 8
+ * row-major fp32 tensors into ONE packed [num_rows, sum of widths] buffer (the all-reduce payload), and the
+ * inverse scatter, which multiplies by `scale` (1/world for an average).  rows: device int64 [num_rows]. */
+H3DGS_API int h3dgs_pack_rows(const H3dgsRowTensor* tensors, int32_t num_tensors, const int64_t* rows,
+                    int64_t num_rows, float* packed, h3dgs_stream_t stream);
+H3DGS_API int h3dgs_unpack_rows(const H3dgsRowTensor* tensors, int32_t num_tensors, const int64_t* rows,
+                    int64_t num_rows, const float* packed, float scale, h3dgs_stream_t stream);
+
 #define H3DGS_ADAM_MAX_TENSORS 8
 /* relevant: device int64 [num_relevant] row ids, or NULL for a dense update of rows [0,num_rows). */
 H3DGS_API int h3dgs_sparse_adam(const H3dgsAdamTensor* tensors, int32_t num_tensors,
@@ -303,6 +311,12 @@ H3DGS_API int h3dgs_sparse_adam(const H3dgsAdamTensor* tensors, int32_t num_tens
  * every kernel in a pair of CUDA events on the launching stream while enabled.
  * ------------------------------------------------------------------------------------------------ */
 #define H3DGS_PROF_KERNELS 16
+/* Instrumented pass for the FLOP accounting of the blend kernels: while `counters` (device,
+ * 9 x uint64, zeroed by the caller) is set, the blend kernels run a counting variant and add, per evaluated
+ * (live pixel, list entry) pair: [0] forward pairs rejected at power > 0, [1] at alpha < 1/255, [2] at the T
+ * test, [3] blended, [4] forward lane slots issued; [5] backward pairs rejected at power > 0, [6] at
+ * alpha < 1/255, [7] contributing, [8] backward lane slots issued.  NULL switches it off.  Never timed. */
+H3DGS_API int h3dgs_blend_stats(void* counters);
 H3DGS_API int64_t h3dgs_launch_count(void);          /* kernels launched by this library so far (process-wide) */
 H3DGS_API int h3dgs_profile_enable(int enable);      /* returns the previous setting */
 /* Synchronises pending events and adds their durations; ms[i] / launches[i] are per kernel id

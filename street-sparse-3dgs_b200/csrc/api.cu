@@ -56,6 +56,9 @@ void prof_end(int id, cudaStream_t s) {
   g_prof.cur[id] = nullptr;
 }
 
+// device pointer of the pair-category counters while an instrumented pass is on (h3dgs_blend_stats)
+static unsigned long long* g_blend_stats = nullptr;
+
 // H3DGS_STAGE=tma|ldgsts selects how the blend kernels stage records into shared memory.
 int blend_stage_mode() {
   static int mode = -1;
@@ -144,6 +147,8 @@ cudaError_t run_interpolation_weights(int K, const int* indices, float target_si
                                       int* kids, cudaStream_t s);
 cudaError_t run_sparse_adam(const H3dgsAdamTensor* tensors, int n, const long long* relevant,
                             long long num_relevant, long long num_rows, cudaStream_t s);
+cudaError_t run_pack_rows(const H3dgsRowTensor* tensors, int n, const long long* rows, long long K, float* packed,
+                          float scale, bool pack, cudaStream_t s);
 
 namespace {
 
@@ -310,7 +315,7 @@ int h3dgs_forward_render(const H3dgsView* view, const H3dgsGaussians* g, void* g
   b.ranges = iw.ranges; b.point_list = bw.tvals[bw.sorted]; b.rec = gw.rec; b.bg = view->background;
   b.final_T = iw.final_T; b.n_contrib = iw.n_contrib; b.accum = iw.accum;
   b.out_color = out_color; b.out_invdepth = out_invdepth;
-  b.order = iw.order_fwd; b.tile_last = iw.tile_last;
+  b.order = iw.order_fwd; b.tile_last = iw.tile_last; b.stats = g_blend_stats;
   if (pre_blend_event) H3_CUDA(cudaEventRecord((cudaEvent_t)pre_blend_event, s));
   H3_CUDA(launch_blend_fwd(b, s));
   if ((rc = debug_sync(debug, s, "blend_fwd"))) return rc;
@@ -383,7 +388,7 @@ int h3dgs_backward(const H3dgsView* view, const H3dgsGaussians* g, const int32_t
   b.final_T = iw.final_T; b.n_contrib = iw.n_contrib; b.accum = iw.accum;
   b.dL_dcolor = dL_dout_color; b.dL_dinvdepth = dL_dout_invdepth; b.grad = ww.grad;
   H3_CUDA(launch_tile_order(nullptr, iw.tile_last, b.grid_x * b.grid_y, iw.order_bwd, s));
-  b.order = iw.order_bwd;
+  b.order = iw.order_bwd; b.stats = g_blend_stats;
   H3_CUDA(launch_blend_bwd(b, s));
   if ((rc = debug_sync(debug, s, "blend_bwd"))) return rc;
 
@@ -565,6 +570,32 @@ int h3dgs_sparse_adam(const H3dgsAdamTensor* tensors, int32_t num_tensors, const
   if (num_relevant < 0 || num_rows < 0) return fail(H3DGS_EINVAL, "negative row count");
   H3_CUDA(run_sparse_adam(tensors, num_tensors, reinterpret_cast<const long long*>(relevant), num_relevant,
                           num_rows, (cudaStream_t)stream));
+  return 0;
+}
+
+static int pack_rows_common(const H3dgsRowTensor* tensors, int32_t n, const int64_t* rows, int64_t K, float* packed,
+                            float scale, bool pack, h3dgs_stream_t stream) {
+  if (!tensors || n <= 0 || n > 8) return fail(H3DGS_EINVAL, "pack/unpack rows: 1..8 tensors required");
+  if (K < 0) return fail(H3DGS_EINVAL, "pack/unpack rows: negative row count");
+  if (K == 0) return 0;
+  if (!rows || !packed) return fail(H3DGS_EINVAL, "pack/unpack rows: rows and packed are required");
+  for (int i = 0; i < n; ++i)
+    if (!tensors[i].data || tensors[i].width <= 0) return fail(H3DGS_EINVAL, "pack/unpack rows: null tensor or non-positive width");
+  H3_CUDA(run_pack_rows(tensors, n, reinterpret_cast<const long long*>(rows), K, packed, scale, pack,
+                        (cudaStream_t)stream));
+  return 0;
+}
+int h3dgs_pack_rows(const H3dgsRowTensor* tensors, int32_t num_tensors, const int64_t* rows, int64_t num_rows,
+                    float* packed, h3dgs_stream_t stream) {
+  return pack_rows_common(tensors, num_tensors, rows, num_rows, packed, 1.0f, true, stream);
+}
+int h3dgs_unpack_rows(const H3dgsRowTensor* tensors, int32_t num_tensors, const int64_t* rows, int64_t num_rows,
+                      const float* packed, float scale, h3dgs_stream_t stream) {
+  return pack_rows_common(tensors, num_tensors, rows, num_rows, const_cast<float*>(packed), scale, false, stream);
+}
+
+int h3dgs_blend_stats(void* counters) {
+  g_blend_stats = reinterpret_cast<unsigned long long*>(counters);
   return 0;
 }
 

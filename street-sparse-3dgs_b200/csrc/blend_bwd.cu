@@ -27,7 +27,9 @@ struct BwdSmem {
   int red[BLEND_THREADS / 32];
 };
 
-template <bool INTERP, bool DEPTH, bool TMA>
+// COUNT: instrumented pass -- stats[5] live pairs rejected at power > 0, [6] at alpha < 1/255, [7] contributing,
+// [8] lane slots issued.
+template <bool INTERP, bool DEPTH, bool TMA, bool COUNT = false>
 __global__ void __launch_bounds__(BLEND_THREADS) blend_bwd_kernel(const BlendArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   BwdSmem& sm = *reinterpret_cast<BwdSmem*>(smem_raw);
@@ -114,6 +116,7 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_bwd_kernel(const BlendArg
     if (!DEPTH && red_dst == 9) red_dst = -1;
   }
   float T = T_final, accum_u = 0.f, last_alpha = 0.f, last_u = 0.f;
+  unsigned cntA = 0, cntB = 0, cntD = 0, cntS = 0;
   const float half_w = 0.5f * (float)a.W, half_h = 0.5f * (float)a.H;
 
   // staging slot k of round b holds list position nn - 1 - (b * BATCH + k): back to front
@@ -180,6 +183,12 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_bwd_kernel(const BlendArg
           }
         }
         const bool contrib = (nn - 1 - (base + jj) < last) & !(power > 0.0f) & !(alpha < 1.0f / 255.0f);
+        if (COUNT) {
+          if (nn - 1 - (base + jj) < last) {
+            if (power > 0.0f) ++cntA; else if (!contrib) ++cntB; else ++cntD;
+          }
+          ++cntS;
+        }
         if (!__any_sync(0xffffffffu, contrib)) continue;
         const float4 q2 = recs[jj].q2;
         // 1 - alpha is in [0.01, 1]: the approximate reciprocal plus one Newton step is exact to an ulp there
@@ -262,6 +271,14 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_bwd_kernel(const BlendArg
     id_cur = id_next;
     id_next = id_after;
   }
+  if (COUNT && a.stats) {
+    const unsigned v[4] = {cntA, cntB, cntD, cntS};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const unsigned t = __reduce_add_sync(0xffffffffu, v[k]);
+      if (lane == 0 && t) atomicAdd(a.stats + 5 + k, (unsigned long long)t);
+    }
+  }
 }
 
 template <bool INTERP, bool DEPTH>
@@ -270,7 +287,12 @@ cudaError_t launch2(const BlendArgs& a, bool tma, cudaStream_t s) {
   const size_t smem = sizeof(BwdSmem);
   cudaError_t e;
   ProfScope ps(K_BLEND_BWD, s);
-  if (tma) {
+  if (a.stats) {
+    auto k = blend_bwd_kernel<INTERP, DEPTH, false, true>;
+    e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    k<<<tiles, BLEND_THREADS, smem, s>>>(a);
+  } else if (tma) {
     auto k = blend_bwd_kernel<INTERP, DEPTH, true>;
     e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;

@@ -17,7 +17,9 @@ struct FwdSmem {
   unsigned long long bar[2];
 };
 
-template <bool INTERP, bool DEPTH, bool TMA>
+// COUNT: the untimed instrumented pass of bench.py -- per (live pixel, evaluated entry) pair, how far it got:
+// stats[0] rejected at power > 0, [1] at alpha < 1/255, [2] at the T test, [3] blended, [4] lane slots issued.
+template <bool INTERP, bool DEPTH, bool TMA, bool COUNT = false>
 __global__ void __launch_bounds__(BLEND_THREADS) blend_fwd_kernel(const BlendArgs a) {
   __shared__ FwdSmem sm;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -70,6 +72,7 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_fwd_kernel(const BlendArg
   float T = inside ? 1.0f : -1.0f;   // sign bit = "done" (saturated, or outside the image)
   float C0 = 0.f, C1 = 0.f, C2 = 0.f, D = 0.f;
   uint32_t last_contributor = 0;
+  unsigned cntA = 0, cntB = 0, cntC = 0, cntD = 0, cntS = 0;
 
   // software pipeline: ids two rounds ahead, records one round ahead
   uint32_t id_next = 0;
@@ -106,7 +109,7 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_fwd_kernel(const BlendArg
         // that does not depend on the running transmittance; survivors are taken two at a time so that two
         // such chains (LDS -> power -> exp -> alpha) are in flight per warp -- what bounds the long horizon
         // tiles that end up alone on their SM.  `apply` then blends in list order.
-        auto eval = [&](int jj, float& alpha, bool& ok) {
+        auto eval = [&](int jj, float& alpha, bool& ok, bool& pos) {
           const float2 xy = *reinterpret_cast<const float2*>(&recs[jj].q0);
           const float4 con_o = recs[jj].q1;
           const float dx = xy.x - pixx, dy = xy.y - pixy;
@@ -122,11 +125,18 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_fwd_kernel(const BlendArg
             }
           }
           ok = !(power > 0.0f) & !(alpha < 1.0f / 255.0f);
+          pos = power > 0.0f;
         };
-        auto apply = [&](int jj, float alpha, bool ok) {
+        auto apply = [&](int jj, float alpha, bool ok, bool pos) {
           // a saturated pixel carries -T: its test_T is negative, so it can never take another entry
           const float test_T = T * (1 - alpha);
           const bool take = ok & !(test_T < 0.0001f);
+          if (COUNT) {
+            if (T > 0.0f) {
+              if (pos) ++cntA; else if (!ok) ++cntB; else if (!take) ++cntC; else ++cntD;
+            }
+            ++cntS;
+          }
           if (ok & !take) T = -fabsf(T);
           const float4 q2 = recs[jj].q2;
           if (take) {
@@ -142,17 +152,17 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_fwd_kernel(const BlendArg
           const int j0 = c + __ffs(m) - 1;
           m &= m - 1;
           float a0, a1;
-          bool k0, k1;
+          bool k0, k1, p0, p1;
           if (m) {
             const int j1 = c + __ffs(m) - 1;
             m &= m - 1;
-            eval(j0, a0, k0);
-            eval(j1, a1, k1);
-            apply(j0, a0, k0);
-            apply(j1, a1, k1);
+            eval(j0, a0, k0, p0);
+            eval(j1, a1, k1, p1);
+            apply(j0, a0, k0, p0);
+            apply(j1, a1, k1, p1);
           } else {
-            eval(j0, a0, k0);
-            apply(j0, a0, k0);
+            eval(j0, a0, k0, p0);
+            apply(j0, a0, k0, p0);
           }
         }
         if (!__any_sync(0xffffffffu, T > 0.0f)) break;
@@ -162,6 +172,14 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_fwd_kernel(const BlendArg
     if (__syncthreads_and(T < 0.0f ? 1 : 0)) break;
   }
 
+  if (COUNT && a.stats) {
+    const unsigned v[5] = {cntA, cntB, cntC, cntD, cntS};
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+      const unsigned t = __reduce_add_sync(0xffffffffu, v[k]);
+      if (lane == 0 && t) atomicAdd(a.stats + k, (unsigned long long)t);
+    }
+  }
   if (a.tile_last) {
     const uint32_t wl = __reduce_max_sync(0xffffffffu, last_contributor);
     if (lane == 0 && wl) atomicMax(a.tile_last + tile, wl);
@@ -184,7 +202,9 @@ template <bool INTERP, bool DEPTH>
 cudaError_t launch2(const BlendArgs& a, bool tma, cudaStream_t s) {
   const int tiles = a.grid_x * a.grid_y;
   ProfScope ps(K_BLEND_FWD, s);
-  if (tma)
+  if (a.stats)
+    blend_fwd_kernel<INTERP, DEPTH, false, true><<<tiles, BLEND_THREADS, 0, s>>>(a);
+  else if (tma)
     blend_fwd_kernel<INTERP, DEPTH, true><<<tiles, BLEND_THREADS, 0, s>>>(a);
   else
     blend_fwd_kernel<INTERP, DEPTH, false><<<tiles, BLEND_THREADS, 0, s>>>(a);

@@ -303,6 +303,7 @@ struct BlendArgs {
   const float* dL_dcolor; const float* dL_dinvdepth; GradRec* grad;  // bwd
   const uint32_t* order;   // CTA i processes tile order[i] (heavy tiles first); NULL = identity
   uint32_t* tile_last;     // fwd: per-tile max of n_contrib (pre-zeroed)
+  unsigned long long* stats;  // instrumented pass (h3dgs_blend_stats): pair-category counters, else NULL
 };
 cudaError_t launch_blend_fwd(const BlendArgs& a, cudaStream_t s);
 cudaError_t launch_blend_bwd(const BlendArgs& a, cudaStream_t s);

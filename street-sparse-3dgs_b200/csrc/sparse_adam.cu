@@ -51,7 +51,51 @@ __global__ void __launch_bounds__(256) sparse_adam_kernel(const AdamPack pk,
   T.param[off] = p;
 }
 
+struct RowPack {
+  H3dgsRowTensor t[8];
+  int start[9];   // prefix sums of widths
+  int n;
+};
+
+// one thread per packed float: element e of packed row k lives in tensor ti at row rows[k]
+template <bool PACK>
+__global__ void __launch_bounds__(256) pack_rows_kernel(const RowPack pk, const long long* __restrict__ rows,
+                                                        long long K, float* __restrict__ packed, float scale) {
+  const int total_w = pk.start[pk.n];
+  const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= K * total_w) return;
+  const long long k = gid / total_w;
+  const int e = (int)(gid - k * total_w);
+  int ti = 0;
+#pragma unroll
+  for (int i = 1; i < 8; ++i)
+    if (i < pk.n && e >= pk.start[i]) ti = i;
+  float* p = pk.t[ti].data + (size_t)rows[k] * pk.t[ti].width + (e - pk.start[ti]);
+  if (PACK) packed[gid] = *p;
+  else *p = packed[gid] * scale;
+}
+
 }  // namespace
+
+cudaError_t run_pack_rows(const H3dgsRowTensor* tensors, int n, const long long* rows, long long K, float* packed,
+                          float scale, bool pack, cudaStream_t s) {
+  RowPack pk;
+  pk.n = n;
+  int acc = 0;
+  for (int i = 0; i < n; ++i) {
+    pk.t[i] = tensors[i];
+    pk.start[i] = acc;
+    acc += tensors[i].width;
+  }
+  for (int i = n; i <= 8; ++i) pk.start[i] = acc;
+  const long long work = K * acc;
+  if (work <= 0) return cudaSuccess;
+  const long long blocks = (work + 255) / 256;
+  ProfScope ps(K_ADAM, s);
+  if (pack) pack_rows_kernel<true><<<(unsigned)blocks, 256, 0, s>>>(pk, rows, K, packed, scale);
+  else pack_rows_kernel<false><<<(unsigned)blocks, 256, 0, s>>>(pk, rows, K, packed, scale);
+  return cudaGetLastError();
+}
 
 cudaError_t run_sparse_adam(const H3dgsAdamTensor* tensors, int n, const long long* relevant,
                             long long num_relevant, long long num_rows, cudaStream_t s) {

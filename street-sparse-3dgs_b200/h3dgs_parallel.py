@@ -47,9 +47,9 @@ def allreduce_dense(tensors: Iterable[torch.Tensor], average: bool = True, group
 
 
 def union_rows(row_mask: torch.Tensor, group=None) -> torch.Tensor:
-    """Row ids (int64, ascending) that are set in ANY rank's boolean mask."""
+    """Row ids (int64, ascending) that are set in ANY rank's boolean mask (one byte per row on the wire)."""
     rank, world = world_info()
-    m = row_mask.to(torch.int32)
+    m = row_mask.to(torch.uint8)
     if world > 1:
         dist.all_reduce(m, op=dist.ReduceOp.MAX, group=group)
     return m.nonzero().flatten()
@@ -67,6 +67,26 @@ def allreduce_sparse_rows(tensors: Sequence[torch.Tensor], row_mask: torch.Tenso
     rows = union_rows(row_mask, group=group)
     if world == 1 or rows.numel() == 0:
         return rows
+    if all(t.is_cuda and t.dtype == torch.float32 and t.is_contiguous() for t in tensors) and len(tensors) <= 8:
+        # device path: ONE gather kernel into a packed [U, sum of widths] payload, ONE all-reduce, ONE scatter
+        # kernel that also applies the 1/world average (h3dgs_pack_rows / h3dgs_unpack_rows)
+        import h3dgs_native as nat
+        L = nat.lib()
+        arr = (nat.RowTensor * len(tensors))()
+        width = 0
+        for i, t in enumerate(tensors):
+            arr[i].data = t.data_ptr()
+            arr[i].width = t[0].numel()
+            width += arr[i].width
+        U = rows.numel()
+        packed = torch.empty((U, width), dtype=torch.float32, device=rows.device)
+        stream = nat.stream_handle()
+        nat.check(L.h3dgs_pack_rows(arr, len(tensors), rows.data_ptr(), U, packed.data_ptr(), stream), "h3dgs_pack_rows")
+        dist.all_reduce(packed, op=dist.ReduceOp.SUM, group=group)
+        nat.check(L.h3dgs_unpack_rows(arr, len(tensors), rows.data_ptr(), U, packed.data_ptr(),
+                                      1.0 / world if average else 1.0, stream), "h3dgs_unpack_rows")
+        return rows
+    # host tensors (the gloo tests of this logic)
     packed = [t.index_select(0, rows) for t in tensors]
     works = [dist.all_reduce(p, op=dist.ReduceOp.SUM, group=group, async_op=True) for p in packed]
     for w in works:

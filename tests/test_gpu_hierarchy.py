@@ -342,3 +342,33 @@ def test_gradient_arena_recycles(monkeypatch):
     for p, ref in zip(model.parameters(), grads[2]):
         assert util.relerr(p.grad, ref) <= 1e-5
     dgr._C.release_gradient_arena()
+
+
+@pytest.mark.gpu
+def test_pack_unpack_rows_match_index_ops():
+    """h3dgs_pack_rows / h3dgs_unpack_rows (the payload of the data-parallel gradient exchange) against
+    index_select / index_copy_ on ragged widths, including an empty row list."""
+    import h3dgs_native as nat
+    L = nat.lib()
+    g = torch.Generator().manual_seed(3)
+    n = 5000
+    widths = (3, 3, 45, 1, 3, 4)
+    tensors = [torch.randn(n, w, generator=g).to(DEV) for w in widths]
+    rows = torch.randperm(n, generator=g)[:1234].sort().values.to(DEV)
+    arr = (nat.RowTensor * len(tensors))()
+    for i, t in enumerate(tensors):
+        arr[i].data, arr[i].width = t.data_ptr(), t.size(1)
+    packed = torch.empty(rows.numel(), sum(widths), device=DEV)
+    nat.check(L.h3dgs_pack_rows(arr, len(tensors), rows.data_ptr(), rows.numel(), packed.data_ptr(),
+                                nat.stream_handle()), "pack")
+    want = torch.cat([t.index_select(0, rows) for t in tensors], dim=1)
+    assert torch.equal(packed, want)
+    before = [t.clone() for t in tensors]
+    nat.check(L.h3dgs_unpack_rows(arr, len(tensors), rows.data_ptr(), rows.numel(), packed.data_ptr(), 0.5,
+                                  nat.stream_handle()), "unpack")
+    for t, b in zip(tensors, before):
+        ref = b.clone()
+        ref[rows] = b[rows] * 0.5
+        assert torch.equal(t, ref)
+    assert L.h3dgs_pack_rows(arr, len(tensors), None, 0, None, nat.stream_handle()) == 0
+    assert L.h3dgs_pack_rows(arr, 0, rows.data_ptr(), 1, packed.data_ptr(), nat.stream_handle()) != 0
