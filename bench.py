@@ -280,13 +280,13 @@ def main():
         # instrumented pass (untimed): how far every evaluated (pixel, entry) pair gets -> FLOP of the blend kernels
         # by the contract of SURVEY.md 8(d) (interp + depth variants): forward 11 / 30 / 32 / 49 FLOP for a pair
         # rejected at power > 0 / at alpha < 1/255 / at the T test / blended; backward 11 / 30 / 100
-        cnt = torch.zeros(9, dtype=torch.int64, device=dev)
+        cnt = torch.zeros(16 + 4 * ((W + 15) // 16) * ((H + 15) // 16), dtype=torch.int64, device=dev)
         nat.lib().h3dgs_blend_stats(cnt.data_ptr())
         for i in range(n_prof):
             resident_step(i)
         torch.cuda.synchronize()
         nat.lib().h3dgs_blend_stats(None)
-        cs = [x / n_prof for x in cnt.tolist()]
+        cs = [x / n_prof for x in cnt[:9].tolist()]
         flop = {"blend_fwd": 11 * cs[0] + 30 * cs[1] + 32 * cs[2] + 49 * cs[3],
                 "blend_bwd": 11 * cs[5] + 30 * cs[6] + 100 * cs[7]}
         sms = torch.cuda.get_device_properties(dev).multi_processor_count

@@ -312,10 +312,12 @@ H3DGS_API int h3dgs_sparse_adam(const H3dgsAdamTensor* tensors, int32_t num_tens
  * ------------------------------------------------------------------------------------------------ */
 #define H3DGS_PROF_KERNELS 16
 /* Instrumented pass for the FLOP accounting of the blend kernels: while `counters` (device,
- * 9 x uint64, zeroed by the caller) is set, the blend kernels run a counting variant and add, per evaluated
+ * (16 + 4 x tiles) x uint64, zeroed by the caller) is set, the blend kernels run a counting variant and add, per evaluated
  * (live pixel, list entry) pair: [0] forward pairs rejected at power > 0, [1] at alpha < 1/255, [2] at the T
  * test, [3] blended, [4] forward lane slots issued; [5] backward pairs rejected at power > 0, [6] at
- * alpha < 1/255, [7] contributing, [8] backward lane slots issued.  NULL switches it off.  Never timed. */
+ * alpha < 1/255, [7] contributing, [8] backward lane slots issued; from word 16 on, four words per tile: global-timer ns
+ * at which the tile's forward CTA started / ended and its backward CTA started / ended (load-balance diagnostics,
+ * harness/diag_balance.py).  NULL switches it off.  Never timed. */
 H3DGS_API int h3dgs_blend_stats(void* counters);
 H3DGS_API int64_t h3dgs_launch_count(void);          /* kernels launched by this library so far (process-wide) */
 H3DGS_API int h3dgs_profile_enable(int enable);      /* returns the previous setting */

@@ -45,6 +45,8 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_bwd_kernel(const BlendArg
   const size_t pix = (size_t)py * a.W + px;
   const size_t plane = (size_t)a.W * a.H;
 
+  unsigned long long t_start = 0;
+  if (COUNT) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));
   const uint2 range = a.ranges[tile];
   const int n = (int)(range.y - range.x);
   const uint32_t* __restrict__ list = a.point_list + range.x;
@@ -272,6 +274,12 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_bwd_kernel(const BlendArg
     id_next = id_after;
   }
   if (COUNT && a.stats) {
+    if (tid == 0) {
+      unsigned long long t_end;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_end));
+      a.stats[16 + 4 * tile + 2] = t_start;
+      a.stats[16 + 4 * tile + 3] = t_end;
+    }
     const unsigned v[4] = {cntA, cntB, cntD, cntS};
 #pragma unroll
     for (int k = 0; k < 4; ++k) {

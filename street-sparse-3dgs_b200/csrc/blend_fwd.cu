@@ -32,6 +32,8 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_fwd_kernel(const BlendArg
   const float pixx = (float)px, pixy = (float)py;
   const float fx0 = (float)bx0, fy0 = (float)by0;
 
+  unsigned long long t_start = 0;
+  if (COUNT) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));
   const uint2 range = a.ranges[tile];
   const int n = (int)(range.y - range.x);
   const int rounds = (n + BLEND_BATCH - 1) / BLEND_BATCH;
@@ -173,6 +175,12 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_fwd_kernel(const BlendArg
   }
 
   if (COUNT && a.stats) {
+    if (tid == 0) {   // per-tile (start, end) in ns of the global timer: load-balance diagnostics
+      unsigned long long t_end;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_end));
+      a.stats[16 + 4 * tile] = t_start;
+      a.stats[16 + 4 * tile + 1] = t_end;
+    }
     const unsigned v[5] = {cntA, cntB, cntC, cntD, cntS};
 #pragma unroll
     for (int k = 0; k < 5; ++k) {
