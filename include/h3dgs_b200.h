@@ -310,7 +310,28 @@ H3DGS_API int h3dgs_sparse_adam(const H3dgsAdamTensor* tensors, int32_t num_tens
  * Instrumentation (no reference counterpart).  Launch counting is always on; per-kernel timing wraps
  * every kernel in a pair of CUDA events on the launching stream while enabled.
  * ------------------------------------------------------------------------------------------------ */
-#define H3DGS_PROF_KERNELS 16
+#define H3DGS_PROF_KERNELS 17
+/*
+ * Fused photometric loss.  Replaces utils/loss_utils.py:17-63 (l1_loss, ssim / _ssim: five
+ * depthwise conv2d, ~15 elementwise kernels and their autograd) as used by train_single.py:116-141 and
+ * train_post.py:132-137.  Images are [C,H,W] fp32; window11 is the HOST array of the 11 normalised Gaussian
+ * weights (loss_utils.py:23-25, sigma 1.5); convolution borders are zero padded like conv2d(padding=5).
+ * Forward: adds the sum of the SSIM map to sums[0] and the sum of |img1 - img2| to sums[1] (device doubles,
+ * zeroed by the caller); optionally writes the map and, when a backward will follow, the three per-pixel partial
+ * derivatives of the map with respect to the windowed moments (mu1, E[img1^2], E[img1 img2]).
+ * Backward: dL_dimg1 = upstream * (conv(g dm_dmu1) + 2 img1 conv(g dm_de11) + img2 conv(g dm_de12)
+ *                                 + l1_scale * sign(img1 - img2)),
+ * g = dL_dmap per pixel, or the uniform ssim_scale when dL_dmap is NULL; upstream is a DEVICE scalar or NULL (= 1).
+ * For loss = (1 - l) * mean|x - y| + l * (1 - mean(ssim)): ssim_scale = -l / (C H W), l1_scale = (1 - l) / (C H W).
+ */
+H3DGS_API int h3dgs_ssim_forward(int32_t C, int32_t H, int32_t W, const float* img1, const float* img2,
+                       const float* window11, float* ssim_map, float* dm_dmu1, float* dm_de11, float* dm_de12,
+                       double* sums, h3dgs_stream_t stream);
+H3DGS_API int h3dgs_ssim_backward(int32_t C, int32_t H, int32_t W, const float* img1, const float* img2,
+                        const float* window11, const float* dm_dmu1, const float* dm_de11, const float* dm_de12,
+                        const float* dL_dmap, const float* upstream, float ssim_scale, float l1_scale,
+                        float* dL_dimg1, h3dgs_stream_t stream);
+
 /* Instrumented pass for the FLOP accounting of the blend kernels: while `counters` (device,
  * (16 + 4 x tiles) x uint64, zeroed by the caller) is set, the blend kernels run a counting variant and add, per evaluated
  * (live pixel, list entry) pair: [0] forward pairs rejected at power > 0, [1] at alpha < 1/255, [2] at the T

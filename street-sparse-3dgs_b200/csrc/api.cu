@@ -39,7 +39,7 @@ struct Prof {
 const char* const kKernelNames[K_COUNT] = {
   "preprocess_fwd", "scan", "emit_instances", "sort_histogram", "sort_scan", "sort_onesweep_pass",
   "tile_ranges", "blend_fwd", "blend_bwd", "preprocess_bwd", "cut_mark_nodes", "cut_put_indices",
-  "cut_interp_weights", "sparse_adam", "mark_visible", "memset"};
+  "cut_interp_weights", "sparse_adam", "mark_visible", "memset", "loss"};
 }  // namespace
 
 void prof_begin(int id, cudaStream_t s) {
@@ -147,6 +147,13 @@ cudaError_t run_interpolation_weights(int K, const int* indices, float target_si
                                       int* kids, cudaStream_t s);
 cudaError_t run_sparse_adam(const H3dgsAdamTensor* tensors, int n, const long long* relevant,
                             long long num_relevant, long long num_rows, cudaStream_t s);
+cudaError_t run_ssim_forward(int C, int H, int W, const float* img1, const float* img2, const float* window,
+                             float* ssim_map, float* dm_dmu1, float* dm_de11, float* dm_de12, double* sums,
+                             cudaStream_t s);
+cudaError_t run_ssim_backward(int C, int H, int W, const float* img1, const float* img2, const float* window,
+                              const float* dm_dmu1, const float* dm_de11, const float* dm_de12,
+                              const float* dL_dmap, const float* upstream, float ssim_scale, float l1_scale,
+                              float* dL_dimg1, cudaStream_t s);
 cudaError_t run_pack_rows(const H3dgsRowTensor* tensors, int n, const long long* rows, long long K, float* packed,
                           float scale, bool pack, cudaStream_t s);
 
@@ -396,6 +403,7 @@ int h3dgs_backward(const H3dgsView* view, const H3dgsGaussians* g, const int32_t
   PreBwdArgs pb;
   pb.f = make_pre(view, g, const_cast<int*>(radii), const_cast<void*>(geom));
   pb.grad = ww.grad;
+  pb.vis_list = ww.vis_list;
   pb.has_invdepth = dL_dout_invdepth != nullptr;
   pb.out = *grads;
   H3_CUDA(launch_preprocess_bwd(pb, s));
@@ -592,6 +600,34 @@ int h3dgs_pack_rows(const H3dgsRowTensor* tensors, int32_t num_tensors, const in
 int h3dgs_unpack_rows(const H3dgsRowTensor* tensors, int32_t num_tensors, const int64_t* rows, int64_t num_rows,
                       const float* packed, float scale, h3dgs_stream_t stream) {
   return pack_rows_common(tensors, num_tensors, rows, num_rows, const_cast<float*>(packed), scale, false, stream);
+}
+
+int h3dgs_ssim_forward(int32_t C, int32_t H, int32_t W, const float* img1, const float* img2, const float* window11,
+                       float* ssim_map, float* dm_dmu1, float* dm_de11, float* dm_de12, double* sums,
+                       h3dgs_stream_t stream) {
+  if (C < 0 || H < 0 || W < 0) return fail(H3DGS_EINVAL, "h3dgs_ssim_forward: negative size");
+  if (C == 0 || H == 0 || W == 0) return 0;
+  if (C > 65535) return fail(H3DGS_EINVAL, "h3dgs_ssim_forward: more than 65535 channels");
+  if (!img1 || !img2 || !window11 || !sums) return fail(H3DGS_EINVAL, "h3dgs_ssim_forward: img1, img2, window and sums are required");
+  if ((dm_dmu1 != nullptr) != (dm_de11 != nullptr) || (dm_dmu1 != nullptr) != (dm_de12 != nullptr))
+    return fail(H3DGS_EINVAL, "h3dgs_ssim_forward: pass all three derivative maps or none");
+  H3_CUDA(run_ssim_forward(C, H, W, img1, img2, window11, ssim_map, dm_dmu1, dm_de11, dm_de12, sums,
+                           (cudaStream_t)stream));
+  return 0;
+}
+
+int h3dgs_ssim_backward(int32_t C, int32_t H, int32_t W, const float* img1, const float* img2, const float* window11,
+                        const float* dm_dmu1, const float* dm_de11, const float* dm_de12, const float* dL_dmap,
+                        const float* upstream, float ssim_scale, float l1_scale, float* dL_dimg1,
+                        h3dgs_stream_t stream) {
+  if (C < 0 || H < 0 || W < 0) return fail(H3DGS_EINVAL, "h3dgs_ssim_backward: negative size");
+  if (C == 0 || H == 0 || W == 0) return 0;
+  if (C > 65535) return fail(H3DGS_EINVAL, "h3dgs_ssim_backward: more than 65535 channels");
+  if (!img1 || !img2 || !window11 || !dm_dmu1 || !dm_de11 || !dm_de12 || !dL_dimg1)
+    return fail(H3DGS_EINVAL, "h3dgs_ssim_backward: null argument");
+  H3_CUDA(run_ssim_backward(C, H, W, img1, img2, window11, dm_dmu1, dm_de11, dm_de12, dL_dmap, upstream, ssim_scale,
+                            l1_scale, dL_dimg1, (cudaStream_t)stream));
+  return 0;
 }
 
 int h3dgs_blend_stats(void* counters) {

@@ -214,12 +214,14 @@ struct BinWs {
 
 struct BwdWs {
   GradRec* grad;
+  uint32_t* vis_list;   // visible slots in slot order (compacted for the per-slot backward kernel)
   size_t bytes;
   static BwdWs make(void* base, int P) {
     BwdWs w;
     char* p = reinterpret_cast<char*>(base);
     char* p0 = p;
     carve(p, w.grad, (size_t)(P > 0 ? P : 1));
+    carve(p, w.vis_list, (size_t)(P > 0 ? P : 1));
     w.bytes = (size_t)(p - p0) + 256;
     return w;
   }
@@ -238,7 +240,7 @@ int cuda_fail(cudaError_t e, const char* what);
 enum KernelId {
   K_PREPROCESS_FWD = 0, K_SCAN, K_EMIT, K_SORT_HIST, K_SORT_SCAN, K_SORT_PASS, K_TILE_RANGES, K_BLEND_FWD,
   K_BLEND_BWD, K_PREPROCESS_BWD, K_CUT_MARK, K_CUT_PUT, K_CUT_WEIGHTS, K_ADAM, K_MARK_VISIBLE, K_MEMSET,
-  K_COUNT
+  K_LOSS, K_COUNT
 };
 static_assert(K_COUNT == H3DGS_PROF_KERNELS, "kernel id table out of sync with the header");
 void prof_begin(int id, cudaStream_t s);
@@ -313,6 +315,7 @@ struct PreBwdArgs {
   const GradRec* grad;
   int has_invdepth;
   H3dgsGrads out;
+  uint32_t* vis_list;
 };
 cudaError_t launch_preprocess_bwd(const PreBwdArgs& a, cudaStream_t s);
 

@@ -1,0 +1,220 @@
+// Fused photometric loss: L1 + SSIM (11x11 Gaussian window) forward and backward.
+// Replaces utils/loss_utils.py:17-63 (l1_loss, ssim / _ssim: five depthwise conv2d passes, ~15 elementwise
+// kernels and their autograd) as used by train_single.py:116-141 and train_post.py:132-137.
+//
+// Forward, one pass over the two images: a 16x16 pixel tile (+5 halo, zero padded like conv2d(padding=5)) of both
+// images is staged in shared memory, the five windowed moments (mu1, mu2, E[x^2], E[y^2], E[xy]) are formed
+// separably (11 horizontal taps, then 11 vertical taps -- the 2-D window of create_window is the outer product
+// of the 1-D one), the SSIM map value and its three partial derivatives with respect to (mu1, E[x^2], E[xy]) are
+// computed per pixel, and the tile's sums of SSIM and |x - y| go to two double accumulators.
+// Backward: d loss / d x = conv(g dm/dmu1) + 2 x conv(g dm/dE11) + y conv(g dm/dE12) + l1 term, the same zero-padded
+// separable convolution applied to the three derivative maps (the window is symmetric).
+#include <cstring>
+
+#include "common.cuh"
+
+namespace h3dgs {
+
+namespace {
+
+constexpr int LT = 16;          // tile edge
+constexpr int LH = 5;           // halo (window_size // 2)
+constexpr int LW = LT + 2 * LH; // 26
+
+struct LossArgs {
+  int C, H, W;
+  const float* img1;      // rendered image [C,H,W]
+  const float* img2;      // ground truth   [C,H,W]
+  float w[11];            // normalised 1-D Gaussian window (utils/loss_utils.py:23-25)
+  float* ssim_map;        // [C,H,W] or NULL
+  float* dm_dmu1;         // [C,H,W] or NULL (no gradient wanted)
+  float* dm_de11;
+  float* dm_de12;
+  double* sums;           // [0] += sum of the SSIM map, [1] += sum of |img1 - img2|
+  // backward
+  const float* dL_dmap;   // [C,H,W] per-pixel upstream gradient of the SSIM map, or NULL: uniform *ssim_scale
+  const float* upstream;  // device scalar multiplied into both terms (d total / d loss), or NULL = 1
+  float ssim_scale;       // d loss / d map value (uniform case), e.g. -lambda / (C H W)
+  float l1_scale;         // d loss / d |x - y|, e.g. (1 - lambda) / (C H W); 0 = no L1 term
+  float* dL_dimg1;        // [C,H,W]
+};
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+  return v;
+}
+
+template <bool GRAD>
+__global__ void __launch_bounds__(LT * LT) ssim_fwd_kernel(const LossArgs a) {
+  __shared__ float s1[LW][LW + 1], s2[LW][LW + 1];
+  __shared__ float hz[5][LW][LT];
+  __shared__ float red[2][LT * LT / 32];
+  const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * LT + tx;
+  const int x0 = blockIdx.x * LT, y0 = blockIdx.y * LT, ch = blockIdx.z;
+  const size_t plane = (size_t)a.H * a.W;
+  const float* __restrict__ p1 = a.img1 + ch * plane;
+  const float* __restrict__ p2 = a.img2 + ch * plane;
+
+  for (int i = tid; i < LW * LW; i += LT * LT) {
+    const int ly = i / LW, lx = i - ly * LW;
+    const int gy = y0 + ly - LH, gx = x0 + lx - LH;
+    float v1 = 0.f, v2 = 0.f;
+    if (gy >= 0 && gy < a.H && gx >= 0 && gx < a.W) {
+      v1 = __ldg(p1 + (size_t)gy * a.W + gx);
+      v2 = __ldg(p2 + (size_t)gy * a.W + gx);
+    }
+    s1[ly][lx] = v1;
+    s2[ly][lx] = v2;
+  }
+  __syncthreads();
+  for (int i = tid; i < LW * LT; i += LT * LT) {
+    const int row = i / LT, col = i - row * LT;
+    float m1 = 0.f, m2 = 0.f, e11 = 0.f, e22 = 0.f, e12 = 0.f;
+#pragma unroll
+    for (int k = 0; k < 11; ++k) {
+      const float wk = a.w[k], u = s1[row][col + k], v = s2[row][col + k];
+      m1 += wk * u;
+      m2 += wk * v;
+      e11 += wk * (u * u);
+      e22 += wk * (v * v);
+      e12 += wk * (u * v);
+    }
+    hz[0][row][col] = m1; hz[1][row][col] = m2; hz[2][row][col] = e11; hz[3][row][col] = e22; hz[4][row][col] = e12;
+  }
+  __syncthreads();
+  float mu1 = 0.f, mu2 = 0.f, e11 = 0.f, e22 = 0.f, e12 = 0.f;
+#pragma unroll
+  for (int k = 0; k < 11; ++k) {
+    const float wk = a.w[k];
+    mu1 += wk * hz[0][ty + k][tx];
+    mu2 += wk * hz[1][ty + k][tx];
+    e11 += wk * hz[2][ty + k][tx];
+    e22 += wk * hz[3][ty + k][tx];
+    e12 += wk * hz[4][ty + k][tx];
+  }
+  const int gx = x0 + tx, gy = y0 + ty;
+  const bool inside = gx < a.W && gy < a.H;
+  float map = 0.f, ad = 0.f;
+  if (inside) {
+    // utils/loss_utils.py:43-56
+    const float C1 = 0.01f * 0.01f, C2 = 0.03f * 0.03f;
+    const float mu1_sq = mu1 * mu1, mu2_sq = mu2 * mu2, mu1_mu2 = mu1 * mu2;
+    const float sigma1_sq = e11 - mu1_sq, sigma2_sq = e22 - mu2_sq, sigma12 = e12 - mu1_mu2;
+    const float A = 2.f * mu1_mu2 + C1, B = 2.f * sigma12 + C2;
+    const float Cc = mu1_sq + mu2_sq + C1, D = sigma1_sq + sigma2_sq + C2;
+    const float inv = 1.f / (Cc * D);
+    map = (A * B) * inv;
+    const size_t o = ch * plane + (size_t)gy * a.W + gx;
+    if (a.ssim_map) a.ssim_map[o] = map;
+    ad = fabsf(s1[ty + LH][tx + LH] - s2[ty + LH][tx + LH]);
+    if (GRAD) {
+      // with sigma1_sq = E11 - mu1^2 and sigma12 = E12 - mu1 mu2 substituted
+      a.dm_dmu1[o] = 2.f * mu2 * (B - A) * inv - map * (2.f * mu1 * (D - Cc)) * inv;
+      a.dm_de11[o] = -map / D;
+      a.dm_de12[o] = 2.f * A * inv;
+    }
+  }
+  const float sm = warp_sum(map), sa = warp_sum(ad);
+  if ((tid & 31) == 0) { red[0][tid >> 5] = sm; red[1][tid >> 5] = sa; }
+  __syncthreads();
+  if (tid < 2) {
+    double t = 0.0;
+    for (int i = 0; i < LT * LT / 32; ++i) t += (double)red[tid][i];
+    atomicAdd(a.sums + tid, t);
+  }
+}
+
+__global__ void __launch_bounds__(LT * LT) ssim_bwd_kernel(const LossArgs a) {
+  __shared__ float s[3][LW][LW + 1];
+  __shared__ float hz[3][LW][LT];
+  const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * LT + tx;
+  const int x0 = blockIdx.x * LT, y0 = blockIdx.y * LT, ch = blockIdx.z;
+  const size_t plane = (size_t)a.H * a.W;
+  const size_t base = ch * plane;
+  for (int i = tid; i < LW * LW; i += LT * LT) {
+    const int ly = i / LW, lx = i - ly * LW;
+    const int gy = y0 + ly - LH, gx = x0 + lx - LH;
+    float v0 = 0.f, v1 = 0.f, v2 = 0.f;
+    if (gy >= 0 && gy < a.H && gx >= 0 && gx < a.W) {
+      const size_t o = base + (size_t)gy * a.W + gx;
+      const float g = a.dL_dmap ? __ldg(a.dL_dmap + o) : 1.0f;
+      v0 = g * __ldg(a.dm_dmu1 + o);
+      v1 = g * __ldg(a.dm_de11 + o);
+      v2 = g * __ldg(a.dm_de12 + o);
+    }
+    s[0][ly][lx] = v0; s[1][ly][lx] = v1; s[2][ly][lx] = v2;
+  }
+  __syncthreads();
+  for (int i = tid; i < LW * LT; i += LT * LT) {
+    const int row = i / LT, col = i - row * LT;
+    float c0 = 0.f, c1 = 0.f, c2 = 0.f;
+#pragma unroll
+    for (int k = 0; k < 11; ++k) {
+      const float wk = a.w[k];
+      c0 += wk * s[0][row][col + k];
+      c1 += wk * s[1][row][col + k];
+      c2 += wk * s[2][row][col + k];
+    }
+    hz[0][row][col] = c0; hz[1][row][col] = c1; hz[2][row][col] = c2;
+  }
+  __syncthreads();
+  const int gx = x0 + tx, gy = y0 + ty;
+  if (gx >= a.W || gy >= a.H) return;
+  float c0 = 0.f, c1 = 0.f, c2 = 0.f;
+#pragma unroll
+  for (int k = 0; k < 11; ++k) {
+    const float wk = a.w[k];
+    c0 += wk * hz[0][ty + k][tx];
+    c1 += wk * hz[1][ty + k][tx];
+    c2 += wk * hz[2][ty + k][tx];
+  }
+  const size_t o = base + (size_t)gy * a.W + gx;
+  const float x = __ldg(a.img1 + o), y = __ldg(a.img2 + o);
+  const float up = a.upstream ? __ldg(a.upstream) : 1.0f;
+  float g = (c0 + 2.f * x * c1 + y * c2) * (a.dL_dmap ? 1.0f : a.ssim_scale);
+  if (a.l1_scale != 0.f) {
+    const float d = x - y;
+    g += a.l1_scale * (d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f));   // torch.abs backward: sign(x - y)
+  }
+  a.dL_dimg1[o] = g * up;
+}
+
+LossArgs make_args(int C, int H, int W, const float* img1, const float* img2, const float* window) {
+  LossArgs a;
+  std::memset(&a, 0, sizeof(a));
+  a.C = C; a.H = H; a.W = W; a.img1 = img1; a.img2 = img2;
+  for (int i = 0; i < 11; ++i) a.w[i] = window[i];
+  return a;
+}
+
+}  // namespace
+
+cudaError_t run_ssim_forward(int C, int H, int W, const float* img1, const float* img2, const float* window,
+                             float* ssim_map, float* dm_dmu1, float* dm_de11, float* dm_de12, double* sums,
+                             cudaStream_t s) {
+  LossArgs a = make_args(C, H, W, img1, img2, window);
+  a.ssim_map = ssim_map; a.dm_dmu1 = dm_dmu1; a.dm_de11 = dm_de11; a.dm_de12 = dm_de12; a.sums = sums;
+  const dim3 grid((W + LT - 1) / LT, (H + LT - 1) / LT, C), block(LT, LT);
+  ProfScope ps(K_LOSS, s);
+  if (dm_dmu1) ssim_fwd_kernel<true><<<grid, block, 0, s>>>(a);
+  else ssim_fwd_kernel<false><<<grid, block, 0, s>>>(a);
+  return cudaGetLastError();
+}
+
+cudaError_t run_ssim_backward(int C, int H, int W, const float* img1, const float* img2, const float* window,
+                              const float* dm_dmu1, const float* dm_de11, const float* dm_de12,
+                              const float* dL_dmap, const float* upstream, float ssim_scale, float l1_scale,
+                              float* dL_dimg1, cudaStream_t s) {
+  LossArgs a = make_args(C, H, W, img1, img2, window);
+  a.dm_dmu1 = const_cast<float*>(dm_dmu1); a.dm_de11 = const_cast<float*>(dm_de11);
+  a.dm_de12 = const_cast<float*>(dm_de12);
+  a.dL_dmap = dL_dmap; a.upstream = upstream; a.ssim_scale = ssim_scale; a.l1_scale = l1_scale;
+  a.dL_dimg1 = dL_dimg1;
+  const dim3 grid((W + LT - 1) / LT, (H + LT - 1) / LT, C), block(LT, LT);
+  ProfScope ps(K_LOSS, s);
+  ssim_bwd_kernel<<<grid, block, 0, s>>>(a);
+  return cudaGetLastError();
+}
+
+}  // namespace h3dgs

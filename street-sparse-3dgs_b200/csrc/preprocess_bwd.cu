@@ -64,43 +64,58 @@ __device__ __forceinline__ void put2(float* base, size_t row, int width, int k, 
   }
 }
 
+// Pass 1, one thread per slot: culled slots get their zero rows (plain mode: of every output; fused-cut mode: of
+// dL_dmeans2D only, the store rows are zero-filled by the caller), visible slots are listed in slot order.
 template <bool FUSED>
-__global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdArgs b) {
+__global__ void __launch_bounds__(256) list_visible_kernel(const PreBwdArgs b) {
   const PreArgs& a = b.f;
   const int t_idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (t_idx >= a.P) return;
   const H3dgsGrads& o = b.out;
   const int M = a.M;
-  const bool visible = a.radii[t_idx] > 0;
-
-  if (!visible) {
-    if (o.dL_dmeans2D) {
-      o.dL_dmeans2D[(size_t)t_idx * 3] = 0.f;
-      o.dL_dmeans2D[(size_t)t_idx * 3 + 1] = 0.f;
-      o.dL_dmeans2D[(size_t)t_idx * 3 + 2] = 0.f;
-    }
-    if (!FUSED) {
-      const size_t r = (size_t)t_idx;
-      if (o.dL_dmeans3D) { o.dL_dmeans3D[r * 3] = 0.f; o.dL_dmeans3D[r * 3 + 1] = 0.f; o.dL_dmeans3D[r * 3 + 2] = 0.f; }
-      if (o.dL_dcolors) { o.dL_dcolors[r * 3] = 0.f; o.dL_dcolors[r * 3 + 1] = 0.f; o.dL_dcolors[r * 3 + 2] = 0.f; }
-      if (o.dL_dopacity) o.dL_dopacity[r] = 0.f;
-      if (o.dL_dscales) { o.dL_dscales[r * 3] = 0.f; o.dL_dscales[r * 3 + 1] = 0.f; o.dL_dscales[r * 3 + 2] = 0.f; }
-      if (o.dL_drotations) *reinterpret_cast<float4*>(o.dL_drotations + r * 4) = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (o.dL_dcov3D) for (int i = 0; i < 6; ++i) o.dL_dcov3D[r * 6 + i] = 0.f;
-      if (o.dL_dsh && o.dL_dsh_rest) {
-        for (int i = 0; i < 3; ++i) o.dL_dsh[r * 3 + i] = 0.f;
-        for (int i = 0; i < (M - 1) * 3; ++i) o.dL_dsh_rest[r * (size_t)(M - 1) * 3 + i] = 0.f;
-      } else if (o.dL_dsh) {
-        float* d = o.dL_dsh + r * (size_t)M * 3;
-        if (((M * 3) & 3) == 0 && ((reinterpret_cast<size_t>(o.dL_dsh) & 15) == 0)) {
-          for (int i = 0; i < M * 3 / 4; ++i) reinterpret_cast<float4*>(d)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-        } else {
-          for (int i = 0; i < M * 3; ++i) d[i] = 0.f;
-        }
-      }
-    }
+  if (a.radii[t_idx] > 0) {
+    b.vis_list[a.ws.offsets[t_idx] - 1u] = (uint32_t)t_idx;
     return;
   }
+  if (o.dL_dmeans2D) {
+    o.dL_dmeans2D[(size_t)t_idx * 3] = 0.f;
+    o.dL_dmeans2D[(size_t)t_idx * 3 + 1] = 0.f;
+    o.dL_dmeans2D[(size_t)t_idx * 3 + 2] = 0.f;
+  }
+  if (!FUSED) {
+    const size_t r = (size_t)t_idx;
+    if (o.dL_dmeans3D) { o.dL_dmeans3D[r * 3] = 0.f; o.dL_dmeans3D[r * 3 + 1] = 0.f; o.dL_dmeans3D[r * 3 + 2] = 0.f; }
+    if (o.dL_dcolors) { o.dL_dcolors[r * 3] = 0.f; o.dL_dcolors[r * 3 + 1] = 0.f; o.dL_dcolors[r * 3 + 2] = 0.f; }
+    if (o.dL_dopacity) o.dL_dopacity[r] = 0.f;
+    if (o.dL_dscales) { o.dL_dscales[r * 3] = 0.f; o.dL_dscales[r * 3 + 1] = 0.f; o.dL_dscales[r * 3 + 2] = 0.f; }
+    if (o.dL_drotations) *reinterpret_cast<float4*>(o.dL_drotations + r * 4) = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (o.dL_dcov3D) for (int i = 0; i < 6; ++i) o.dL_dcov3D[r * 6 + i] = 0.f;
+    if (o.dL_dsh && o.dL_dsh_rest) {
+      for (int i = 0; i < 3; ++i) o.dL_dsh[r * 3 + i] = 0.f;
+      for (int i = 0; i < (M - 1) * 3; ++i) o.dL_dsh_rest[r * (size_t)(M - 1) * 3 + i] = 0.f;
+    } else if (o.dL_dsh) {
+      float* d = o.dL_dsh + r * (size_t)M * 3;
+      if (((M * 3) & 3) == 0 && ((reinterpret_cast<size_t>(o.dL_dsh) & 15) == 0)) {
+        for (int i = 0; i < M * 3 / 4; ++i) reinterpret_cast<float4*>(d)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+      } else {
+        for (int i = 0; i < M * 3; ++i) d[i] = 0.f;
+      }
+    }
+  }
+}
+
+// Pass 2, one thread per VISIBLE slot (typically a quarter of the slots of a cut: launching over all slots left
+// three lanes in four idle through ~1500 instructions of a latency-bound kernel).  The grid covers P; CTAs
+// beyond the visible count, which the forward left in the geometry workspace, exit at once.
+template <bool FUSED>
+__global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdArgs b) {
+  const PreArgs& a = b.f;
+  const unsigned long long V = *reinterpret_cast<const unsigned long long*>(a.ws.counters + 2);
+  const unsigned long long vi = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (vi >= V) return;
+  const int t_idx = (int)b.vis_list[vi];
+  const H3dgsGrads& o = b.out;
+  const int M = a.M;
 
   // ---- which rows? (same decode as the forward) ----
   size_t r = (size_t)t_idx;
@@ -463,10 +478,13 @@ cudaError_t launch_preprocess_bwd(const PreBwdArgs& b, cudaStream_t s) {
   if (b.f.P <= 0) return cudaSuccess;
   const int blocks = (b.f.P + 255) / 256;
   ProfScope ps(K_PREPROCESS_BWD, s);
-  if (b.f.idx != nullptr)
+  if (b.f.idx != nullptr) {
+    list_visible_kernel<true><<<blocks, 256, 0, s>>>(b);
     preprocess_bwd_kernel<true><<<blocks, 256, 0, s>>>(b);
-  else
+  } else {
+    list_visible_kernel<false><<<blocks, 256, 0, s>>>(b);
     preprocess_bwd_kernel<false><<<blocks, 256, 0, s>>>(b);
+  }
   return cudaGetLastError();
 }
 

@@ -106,13 +106,17 @@ SIGNATURES = {
     "h3dgs_sparse_adam": (c_int, [POINTER(AdamTensor), c_int32, c_void_p, c_int64, c_int64, c_void_p]),
     "h3dgs_pack_rows": (c_int, [POINTER(RowTensor), c_int32, c_void_p, c_int64, c_void_p, c_void_p]),
     "h3dgs_unpack_rows": (c_int, [POINTER(RowTensor), c_int32, c_void_p, c_int64, c_void_p, c_float, c_void_p]),
+    "h3dgs_ssim_forward": (c_int, [c_int32, c_int32, c_int32, c_void_p, c_void_p, POINTER(c_float), c_void_p, c_void_p,
+                                    c_void_p, c_void_p, c_void_p, c_void_p]),
+    "h3dgs_ssim_backward": (c_int, [c_int32, c_int32, c_int32, c_void_p, c_void_p, POINTER(c_float), c_void_p, c_void_p,
+                                     c_void_p, c_void_p, c_void_p, c_float, c_float, c_void_p, c_void_p]),
     "h3dgs_blend_stats": (c_int, [c_void_p]),
     "h3dgs_launch_count": (c_int64, []),
     "h3dgs_profile_enable": (c_int, [c_int]),
     "h3dgs_profile_read": (c_int, [POINTER(ctypes.c_double), POINTER(c_int64), c_int]),
     "h3dgs_profile_name": (c_char_p, [c_int]),
 }
-PROF_KERNELS = 16
+PROF_KERNELS = 17
 
 
 def profile_read(reset=True):

@@ -1,0 +1,30 @@
+"""The CPU restatement of the photometric loss (oracle/loss_reference.py) against fixtures produced by the
+reference's own utils/loss_utils.py (tests/golden/make_golden_loss.py)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import loss_reference as lr
+
+GOLD = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "loss_l1_ssim.npz"))
+
+
+@pytest.mark.parametrize("name", ["a", "b", "c", "d"])
+def test_loss_oracle_matches_reference_fixture(name):
+    img = torch.from_numpy(GOLD[f"{name}_image"]).requires_grad_(True)
+    gt = torch.from_numpy(GOLD[f"{name}_gt"])
+    lam = float(GOLD[f"{name}_lam"])
+    loss, ll1 = lr.l1_ssim_loss(img, gt, lam)
+    loss.backward()
+    assert abs(ll1.item() - float(GOLD[f"{name}_l1"])) <= 1e-7
+    assert abs(lr.ssim(img.detach(), gt).item() - float(GOLD[f"{name}_ssim"])) <= 1e-6
+    assert abs(loss.item() - float(GOLD[f"{name}_loss"])) <= 1e-6
+    np.testing.assert_allclose(img.grad.numpy(), GOLD[f"{name}_grad"], rtol=1e-5, atol=1e-9)
+
+
+def test_window_is_the_reference_window():
+    w = lr.gaussian(11, 1.5)
+    assert abs(float(w.sum()) - 1.0) < 1e-6 and torch.equal(w, w.flip(0)) and float(w[5]) == float(w.max())
+    assert lr.create_window(11, 3).shape == (3, 1, 11, 11)

@@ -1,0 +1,82 @@
+"""Fused L1 + SSIM loss kernels (csrc/loss.cu through the C ABI and the utils.loss_utils drop-in) against the
+reference-made fixtures and the CPU oracle.  fp32 with a different (separable) summation order than cuDNN's/MKL's
+2-D depthwise convolution: values within 2e-6 absolute, gradients within 1e-4 relative of the largest entry."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from harness import add_paths
+
+add_paths()
+from oracle import loss_reference as lr  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+GOLD = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "loss_l1_ssim.npz"))
+
+
+def rel(a, b):
+    return float((a.double() - b.double()).abs().max() / (b.double().abs().max() + 1e-30))
+
+
+@pytest.mark.parametrize("name", ["a", "b", "c", "d"])
+def test_fused_loss_matches_reference_fixture(name):
+    from utils import loss_utils as lu
+    img = torch.from_numpy(GOLD[f"{name}_image"]).to(DEV).requires_grad_(True)
+    gt = torch.from_numpy(GOLD[f"{name}_gt"]).to(DEV)
+    lam = float(GOLD[f"{name}_lam"])
+    loss, ll1 = lu.fused_l1_ssim_loss(img, gt, lam)
+    loss.backward()
+    assert abs(ll1.item() - float(GOLD[f"{name}_l1"])) <= 2e-6
+    assert abs(loss.item() - float(GOLD[f"{name}_loss"])) <= 2e-6
+    assert abs(lu.ssim(img.detach(), gt).item() - float(GOLD[f"{name}_ssim"])) <= 2e-6
+    assert rel(img.grad.cpu(), torch.from_numpy(GOLD[f"{name}_grad"])) <= 1e-4
+    assert not ll1.requires_grad
+
+
+@pytest.mark.parametrize("shape", [(3, 1080, 1920), (3, 137, 211), (1, 16, 16), (2, 3, 40, 56), (3, 5, 300)])
+def test_ssim_matches_cpu_oracle(shape):
+    from utils import loss_utils as lu
+    g = torch.Generator().manual_seed(sum(shape))
+    gt = torch.rand(shape, generator=g)
+    img = (gt + 0.2 * torch.randn(shape, generator=g)).clamp(0, 1)
+    a = img.clone().requires_grad_(True)
+    b4 = gt if gt.dim() == 4 else gt.unsqueeze(0)
+    want_map = lr.ssim_map(a if a.dim() == 4 else a.unsqueeze(0), b4)
+    want = want_map.mean()
+    up = torch.tensor(0.37)
+    (want * up).backward()
+    x = img.to(DEV).requires_grad_(True)
+    got = lu.ssim(x, gt.to(DEV))
+    (got * up.to(DEV)).backward()
+    assert abs(got.item() - want.item()) <= 2e-6
+    assert rel(x.grad.cpu(), a.grad) <= 1e-4
+    m = lu.ssim_map(img.to(DEV), gt.to(DEV)).cpu()
+    assert float((m.reshape(want_map.shape) - want_map.detach()).abs().max()) <= 2e-5
+    if len(shape) == 4:   # size_average=False: one value per batch entry (loss_utils.py:62-63)
+        per = lu.ssim(img.to(DEV), gt.to(DEV), size_average=False).cpu()
+        assert torch.allclose(per, want_map.detach().mean(1).mean(1).mean(1), atol=2e-6)
+
+
+def test_identical_images_and_argument_checks():
+    from utils import loss_utils as lu
+    x = torch.rand(3, 64, 64, device=DEV)
+    assert abs(lu.ssim(x, x.clone()).item() - 1.0) <= 1e-6
+    loss, ll1 = lu.fused_l1_ssim_loss(x, x.clone(), 0.2)
+    assert abs(loss.item()) <= 1e-6 and ll1.item() == 0.0
+    with pytest.raises(ValueError):
+        lu.ssim(x.cpu(), x.cpu())
+    with pytest.raises(TypeError):
+        lu.ssim(x.double(), x.double())
+    with pytest.raises(RuntimeError):
+        lu.ssim(x, x[:, :32])
+    with pytest.raises(NotImplementedError):
+        lu.ssim(x, x, window_size=7)
+    # no gradient requested: no derivative maps are produced, the value is the same
+    y = (x + 0.1).clamp(0, 1)
+    with torch.no_grad():
+        v0 = lu.ssim(y, x)
+    v1 = lu.ssim(y.clone().requires_grad_(True), x)
+    assert v0.item() == pytest.approx(v1.item(), abs=1e-7)
