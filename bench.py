@@ -314,6 +314,12 @@ def main():
                         "note": "the blend kernels are bound by issue slots / the FP32 pipe, not by HBM (ncu: issue "
                                 "slots ~85 % busy, DRAM ~1 %): the HBM fraction is reported as the contract asks, the "
                                 "FP32 figure next to it is the meaningful one"}
+            try:   # DRAM traffic of the same kernel from the committed ncu --set full capture (per launch)
+                tr = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+                roofline["traffic"] = tr[top]["dram_bytes_per_launch"]
+                roofline["traffic_source"] = tr["_source"]
+            except Exception:
+                pass
             if top in flop:
                 roofline["fp32"] = {"achieved": kernels[top]["fp32_tflops"], "peak": fp32_peak, "unit": "TFLOP/s",
                                     "frac": kernels[top]["fp32_frac"],

@@ -26,11 +26,13 @@ def main(path):
     total = 0.0
     for r in rows[s:e]:
         n = r[4]
-        ours = "h3dgs::" in n
+        ours = "h3dgs::" in n or any(k in n for k in ("fill_spans_kernel", "zero_rows_kernel", "fill_zero_kernel"))
         key = re.sub(r"\(.*", "", n)
         key = key.replace("void ", "").replace("h3dgs::<unnamed>::", "h3dgs::")
         if not ours:
             key = "torch: " + key[:70]
+        elif "h3dgs::" not in key:
+            key = "h3dgs::" + key
         t = float(r[-1]) / 1e3
         total += t
         a = agg.setdefault(key, [0.0, 0, r[8], r[7]])
