@@ -233,4 +233,36 @@ __device__ __forceinline__ float4 act_rotation_grad(int act, int variant, const 
   return r;
 }
 
+
+// Visit the 45 consecutive floats of a `_features_rest` row (180 bytes, only 4-byte aligned: the 16-byte phase
+// depends on the row id) with the widest aligned loads: f(i, value) for i = 0..44, i a compile-time constant
+// after unrolling.  11 or 12 load instructions per row instead of 45 -- the per-slot kernels are bound by the
+// number of memory operations of their scattered rows, not by bytes.
+template <int HEAD, typename F>
+__device__ __forceinline__ void row45_aligned(const float* __restrict__ q, F&& f) {
+  if (HEAD == 1 || HEAD == 3) f(0, __ldg(q));
+  if (HEAD == 2) { const float2 x = __ldg(reinterpret_cast<const float2*>(q)); f(0, x.x); f(1, x.y); }
+  if (HEAD == 3) { const float2 x = __ldg(reinterpret_cast<const float2*>(q + 1)); f(1, x.x); f(2, x.y); }
+  constexpr int Q = (45 - HEAD) / 4;
+#pragma unroll
+  for (int g = 0; g < Q; ++g) {
+    const int i = HEAD + 4 * g;
+    const float4 x = __ldg(reinterpret_cast<const float4*>(q + i));
+    f(i, x.x); f(i + 1, x.y); f(i + 2, x.z); f(i + 3, x.w);
+  }
+  constexpr int T = HEAD + 4 * Q;   // 44, 45, 42, 43
+  if (T == 44) f(44, __ldg(q + 44));
+  if (T == 42) { const float2 x = __ldg(reinterpret_cast<const float2*>(q + 42)); f(42, x.x); f(43, x.y); f(44, __ldg(q + 44)); }
+  if (T == 43) { const float2 x = __ldg(reinterpret_cast<const float2*>(q + 43)); f(43, x.x); f(44, x.y); }
+}
+template <typename F>
+__device__ __forceinline__ void row45(const float* __restrict__ q, F&& f) {
+  switch (((16 - (int)(reinterpret_cast<size_t>(q) & 15)) >> 2) & 3) {   // floats up to the next 16-byte boundary
+    case 0: row45_aligned<0>(q, f); break;
+    case 1: row45_aligned<1>(q, f); break;
+    case 2: row45_aligned<2>(q, f); break;
+    default: row45_aligned<3>(q, f); break;
+  }
+}
+
 }  // namespace h3dgs

@@ -66,6 +66,50 @@ __device__ __forceinline__ void put2(float* base, size_t row, int width, int k, 
 
 // Pass 1, one thread per slot: culled slots get their zero rows (plain mode: of every output; fused-cut mode: of
 // dL_dmeans2D only, the store rows are zero-filled by the caller), visible slots are listed in slot order.
+// ---- vector reductions to global memory (sm_90+) ----
+// The scatter of fused-cut mode is bound by the NUMBER of L2 reduction operations (one per lane and
+// instruction; 118 scalar ones per interpolated slot), not by bytes: rows are therefore added with the widest
+// reduction their alignment allows -- 16 bytes per operation on the 180/192-byte SH rows and the quaternions,
+// 8 + 4 bytes on the 12-byte rows.
+__device__ __forceinline__ void red1(float* p, float a) {
+  asm volatile("red.global.add.f32 [%0], %1;\n" ::"l"(p), "f"(a) : "memory");
+}
+__device__ __forceinline__ void red2(float* p, float a, float b) {
+  asm volatile("red.global.add.v2.f32 [%0], {%1, %2};\n" ::"l"(p), "f"(a), "f"(b) : "memory");
+}
+__device__ __forceinline__ void red4(float* p, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};\n" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d)
+               : "memory");
+}
+// three consecutive floats at a 4-byte aligned address
+__device__ __forceinline__ void red_row3(float* p, float a, float b, float c) {
+  if ((reinterpret_cast<size_t>(p) & 7) == 0) { red2(p, a, b); red1(p + 2, c); }
+  else { red1(p, a); red2(p + 1, b, c); }
+}
+// N consecutive floats s * v[0..N) at an address that is 4 * HEAD bytes short of 16-byte alignment
+template <int HEAD, int N>
+__device__ __forceinline__ void red_row_aligned(float* p, const float (&v)[48], float s) {
+#pragma unroll
+  for (int i = 0; i < HEAD; ++i) red1(p + i, s * v[i]);
+  constexpr int Q = (N - HEAD) / 4;
+#pragma unroll
+  for (int q = 0; q < Q; ++q) {
+    const int i = HEAD + 4 * q;
+    red4(p + i, s * v[i], s * v[i + 1], s * v[i + 2], s * v[i + 3]);
+  }
+#pragma unroll
+  for (int i = HEAD + 4 * Q; i < N; ++i) red1(p + i, s * v[i]);
+}
+template <int N>
+__device__ __forceinline__ void red_row(float* p, const float (&v)[48], float s) {
+  switch ((16 - (int)(reinterpret_cast<size_t>(p) & 15)) >> 2 & 3) {   // floats up to the next 16-byte boundary
+    case 0: red_row_aligned<0, N>(p, v, s); break;
+    case 1: red_row_aligned<1, N>(p, v, s); break;
+    case 2: red_row_aligned<2, N>(p, v, s); break;
+    default: red_row_aligned<3, N>(p, v, s); break;
+  }
+}
+
 template <bool FUSED>
 __global__ void __launch_bounds__(256) list_visible_kernel(const PreBwdArgs b) {
   const PreArgs& a = b.f;
@@ -108,7 +152,7 @@ __global__ void __launch_bounds__(256) list_visible_kernel(const PreBwdArgs b) {
 // three lanes in four idle through ~1500 instructions of a latency-bound kernel).  The grid covers P; CTAs
 // beyond the visible count, which the forward left in the geometry workspace, exit at once.
 template <bool FUSED>
-__global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdArgs b) {
+__global__ void __launch_bounds__(256, 2) preprocess_bwd_kernel(const PreBwdArgs b) {
   const PreArgs& a = b.f;
   const unsigned long long V = *reinterpret_cast<const unsigned long long*>(a.ws.counters + 2);
   const unsigned long long vi = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -139,6 +183,36 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdArgs b)
     }
   }
   const size_t pr = (size_t)(p < 0 ? 0 : p);
+
+  // The kernel is a long chain of dependent arithmetic fed by ~25 scattered rows (child and parent parameters,
+  // then the same rows of the gradient tensors): without help every row is a separate DRAM round trip in the
+  // middle of the chain.  Ask L2 for all of them now.
+  if (FUSED) {
+    auto pf = [](const void* q) { asm volatile("prefetch.global.L2 [%0];" ::"l"(q)); };
+    auto pf_row = [&](const float* base, size_t row, int width) {
+      if (base == nullptr) return;
+      const char* q = reinterpret_cast<const char*>(base + row * (size_t)width);
+      pf(q);
+      if (width > 16) pf(q + width * 4 - 4);   // rows longer than 64 B: both ends (the 180/192-byte SH rows)
+      if (width > 32) pf(q + 128);
+    };
+    const bool split = a.shs_rest != nullptr;
+    const int wsh = split ? (M - 1) * 3 : M * 3;
+    for (int side = 0; side < (lerp ? 2 : 1); ++side) {
+      const size_t row = side ? pr : r;
+      pf_row(a.means, row, 3);
+      pf_row(a.scales, row, 3);
+      pf_row(a.rots, row, 4);
+      pf_row(a.opac, row, 1);
+      pf_row(split ? a.shs_rest : a.shs, row, wsh);
+      pf_row(o.dL_dmeans3D, row, 3);
+      pf_row(o.dL_dscales, row, 3);
+      pf_row(o.dL_drotations, row, 4);
+      pf_row(o.dL_dopacity, row, 1);
+      pf_row(split ? o.dL_dsh_rest : o.dL_dsh, row, wsh);
+      if (split) { pf_row(a.shs, row, 3); pf_row(o.dL_dsh, row, 3); }
+    }
+  }
 
   if (FUSED && o.dirty_rows != nullptr) {
     // remember which store rows this render adds into (child, and parent when interpolating)
@@ -307,7 +381,51 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdArgs b)
     const float* __restrict__ shp = split ? a.shs_rest + pr * (size_t)(M - 1) * 3 - 3 : a.shs + pr * (size_t)M * 3;
 
     // dL/dsh rows
-    if (split) {
+    if (FUSED && M == 16 && o.dL_dsh != nullptr && (!split || o.dL_dsh_rest != nullptr)) {
+      // all 48 products in registers, then wide reductions into the child row (weight t) and the parent row (1-t)
+      float v[48];
+#pragma unroll
+      for (int k = 0; k < 16; ++k) {
+        const float w = (k < n) ? bs[k] : 0.f;
+        v[3 * k] = w * dL_dRGB.x; v[3 * k + 1] = w * dL_dRGB.y; v[3 * k + 2] = w * dL_dRGB.z;
+      }
+      for (int side = 0; side < (lerp ? 2 : 1); ++side) {
+        const size_t row = side ? pr : r;
+        const float sc = lerp ? (side ? omt : t) : 1.0f;
+        if (split) {
+          red_row3(o.dL_dsh + row * 3, sc * v[0], sc * v[1], sc * v[2]);
+          float* q = o.dL_dsh_rest + row * 45;
+          // rest row = v[3..48): shift the view by three floats
+          switch ((16 - (int)(reinterpret_cast<size_t>(q) & 15)) >> 2 & 3) {
+            case 0:
+#pragma unroll
+              for (int i = 0; i < 44; i += 4) red4(q + i, sc * v[3 + i], sc * v[4 + i], sc * v[5 + i], sc * v[6 + i]);
+              red1(q + 44, sc * v[47]);
+              break;
+            case 1:
+              red1(q, sc * v[3]);
+#pragma unroll
+              for (int i = 1; i < 45; i += 4) red4(q + i, sc * v[3 + i], sc * v[4 + i], sc * v[5 + i], sc * v[6 + i]);
+              break;
+            case 2:
+              red2(q, sc * v[3], sc * v[4]);
+#pragma unroll
+              for (int i = 2; i < 42; i += 4) red4(q + i, sc * v[3 + i], sc * v[4 + i], sc * v[5 + i], sc * v[6 + i]);
+              red2(q + 42, sc * v[45], sc * v[46]);
+              red1(q + 44, sc * v[47]);
+              break;
+            default:
+              red1(q, sc * v[3]); red2(q + 1, sc * v[4], sc * v[5]);
+#pragma unroll
+              for (int i = 3; i < 43; i += 4) red4(q + i, sc * v[3 + i], sc * v[4 + i], sc * v[5 + i], sc * v[6 + i]);
+              red2(q + 43, sc * v[46], sc * v[47]);
+              break;
+          }
+        } else {
+          red_row<48>(o.dL_dsh + row * 48, v, sc);
+        }
+      }
+    } else if (split) {
       put<FUSED>(o.dL_dsh, r, 3, 0, bs[0] * dL_dRGB.x, pr, lerp, t, omt);
       put<FUSED>(o.dL_dsh, r, 3, 1, bs[0] * dL_dRGB.y, pr, lerp, t, omt);
       put<FUSED>(o.dL_dsh, r, 3, 2, bs[0] * dL_dRGB.z, pr, lerp, t, omt);
@@ -333,7 +451,37 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdArgs b)
 
     // d colour / d direction
     float3 dx3 = {0, 0, 0}, dy3 = {0, 0, 0}, dz3 = {0, 0, 0};
+    // lerped coefficients 1..15: whole rows with aligned vector loads when the layout allows (gsmath.cuh), else
+    // coefficient by coefficient
+    const bool rows_vec = FUSED && M == 16 && a.D == 3 &&
+                          (split || (reinterpret_cast<size_t>(a.shs) & 15) == 0);
+    float sv[48];
+    if (rows_vec) {
+      if (split) {
+        row45(a.shs_rest + r * 45, [&](int i, float x) { sv[3 + i] = x; });
+        if (lerp) row45(a.shs_rest + pr * 45, [&](int i, float x) { sv[3 + i] = lerp_rn(t, sv[3 + i], omt, x); });
+      } else {
+        const float4* c4 = reinterpret_cast<const float4*>(a.shs + r * 48);
+        const float4* p4 = reinterpret_cast<const float4*>(a.shs + pr * 48);
+#pragma unroll
+        for (int i = 0; i < 12; ++i) {
+          const float4 x = __ldg(c4 + i);
+          sv[4 * i] = x.x; sv[4 * i + 1] = x.y; sv[4 * i + 2] = x.z; sv[4 * i + 3] = x.w;
+        }
+        if (lerp) {
+#pragma unroll
+          for (int i = 0; i < 12; ++i) {
+            const float4 y = __ldg(p4 + i);
+            sv[4 * i] = lerp_rn(t, sv[4 * i], omt, y.x);
+            sv[4 * i + 1] = lerp_rn(t, sv[4 * i + 1], omt, y.y);
+            sv[4 * i + 2] = lerp_rn(t, sv[4 * i + 2], omt, y.z);
+            sv[4 * i + 3] = lerp_rn(t, sv[4 * i + 3], omt, y.w);
+          }
+        }
+      }
+    }
     auto S = [&](int k) -> float3 {   // k >= 1 only: `sh` is biased by one coefficient in split mode
+      if (rows_vec) return make_float3(sv[3 * k], sv[3 * k + 1], sv[3 * k + 2]);
       float3 v = make_float3(__ldg(sh + 3 * k), __ldg(sh + 3 * k + 1), __ldg(sh + 3 * k + 2));
       if (FUSED && lerp) {
         v.x = lerp_rn(t, v.x, omt, __ldg(shp + 3 * k));
@@ -384,9 +532,15 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdArgs b)
     if (!FUSED && o.dL_dsh && !o.dL_dsh_rest) for (int i = 0; i < M * 3; ++i) o.dL_dsh[r * (size_t)M * 3 + i] = 0.f;
   }
 
-  put<FUSED>(o.dL_dmeans3D, r, 3, 0, dL_dmean.x, pr, lerp, t, omt);
-  put<FUSED>(o.dL_dmeans3D, r, 3, 1, dL_dmean.y, pr, lerp, t, omt);
-  put<FUSED>(o.dL_dmeans3D, r, 3, 2, dL_dmean.z, pr, lerp, t, omt);
+  if (FUSED && o.dL_dmeans3D != nullptr) {
+    const float sc = lerp ? t : 1.0f;
+    red_row3(o.dL_dmeans3D + r * 3, sc * dL_dmean.x, sc * dL_dmean.y, sc * dL_dmean.z);
+    if (lerp) red_row3(o.dL_dmeans3D + pr * 3, omt * dL_dmean.x, omt * dL_dmean.y, omt * dL_dmean.z);
+  } else {
+    put<FUSED>(o.dL_dmeans3D, r, 3, 0, dL_dmean.x, pr, lerp, t, omt);
+    put<FUSED>(o.dL_dmeans3D, r, 3, 1, dL_dmean.y, pr, lerp, t, omt);
+    put<FUSED>(o.dL_dmeans3D, r, 3, 2, dL_dmean.z, pr, lerp, t, omt);
+  }
   put2<FUSED>(o.dL_dopacity, r, 1, 0, tc * dL_dopacity_out * act_scalar_grad(a.act_opac, o_raw, o_act), pr,
               lerp, omt * dL_dopacity_out * act_scalar_grad(a.act_opac, op_raw, op_act));
 
@@ -444,12 +598,12 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdArgs b)
     dq.z = 2 * x * (dMt.c[1][0] + dMt.c[0][1]) + 2 * rr * (dMt.c[2][0] - dMt.c[0][2]) + 2 * z * (dMt.c[1][2] + dMt.c[2][1]) - 4 * y * (dMt.c[2][2] + dMt.c[0][0]);
     dq.w = 2 * rr * (dMt.c[0][1] - dMt.c[1][0]) + 2 * x * (dMt.c[2][0] + dMt.c[0][2]) + 2 * y * (dMt.c[1][2] + dMt.c[2][1]) - 4 * z * (dMt.c[1][1] + dMt.c[0][0]);
 
-    put2<FUSED>(o.dL_dscales, r, 3, 0, tc * ds0 * act_scalar_grad(a.act_scale, s_raw.x, s_act.x), pr, lerp,
-                omt * ds0 * act_scalar_grad(a.act_scale, sp_raw.x, sp_act.x));
-    put2<FUSED>(o.dL_dscales, r, 3, 1, tc * ds1 * act_scalar_grad(a.act_scale, s_raw.y, s_act.y), pr, lerp,
-                omt * ds1 * act_scalar_grad(a.act_scale, sp_raw.y, sp_act.y));
-    put2<FUSED>(o.dL_dscales, r, 3, 2, tc * ds2 * act_scalar_grad(a.act_scale, s_raw.z, s_act.z), pr, lerp,
-                omt * ds2 * act_scalar_grad(a.act_scale, sp_raw.z, sp_act.z));
+    const float gs0 = tc * ds0 * act_scalar_grad(a.act_scale, s_raw.x, s_act.x);
+    const float gs1 = tc * ds1 * act_scalar_grad(a.act_scale, s_raw.y, s_act.y);
+    const float gs2 = tc * ds2 * act_scalar_grad(a.act_scale, s_raw.z, s_act.z);
+    const float gp0 = omt * ds0 * act_scalar_grad(a.act_scale, sp_raw.x, sp_act.x);
+    const float gp1 = omt * ds1 * act_scalar_grad(a.act_scale, sp_raw.y, sp_act.y);
+    const float gp2 = omt * ds2 * act_scalar_grad(a.act_scale, sp_raw.z, sp_act.z);
     // dq is in (r, x, y, z) = float4 (x, y, z, w) component order, like the stored quaternion
     const float4 gc = act_rotation_grad(a.act_rot, a.norm_variant, q_raw,
                                         make_float4(tc * dq.x, tc * dq.y, tc * dq.z, tc * dq.w));
@@ -458,10 +612,24 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdArgs b)
       const float w = omt * psign;
       gp = act_rotation_grad(a.act_rot, a.norm_variant, qp_raw, make_float4(w * dq.x, w * dq.y, w * dq.z, w * dq.w));
     }
-    put2<FUSED>(o.dL_drotations, r, 4, 0, gc.x, pr, lerp, gp.x);
-    put2<FUSED>(o.dL_drotations, r, 4, 1, gc.y, pr, lerp, gp.y);
-    put2<FUSED>(o.dL_drotations, r, 4, 2, gc.z, pr, lerp, gp.z);
-    put2<FUSED>(o.dL_drotations, r, 4, 3, gc.w, pr, lerp, gp.w);
+    if (FUSED) {
+      if (o.dL_dscales != nullptr) {
+        red_row3(o.dL_dscales + r * 3, gs0, gs1, gs2);
+        if (lerp) red_row3(o.dL_dscales + pr * 3, gp0, gp1, gp2);
+      }
+      if (o.dL_drotations != nullptr) {
+        red4(o.dL_drotations + r * 4, gc.x, gc.y, gc.z, gc.w);
+        if (lerp) red4(o.dL_drotations + pr * 4, gp.x, gp.y, gp.z, gp.w);
+      }
+    } else {
+      put2<FUSED>(o.dL_dscales, r, 3, 0, gs0, pr, lerp, gp0);
+      put2<FUSED>(o.dL_dscales, r, 3, 1, gs1, pr, lerp, gp1);
+      put2<FUSED>(o.dL_dscales, r, 3, 2, gs2, pr, lerp, gp2);
+      put2<FUSED>(o.dL_drotations, r, 4, 0, gc.x, pr, lerp, gp.x);
+      put2<FUSED>(o.dL_drotations, r, 4, 1, gc.y, pr, lerp, gp.y);
+      put2<FUSED>(o.dL_drotations, r, 4, 2, gc.z, pr, lerp, gp.z);
+      put2<FUSED>(o.dL_drotations, r, 4, 3, gc.w, pr, lerp, gp.w);
+    }
     if (!FUSED && o.dL_dcov3D) for (int i = 0; i < 6; ++i) o.dL_dcov3D[r * 6 + i] = dcov[i];
   } else {
     for (int i = 0; i < 6; ++i) put<FUSED>(o.dL_dcov3D, r, 6, i, dcov[i], pr, lerp, t, omt);
