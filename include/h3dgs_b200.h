@@ -229,6 +229,9 @@ typedef struct H3dgsDebugView {
   const float* records;          /* [P,16] packed per-slot record, see DESIGN.md */
   const float* cov3D;            /* [P,6] */
   const uint16_t* tile_rects;    /* [P,4] x0,y0,x1,y1 in tiles */
+  const uint32_t* order_fwd;     /* [tiles] launch order of the forward blend (heaviest tile first) */
+  const uint32_t* order_bwd;     /* [tiles] launch order of the backward blend (valid after a backward) */
+  const uint32_t* tile_last;     /* [tiles] max n_contrib over the tile's pixels */
 } H3dgsDebugView;
 H3DGS_API int h3dgs_debug_view(int32_t P, int32_t image_width, int32_t image_height, int64_t num_rendered,
                      const void* geom, const void* binning, const void* image, H3dgsDebugView* out);

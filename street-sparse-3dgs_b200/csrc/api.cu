@@ -534,6 +534,9 @@ int h3dgs_debug_view(int32_t P, int32_t W, int32_t H, int64_t R, const void* geo
     out->ranges = reinterpret_cast<const uint32_t*>(iw.ranges);
     out->final_T = iw.final_T;
     out->n_contrib = iw.n_contrib;
+    out->order_fwd = iw.order_fwd;
+    out->order_bwd = iw.order_bwd;
+    out->tile_last = iw.tile_last;
   }
   return 0;
 }

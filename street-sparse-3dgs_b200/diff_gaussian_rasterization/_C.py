@@ -393,6 +393,9 @@ def debug_view(P, W, H, R, geom, binning, img):
         "ranges": view_of(img, dv.ranges, tiles * 2, torch.int32),
         "final_T": view_of(img, dv.final_T, W * H, torch.float32),
         "n_contrib": view_of(img, dv.n_contrib, W * H, torch.int32),
+        "order_fwd": view_of(img, dv.order_fwd, tiles, torch.int32),
+        "order_bwd": view_of(img, dv.order_bwd, tiles, torch.int32),
+        "tile_last": view_of(img, dv.tile_last, tiles, torch.int32),
         "depths": view_of(geom, dv.depths, P, torch.float32),
         "tiles_touched": view_of(geom, dv.tiles_touched, P, torch.int32),
         "point_offsets": view_of(geom, dv.point_offsets, P, torch.int32),

@@ -60,7 +60,8 @@ class DebugView(Structure):
     _fields_ = [("point_list_keys", c_void_p), ("point_list", c_void_p), ("ranges", c_void_p),
                 ("final_T", c_void_p), ("n_contrib", c_void_p), ("depths", c_void_p),
                 ("tiles_touched", c_void_p), ("point_offsets", c_void_p), ("records", c_void_p),
-                ("cov3D", c_void_p), ("tile_rects", c_void_p)]
+                ("cov3D", c_void_p), ("tile_rects", c_void_p), ("order_fwd", c_void_p), ("order_bwd", c_void_p),
+                ("tile_last", c_void_p)]
 
 
 class AdamTensor(Structure):

@@ -49,6 +49,20 @@ def test_usage_errors_are_reported_not_crashed():
     cnt = ctypes.c_int32(7)
     assert L.h3dgs_expand_to_size(-5, 1.0, None, None, None, None, None, None, None, 0, ctypes.byref(cnt), None) == -1
     assert L.h3dgs_sparse_adam(None, 0, None, 0, 0, None) == -1
+    # ABI v5 additions: argument checks come before any device work
+    assert L.h3dgs_zero_fill(None, 3, 0, None) == -1 and L.h3dgs_zero_fill(None, 0, 0, None) == 0
+    assert L.h3dgs_zero_fill(None, 0, 9, None) == -1
+    span = (nat.Span * 1)(nat.Span(None, -4))
+    assert L.h3dgs_zero_fill(span, 1, 0, None) == -1
+    assert L.h3dgs_pack_rows(None, 2, None, 5, None, None) == -1
+    rt = (nat.RowTensor * 1)()
+    assert L.h3dgs_unpack_rows(rt, 1, None, 0, None, 1.0, None) == 0      # no rows: nothing to do
+    assert L.h3dgs_unpack_rows(rt, 1, None, 3, None, 1.0, None) == -1     # rows / payload missing
+    w = (ctypes.c_float * 11)(*([1.0 / 11] * 11))
+    assert L.h3dgs_ssim_forward(3, 0, 16, None, None, w, None, None, None, None, None, None) == 0   # empty image
+    assert L.h3dgs_ssim_forward(3, 8, 8, None, None, w, None, None, None, None, None, None) == -1
+    assert L.h3dgs_ssim_backward(3, 8, 8, None, None, w, None, None, None, None, None, 1.0, 0.0, None, None) == -1
+    assert L.h3dgs_blend_stats(None) == 0
     with pytest.raises(nat.H3dgsError):
         nat.check(-1, "x")
 

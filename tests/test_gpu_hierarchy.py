@@ -372,3 +372,74 @@ def test_pack_unpack_rows_match_index_ops():
         assert torch.equal(t, ref)
     assert L.h3dgs_pack_rows(arr, len(tensors), None, 0, None, nat.stream_handle()) == 0
     assert L.h3dgs_pack_rows(arr, 0, rows.data_ptr(), 1, packed.data_ptr(), nat.stream_handle()) != 0
+
+
+@pytest.mark.gpu
+def test_prezero_side_stream_matches_inline_zero_fill(monkeypatch):
+    """The gradient tensors zero-filled on the side stream during the forward (_C._Prezero) hold what the
+    backward's own zero fill produces: same gradients (up to the order of the float reductions), exact zeros in
+    untouched rows, and the store-sized screen-space gradient is zero beyond the rendered slots."""
+    import diff_gaussian_rasterization as dgr
+    import gaussian_hierarchy
+    sky = 300
+    attrs = workload.build_scene(14, sky, 4, DEV)
+    cam = scenes.street_camera(800, 600, seed=2, device=DEV, yaw_deg=3.0, x=-5.0)
+    bg = torch.zeros(3, device=DEV)
+    n = attrs["means3D"].size(0)
+    g = torch.Generator().manual_seed(5)
+    dcol = (torch.randn(3, 600, 800, generator=g) / 480000).to(DEV)
+    grads = {}
+    for mode in (True, False):
+        monkeypatch.setattr(dgr._C, "PREZERO", mode)
+        model = workload.ActivatedModel(attrs, sky)
+        limit = workload.find_limit(gaussian_hierarchy._C, model, cam, 6000, DEV)
+        cut = workload.Cut(n, DEV)
+        cut.compute(gaussian_hierarchy._C, model, cam, limit)
+        out = workload.ours_render_post(cam, model, bg, cut, do_depth=False)
+        (out["render"] * dcol).sum().backward()
+        torch.cuda.synchronize()
+        grads[mode] = [p.grad.clone() for p in model.parameters()] + [out["viewspace_points"].grad.clone()]
+        P = cut.count + sky
+    for a, b in zip(grads[True], grads[False]):
+        assert a.shape == b.shape
+        assert torch.equal(a == 0, b == 0)
+        assert float((a - b).abs().max()) <= 1e-4 * float(b.abs().max()) + 1e-12
+    vp = grads[True][-1]
+    assert vp.size(0) == n and float(vp[P:].abs().sum()) == 0.0 and float(vp[:P].abs().sum()) > 0.0
+
+
+@pytest.mark.gpu
+def test_tile_launch_orders_are_permutations():
+    """order_fwd / order_bwd (heavy-first launch order of the blend kernels) are permutations of the tile ids,
+    sorted by descending work bucket."""
+    import diff_gaussian_rasterization as dgr
+    sc = scenes.street_gaussians(30000, seed=3, device=DEV)
+    cam = scenes.street_camera(640, 480, seed=1, device=DEV)
+    rs = refglue.make_settings(dgr.GaussianRasterizationSettings, cam, torch.zeros(3, device=DEV), do_depth=True)
+    e = torch.Tensor([])
+    fa = (rs.bg, rs.render_indices, rs.parent_indices, rs.interpolation_weights, rs.num_node_kids, sc["means3D"], e,
+          sc["opacities"], sc["scales"], sc["rotations"], 1.0, e, rs.viewmatrix, rs.projmatrix, rs.tanfovx,
+          rs.tanfovy, rs.image_height, rs.image_width, sc["shs"], 3, rs.campos, False, False, True)
+    R, color, radii, geom, binning, img, invd = dgr._C.rasterize_gaussians(*fa)
+    g = torch.Generator().manual_seed(1)
+    dcol = torch.randn(3, 480, 640, generator=g).to(DEV)
+    ba = (rs.bg, rs.render_indices, rs.parent_indices, rs.interpolation_weights, rs.num_node_kids, sc["means3D"],
+          radii, e, sc["opacities"], sc["scales"], sc["rotations"], 1.0, e, rs.viewmatrix, rs.projmatrix, rs.tanfovx,
+          rs.tanfovy, dcol, torch.zeros(1, 480, 640, device=DEV), sc["shs"], 3, rs.campos, geom, R, binning, img,
+          False)
+    dgr._C.rasterize_gaussians_backward(*ba)
+    torch.cuda.synchronize()
+    dv = dgr._C.debug_view(30000, 640, 480, R, geom, binning, img)
+    tiles = 40 * 30
+    rg = dv["ranges"].view(-1, 2).long()
+    length = rg[:, 1] - rg[:, 0]
+    nc = dv["n_contrib"].view(480, 640).long()
+    tile_max = nc.view(30, 16, 40, 16).amax(dim=(1, 3)).flatten()
+    assert torch.equal(dv["tile_last"].long(), tile_max)
+    for key, work in (("order_fwd", length), ("order_bwd", tile_max)):
+        order = dv[key].long()
+        assert torch.equal(order.sort().values, torch.arange(tiles, device=DEV))
+        w = work[order]
+        # heavy first: a later tile is never more than one bucket (a quarter octave, x 1.25) heavier than an earlier one
+        running_min = torch.cummin(w.clamp(min=4), dim=0).values
+        assert bool((w.clamp(min=4).double() <= running_min.double() * 1.26 + 1).all())
