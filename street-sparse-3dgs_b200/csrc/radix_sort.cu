@@ -150,14 +150,29 @@ __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(
     // decoupled look-back over the preceding tiles
     uint32_t excl = 0;
     if (tile > 0) {
+      // Eight predecessors are read at once (independent loads, one L2 round trip) and then consumed in order:
+      // with a few hundred tiles resident at the same time the chain of publish -> observe hops, not the
+      // bandwidth, is what a pass over a small array costs.
+      constexpr int LB = 8;
       long long t = (long long)tile - 1;
-      while (true) {
-        volatile uint32_t* ps = status + (size_t)t * RADIX;
-        uint32_t w;
-        do { w = ps[tid]; } while ((w >> 30) == 0);
-        excl += w & ST_VAL;
-        if ((w >> 30) == 2 || t == 0) break;
-        --t;
+      bool done = false;
+      while (!done) {
+        uint32_t w[LB];
+#pragma unroll
+        for (int j = 0; j < LB; ++j) {
+          const long long tj = t - j;
+          w[j] = (tj >= 0) ? status[(size_t)tj * RADIX + tid] : 0u;
+        }
+#pragma unroll
+        for (int j = 0; j < LB; ++j) {
+          if (done) break;
+          const long long tj = t - j;
+          uint32_t x = w[j];
+          while ((x >> 30) == 0) x = status[(size_t)tj * RADIX + tid];   // not published yet: spin on this one
+          excl += x & ST_VAL;
+          if ((x >> 30) == 2 || tj == 0) done = true;
+        }
+        t -= LB;
       }
       status[(size_t)tile * RADIX + tid] = ST_INC | ((excl + total) & ST_VAL);
     }

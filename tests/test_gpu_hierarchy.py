@@ -403,7 +403,10 @@ def test_prezero_side_stream_matches_inline_zero_fill(monkeypatch):
     for a, b in zip(grads[True], grads[False]):
         assert a.shape == b.shape
         assert torch.equal(a == 0, b == 0)
-        assert float((a - b).abs().max()) <= 1e-4 * float(b.abs().max()) + 1e-12
+        # two runs of the SAME mode differ by up to 1.3e-4 of the tensor's max in one ill-conditioned rotation
+        # row (float reduction order; harness/diag_prezero.py prints the spread of both modes), so the bar
+        # here is 5e-4: a missed zero fill would be off by the magnitude of a whole gradient
+        assert float((a - b).abs().max()) <= 5e-4 * float(b.abs().max()) + 1e-12
     vp = grads[True][-1]
     assert vp.size(0) == n and float(vp[P:].abs().sum()) == 0.0 and float(vp[:P].abs().sum()) > 0.0
 
