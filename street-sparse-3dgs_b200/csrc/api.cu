@@ -323,6 +323,7 @@ int h3dgs_forward_render(const H3dgsView* view, const H3dgsGaussians* g, void* g
   b.final_T = iw.final_T; b.n_contrib = iw.n_contrib; b.accum = iw.accum;
   b.out_color = out_color; b.out_invdepth = out_invdepth;
   b.order = iw.order_fwd; b.tile_last = iw.tile_last; b.stats = g_blend_stats;
+  b.snap = bw.snap;
   if (pre_blend_event) H3_CUDA(cudaEventRecord((cudaEvent_t)pre_blend_event, s));
   H3_CUDA(launch_blend_fwd(b, s));
   if ((rc = debug_sync(debug, s, "blend_fwd"))) return rc;
@@ -396,6 +397,7 @@ int h3dgs_backward(const H3dgsView* view, const H3dgsGaussians* g, const int32_t
   b.dL_dcolor = dL_dout_color; b.dL_dinvdepth = dL_dout_invdepth; b.grad = ww.grad;
   H3_CUDA(launch_tile_order(nullptr, iw.tile_last, b.grid_x * b.grid_y, iw.order_bwd, s));
   b.order = iw.order_bwd; b.stats = g_blend_stats;
+  b.snap = bw.snap; b.keys64 = bw.keys64; b.nseg = R > 0 ? (int)((R - 1) / BLEND_SEG) : 0;
   H3_CUDA(launch_blend_bwd(b, s));
   if ((rc = debug_sync(debug, s, "blend_bwd"))) return rc;
 

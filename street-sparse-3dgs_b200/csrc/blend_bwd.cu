@@ -34,7 +34,20 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_bwd_kernel(const BlendArg
   extern __shared__ __align__(16) unsigned char smem_raw[];
   BwdSmem& sm = *reinterpret_cast<BwdSmem*>(smem_raw);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int tile = a.order ? (int)a.order[blockIdx.x] : (int)blockIdx.x;
+  // Work item = (tile, k): list positions [k SEG, (k+1) SEG) of the tile.  Items with k >= 1 lead the grid, one
+  // CTA per possible cut number x = floor(global list position / SEG): the tile that owns list position x SEG
+  // is read off the sorted keys, and the item exists if that tile has a cut inside block x.
+  int tile, k = 0;
+  if ((int)blockIdx.x < a.nseg) {
+    const unsigned x = blockIdx.x + 1;
+    tile = (int)(a.keys64[(size_t)x * BLEND_SEG] >> 32);
+    const uint2 r = a.ranges[tile];
+    k = (int)x - (int)(r.x / BLEND_SEG);
+    if (k < 1 || r.x + (unsigned)k * BLEND_SEG >= r.y) return;
+  } else {
+    const int i = (int)blockIdx.x - a.nseg;
+    tile = a.order ? (int)a.order[i] : i;
+  }
   const int tx = tile % a.grid_x, ty = tile / a.grid_x;
   const int bx0 = tx * TILE_X + (warp & 1) * SUB_W;
   const int by0 = ty * TILE_Y + (warp >> 1) * SUB_H;
@@ -79,21 +92,23 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_bwd_kernel(const BlendArg
   int blast = 0;
 #pragma unroll
   for (int w = 0; w < BLEND_THREADS / 32; ++w) blast = max(blast, sm.red[w]);
-  const int rounds = (min(blast, n) + BLEND_BATCH - 1) / BLEND_BATCH;
-  if (rounds == 0) return;
-  const int nn = min(blast, n);  // entries that matter to anyone in this tile
+  const int seg_lo = k * BLEND_SEG;
+  if (seg_lo >= min(blast, n)) return;   // nobody in this tile got that deep
+  const int nn = min(seg_lo + BLEND_SEG, min(blast, n));  // one past the deepest list position of this item
+  const int len = nn - seg_lo;
+  const int rounds = (len + BLEND_BATCH - 1) / BLEND_BATCH;
 
   auto issue = [&](int b, uint32_t id) {
     const int j = b * BLEND_BATCH + tid;
     const int s = b & 1;
     if (TMA) {
       if (tid == 0) {
-        const int cnt = min(BLEND_BATCH, nn - b * BLEND_BATCH);
+        const int cnt = min(BLEND_BATCH, len - b * BLEND_BATCH);
         mbar_expect_tx(&sm.bar[s], (unsigned)cnt * REC_BYTES);
       }
-      if (j < nn) bulk_g2s(&sm.rec[s][tid], a.rec + id, REC_BYTES, &sm.bar[s]);
+      if (j < len) bulk_g2s(&sm.rec[s][tid], a.rec + id, REC_BYTES, &sm.bar[s]);
     } else {
-      if (j < nn) {
+      if (j < len) {
         const char* src = reinterpret_cast<const char*>(a.rec + id);
         char* dst = reinterpret_cast<char*>(&sm.rec[s][tid]);
         cp_async16(dst, src);
@@ -118,13 +133,24 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_bwd_kernel(const BlendArg
     if (!DEPTH && red_dst == 9) red_dst = -1;
   }
   float T = T_final, accum_u = 0.f, last_alpha = 0.f, last_u = 0.f;
+  if (inside && last > nn) {
+    // this pixel's walk started in a deeper item: pick it up at the cut from the forward's snapshot.  What lies
+    // behind the cut, contracted with the pixel gradient, is (total - in front of the cut) / T at the cut.
+    const float* __restrict__ sp =
+        a.snap + ((size_t)(range.x / BLEND_SEG) + (size_t)(k + 1)) * SNAP_FLOATS + tid;
+    const float4 tot = a.accum[pix];
+    T = sp[0];
+    float behind = (tot.x - sp[TILE_PIX]) * g0 + (tot.y - sp[2 * TILE_PIX]) * g1 + (tot.z - sp[3 * TILE_PIX]) * g2;
+    if (DEPTH) behind += (tot.w - sp[4 * TILE_PIX]) * gD;
+    accum_u = behind / T;
+  }
   unsigned cntA = 0, cntB = 0, cntD = 0, cntS = 0;
   const float half_w = 0.5f * (float)a.W, half_h = 0.5f * (float)a.H;
 
   // staging slot k of round b holds list position nn - 1 - (b * BATCH + k): back to front
-  uint32_t id_cur = (tid < nn) ? __ldg(list + (nn - 1 - tid)) : 0u;
+  uint32_t id_cur = (tid < len) ? __ldg(list + (nn - 1 - tid)) : 0u;
   issue(0, id_cur);
-  uint32_t id_next = (BLEND_BATCH + tid < nn) ? __ldg(list + (nn - 1 - BLEND_BATCH - tid)) : 0u;
+  uint32_t id_next = (BLEND_BATCH + tid < len) ? __ldg(list + (nn - 1 - BLEND_BATCH - tid)) : 0u;
 
   for (int b = 0; b < rounds; ++b) {
     const int s = b & 1;
@@ -132,7 +158,7 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_bwd_kernel(const BlendArg
     if (b + 1 < rounds) {
       issue(b + 1, id_next);
       const int j2 = (b + 2) * BLEND_BATCH + tid;
-      id_after = (j2 < nn) ? __ldg(list + (nn - 1 - j2)) : 0u;
+      id_after = (j2 < len) ? __ldg(list + (nn - 1 - j2)) : 0u;
       if (!TMA) cp_async_wait<1>();
     } else {
       if (!TMA) cp_async_wait<0>();
@@ -141,9 +167,9 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_bwd_kernel(const BlendArg
     __syncthreads();  // records of round b visible; accumulator zeroed by the previous flush
 
     const int base = b * BLEND_BATCH;
-    const int cnt = min(BLEND_BATCH, nn - base);
+    const int cnt = min(BLEND_BATCH, len - base);
     // slots whose list position is >= this warp's last contributor come first; skip them
-    const int first = max(0, nn - wlast - base);
+    const int first = max(0, nn - min(wlast, nn) - base);
     const Rec* __restrict__ recs = sm.rec[s];
     for (int c = first & ~31; c < cnt; c += 32) {
       const int j = c + lane;
@@ -274,7 +300,7 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_bwd_kernel(const BlendArg
     id_next = id_after;
   }
   if (COUNT && a.stats) {
-    if (tid == 0) {
+    if (tid == 0 && k == 0) {   // per-tile times cover the tile's first work item only
       unsigned long long t_end;
       asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_end));
       a.stats[16 + 4 * tile + 2] = t_start;
@@ -291,7 +317,7 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_bwd_kernel(const BlendArg
 
 template <bool INTERP, bool DEPTH>
 cudaError_t launch2(const BlendArgs& a, bool tma, cudaStream_t s) {
-  const int tiles = a.grid_x * a.grid_y;
+  const int tiles = a.grid_x * a.grid_y + a.nseg;
   const size_t smem = sizeof(BwdSmem);
   cudaError_t e;
   ProfScope ps(K_BLEND_BWD, s);

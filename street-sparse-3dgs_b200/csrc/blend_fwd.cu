@@ -6,6 +6,8 @@
 // ballot gives the survivors) and only evaluates survivors per pixel, in list order, so every pixel
 // sees exactly the sequence of blends the reference performs: alpha, the 1/255 and T<1e-4 decisions,
 // n_contrib and final_T are bit-identical.  Warps retire as soon as their 32 pixels are saturated.
+// Every BLEND_SEG entries the per-pixel state is also written out (a few dozen long horizon tiles only): the
+// backward pass cuts long lists there into independent work items.
 #include "blend_common.cuh"
 
 namespace h3dgs {
@@ -86,6 +88,17 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_fwd_kernel(const BlendArg
 
   for (int b = 0; b < rounds; ++b) {
     const int s = b & 1;
+    // list cut: leave what every pixel has accumulated in front of it for the backward work item that starts
+    // (in walking order: ends) here -- see blend_bwd.cu
+    if (a.snap && b > 0 && (b & (BLEND_SEG / BLEND_BATCH - 1)) == 0) {
+      const size_t slot = (size_t)(range.x / BLEND_SEG) + (size_t)(b / (BLEND_SEG / BLEND_BATCH));
+      float* __restrict__ sp = a.snap + slot * SNAP_FLOATS + tid;
+      sp[0] = T;
+      sp[TILE_PIX] = C0;
+      sp[2 * TILE_PIX] = C1;
+      sp[3 * TILE_PIX] = C2;
+      if (DEPTH) sp[4 * TILE_PIX] = D;
+    }
     if (b + 1 < rounds) {
       issue(b + 1, id_next);
       const int j2 = (b + 2) * BLEND_BATCH + tid;

@@ -110,6 +110,12 @@ constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;
 constexpr int SORT_MAX_PASSES = 4;
 constexpr int SORT_DEPTH_PASSES = 4;   // 32 depth bits, 8 per pass
 constexpr int EMIT_CHUNK = 2048;       // instances written per CTA of the emission kernel
+// Backward blend work items: a tile list is cut every BLEND_SEG entries (tile-relative); the forward blend
+// leaves a per-pixel snapshot (T, C, D in front of the cut) at every cut it crosses.  Cuts of different tiles
+// are more than BLEND_SEG list positions apart, so floor(global position / BLEND_SEG) numbers them uniquely.
+constexpr int BLEND_SEG = 1024;
+constexpr int SNAP_PLANES = 5;         // T, C.r, C.g, C.b, D -- one float per pixel of the tile each
+constexpr int SNAP_FLOATS = SNAP_PLANES * TILE_X * TILE_Y;
 
 struct SortShifts {
   int shift[SORT_MAX_PASSES];
@@ -161,6 +167,7 @@ struct BinWs {
   void* tkeys[2];               // tile ids of the emitted instances (u16 or u32), double buffered
   uint32_t* tvals[2];           // slot of each instance, double buffered; tvals[sorted] is point_list
   unsigned long long* keys64;   // point_list_keys: (tile << 32) | depth bits, sorted
+  float* snap;                  // [R / BLEND_SEG + 2][SNAP_FLOATS] forward snapshots at the list cuts
   uint32_t* dkeys[2];           // depth bits of the visible slots, double buffered
   uint32_t* dvals[2];           // visible slots; dvals[0] ends up in (depth, slot) order
   uint32_t* soffs;              // inclusive scan of tiles_touched in that order
@@ -190,6 +197,7 @@ struct BinWs {
     carve(p, w.tvals[0], n);
     carve(p, w.tvals[1], n);
     carve(p, w.keys64, n);
+    carve(p, w.snap, (n / BLEND_SEG + 2) * (size_t)SNAP_FLOATS);
     w.sorted = pl.tile_passes & 1;
     // ---- V-sized part ----
     carve(p, w.dkeys[0], v);
@@ -305,6 +313,9 @@ struct BlendArgs {
   const float* dL_dcolor; const float* dL_dinvdepth; GradRec* grad;  // bwd
   const uint32_t* order;   // CTA i processes tile order[i] (heavy tiles first); NULL = identity
   uint32_t* tile_last;     // fwd: per-tile max of n_contrib (pre-zeroed)
+  float* snap;             // fwd writes, bwd reads: per-pixel state at the list cuts (BinWs::snap)
+  const unsigned long long* keys64;  // bwd: sorted keys, tile id in the high word (finds the tile of a cut)
+  int nseg;                // bwd: work items that start at a cut, (R - 1) / BLEND_SEG; they lead the grid
   unsigned long long* stats;  // instrumented pass (h3dgs_blend_stats): pair-category counters, else NULL
 };
 cudaError_t launch_blend_fwd(const BlendArgs& a, cudaStream_t s);
