@@ -118,6 +118,47 @@ def test_backward_matches_reference(n, w, h, interp, depth):
         util.assert_grad_close(go[k], gr[k], gr2[k], k, more_refs=[m[k] for m in more])
 
 
+@pytest.mark.parametrize("interp,depth", [(False, True), (True, True), (True, False)])
+def test_backward_long_lists_cut_into_work_items(interp, depth):
+    """Lists longer than the backward's work-item length (1024 entries, csrc/common.cuh BLEND_SEG): faint, wide
+    Gaussians on a small image, so that pixels keep blending thousands of entries deep and the deeper work
+    items start from the forward's snapshots at the cuts.  Gradients against the reference build."""
+    util.need_ref()
+    import diff_gaussian_rasterization as dgr
+    n, w, h = 120000, 320, 240
+    sc, cam, ts, kids = util.make_scene(n, w, h, seed=11, dev=DEV, interp=interp)
+    sc["opacities"] = (sc["opacities"] * 0.02).contiguous()
+    sc["scales"] = (sc["scales"] * 2.0).contiguous()
+    bg = torch.tensor([0.3, 0.1, 0.2], device=DEV)
+    rs = _settings(cam, bg, do_depth=depth, ts=ts, kids=kids)
+    args = util.forward_args(rs, sc)
+    R, color, radii, geom, binning, img, invd = dgr._C.rasterize_gaussians(*args)
+    dv = dgr._C.debug_view(n, w, h, R, geom, binning, img)
+    deep = int(dv["tile_last"].max())
+    assert deep > 3 * 1024, f"scene too shallow for this test: deepest last contributor {deep}"
+    assert int((dv["tile_last"] > 1024).sum()) >= 10
+    g = torch.Generator().manual_seed(7)
+    dcol = (torch.randn(3, h, w, generator=g) / (w * h)).to(DEV)
+    ddep = (torch.randn(1, h, w, generator=g) / (w * h)).to(DEV)
+
+    def ours(p, m2d):
+        return dgr.GaussianRasterizer(rs)(means3D=p["means3D"], means2D=m2d, opacities=p["opacities"],
+                                          shs=p["shs"], scales=p["scales"], rotations=p["rotations"])
+
+    def ref(p, m2d):
+        return refglue.ref_rasterize(rs, p["means3D"], m2d, p["opacities"], shs=p["shs"], scales=p["scales"],
+                                     rotations=p["rotations"])
+
+    co, ro, go = _run_backward(ours, sc, dcol, ddep)
+    cr, rr, gr = _run_backward(ref, sc, dcol, ddep)
+    more = [_run_backward(ref, sc, dcol, ddep)[2] for _ in range(4)]
+    gr2 = more.pop()
+    torch.cuda.synchronize()
+    assert torch.equal(bits(co), bits(cr))
+    for k in go:
+        util.assert_grad_close(go[k], gr[k], gr2[k], k, more_refs=[m[k] for m in more])
+
+
 def test_precomputed_colors_and_low_sh_degree():
     util.need_ref()
     import diff_gaussian_rasterization as dgr
