@@ -46,6 +46,8 @@ def parse():
     ap.add_argument("--loss", default="l1ssim", choices=["l1ssim", "l1"],
                     help="e2e loss: train_post.py's 0.8 L1 + 0.2 (1 - SSIM), or L1 alone")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--serial-cut", action="store_true",
+                    help="e2e: compute each step's cut at the top of the step instead of one step ahead")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-profile", action="store_true")
     return ap.parse_args()
@@ -365,6 +367,40 @@ def main():
         h2d = gt_host[0].numel() * 4 + 35 * 4
         losses = []
 
+        # host pipeline, second part (ours only; the reference arm keeps its serial loop): the cut of step i+1
+        # depends on the camera and the hierarchy's boxes, not on the parameters, so it is launched on a side
+        # stream right after step i's backward and its bandwidth-bound kernels run under the issue-bound blend.
+        # Every step still runs exactly one cut and copies its own camera from pinned host memory.
+        cut_ahead = args.impl == "ours" and not args.serial_cut
+        if cut_ahead:
+            cuts2 = [cut, workload.Cut(n_store, dev)]
+            cam_dev2 = [cam_dev, torch.empty(35, device=dev)]
+            cut_stream = torch.cuda.Stream(device=dev)
+            cut_done = [torch.cuda.Event() for _ in range(2)]
+            cut_free = [torch.cuda.Event() for _ in range(2)]
+            for ev in cut_free:
+                ev.record()
+            cut_state = {"next": None}
+
+        def cam_index(i):
+            return (i * world + rank) % len(cams) if dp else i % len(cams)
+
+        def cam_view(k, buf):
+            c0 = cams[k]
+            return SimpleNamespace(image_width=W, image_height=H, FoVx=c0.FoVx, FoVy=c0.FoVy,
+                                   world_view_transform=buf[:16].view(4, 4),
+                                   full_proj_transform=buf[16:32].view(4, 4), camera_center=buf[32:35],
+                                   image_name=c0.image_name)
+
+        def launch_cut(i):
+            k, b = cam_index(i), i % 2
+            cut_stream.wait_event(cut_free[b])   # the render that last read these buffers has been back-propagated
+            with torch.cuda.stream(cut_stream):
+                cam_dev2[b].copy_(cam_host[k], non_blocking=True)
+                cuts2[b].compute(gh, hm, cam_view(k, cam_dev2[b]), limit, campos_host=cam_host[k][32:35])
+                cut_done[b].record(cut_stream)
+            cut_state["next"] = i
+
         # the loss of train_post.py:132-137: (1 - lambda_dssim) L1 + lambda_dssim (1 - SSIM), lambda_dssim = 0.2
         if args.loss == "l1":
             def loss_fn(image, gt):
@@ -381,7 +417,8 @@ def main():
                 return loss_reference.l1_ssim_loss(image, gt, 0.2)[0]
 
         def e2e_step(i):
-            k = (i * world + rank) % len(cams) if dp else i % len(cams)
+            step_i = i
+            k = cam_index(i)
             c0 = cams[k]
             i = k
             n = pipe_state["n"]
@@ -390,19 +427,26 @@ def main():
                 prefetch(n)
                 pipe_state["primed"] = True
             prefetch(n + 1)
-            cam_dev.copy_(cam_host[i % len(cams)], non_blocking=True)
-            c = SimpleNamespace(image_width=W, image_height=H, FoVx=c0.FoVx, FoVy=c0.FoVy,
-                                world_view_transform=cam_dev[:16].view(4, 4),
-                                full_proj_transform=cam_dev[16:32].view(4, 4), camera_center=cam_dev[32:35],
-                                image_name=c0.image_name)
-            cut.compute(gh, hm, c, limit, campos_host=cam_host[i % len(cams)][32:35])
+            if cut_ahead:
+                if cut_state["next"] != step_i:
+                    launch_cut(step_i)
+                b = step_i % 2
+                torch.cuda.current_stream().wait_event(cut_done[b])
+                c, this_cut = cam_view(k, cam_dev2[b]), cuts2[b]
+            else:
+                cam_dev.copy_(cam_host[i % len(cams)], non_blocking=True)
+                c, this_cut = cam_view(k, cam_dev), cut
+                cut.compute(gh, hm, c, limit, campos_host=cam_host[i % len(cams)][32:35])
             for p in hm.parameters():
                 p.grad = None
-            out = render_post(c, hm, bg, cut, do_depth=False)
+            out = render_post(c, hm, bg, this_cut, do_depth=False)
             torch.cuda.current_stream().wait_event(ready[n % 2])
             loss = loss_fn(out["render"], gt_dev[n % 2])
             loss.backward()
             consumed[n % 2].record()
+            if cut_ahead:
+                cut_free[b].record()
+                launch_cut(step_i + 1)
             if dp:
                 relevant = par.allreduce_sparse_rows([p.grad for p in hm.parameters()],
                                                      hm._opacity.grad.flatten() != 0)
@@ -417,7 +461,9 @@ def main():
                "ms_per_step": ms_e2e / args.steps, "clocks": clocks_e2e,
                "step": "cut + render_post + " + ("0.8 L1 + 0.2 (1 - SSIM)" if args.loss == "l1ssim" else "L1") +
                        " + backward + sparse Adam + loss.item(); ground-truth image prefetched "
-                       "one step ahead on a copy stream (one 24.9 MB H2D per step)"}
+                       "one step ahead on a copy stream (one 24.9 MB H2D per step)" +
+                       ("; the cut of the next step runs on a side stream under this step's backward"
+                        if cut_ahead else "")}
 
     # ---------------- CPU baseline (oracle port, bounded sample) ----------------
     cpu_baseline = None
