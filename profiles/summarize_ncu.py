@@ -1,5 +1,5 @@
 """Turn an `ncu --set full` report into the committed text summary and the per-kernel DRAM traffic table.
-    python profiles/summarize_ncu.py gpurun_out/r01e_full.ncu-rep profiles/r01e_ncu_full.txt "<header line>"
+    python profiles/summarize_ncu.py gpurun_out/r01e_full.ncu-rep profiles/r01e_ncu_full.txt "<header line>" [--no-traffic]
 Writes the summary and refreshes profiles/ncu_traffic.json (dram__bytes_read.sum + dram__bytes_write.sum per
 launch, averaged over the captured launches of each kernel id bench.py reports)."""
 import csv
@@ -53,8 +53,10 @@ def main():
                         tot += float(r[col[k]].replace(",", "")) * UNIT[units[col[k]]]
                     traffic.setdefault(kid, []).append(tot)
     tj = {k: {"dram_bytes_per_launch": sum(v) / len(v), "launches_captured": len(v)} for k, v in traffic.items()}
-    tj["_source"] = (f"{out} (ncu --set full --clock-control none, {header}), dram__bytes_read.sum + "
+    tj["_source"] = (f"{out} ({header}), dram__bytes_read.sum + "
                      "dram__bytes_write.sum averaged over the captured launches")
+    if "--no-traffic" in sys.argv[4:]:
+        return
     with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "ncu_traffic.json"), "w") as f:
         json.dump(tj, f, indent=1)
     print(json.dumps(tj, indent=1))
