@@ -77,7 +77,7 @@ struct SweepSmem {
 // OUT 0: write (key, value).  OUT 1: write value only (last depth pass: only the order is needed).
 // OUT 2: write value and the 64-bit key (key << 32 | depth bits of the slot) -- last tile pass.
 template <typename K, int OUT>
-__global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(
+__global__ void __launch_bounds__(SORT_THREADS, 3) onesweep_kernel(
     const K* __restrict__ kin, K* __restrict__ kout, const uint32_t* __restrict__ vin,
     uint32_t* __restrict__ vout, unsigned long long* __restrict__ kout64,
     const uint32_t* __restrict__ depth_bits, long long n, int shift, uint32_t mask,
