@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define H3DGS_ABI_VERSION 5
+#define H3DGS_ABI_VERSION 6
 
 #if defined(__GNUC__)
 #define H3DGS_API __attribute__((visibility("default")))
@@ -326,14 +326,27 @@ H3DGS_API int h3dgs_sparse_adam(const H3dgsAdamTensor* tensors, int32_t num_tens
  *                                 + l1_scale * sign(img1 - img2)),
  * g = dL_dmap per pixel, or the uniform ssim_scale when dL_dmap is NULL; upstream is a DEVICE scalar or NULL (= 1).
  * For loss = (1 - l) * mean|x - y| + l * (1 - mean(ssim)): ssim_scale = -l / (C H W), l1_scale = (1 - l) / (C H W).
+ * mask ([H,W], device, or NULL): the alpha mask of train_single.py:118-120 / train_post.py:134-136 -- every formula
+ * above is evaluated on img1 * mask (broadcast over the channels) and dL_dimg1 carries the extra factor mask.
  */
 H3DGS_API int h3dgs_ssim_forward(int32_t C, int32_t H, int32_t W, const float* img1, const float* img2,
-                       const float* window11, float* ssim_map, float* dm_dmu1, float* dm_de11, float* dm_de12,
+                       const float* mask, const float* window11, float* ssim_map, float* dm_dmu1, float* dm_de11, float* dm_de12,
                        double* sums, h3dgs_stream_t stream);
 H3DGS_API int h3dgs_ssim_backward(int32_t C, int32_t H, int32_t W, const float* img1, const float* img2,
-                        const float* window11, const float* dm_dmu1, const float* dm_de11, const float* dm_de12,
+                        const float* mask, const float* window11, const float* dm_dmu1, const float* dm_de11, const float* dm_de12,
                         const float* dL_dmap, const float* upstream, float ssim_scale, float l1_scale,
                         float* dL_dimg1, h3dgs_stream_t stream);
+
+/*
+ * Depth loss of train_single.py:133-139, `torch.abs((invDepth - mono_invdepth) * depth_mask).mean()`, over n
+ * elements (mask NULL = all ones).  Forward adds sum |(pred - target) mask| to *sum (device double, zeroed by the
+ * caller).  Backward: dL_dpred = upstream * scale * mask * sign((pred - target) mask); upstream is a DEVICE scalar or
+ * NULL (= 1); for the mean, scale = 1 / n.
+ */
+H3DGS_API int h3dgs_masked_l1_forward(int64_t n, const float* pred, const float* target, const float* mask, double* sum,
+                            h3dgs_stream_t stream);
+H3DGS_API int h3dgs_masked_l1_backward(int64_t n, const float* pred, const float* target, const float* mask,
+                             const float* upstream, float scale, float* dL_dpred, h3dgs_stream_t stream);
 
 /* Instrumented pass for the FLOP accounting of the blend kernels: while `counters` (device,
  * (16 + 4 x tiles) x uint64, zeroed by the caller) is set, the blend kernels run a counting variant and add, per evaluated

@@ -2,7 +2,9 @@
 the checker for csrc/loss.cu.  Follows utils/loss_utils.py:17-18 (l1_loss), :23-31 (gaussian, create_window),
 :33-63 (ssim, _ssim) and the loss assembly of train_single.py:122-125 / train_post.py:132-137.
 Pinned against outputs of the reference's own module (tests/golden/loss_l1_ssim.npz, made by
-tests/golden/make_golden_loss.py, which imports /root/reference/utils/loss_utils.py)."""
+tests/golden/make_golden_loss.py, which imports /root/reference/utils/loss_utils.py); the masked cases and the depth
+loss (formulas written inline in train_single.py:116-139, not importable functions) are pinned against the same
+script's transcription of those lines around the reference's l1_loss / ssim."""
 from math import exp
 
 import torch
@@ -42,6 +44,15 @@ def l1_loss(a, b):                                     # loss_utils.py:17-18
     return torch.abs(a - b).mean()
 
 
-def l1_ssim_loss(image, gt, lambda_dssim=0.2):         # train_single.py:122-125
+def l1_ssim_loss(image, gt, lambda_dssim=0.2, mask=None):   # train_single.py:116-125, train_post.py:132-137
+    if mask is not None:                                    # train_single.py:118-120: image *= alpha_mask
+        image = image * mask
     ll1 = l1_loss(image, gt)
     return (1.0 - lambda_dssim) * ll1 + lambda_dssim * (1.0 - ssim(image, gt)), ll1
+
+
+def depth_l1(inv_depth, mono_invdepth, depth_mask=None):    # train_single.py:133-139 (Ll1depth_pure)
+    d = inv_depth - mono_invdepth
+    if depth_mask is not None:
+        d = d * depth_mask
+    return torch.abs(d).mean()

@@ -147,11 +147,13 @@ cudaError_t run_interpolation_weights(int K, const int* indices, float target_si
                                       int* kids, cudaStream_t s);
 cudaError_t run_sparse_adam(const H3dgsAdamTensor* tensors, int n, const long long* relevant,
                             long long num_relevant, long long num_rows, cudaStream_t s);
-cudaError_t run_ssim_forward(int C, int H, int W, const float* img1, const float* img2, const float* window,
-                             float* ssim_map, float* dm_dmu1, float* dm_de11, float* dm_de12, double* sums,
+cudaError_t run_ssim_forward(int C, int H, int W, const float* img1, const float* img2, const float* mask,
+                             const float* window, float* ssim_map, float* dm_dmu1, float* dm_de11, float* dm_de12, double* sums,
                              cudaStream_t s);
-cudaError_t run_ssim_backward(int C, int H, int W, const float* img1, const float* img2, const float* window,
-                              const float* dm_dmu1, const float* dm_de11, const float* dm_de12,
+cudaError_t run_masked_l1(long long n, const float* pred, const float* target, const float* mask, double* sum,
+                          const float* upstream, float scale, float* grad, cudaStream_t s);
+cudaError_t run_ssim_backward(int C, int H, int W, const float* img1, const float* img2, const float* mask,
+                              const float* window, const float* dm_dmu1, const float* dm_de11, const float* dm_de12,
                               const float* dL_dmap, const float* upstream, float ssim_scale, float l1_scale,
                               float* dL_dimg1, cudaStream_t s);
 cudaError_t run_pack_rows(const H3dgsRowTensor* tensors, int n, const long long* rows, long long K, float* packed,
@@ -607,8 +609,8 @@ int h3dgs_unpack_rows(const H3dgsRowTensor* tensors, int32_t num_tensors, const 
   return pack_rows_common(tensors, num_tensors, rows, num_rows, const_cast<float*>(packed), scale, false, stream);
 }
 
-int h3dgs_ssim_forward(int32_t C, int32_t H, int32_t W, const float* img1, const float* img2, const float* window11,
-                       float* ssim_map, float* dm_dmu1, float* dm_de11, float* dm_de12, double* sums,
+int h3dgs_ssim_forward(int32_t C, int32_t H, int32_t W, const float* img1, const float* img2, const float* mask,
+                       const float* window11, float* ssim_map, float* dm_dmu1, float* dm_de11, float* dm_de12, double* sums,
                        h3dgs_stream_t stream) {
   if (C < 0 || H < 0 || W < 0) return fail(H3DGS_EINVAL, "h3dgs_ssim_forward: negative size");
   if (C == 0 || H == 0 || W == 0) return 0;
@@ -616,13 +618,13 @@ int h3dgs_ssim_forward(int32_t C, int32_t H, int32_t W, const float* img1, const
   if (!img1 || !img2 || !window11 || !sums) return fail(H3DGS_EINVAL, "h3dgs_ssim_forward: img1, img2, window and sums are required");
   if ((dm_dmu1 != nullptr) != (dm_de11 != nullptr) || (dm_dmu1 != nullptr) != (dm_de12 != nullptr))
     return fail(H3DGS_EINVAL, "h3dgs_ssim_forward: pass all three derivative maps or none");
-  H3_CUDA(run_ssim_forward(C, H, W, img1, img2, window11, ssim_map, dm_dmu1, dm_de11, dm_de12, sums,
+  H3_CUDA(run_ssim_forward(C, H, W, img1, img2, mask, window11, ssim_map, dm_dmu1, dm_de11, dm_de12, sums,
                            (cudaStream_t)stream));
   return 0;
 }
 
-int h3dgs_ssim_backward(int32_t C, int32_t H, int32_t W, const float* img1, const float* img2, const float* window11,
-                        const float* dm_dmu1, const float* dm_de11, const float* dm_de12, const float* dL_dmap,
+int h3dgs_ssim_backward(int32_t C, int32_t H, int32_t W, const float* img1, const float* img2, const float* mask,
+                        const float* window11, const float* dm_dmu1, const float* dm_de11, const float* dm_de12, const float* dL_dmap,
                         const float* upstream, float ssim_scale, float l1_scale, float* dL_dimg1,
                         h3dgs_stream_t stream) {
   if (C < 0 || H < 0 || W < 0) return fail(H3DGS_EINVAL, "h3dgs_ssim_backward: negative size");
@@ -630,8 +632,27 @@ int h3dgs_ssim_backward(int32_t C, int32_t H, int32_t W, const float* img1, cons
   if (C > 65535) return fail(H3DGS_EINVAL, "h3dgs_ssim_backward: more than 65535 channels");
   if (!img1 || !img2 || !window11 || !dm_dmu1 || !dm_de11 || !dm_de12 || !dL_dimg1)
     return fail(H3DGS_EINVAL, "h3dgs_ssim_backward: null argument");
-  H3_CUDA(run_ssim_backward(C, H, W, img1, img2, window11, dm_dmu1, dm_de11, dm_de12, dL_dmap, upstream, ssim_scale,
+  H3_CUDA(run_ssim_backward(C, H, W, img1, img2, mask, window11, dm_dmu1, dm_de11, dm_de12, dL_dmap, upstream, ssim_scale,
                             l1_scale, dL_dimg1, (cudaStream_t)stream));
+  return 0;
+}
+
+int h3dgs_masked_l1_forward(int64_t n, const float* pred, const float* target, const float* mask, double* sum,
+                            h3dgs_stream_t stream) {
+  if (n < 0) return fail(H3DGS_EINVAL, "h3dgs_masked_l1_forward: negative size");
+  if (n == 0) return 0;
+  if (!pred || !target || !sum) return fail(H3DGS_EINVAL, "h3dgs_masked_l1_forward: pred, target and sum are required");
+  H3_CUDA(run_masked_l1(n, pred, target, mask, sum, nullptr, 0.f, nullptr, (cudaStream_t)stream));
+  return 0;
+}
+
+int h3dgs_masked_l1_backward(int64_t n, const float* pred, const float* target, const float* mask,
+                             const float* upstream, float scale, float* dL_dpred, h3dgs_stream_t stream) {
+  if (n < 0) return fail(H3DGS_EINVAL, "h3dgs_masked_l1_backward: negative size");
+  if (n == 0) return 0;
+  if (!pred || !target || !dL_dpred)
+    return fail(H3DGS_EINVAL, "h3dgs_masked_l1_backward: pred, target and dL_dpred are required");
+  H3_CUDA(run_masked_l1(n, pred, target, mask, nullptr, upstream, scale, dL_dpred, (cudaStream_t)stream));
   return 0;
 }
 

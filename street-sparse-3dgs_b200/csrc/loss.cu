@@ -25,6 +25,7 @@ struct LossArgs {
   int C, H, W;
   const float* img1;      // rendered image [C,H,W]
   const float* img2;      // ground truth   [C,H,W]
+  const float* mask;      // [H,W] multiplied into img1 (train_single.py:118-120 `image *= alpha_mask`), or NULL
   float w[11];            // normalised 1-D Gaussian window (utils/loss_utils.py:23-25)
   float* ssim_map;        // [C,H,W] or NULL
   float* dm_dmu1;         // [C,H,W] or NULL (no gradient wanted)
@@ -63,6 +64,7 @@ __global__ void __launch_bounds__(LT * LT) ssim_fwd_kernel(const LossArgs a) {
     if (gy >= 0 && gy < a.H && gx >= 0 && gx < a.W) {
       v1 = __ldg(p1 + (size_t)gy * a.W + gx);
       v2 = __ldg(p2 + (size_t)gy * a.W + gx);
+      if (a.mask) v1 *= __ldg(a.mask + (size_t)gy * a.W + gx);
     }
     s1[ly][lx] = v1;
     s2[ly][lx] = v2;
@@ -170,8 +172,9 @@ __global__ void __launch_bounds__(LT * LT) ssim_bwd_kernel(const LossArgs a) {
     c2 += wk * hz[2][ty + k][tx];
   }
   const size_t o = base + (size_t)gy * a.W + gx;
-  const float x = __ldg(a.img1 + o), y = __ldg(a.img2 + o);
-  const float up = a.upstream ? __ldg(a.upstream) : 1.0f;
+  const float m = a.mask ? __ldg(a.mask + (size_t)gy * a.W + gx) : 1.0f;
+  const float x = __ldg(a.img1 + o) * m, y = __ldg(a.img2 + o);
+  const float up = (a.upstream ? __ldg(a.upstream) : 1.0f) * m;   // d (img1 m) / d img1 = m
   float g = (c0 + 2.f * x * c1 + y * c2) * (a.dL_dmap ? 1.0f : a.ssim_scale);
   if (a.l1_scale != 0.f) {
     const float d = x - y;
@@ -180,20 +183,56 @@ __global__ void __launch_bounds__(LT * LT) ssim_bwd_kernel(const LossArgs a) {
   a.dL_dimg1[o] = g * up;
 }
 
-LossArgs make_args(int C, int H, int W, const float* img1, const float* img2, const float* window) {
+// Depth loss of train_single.py:133-139: mean |(pred - target) mask| over n elements.  Forward adds the sum to
+// *sum; backward writes upstream * scale * sign((pred - target) mask) * mask.
+__global__ void __launch_bounds__(256) masked_l1_fwd_kernel(long long n, const float* __restrict__ pred,
+                                                            const float* __restrict__ target,
+                                                            const float* __restrict__ mask, double* sum) {
+  __shared__ float red[8];
+  float acc = 0.f;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    float d = __ldg(pred + i) - __ldg(target + i);
+    if (mask) d *= __ldg(mask + i);
+    acc += fabsf(d);
+  }
+  acc = warp_sum(acc);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0.0;
+    for (int i = 0; i < 8; ++i) t += (double)red[i];
+    atomicAdd(sum, t);
+  }
+}
+
+__global__ void __launch_bounds__(256) masked_l1_bwd_kernel(long long n, const float* __restrict__ pred,
+                                                            const float* __restrict__ target,
+                                                            const float* __restrict__ mask,
+                                                            const float* __restrict__ upstream, float scale,
+                                                            float* __restrict__ grad) {
+  const float up = (upstream ? __ldg(upstream) : 1.0f) * scale;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const float m = mask ? __ldg(mask + i) : 1.0f;
+    const float d = (__ldg(pred + i) - __ldg(target + i)) * m;
+    grad[i] = up * m * (d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f));
+  }
+}
+
+LossArgs make_args(int C, int H, int W, const float* img1, const float* img2, const float* mask,
+                   const float* window) {
   LossArgs a;
   std::memset(&a, 0, sizeof(a));
-  a.C = C; a.H = H; a.W = W; a.img1 = img1; a.img2 = img2;
+  a.C = C; a.H = H; a.W = W; a.img1 = img1; a.img2 = img2; a.mask = mask;
   for (int i = 0; i < 11; ++i) a.w[i] = window[i];
   return a;
 }
 
 }  // namespace
 
-cudaError_t run_ssim_forward(int C, int H, int W, const float* img1, const float* img2, const float* window,
-                             float* ssim_map, float* dm_dmu1, float* dm_de11, float* dm_de12, double* sums,
+cudaError_t run_ssim_forward(int C, int H, int W, const float* img1, const float* img2, const float* mask,
+                             const float* window, float* ssim_map, float* dm_dmu1, float* dm_de11, float* dm_de12, double* sums,
                              cudaStream_t s) {
-  LossArgs a = make_args(C, H, W, img1, img2, window);
+  LossArgs a = make_args(C, H, W, img1, img2, mask, window);
   a.ssim_map = ssim_map; a.dm_dmu1 = dm_dmu1; a.dm_de11 = dm_de11; a.dm_de12 = dm_de12; a.sums = sums;
   const dim3 grid((W + LT - 1) / LT, (H + LT - 1) / LT, C), block(LT, LT);
   ProfScope ps(K_LOSS, s);
@@ -202,11 +241,11 @@ cudaError_t run_ssim_forward(int C, int H, int W, const float* img1, const float
   return cudaGetLastError();
 }
 
-cudaError_t run_ssim_backward(int C, int H, int W, const float* img1, const float* img2, const float* window,
-                              const float* dm_dmu1, const float* dm_de11, const float* dm_de12,
+cudaError_t run_ssim_backward(int C, int H, int W, const float* img1, const float* img2, const float* mask,
+                              const float* window, const float* dm_dmu1, const float* dm_de11, const float* dm_de12,
                               const float* dL_dmap, const float* upstream, float ssim_scale, float l1_scale,
                               float* dL_dimg1, cudaStream_t s) {
-  LossArgs a = make_args(C, H, W, img1, img2, window);
+  LossArgs a = make_args(C, H, W, img1, img2, mask, window);
   a.dm_dmu1 = const_cast<float*>(dm_dmu1); a.dm_de11 = const_cast<float*>(dm_de11);
   a.dm_de12 = const_cast<float*>(dm_de12);
   a.dL_dmap = dL_dmap; a.upstream = upstream; a.ssim_scale = ssim_scale; a.l1_scale = l1_scale;
@@ -214,6 +253,17 @@ cudaError_t run_ssim_backward(int C, int H, int W, const float* img1, const floa
   const dim3 grid((W + LT - 1) / LT, (H + LT - 1) / LT, C), block(LT, LT);
   ProfScope ps(K_LOSS, s);
   ssim_bwd_kernel<<<grid, block, 0, s>>>(a);
+  return cudaGetLastError();
+}
+
+cudaError_t run_masked_l1(long long n, const float* pred, const float* target, const float* mask, double* sum,
+                          const float* upstream, float scale, float* grad, cudaStream_t s) {
+  if (n <= 0) return cudaSuccess;
+  long long blocks = (n + 256 * 8 - 1) / (256 * 8);
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  ProfScope ps(K_LOSS, s);
+  if (grad) masked_l1_bwd_kernel<<<(unsigned)blocks, 256, 0, s>>>(n, pred, target, mask, upstream, scale, grad);
+  else masked_l1_fwd_kernel<<<(unsigned)blocks, 256, 0, s>>>(n, pred, target, mask, sum);
   return cudaGetLastError();
 }
 

@@ -107,10 +107,12 @@ SIGNATURES = {
     "h3dgs_sparse_adam": (c_int, [POINTER(AdamTensor), c_int32, c_void_p, c_int64, c_int64, c_void_p]),
     "h3dgs_pack_rows": (c_int, [POINTER(RowTensor), c_int32, c_void_p, c_int64, c_void_p, c_void_p]),
     "h3dgs_unpack_rows": (c_int, [POINTER(RowTensor), c_int32, c_void_p, c_int64, c_void_p, c_float, c_void_p]),
-    "h3dgs_ssim_forward": (c_int, [c_int32, c_int32, c_int32, c_void_p, c_void_p, POINTER(c_float), c_void_p, c_void_p,
-                                    c_void_p, c_void_p, c_void_p, c_void_p]),
-    "h3dgs_ssim_backward": (c_int, [c_int32, c_int32, c_int32, c_void_p, c_void_p, POINTER(c_float), c_void_p, c_void_p,
-                                     c_void_p, c_void_p, c_void_p, c_float, c_float, c_void_p, c_void_p]),
+    "h3dgs_ssim_forward": (c_int, [c_int32, c_int32, c_int32, c_void_p, c_void_p, c_void_p, POINTER(c_float), c_void_p,
+                                    c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "h3dgs_ssim_backward": (c_int, [c_int32, c_int32, c_int32, c_void_p, c_void_p, c_void_p, POINTER(c_float), c_void_p,
+                                     c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_float, c_void_p, c_void_p]),
+    "h3dgs_masked_l1_forward": (c_int, [c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "h3dgs_masked_l1_backward": (c_int, [c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_void_p, c_void_p]),
     "h3dgs_blend_stats": (c_int, [c_void_p]),
     "h3dgs_launch_count": (c_int64, []),
     "h3dgs_profile_enable": (c_int, [c_int]),
@@ -144,7 +146,7 @@ def lib():
             fn = getattr(handle, name)
             fn.restype = res
             fn.argtypes = args
-        if handle.h3dgs_abi_version() != 5:
+        if handle.h3dgs_abi_version() != 6:
             raise H3dgsError("libh3dgs_b200.so ABI version mismatch")
         _lib = handle
     return _lib

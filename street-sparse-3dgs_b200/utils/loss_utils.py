@@ -48,24 +48,39 @@ def _check(img1, img2):
     return img1.contiguous(), img2.contiguous()
 
 
-def _forward(img1, img2, want_grad, want_map=False):
+def _check_mask(mask, img):
+    """The alpha mask of train_single.py:118-120 (``image *= alpha_mask``): [H,W] or [1,H,W], broadcast over the
+    channels.  It receives no gradient."""
+    if mask is None:
+        return None
+    if not mask.is_cuda or mask.dtype != torch.float32:
+        raise TypeError("fused loss: the mask must be a CUDA float32 tensor")
+    H, W = img.shape[-2:]
+    if mask.numel() != H * W or img.dim() != 3:
+        raise RuntimeError("fused loss: the mask must be [H,W] or [1,H,W] for a [C,H,W] image")
+    return mask.detach().contiguous()
+
+
+def _forward(img1, img2, want_grad, want_map=False, mask=None):
     H, W = img1.shape[-2:]
     C = img1.numel() // (H * W)
     sums = torch.zeros(2, dtype=torch.float64, device=img1.device)
     maps = [torch.empty_like(img1) for _ in range(3)] if want_grad else [None, None, None]
     smap = torch.empty_like(img1) if want_map else None
-    nat.check(nat.lib().h3dgs_ssim_forward(C, H, W, nat.ptr(img1), nat.ptr(img2), _window11(), nat.ptr(smap),
+    nat.check(nat.lib().h3dgs_ssim_forward(C, H, W, nat.ptr(img1), nat.ptr(img2), nat.ptr(mask), _window11(),
+                                           nat.ptr(smap),
                                            nat.ptr(maps[0]), nat.ptr(maps[1]), nat.ptr(maps[2]), nat.ptr(sums),
                                            nat.stream_handle()), "h3dgs_ssim_forward")
     return sums, maps, smap
 
 
-def _backward(img1, img2, maps, upstream, ssim_scale, l1_scale):
+def _backward(img1, img2, maps, upstream, ssim_scale, l1_scale, mask=None):
     H, W = img1.shape[-2:]
     C = img1.numel() // (H * W)
     grad = torch.empty_like(img1)
     up = upstream.to(torch.float32).contiguous()
-    nat.check(nat.lib().h3dgs_ssim_backward(C, H, W, nat.ptr(img1), nat.ptr(img2), _window11(), nat.ptr(maps[0]),
+    nat.check(nat.lib().h3dgs_ssim_backward(C, H, W, nat.ptr(img1), nat.ptr(img2), nat.ptr(mask), _window11(),
+                                            nat.ptr(maps[0]),
                                             nat.ptr(maps[1]), nat.ptr(maps[2]), None, nat.ptr(up), ssim_scale,
                                             l1_scale, nat.ptr(grad), nat.stream_handle()), "h3dgs_ssim_backward")
     return grad
@@ -89,10 +104,12 @@ class _SSIMMean(torch.autograd.Function):
 
 class _L1SSIM(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, image, gt, lambda_dssim):
+    def forward(ctx, image, gt, lambda_dssim, mask):
         image, gt = _check(image, gt)
+        mask = _check_mask(mask, image)
         want = ctx.needs_input_grad[0]
-        sums, maps, _ = _forward(image, gt, want)
+        sums, maps, _ = _forward(image, gt, want, mask=mask)
+        ctx.mask = mask
         n = image.numel()
         means = (sums / n).to(torch.float32)
         ll1 = means[1]
@@ -107,7 +124,8 @@ class _L1SSIM(torch.autograd.Function):
     def backward(ctx, grad_loss, _grad_l1):
         image, gt, m0, m1, m2 = ctx.saved_tensors
         n = image.numel()
-        return _backward(image, gt, (m0, m1, m2), grad_loss, -ctx.lam / n, (1.0 - ctx.lam) / n), None, None
+        return (_backward(image, gt, (m0, m1, m2), grad_loss, -ctx.lam / n, (1.0 - ctx.lam) / n, mask=ctx.mask),
+                None, None, None)
 
 
 def ssim(img1, img2, window_size=11, size_average=True):
@@ -127,7 +145,48 @@ def ssim_map(img1, img2):
     return _forward(img1, img2, False, want_map=True)[2]
 
 
-def fused_l1_ssim_loss(image, gt, lambda_dssim=0.2):
+def fused_l1_ssim_loss(image, gt, lambda_dssim=0.2, mask=None):
     """``(loss, Ll1)`` with ``loss = (1 - lambda) * l1_loss(image, gt) + lambda * (1 - ssim(image, gt))``
-    (train_single.py:122-125, train_post.py:132-137); ``Ll1`` is returned for logging and carries no gradient."""
-    return _L1SSIM.apply(image, gt, float(lambda_dssim))
+    (train_single.py:122-125, train_post.py:132-137); ``Ll1`` is returned for logging and carries no gradient.
+    With ``mask`` (the camera's ``alpha_mask``, [H,W] or [1,H,W]) both terms are evaluated on ``image * mask`` as
+    train_single.py:118-120 / train_post.py:134-136 do, without materialising the product."""
+    return _L1SSIM.apply(image, gt, float(lambda_dssim), mask)
+
+
+class _MaskedL1(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, pred, target, mask):
+        if not (pred.is_cuda and target.is_cuda) or pred.dtype != torch.float32 or target.dtype != torch.float32:
+            raise TypeError("masked_l1_loss needs CUDA float32 tensors (no CPU fallback)")
+        if pred.shape != target.shape or (mask is not None and mask.numel() != pred.numel()):
+            raise RuntimeError("masked_l1_loss: pred, target and mask must have the same number of elements")
+        pred, target = pred.contiguous(), target.contiguous()
+        if mask is not None:
+            if not mask.is_cuda or mask.dtype != torch.float32:
+                raise TypeError("masked_l1_loss: the mask must be a CUDA float32 tensor")
+            mask = mask.detach().contiguous()
+        n = pred.numel()
+        s = torch.zeros(1, dtype=torch.float64, device=pred.device)
+        nat.check(nat.lib().h3dgs_masked_l1_forward(n, nat.ptr(pred), nat.ptr(target), nat.ptr(mask), nat.ptr(s),
+                                                    nat.stream_handle()), "h3dgs_masked_l1_forward")
+        ctx.save_for_backward(pred, target)
+        ctx.mask = mask
+        return (s[0] / max(n, 1)).to(torch.float32)
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        pred, target = ctx.saved_tensors
+        n = pred.numel()
+        grad = torch.empty_like(pred)
+        up = grad_out.to(torch.float32).contiguous()
+        nat.check(nat.lib().h3dgs_masked_l1_backward(n, nat.ptr(pred), nat.ptr(target), nat.ptr(ctx.mask), nat.ptr(up),
+                                                     1.0 / max(n, 1), nat.ptr(grad), nat.stream_handle()),
+                  "h3dgs_masked_l1_backward")
+        return grad, None, None
+
+
+def masked_l1_loss(pred, target, mask=None):
+    """``torch.abs((pred - target) * mask).mean()`` -- the depth loss of train_single.py:133-139
+    (``Ll1depth_pure`` with ``pred = invDepth``, ``target = mono_invdepth``, ``mask = depth_mask``) in one forward and
+    one backward kernel.  Gradient flows to ``pred`` only."""
+    return _MaskedL1.apply(pred, target, mask)

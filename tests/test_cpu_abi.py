@@ -26,7 +26,7 @@ def test_library_exports_every_declared_symbol():
         assert hasattr(handle, n), f"{n} declared in the header but not exported"
         assert n in nat.SIGNATURES, f"{n} has no ctypes prototype"
     assert sorted(nat.SIGNATURES) == names
-    assert nat.lib().h3dgs_abi_version() == 5
+    assert nat.lib().h3dgs_abi_version() == 6
 
 
 def test_workspace_queries_are_sane():
@@ -59,9 +59,13 @@ def test_usage_errors_are_reported_not_crashed():
     assert L.h3dgs_unpack_rows(rt, 1, None, 0, None, 1.0, None) == 0      # no rows: nothing to do
     assert L.h3dgs_unpack_rows(rt, 1, None, 3, None, 1.0, None) == -1     # rows / payload missing
     w = (ctypes.c_float * 11)(*([1.0 / 11] * 11))
-    assert L.h3dgs_ssim_forward(3, 0, 16, None, None, w, None, None, None, None, None, None) == 0   # empty image
-    assert L.h3dgs_ssim_forward(3, 8, 8, None, None, w, None, None, None, None, None, None) == -1
-    assert L.h3dgs_ssim_backward(3, 8, 8, None, None, w, None, None, None, None, None, 1.0, 0.0, None, None) == -1
+    assert L.h3dgs_ssim_forward(3, 0, 16, None, None, None, w, None, None, None, None, None, None) == 0   # empty image
+    assert L.h3dgs_ssim_forward(3, 8, 8, None, None, None, w, None, None, None, None, None, None) == -1
+    assert L.h3dgs_ssim_backward(3, 8, 8, None, None, None, w, None, None, None, None, None, 1.0, 0.0, None, None) == -1
+    assert L.h3dgs_masked_l1_forward(0, None, None, None, None, None) == 0      # empty
+    assert L.h3dgs_masked_l1_forward(-1, None, None, None, None, None) == -1
+    assert L.h3dgs_masked_l1_forward(16, None, None, None, None, None) == -1
+    assert L.h3dgs_masked_l1_backward(16, None, None, None, None, 1.0, None, None) == -1
     assert L.h3dgs_blend_stats(None) == 0
     with pytest.raises(nat.H3dgsError):
         nat.check(-1, "x")

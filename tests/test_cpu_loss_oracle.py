@@ -24,6 +24,23 @@ def test_loss_oracle_matches_reference_fixture(name):
     np.testing.assert_allclose(img.grad.numpy(), GOLD[f"{name}_grad"], rtol=1e-5, atol=1e-9)
 
 
+@pytest.mark.parametrize("name", ["m1", "m2"])
+def test_masked_loss_and_depth_l1_oracle_match_reference_fixture(name):
+    """Alpha-masked photometric loss (train_single.py:116-125) and the depth loss (:133-139)."""
+    img = torch.from_numpy(GOLD[f"{name}_image"]).requires_grad_(True)
+    gt, mask = torch.from_numpy(GOLD[f"{name}_gt"]), torch.from_numpy(GOLD[f"{name}_mask"])
+    loss, ll1 = lr.l1_ssim_loss(img, gt, float(GOLD[f"{name}_lam"]), mask=mask)
+    loss.backward()
+    assert abs(ll1.item() - float(GOLD[f"{name}_l1"])) <= 1e-7
+    assert abs(loss.item() - float(GOLD[f"{name}_loss"])) <= 1e-6
+    np.testing.assert_allclose(img.grad.numpy(), GOLD[f"{name}_grad"], rtol=1e-5, atol=1e-9)
+    inv = torch.from_numpy(GOLD[f"{name}_inv"]).requires_grad_(True)
+    ld = lr.depth_l1(inv, torch.from_numpy(GOLD[f"{name}_mono"]), torch.from_numpy(GOLD[f"{name}_dmask"]))
+    ld.backward()
+    assert abs(ld.item() - float(GOLD[f"{name}_depth_l1"])) <= 1e-7
+    np.testing.assert_array_equal(inv.grad.numpy(), GOLD[f"{name}_depth_grad"])
+
+
 def test_window_is_the_reference_window():
     w = lr.gaussian(11, 1.5)
     assert abs(float(w.sum()) - 1.0) < 1e-6 and torch.equal(w, w.flip(0)) and float(w[5]) == float(w.max())

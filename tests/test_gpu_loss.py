@@ -36,6 +36,48 @@ def test_fused_loss_matches_reference_fixture(name):
     assert not ll1.requires_grad
 
 
+@pytest.mark.parametrize("name", ["m1", "m2"])
+def test_masked_loss_and_depth_l1_match_reference_fixture(name):
+    """fused_l1_ssim_loss(mask=alpha_mask) and masked_l1_loss against the reference-made fixtures
+    (train_single.py:116-125 with `image *= alpha_mask`, and the depth loss of :133-139)."""
+    from utils import loss_utils as lu
+    img = torch.from_numpy(GOLD[f"{name}_image"]).to(DEV).requires_grad_(True)
+    gt = torch.from_numpy(GOLD[f"{name}_gt"]).to(DEV)
+    mask = torch.from_numpy(GOLD[f"{name}_mask"]).to(DEV)
+    loss, ll1 = lu.fused_l1_ssim_loss(img, gt, float(GOLD[f"{name}_lam"]), mask=mask)
+    loss.backward()
+    assert abs(ll1.item() - float(GOLD[f"{name}_l1"])) <= 2e-6
+    assert abs(loss.item() - float(GOLD[f"{name}_loss"])) <= 2e-6
+    assert rel(img.grad.cpu(), torch.from_numpy(GOLD[f"{name}_grad"])) <= 1e-4
+    inv = torch.from_numpy(GOLD[f"{name}_inv"]).to(DEV).requires_grad_(True)
+    mono = torch.from_numpy(GOLD[f"{name}_mono"]).to(DEV)
+    dmask = torch.from_numpy(GOLD[f"{name}_dmask"]).to(DEV)
+    ld = lu.masked_l1_loss(inv, mono, dmask)
+    (3.0 * ld).backward()
+    assert abs(ld.item() - float(GOLD[f"{name}_depth_l1"])) <= 1e-7
+    assert rel(inv.grad.cpu(), 3.0 * torch.from_numpy(GOLD[f"{name}_depth_grad"])) <= 1e-6
+    # no mask = plain mean absolute difference
+    assert abs(lu.masked_l1_loss(inv.detach(), mono).item() - torch.abs(inv.detach() - mono).mean().item()) <= 1e-7
+
+
+def test_masked_loss_full_size_against_oracle():
+    """1080p: masked photometric loss and depth loss against the CPU oracle on the same seeded inputs."""
+    from utils import loss_utils as lu
+    g = torch.Generator().manual_seed(21)
+    gt = torch.rand(3, 1080, 1920, generator=g)
+    img = (gt + 0.1 * torch.randn(3, 1080, 1920, generator=g)).clamp(0, 1)
+    mask = (torch.rand(1, 1080, 1920, generator=g) > 0.2).float()
+    a = img.clone().requires_grad_(True)
+    want, _ = lr.l1_ssim_loss(a, gt, 0.2, mask=mask)
+    want.backward()
+    b = img.to(DEV).requires_grad_(True)
+    got, _ = lu.fused_l1_ssim_loss(b, gt.to(DEV), 0.2, mask=mask.to(DEV))
+    got.backward()
+    assert abs(got.item() - want.item()) <= 2e-6
+    assert rel(b.grad.cpu(), a.grad) <= 1e-4
+    assert float(b.grad.cpu()[:, mask[0] == 0].abs().max()) == 0.0    # masked-out pixels receive nothing
+
+
 @pytest.mark.parametrize("shape", [(3, 1080, 1920), (3, 137, 211), (1, 16, 16), (2, 3, 40, 56), (3, 5, 300)])
 def test_ssim_matches_cpu_oracle(shape):
     from utils import loss_utils as lu
