@@ -145,6 +145,12 @@ def main():
     W, H = args.width, args.height
     seed = rank if args.mode == "chunks" else 0
     attrs = workload.build_scene(args.levels, args.skybox, seed, dev, free_corridor=True)
+    if args.mode == "dp" and world > 1:
+        # replicas start from rank 0's parameters, bit for bit (host-side scene generation is not guaranteed to
+        # be bit-reproducible from process to process: harness/diag_stage_modes.py)
+        for k in sorted(attrs):
+            if torch.is_tensor(attrs[k]) and attrs[k].is_cuda:
+                dist.broadcast(attrs[k], src=0)
     n_store = attrs["means3D"].size(0)
     cams = workload.cameras(W, H, args.cameras, dev, seed=seed * 100)
     bg = torch.zeros(3, device=dev)

@@ -32,7 +32,7 @@ __device__ __forceinline__ void tile_rect(float px, float py, int ex, int ey, in
 }
 
 template <bool FUSED>
-__global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreArgs a) {
+__global__ void __launch_bounds__(256, 3) preprocess_fwd_kernel(const PreArgs a) {
   const int t_idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (t_idx >= a.P) return;
 

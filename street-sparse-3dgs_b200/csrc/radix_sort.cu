@@ -111,13 +111,11 @@ __global__ void __launch_bounds__(SORT_THREADS, 3) onesweep_kernel(
     const uint32_t peers = __match_any_sync(0xffffffffu, d);
     const int leader = __ffs(peers) - 1;
     uint32_t prior = 0;
-    if (lane == leader) {
-      prior = sm.cnt[warp][d];
-      sm.cnt[warp][d] = prior + __popc(peers);
-    }
+    // one shared-memory atomic by the leader of each digit group (the counters of a warp are its own, so the
+    // atomic is only the fused read-modify-write; program order keeps the ranking stable)
+    if (lane == leader) prior = atomicAdd(&sm.cnt[warp][d], (uint32_t)__popc(peers));
     prior = __shfl_sync(0xffffffffu, prior, leader);
     rank[i] = prior + __popc(peers & lt);
-    __syncwarp();
   }
   __syncthreads();
 
