@@ -52,6 +52,8 @@ def main():
     rg = dv["ranges"].view(-1, 2).long()
     n = (rg[:, 1] - rg[:, 0]).cpu()
     t = cnt[16:].view(T, 4).cpu()
+    print("# backward: since the list cuts (csrc/common.cuh BLEND_SEG) the per-tile times cover the FIRST work item of "
+          "each tile (list positions < 1024); the deeper items lead the grid and are not timed individually")
     for name, a, b in (("forward", 0, 1), ("backward", 2, 3)):
         st, en = t[:, a], t[:, b]
         ok = en > 0

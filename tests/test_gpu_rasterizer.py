@@ -159,6 +159,58 @@ def test_backward_long_lists_cut_into_work_items(interp, depth):
         util.assert_grad_close(go[k], gr[k], gr2[k], k, more_refs=[m[k] for m in more])
 
 
+@pytest.mark.parametrize("n", [1024, 1025, 2048, 2049, 4100])
+def test_backward_work_item_boundaries(n):
+    """List lengths at and around the cuts of the backward work items (1024 entries): n faint Gaussians in four
+    clusters inside ONE tile, each pixel blending only its own cluster's quarter, so the last contributors lie
+    at the very end of an n-entry list and every work item of the tile has live pixels.  Against the reference."""
+    util.need_ref()
+    import diff_gaussian_rasterization as dgr
+    w = h = 64
+    cam = scenes.street_camera(w, h, seed=1, device=DEV)
+    g = torch.Generator().manual_seed(n)
+    centre = torch.tensor([[38.0, 38.0], [42.0, 38.0], [38.0, 42.0], [42.0, 42.0]])[torch.arange(n) % 4]
+    pix = centre + (torch.rand(n, 2, generator=g) - 0.5) * 0.6
+    z = 8.0 + 2.0 * torch.rand(n, generator=g)
+    xv = z * ((pix[:, 0] + 0.5) / (w / 2) - 1.0)           # fovx = fovy = 90 degrees: ndc = x / z
+    yv = z * ((pix[:, 1] + 0.5) / (h / 2) - 1.0)
+    V = cam.world_view_transform.cpu()
+    pos = cam.camera_center.cpu() + xv[:, None] * V[:3, 0] + yv[:, None] * V[:3, 1] + z[:, None] * V[:3, 2]
+    rot = torch.zeros(n, 4)
+    rot[:, 0] = 1.0
+    sc = {"means3D": pos.float().to(DEV).contiguous(),
+          "scales": (0.05 * z)[:, None].repeat(1, 3).float().to(DEV).contiguous(),       # ~1.6 px on screen
+          "rotations": rot.to(DEV), "opacities": torch.full((n, 1), 0.0062, device=DEV),
+          "shs": (torch.randn(n, 16, 3, generator=g) * 0.2).to(DEV).contiguous()}
+    bg = torch.tensor([0.3, 0.1, 0.2], device=DEV)
+    rs = _settings(cam, bg, do_depth=True)
+    R, color, radii, geom, binning, img, invd = dgr._C.rasterize_gaussians(*util.forward_args(rs, sc))
+    dv = dgr._C.debug_view(n, w, h, R, geom, binning, img)
+    rg = dv["ranges"].view(-1, 2).long()
+    assert int((rg[:, 1] - rg[:, 0]).max()) == n, "all Gaussians must share one tile"
+    assert int(dv["tile_last"].max()) > n - 40, f"deepest last contributor {int(dv['tile_last'].max())} of {n}"
+    gen = torch.Generator().manual_seed(7)
+    dcol = torch.randn(3, h, w, generator=gen).to(DEV)
+    ddep = torch.randn(1, h, w, generator=gen).to(DEV)
+
+    def ours(p, m2d):
+        return dgr.GaussianRasterizer(rs)(means3D=p["means3D"], means2D=m2d, opacities=p["opacities"],
+                                          shs=p["shs"], scales=p["scales"], rotations=p["rotations"])
+
+    def ref(p, m2d):
+        return refglue.ref_rasterize(rs, p["means3D"], m2d, p["opacities"], shs=p["shs"], scales=p["scales"],
+                                     rotations=p["rotations"])
+
+    co, ro, go = _run_backward(ours, sc, dcol, ddep)
+    cr, rr, gr = _run_backward(ref, sc, dcol, ddep)
+    more = [_run_backward(ref, sc, dcol, ddep)[2] for _ in range(4)]
+    gr2 = more.pop()
+    torch.cuda.synchronize()
+    assert torch.equal(bits(co), bits(cr))
+    for k in go:
+        util.assert_grad_close(go[k], gr[k], gr2[k], k, more_refs=[m[k] for m in more])
+
+
 def test_precomputed_colors_and_low_sh_degree():
     util.need_ref()
     import diff_gaussian_rasterization as dgr
