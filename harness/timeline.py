@@ -58,6 +58,48 @@ def main():
                            c.camera_center.flatten().cpu()]).pin_memory() for c in cams]
     cam_dev = torch.empty(35, device=dev)
 
+    # the e2e step mirrors bench.py's: fused L1 + SSIM loss, ground truth prefetched on a copy stream, the cut of
+    # step i+1 launched on a side stream right after step i's backward
+    if args.e2e:
+        from utils.loss_utils import fused_l1_ssim_loss
+        gt_dev2 = [torch.empty(3, H, W, device=dev) for _ in range(2)]
+        cam_dev2 = [torch.empty(35, device=dev) for _ in range(2)]
+        cuts2 = [workload.Cut(n_store, dev) for _ in range(2)]
+        copy_stream, cut_stream = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+        ready = [torch.cuda.Event() for _ in range(2)]
+        consumed = [torch.cuda.Event() for _ in range(2)]
+        cut_done = [torch.cuda.Event() for _ in range(2)]
+        cut_free = [torch.cuda.Event() for _ in range(2)]
+        for ev in consumed + cut_free:
+            ev.record()
+        state = {"gt": -1, "cut": -1}
+
+        def view(k, buf):
+            c0 = cams[k]
+            return SimpleNamespace(image_width=W, image_height=H, FoVx=c0.FoVx, FoVy=c0.FoVy,
+                                   world_view_transform=buf[:16].view(4, 4), full_proj_transform=buf[16:32].view(4, 4),
+                                   camera_center=buf[32:35], image_name=c0.image_name)
+
+        def prefetch(j):
+            if state["gt"] >= j:
+                return
+            copy_stream.wait_event(consumed[j % 2])
+            with torch.cuda.stream(copy_stream):
+                gt_dev2[j % 2].copy_(gt_host, non_blocking=True)
+                ready[j % 2].record(copy_stream)
+            state["gt"] = j
+
+        def launch_cut(j):
+            if state["cut"] >= j:
+                return
+            k, b = j % len(cams), j % 2
+            cut_stream.wait_event(cut_free[b])
+            with torch.cuda.stream(cut_stream):
+                cam_dev2[b].copy_(cam_host[k], non_blocking=True)
+                cuts2[b].compute(gh, model, view(k, cam_dev2[b]), limit, campos_host=cam_host[k][32:35])
+                cut_done[b].record(cut_stream)
+            state["cut"] = j
+
     def step(i):
         with torch.profiler.record_function(f"STEP{i}"):
             c0 = cams[i % len(cams)]
@@ -68,16 +110,18 @@ def main():
                 loss = (out["render"] * dcol).sum() + (out["depth"] * ddep).sum()
                 loss.backward()
                 return
-            cam_dev.copy_(cam_host[i % len(cams)], non_blocking=True)
-            gt_dev.copy_(gt_host, non_blocking=True)
-            c = SimpleNamespace(image_width=W, image_height=H, FoVx=c0.FoVx, FoVy=c0.FoVy,
-                                world_view_transform=cam_dev[:16].view(4, 4),
-                                full_proj_transform=cam_dev[16:32].view(4, 4), camera_center=cam_dev[32:35],
-                                image_name=c0.image_name)
-            cut.compute(gh, model, c, limit, campos_host=cam_host[i % len(cams)][32:35])
-            out = workload.ours_render_post(c, model, bg, cut, do_depth=False)
-            loss = torch.abs(out["render"] - gt_dev).mean()
+            b = i % 2
+            prefetch(i)
+            prefetch(i + 1)
+            launch_cut(i)
+            torch.cuda.current_stream().wait_event(cut_done[b])
+            out = workload.ours_render_post(view(i % len(cams), cam_dev2[b]), model, bg, cuts2[b], do_depth=False)
+            torch.cuda.current_stream().wait_event(ready[b])
+            loss = fused_l1_ssim_loss(out["render"], gt_dev2[b], 0.2)[0]
             loss.backward()
+            consumed[b].record()
+            cut_free[b].record()
+            launch_cut(i + 1)
             relevant = (model._opacity.grad.flatten() != 0).nonzero().flatten().long()
             opt.step(relevant)
             loss.item()
@@ -85,10 +129,11 @@ def main():
     for i in range(4):
         step(i)
     torch.cuda.synchronize()
+    base_i = 4
     from torch.profiler import ProfilerActivity, profile
     with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) as prof:
         for i in range(args.steps):
-            step(i)
+            step(base_i + i)
         torch.cuda.synchronize()
     path = os.path.join(tempfile.mkdtemp(), "trace.json")
     prof.export_chrome_trace(path)
