@@ -174,6 +174,31 @@ def ref_render_post(Settings, cam, pc, bg, render_indices, parent_indices, inter
             "radii": radii[vis], "depth": depth}
 
 
+def ref_render(Settings, cam, pc, bg, use_trained_exp=False, debug=False):
+    """gaussian_renderer/__init__.py:20-135 (plain render, indices=None, SH evaluated by the rasterizer) restated
+    on the reference rasterizer: full-store activations through the model's get_* properties, do_depth=True,
+    learnable exposure, clamp; visibility_filter as global ids."""
+    screenspace_points = torch.zeros_like(pc.get_xyz, requires_grad=True) + 0
+    try:
+        screenspace_points.retain_grad()
+    except Exception:
+        pass
+    dev = bg.device
+    rs = make_settings(Settings, cam, bg, sh_degree=pc.active_sh_degree, debug=debug, do_depth=True,
+                       render_indices=torch.empty(0).int().to(dev), parent_indices=torch.empty(0).int().to(dev),
+                       interpolation_weights=torch.empty(0).float().to(dev),
+                       num_node_kids=torch.empty(0).int().to(dev))
+    image, radii, depth = ref_rasterize(rs, pc.get_xyz, screenspace_points, pc.get_opacity, shs=pc.get_features,
+                                        scales=pc.get_scaling, rotations=pc.get_rotation)
+    if use_trained_exp:
+        exposure = pc.get_exposure_from_name(cam.image_name)
+        image = torch.matmul(image.permute(1, 2, 0), exposure[:3, :3]).permute(2, 0, 1) + exposure[:3, 3, None, None]
+    image = image.clamp(0, 1)
+    vis = radii > 0
+    return {"render": image, "depth": depth, "viewspace_points": screenspace_points,
+            "visibility_filter": vis.nonzero().flatten().long(), "radii": radii[vis]}
+
+
 def _align(x, a=128):
     return (x + a - 1) // a * a
 

@@ -55,6 +55,63 @@ class HierModel:
         return [self._xyz, self._features_dc, self._features_rest, self._opacity, self._scaling, self._rotation]
 
 
+class SingleModel:
+    """Parameter store of single-chunk training (train_single.py; scene/gaussian_model.py:40-48,121-153,186-201):
+    raw parameters with exp / normalize / SIGMOID activations, dc/rest features, `skybox_points` skybox rows at the
+    FRONT of the store, one learnable 3x4 exposure per camera."""
+
+    def __init__(self, attrs, skybox_points, camera_names=("cam0",)):
+        f = attrs["shs"]
+        self._xyz = attrs["means3D"].clone().requires_grad_(True)
+        self._features_dc = f[:, :1, :].clone().contiguous().requires_grad_(True)
+        self._features_rest = f[:, 1:, :].clone().contiguous().requires_grad_(True)
+        self._opacity = torch.logit(attrs["opacities"].clamp(1e-4, 1 - 1e-4)).requires_grad_(True)
+        self._scaling = attrs["log_scales"].clone().requires_grad_(True)
+        self._rotation = attrs["rotations"].clone().requires_grad_(True)
+        self.skybox_points = skybox_points
+        self.active_sh_degree = 3
+        self.max_sh_degree = 3
+        self.pretrained_exposures = None
+        self.scaling_activation = torch.exp
+        self.rotation_activation = torch.nn.functional.normalize
+        self.opacity_activation = torch.sigmoid
+        dev = self._xyz.device
+        self.exposure_mapping = {n: i for i, n in enumerate(camera_names)}
+        self._exposure = torch.eye(3, 4, device=dev)[None].repeat(len(camera_names), 1, 1).requires_grad_(True)
+
+    get_xyz = property(lambda self: self._xyz)
+    get_scaling = property(lambda self: self.scaling_activation(self._scaling))
+    get_rotation = property(lambda self: self.rotation_activation(self._rotation))
+    get_opacity = property(lambda self: self.opacity_activation(self._opacity))
+    get_features = property(lambda self: torch.cat((self._features_dc, self._features_rest), dim=1))
+
+    def get_exposure_from_name(self, image_name):
+        return self._exposure[self.exposure_mapping[image_name]]
+
+    param_groups = HierModel.param_groups
+
+    def parameters(self):
+        return [self._xyz, self._features_dc, self._features_rest, self._opacity, self._scaling, self._rotation]
+
+
+def single_chunk_scene(n, skybox, seed, device):
+    """Config 2 scene: `skybox` skybox Gaussians FIRST (scene/gaussian_model.py:186-201), then n street Gaussians."""
+    sc = scenes.street_gaussians(n, seed=seed, device=device, free_corridor=True)
+    if skybox:
+        sky = scenes.skybox_gaussians(skybox, seed=seed + 1, device=device)
+        sc = {k: torch.cat((sky[k], sc[k])).contiguous() for k in sc}
+    return sc
+
+
+def ours_render(cam, model, bg, use_trained_exp=True):
+    from gaussian_renderer import render
+    return render(cam, model, scenes.Pipe, bg, use_trained_exp=use_trained_exp)
+
+
+def ref_render(cam, model, bg, use_trained_exp=True):
+    return refglue.ref_render(refglue.RefSettings, cam, model, bg, use_trained_exp=use_trained_exp)
+
+
 class ActivatedModel:
     """Same store, attributes already activated (leaf tensors): isolates the rasterizer path."""
 

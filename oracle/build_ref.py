@@ -6,6 +6,9 @@ only build products land in ``oracle/_ref/`` (git-ignored, but shipped to the GP
 
     oracle/_ref/ref_hr_C.so   <- submodules/hierarchy-rasterizer  (rasterize_gaussians[_backward])
     oracle/_ref/ref_gh_C.so   <- submodules/gaussianhierarchy     (expand_to_size, get_interpolation_weights, ...)
+    oracle/_ref/ref_gh_tool   <- submodules/gaussianhierarchy host C++ (HierarchyWriter / HierarchyLoader, the
+                                 hierarchy Creator's CPU stages) under the command-line driver
+                                 oracle/reftool/ref_gh_tool.cpp -- plain g++, no torch
 
 These are the bit-exact oracle for ``tests/ -m gpu`` and the timed arm of
 ``bench.py --impl reference``.  The product path never imports them.
@@ -23,10 +26,37 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 OUT = os.path.join(HERE, "_ref")
 
 
-def build(which=("hr", "gh"), verbose=True):
+TOOL_SOURCES = ("hierarchy_writer.cpp", "hierarchy_loader.cpp")
+
+
+def build_tool(verbose=True):
+    """g++ on the reference's own host sources where they lie + our driver; output oracle/_ref/ref_gh_tool."""
+    import hashlib
+    import subprocess
+    gh = os.path.join(REF, "submodules/gaussianhierarchy")
+    driver = os.path.join(HERE, "reftool", "ref_gh_tool.cpp")
+    out = os.path.join(OUT, "ref_gh_tool")
+    stamp = out + ".sha256"
+    h = hashlib.sha256(open(driver, "rb").read() + " ".join(TOOL_SOURCES).encode()).hexdigest()
+    if os.path.exists(out) and os.path.exists(stamp) and open(stamp).read().strip() == h:
+        return True
+    os.makedirs(OUT, exist_ok=True)
+    cmd = ["g++", "-O2", "-std=c++17", "-w", "-fopenmp", "-I" + gh, "-I" + os.path.join(gh, "dependencies/eigen"), driver] + \
+        [os.path.join(gh, s) for s in TOOL_SOURCES] + ["-o", out]
+    if verbose:
+        print("[build_ref]", " ".join(cmd))
+    subprocess.run(cmd, check=True)
+    with open(stamp, "w") as fh:
+        fh.write(h)
+    return True
+
+
+def build(which=("hr", "gh", "tool"), verbose=True):
     if not os.path.isdir(REF):
         print(f"[build_ref] {REF} not present; nothing to do", file=sys.stderr)
         return False
+    if "tool" in which:
+        build_tool(verbose)
     os.environ["TORCH_CUDA_ARCH_LIST"] = "10.0a"
     os.environ.setdefault("MAX_JOBS", str(os.cpu_count() or 4))
     from torch.utils.cpp_extension import load
@@ -65,5 +95,5 @@ def build(which=("hr", "gh"), verbose=True):
 
 
 if __name__ == "__main__":
-    build(tuple(sys.argv[1:]) or ("hr", "gh"))
-    print("[build_ref] done:", sorted(f for f in os.listdir(OUT) if f.endswith(".so")))
+    build(tuple(sys.argv[1:]) or ("hr", "gh", "tool"))
+    print("[build_ref] done:", sorted(f for f in os.listdir(OUT) if f.endswith(".so") or f == "ref_gh_tool"))

@@ -94,8 +94,14 @@ __device__ __forceinline__ bool block_hit(const float4& q0, const float4& q1, fl
   const float a = q1.x, b = q1.y, c = q1.z;
   const float dys = fmaxf(Y0, fminf(__fdividef(-b * dxn, c), Y1));   // best dy on the line dx = dxn
   const float dxs = fmaxf(X0, fminf(__fdividef(-b * dyn, a), X1));   // best dx on the line dy = dyn
-  const float qa = a * dxn * dxn + 2.0f * b * dxn * dys + c * dys * dys;
-  const float qb = a * dxs * dxs + 2.0f * b * dxs * dyn + c * dyn * dyn;
+  // q = s + t with s = a dx^2 + c dy^2 >= 0 and the cross term t; the per-pixel evaluation the blend loop (and the
+  // reference) performs rounds each product, i.e. it can come out lower than the exact value by a few ulp of
+  // s + |t| -- for splats thousands of pixels long and sub-pixel thin that exceeds any fixed margin on q0.z, so
+  // the bound is lowered by 4e-7 (s + |t|) before the comparison.
+  const float sa = a * dxn * dxn + c * dys * dys, ta = 2.0f * b * dxn * dys;
+  const float sb = a * dxs * dxs + c * dyn * dyn, tb = 2.0f * b * dxs * dyn;
+  const float qa = fmaf(-4e-7f, sa + fabsf(ta), sa + ta);
+  const float qb = fmaf(-4e-7f, sb + fabsf(tb), sb + tb);
   return !(fminf(qa, qb) > q0.z);   // NaN anywhere -> keep the entry, the blend itself decides
 }
 

@@ -184,7 +184,12 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_fwd_kernel(const BlendArg
       }
     }
     // all warps saturated -> stop; the barrier also frees stage s for the copy issued next round
-    if (__syncthreads_and(T < 0.0f ? 1 : 0)) break;
+    if (__syncthreads_and(T < 0.0f ? 1 : 0)) {
+      // the bulk copies of round b + 1 are already in flight: a CTA must not exit (and hand its shared memory
+      // and mbarrier to the next CTA on this SM) before they have landed
+      if (TMA && b + 1 < rounds) mbar_wait(&sm.bar[(b + 1) & 1], (unsigned)(((b + 1) >> 1) & 1));
+      break;
+    }
   }
 
   if (COUNT && a.stats) {

@@ -31,6 +31,8 @@ __global__ void __launch_bounds__(256) sparse_adam_kernel(const AdamPack pk,
     if (i < pk.n && e >= pk.start[i]) ti = i;
   const H3dgsAdamTensor& T = pk.t[ti];
   const long long row = relevant ? relevant[k] : k;
+  // a sorted list with repeated ids updates each id once (the reference scatters identical copies, OurAdam.py:334-337)
+  if (relevant && k > 0 && relevant[k - 1] == row) return;
   const size_t off = (size_t)row * T.width + (e - pk.start[ti]);
 
   const float g = T.grad[off];

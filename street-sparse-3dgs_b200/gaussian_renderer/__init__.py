@@ -160,23 +160,34 @@ def _as_index(t):
 
 def render(viewpoint_camera, pc, pipe, bg_color: torch.Tensor, scaling_modifier=1.0, override_color=None,
            indices=None, use_trained_exp=False):
-    """Render the scene (gaussian_renderer/__init__.py:20-135).  Background tensor must be on GPU."""
-    screenspace_points = _screenspace_points(pc)
-    means3D, means2D, opacity = pc.get_xyz, screenspace_points, pc.get_opacity
-    scales, rotations, cov3D_precomp = _geometry(pc, pipe, scaling_modifier)
-    shs, colors_precomp = _appearance(viewpoint_camera, pc, pipe, override_color)
+    """Render the scene (gaussian_renderer/__init__.py:20-135).  Background tensor must be on GPU.
 
-    if indices is not None:
-        idx = _as_index(indices)
-        settings = _settings(viewpoint_camera, pc, bg_color, scaling_modifier, pipe.debug, True, idx,
-                             _empty(torch.int32), _empty(torch.float32), _empty(torch.int32))
-        rendered_image, radii, depth_image = _rasterize(settings, means3D, means2D[indices].contiguous(), opacity,
-                                                        shs, colors_precomp, scales, rotations, cov3D_precomp, 0)
+    On a reference-style ``GaussianModel`` (train_single.py:111) the RAW parameters go to the kernels, which apply
+    exp / normalize / sigmoid and the dc/rest split to the rows they read: the reference activates all N rows
+    with four torch kernels and a 192 B/row ``cat`` per call, and autograd runs their backward over N rows."""
+    screenspace_points = _screenspace_points(pc)
+    none_i, none_f = _empty(torch.int32), _empty(torch.float32)
+    raw = _raw_store(pc, pipe, override_color) if indices is None else None
+    if raw is not None:
+        settings = _settings(viewpoint_camera, pc, bg_color, scaling_modifier, pipe.debug, True, none_i, none_i,
+                             none_f, none_i)
+        (xyz, f_dc, f_rest, op_raw, sc_raw, rot_raw), acts = raw
+        rendered_image, radii, depth_image = rasterize_gaussians_raw(xyz, screenspace_points, f_dc, f_rest, op_raw,
+                                                                     sc_raw, rot_raw, settings, 0, acts)
     else:
-        settings = _settings(viewpoint_camera, pc, bg_color, scaling_modifier, pipe.debug, True,
-                             _empty(torch.int32), _empty(torch.int32), _empty(torch.float32), _empty(torch.int32))
-        rendered_image, radii, depth_image = _rasterize(settings, means3D, means2D, opacity, shs, colors_precomp,
-                                                        scales, rotations, cov3D_precomp)
+        means3D, means2D, opacity = pc.get_xyz, screenspace_points, pc.get_opacity
+        scales, rotations, cov3D_precomp = _geometry(pc, pipe, scaling_modifier)
+        shs, colors_precomp = _appearance(viewpoint_camera, pc, pipe, override_color)
+        if indices is not None:
+            settings = _settings(viewpoint_camera, pc, bg_color, scaling_modifier, pipe.debug, True,
+                                 _as_index(indices), none_i, none_f, none_i)
+            rendered_image, radii, depth_image = _rasterize(settings, means3D, means2D[indices].contiguous(), opacity,
+                                                            shs, colors_precomp, scales, rotations, cov3D_precomp, 0)
+        else:
+            settings = _settings(viewpoint_camera, pc, bg_color, scaling_modifier, pipe.debug, True, none_i, none_i,
+                                 none_f, none_i)
+            rendered_image, radii, depth_image = _rasterize(settings, means3D, means2D, opacity, shs, colors_precomp,
+                                                            scales, rotations, cov3D_precomp)
 
     if use_trained_exp:
         exposure = pc.get_exposure_from_name(viewpoint_camera.image_name)

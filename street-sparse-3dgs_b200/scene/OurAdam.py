@@ -102,7 +102,12 @@ class Adam(Optimizer):
         L = nat.lib()
         if relevant is not None and relevant.numel() > 0:
             if relevant.dim() != 1:
-                raise RuntimeError("relevant must be a 1-D tensor of row indices")
+                # train_coarse.py:133-134 passes the [K,2] result of a 2-D nonzero(): the reference's advanced
+                # indexing (scene/OurAdam.py:290-337) then gathers every listed id (rows and the column zeros),
+                # updates the copies and scatters them back, i.e. each DISTINCT id is updated exactly once
+                relevant = relevant.reshape(-1).unique()
+            # 1-D lists are used as given: sorted (nonzero() output) or duplicate-free; the kernel skips an id
+            # equal to its predecessor, so sorted duplicates are applied once, as the reference's scatter does
             rel = relevant.to(device=dev, dtype=torch.int64).contiguous()
             rel_ptr, K = rel.data_ptr(), rel.numel()
         else:

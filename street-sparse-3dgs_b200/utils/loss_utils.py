@@ -2,13 +2,17 @@
 signatures, plus ``fused_l1_ssim_loss`` -- the photometric loss of train_single.py:116-141 / train_post.py:132-137
 ``(1 - lambda) * L1 + lambda * (1 - SSIM)`` in one forward and one backward kernel.
 
-CUDA fp32 images go through the hand-written kernels of csrc/loss.cu via the C ABI (h3dgs_ssim_forward /
-h3dgs_ssim_backward); the second image (ground truth) receives no gradient, as in training.  There is no fallback
-for CUDA tensors; CPU tensors are rejected (the reference's torch implementation is what runs on a CPU)."""
+CUDA fp32 images with the training window (11) go through the hand-written kernels of csrc/loss.cu via the C ABI
+(h3dgs_ssim_forward / h3dgs_ssim_backward); SSIM is symmetric in its two images, so a second image that requires a
+gradient gets it from a second pass with the roles swapped.  What the kernels do not cover -- CPU tensors, other
+window sizes, and the evaluation-only ``ssim_masked`` (render_hierarchy_final.py:154) -- is evaluated with the same
+torch formulas the reference uses (``_ssim_torch``); the training losses (``fused_l1_ssim_loss``, ``masked_l1_loss``)
+have no such path and reject anything but CUDA fp32."""
 import ctypes
 from math import exp
 
 import torch
+import torch.nn.functional as F
 
 import h3dgs_native as nat
 
@@ -25,6 +29,66 @@ def gaussian(window_size, sigma):
     # utils/loss_utils.py:23-25, same arithmetic: python doubles -> float32 tensor -> normalised in float32
     gauss = torch.Tensor([exp(-(x - window_size // 2) ** 2 / float(2 * sigma ** 2)) for x in range(window_size)])
     return gauss / gauss.sum()
+
+
+def create_window(window_size, channel):
+    # utils/loss_utils.py:27-31: separable window as a [channel,1,ws,ws] depthwise conv2d weight
+    w = gaussian(window_size, 1.5).unsqueeze(1)
+    return w.mm(w.t()).float()[None, None].expand(channel, 1, window_size, window_size).contiguous()
+
+
+def _moments(x, window, pad, channel):
+    return F.conv2d(x, window, padding=pad, groups=channel)
+
+
+def _ssim_torch(img1, img2, window_size, size_average):
+    """utils/loss_utils.py:33-63 in torch ops (depthwise conv2d moments), for inputs the kernels do not take."""
+    channel = img1.size(-3)
+    window = create_window(window_size, channel).to(device=img1.device, dtype=img1.dtype)
+    pad = window_size // 2
+    mu1, mu2 = _moments(img1, window, pad, channel), _moments(img2, window, pad, channel)
+    mu1_sq, mu2_sq, mu12 = mu1.pow(2), mu2.pow(2), mu1 * mu2
+    s1 = _moments(img1 * img1, window, pad, channel) - mu1_sq
+    s2 = _moments(img2 * img2, window, pad, channel) - mu2_sq
+    s12 = _moments(img1 * img2, window, pad, channel) - mu12
+    C1, C2 = 0.01 ** 2, 0.03 ** 2
+    smap = ((2 * mu12 + C1) * (2 * s12 + C2)) / ((mu1_sq + mu2_sq + C1) * (s1 + s2 + C2))
+    return smap.mean() if size_average else smap.mean(1).mean(1).mean(1)
+
+
+def ssim_masked(img1, img2, mask, window_size=11, size_average=True):
+    """SSIM restricted to ``mask`` (utils/loss_utils.py:65-150; evaluation only, render_hierarchy_final.py:154):
+    windowed moments of the masked images renormalised by the windowed mask weight, windows without support and
+    degenerate denominators give 0, the mean runs over masked pixels with a valid window."""
+    channel = img1.size(-3)
+    window = create_window(window_size, channel).to(device=img1.device, dtype=img1.dtype)
+    pad = window_size // 2
+    if mask.dim() == 3:
+        mask = mask.unsqueeze(1)
+    if mask.size(1) == 1 and channel > 1:
+        mask = mask.expand(-1, channel, -1, -1)
+    a, b = img1 * mask, img2 * mask
+    wsum = _moments(mask.float(), window, pad, channel)
+    valid = wsum > 1e-6
+    safe = torch.where(valid, wsum, torch.ones_like(wsum))
+    zero = torch.zeros_like(wsum)
+
+    def local(x):
+        return torch.where(valid, _moments(x, window, pad, channel) / safe, zero)
+
+    mu1, mu2 = local(a), local(b)
+    mu1_sq, mu2_sq, mu12 = mu1.pow(2), mu2.pow(2), mu1 * mu2
+    s1 = torch.where(valid, local(a * a) - mu1_sq, zero)
+    s2 = torch.where(valid, local(b * b) - mu2_sq, zero)
+    s12 = torch.where(valid, local(a * b) - mu12, zero)
+    C1, C2 = 0.01 ** 2, 0.03 ** 2
+    num = (2 * mu12 + C1) * (2 * s12 + C2)
+    den = (mu1_sq + mu2_sq + C1) * (s1 + s2 + C2)
+    ok = (den > 1e-10) & valid
+    smap = torch.where(ok, num / torch.where(ok, den, torch.ones_like(den)), zero) * mask
+    if size_average:
+        return smap.sum() / (mask * valid.float()).sum().clamp(min=1)
+    return smap
 
 
 _WINDOW = None
@@ -90,16 +154,23 @@ class _SSIMMean(torch.autograd.Function):
     @staticmethod
     def forward(ctx, img1, img2):
         img1, img2 = _check(img1, img2)
-        want = ctx.needs_input_grad[0]
-        sums, maps, _ = _forward(img1, img2, want)
-        if want:
-            ctx.save_for_backward(img1, img2, *maps)
+        want1, want2 = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+        sums, maps, _ = _forward(img1, img2, want1)
+        ctx.want = (want1, want2)
+        ctx.save_for_backward(img1, img2, *(maps if want1 else ()))
         return (sums[0] / img1.numel()).to(torch.float32)
 
     @staticmethod
     def backward(ctx, grad_out):
-        img1, img2, m0, m1, m2 = ctx.saved_tensors
-        return _backward(img1, img2, (m0, m1, m2), grad_out, 1.0 / img1.numel(), 0.0), None
+        img1, img2 = ctx.saved_tensors[:2]
+        g1 = g2 = None
+        if ctx.want[0]:
+            g1 = _backward(img1, img2, ctx.saved_tensors[2:], grad_out, 1.0 / img1.numel(), 0.0)
+        if ctx.want[1]:
+            # SSIM(a, b) = SSIM(b, a): the gradient of the second image is that of the first with the roles swapped
+            _, maps, _ = _forward(img2, img1, True)
+            g2 = _backward(img2, img1, maps, grad_out, 1.0 / img1.numel(), 0.0)
+        return g1, g2
 
 
 class _L1SSIM(torch.autograd.Function):
@@ -129,9 +200,10 @@ class _L1SSIM(torch.autograd.Function):
 
 
 def ssim(img1, img2, window_size=11, size_average=True):
-    """Mean SSIM of two images (utils/loss_utils.py:33-63).  Gradients flow to ``img1``."""
-    if window_size != 11:
-        raise NotImplementedError("the fused SSIM implements the window the reference training uses (11)")
+    """Mean SSIM of two images (utils/loss_utils.py:33-63)."""
+    if window_size != 11 or not (img1.is_cuda and img2.is_cuda) or img1.dtype != torch.float32 \
+            or img2.dtype != torch.float32:
+        return _ssim_torch(img1, img2, window_size, size_average)
     if size_average or img1.dim() == 3 or img1.size(0) == 1:
         out = _SSIMMean.apply(img1, img2)
         return out if size_average else out.reshape(1)

@@ -227,3 +227,9 @@ def test_hier_files_interchange_with_reference_build(tmp_path):
         assert torch.equal(a, b)
     # (the reference's write_hierarchy binding segfaults on CPU tensors in this environment, so the
     #  byte-level comparison against the reference writer runs on the GPU box with CUDA tensors)
+
+
+def test_hier_files_match_reference_writer_and_loader_fixture(tmp_path):
+    """Host-side .hier I/O against files written / read by the reference's own C++ classes (tests/hier_fixture.py)."""
+    from tests import hier_fixture
+    hier_fixture.check(tmp_path, "cpu")

@@ -122,3 +122,23 @@ def test_identical_images_and_argument_checks():
         v0 = lu.ssim(y, x)
     v1 = lu.ssim(y.clone().requires_grad_(True), x)
     assert v0.item() == pytest.approx(v1.item(), abs=1e-7)
+
+
+def test_ssim_gradient_of_second_image_and_other_windows():
+    """The drop-in ``ssim`` differentiates BOTH images like the reference's torch version (the second through a
+    swapped pass, SSIM being symmetric); window sizes other than 11 take the torch formula."""
+    from utils import loss_utils as lu
+    g = torch.Generator().manual_seed(31)
+    a0 = torch.rand(3, 90, 130, generator=g).to(DEV)
+    b0 = (a0 + 0.1 * torch.randn(3, 90, 130, generator=g).to(DEV)).clamp(0, 1)
+    a, b = a0.clone().requires_grad_(True), b0.clone().requires_grad_(True)
+    s = lu.ssim(a, b)
+    s.backward()
+    ar, br = a0.clone().requires_grad_(True), b0.clone().requires_grad_(True)
+    sr = lu._ssim_torch(ar, br, 11, True)
+    sr.backward()
+    assert abs(float(s) - float(sr)) <= 2e-6
+    for got, want in ((a.grad, ar.grad), (b.grad, br.grad)):
+        assert got is not None
+        assert float((got - want).abs().max()) <= 1e-4 * float(want.abs().max())
+    assert abs(float(lu.ssim(a0, b0, 7)) - float(lu._ssim_torch(a0, b0, 7, True))) == 0.0

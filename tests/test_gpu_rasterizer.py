@@ -337,3 +337,41 @@ def test_staging_by_bulk_copy_engine_matches(monkeypatch, tmp_path):
         outs.append((line[1], float(line[2])))
     assert outs[0][0] == outs[1][0], "image differs between staging modes"
     assert abs(outs[0][1] - outs[1][1]) <= 1e-4 * abs(outs[0][1])
+
+
+def test_long_thin_splats_bit_exact():
+    """Splats thousands of pixels long and sub-pixel thin: the rounding of a dx^2 + 2 b dx dy + c dy^2 grows with
+    the cancelling terms, so the blend kernels' per-block cull (blend_common.cuh block_hit) scales its margin
+    with them.  n_contrib, final_T and the image must stay bit-identical to the reference's per-pixel test."""
+    util.need_ref()
+    n, w, h = 6000, 1280, 720
+    sc, cam, _, _ = util.make_scene(n, w, h, seed=5, dev=DEV)
+    g = torch.Generator().manual_seed(9)
+    k = 3000
+    # major sigma 4..20 m at 3..60 m distance (thousands of pixels), minor sigma 0.5 mm (the 0.3 px^2 dilation
+    # then sets the width), faint enough that pixels blend hundreds of them
+    sc["scales"][:k] = torch.stack([4.0 + 16.0 * torch.rand(k, generator=g), torch.full((k,), 5e-4),
+                                    torch.full((k,), 5e-4)], dim=1).to(DEV)
+    sc["opacities"][:k] = (0.02 + 0.2 * torch.rand(k, 1, generator=g)).to(DEV)
+    bg = torch.tensor([0.1, 0.2, 0.3], device=DEV)
+    rs = _settings(cam, bg)
+    R = _compare_forward(sc, cam, rs, util.forward_args(rs, sc), n)
+    assert R > 0
+
+
+def test_more_than_65535_tiles_uses_32_bit_tile_keys():
+    """4112 x 4096 pixels = 257 x 256 = 65 792 tiles: tile ids no longer fit 16 bits, the instance sort switches to
+    u32 tile keys and three tile passes (csrc/common.cuh make_sort_plan).  Keys, list, ranges and image against
+    the reference build, bit for bit."""
+    util.need_ref()
+    import diff_gaussian_rasterization as dgr
+    n, w, h = 40000, 4112, 4096
+    sc, cam, _, _ = util.make_scene(n, w, h, seed=8, dev=DEV)
+    bg = torch.tensor([0.2, 0.1, 0.05], device=DEV)
+    rs = _settings(cam, bg)
+    args = util.forward_args(rs, sc)
+    R = _compare_forward(sc, cam, rs, args, n)
+    assert R > 0
+    _, _, _, geom, binning, img, _ = dgr._C.rasterize_gaussians(*args)
+    dv = dgr._C.debug_view(n, w, h, R, geom, binning, img)
+    assert int((dv["point_list_keys"] >> 32).max()) > 65535, "no instance landed in a tile above 65535"

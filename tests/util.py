@@ -15,10 +15,21 @@ def relerr(a, b):
 REL_TOL = 1e-4
 
 
-def assert_grad_close(ours, ref, ref_again, name, more_refs=()):
+# Tensors whose gradients must meet the north_star bar itself: the reference's run-to-run spread on them is far
+# below 1e-4, so the spread-following bound must never be what lets them pass.
+STRICT = ("xyz", "means3D", "opacity", "opacities", "features", "features_dc", "features_rest", "shs", "sh")
+
+# (test id, tensor, relerr, reference spread, bound, branch) of every gradient comparison of the session;
+# tests/conftest.py prints the table at the end of the run and writes it to gpurun_out/grad_parity.jsonl
+GRAD_LOG = []
+
+
+def assert_grad_close(ours, ref, ref_again, name, more_refs=(), strict=None):
     """`ours` against the mean of the reference runs; the bound follows the reference's own spread (largest
     deviation of a run from that mean), which two runs alone estimate poorly for ill-conditioned gradients
-    (anisotropic Gaussians: rotation / scale), hence `more_refs`."""
+    (anisotropic Gaussians: rotation / scale), hence `more_refs`.  For the tensors in STRICT (or strict=True) the
+    bound is REL_TOL, full stop.  Every call logs the measured error, the spread and the bound it used."""
+    import os
     refs = [ref.double(), ref_again.double()] + [r.double() for r in more_refs]
     mean = sum(refs) / len(refs)
     den = float(mean.abs().max()) + 1e-30
@@ -26,9 +37,16 @@ def assert_grad_close(ours, ref, ref_again, name, more_refs=()):
     # Both sides accumulate with float atomics; where the reference's own spread is near the budget (scale /
     # rotation gradients of anisotropic Gaussians reach 1e-4 between two reference runs) the distance of two
     # such noisy results is what is being measured, and its maximum over ~1e6 rows needs the wider factor.
-    bound = max(REL_TOL, 6.0 * noise)
+    if strict is None:
+        strict = name in STRICT
+    bound = REL_TOL if strict else max(REL_TOL, 6.0 * noise)
     err = float((ours.double() - mean).abs().max()) / den
-    assert err <= bound, f"{name}: relerr {err:.3e} > {bound:.3e} (reference spread {noise:.3e}, {len(refs)} runs)"
+    branch = "strict 1e-4" if strict else ("1e-4" if bound == REL_TOL else "6 x spread")
+    test = os.environ.get("PYTEST_CURRENT_TEST", "").split(" ")[0]
+    GRAD_LOG.append(dict(test=test, tensor=name, relerr=err, spread=noise, bound=bound, branch=branch,
+                         runs=len(refs), rows=int(ours.shape[0]) if ours.dim() else 1))
+    print(f"[grad parity] {name}: relerr {err:.3e}  reference spread {noise:.3e}  bound {bound:.3e} ({branch})")
+    assert err <= bound, f"{name}: relerr {err:.3e} > {bound:.3e} (reference spread {noise:.3e}, {len(refs)} runs, {branch})"
     return err
 
 
