@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define H3DGS_ABI_VERSION 6
+#define H3DGS_ABI_VERSION 7
 
 #if defined(__GNUC__)
 #define H3DGS_API __attribute__((visibility("default")))
@@ -356,6 +356,12 @@ H3DGS_API int h3dgs_masked_l1_backward(int64_t n, const float* pred, const float
  * at which the tile's forward CTA started / ended and its backward CTA started / ended (load-balance diagnostics,
  * harness/diag_balance.py).  NULL switches it off.  Never timed. */
 H3DGS_API int h3dgs_blend_stats(void* counters);
+/* Measured pipe ceilings of the device the blend kernels' roofline is quoted against (SURVEY.md 8d asks for an FMA /
+ * ex2 micro-kernel instead of a datasheet figure).  Runs three dependent-chain micro-kernels that fill every SM, best
+ * of `reps` launches each, synchronising `stream`:  out[0] FP32 TFLOP/s with three-register FFMA (2 FLOP each),
+ * out[1] the same with packed fma.rn.f32x2 (FFMA2), out[2] MUFU.EX2 results in G/s, out[3] warp instructions issued
+ * per second (G/s) by the FFMA kernel.  scratch: device pointer to at least one float. */
+H3DGS_API int h3dgs_measure_peaks(double* out4, void* scratch, int32_t reps, h3dgs_stream_t stream);
 H3DGS_API int64_t h3dgs_launch_count(void);          /* kernels launched by this library so far (process-wide) */
 H3DGS_API int h3dgs_profile_enable(int enable);      /* returns the previous setting */
 /* Synchronises pending events and adds their durations; ms[i] / launches[i] are per kernel id

@@ -156,6 +156,7 @@ cudaError_t run_ssim_backward(int C, int H, int W, const float* img1, const floa
                               const float* window, const float* dm_dmu1, const float* dm_de11, const float* dm_de12,
                               const float* dL_dmap, const float* upstream, float ssim_scale, float l1_scale,
                               float* dL_dimg1, cudaStream_t s);
+cudaError_t run_measure_peaks(double* out, float* scratch, int reps, cudaStream_t s);
 cudaError_t run_pack_rows(const H3dgsRowTensor* tensors, int n, const long long* rows, long long K, float* packed,
                           float scale, bool pack, cudaStream_t s);
 
@@ -658,6 +659,12 @@ int h3dgs_masked_l1_backward(int64_t n, const float* pred, const float* target, 
 
 int h3dgs_blend_stats(void* counters) {
   g_blend_stats = reinterpret_cast<unsigned long long*>(counters);
+  return 0;
+}
+
+int h3dgs_measure_peaks(double* out4, void* scratch, int32_t reps, h3dgs_stream_t stream) {
+  if (!out4 || !scratch || reps < 1 || reps > 100) return fail(H3DGS_EINVAL, "h3dgs_measure_peaks: out4, scratch and 1..100 reps");
+  H3_CUDA(run_measure_peaks(out4, reinterpret_cast<float*>(scratch), reps, (cudaStream_t)stream));
   return 0;
 }
 

@@ -132,7 +132,13 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_bwd_kernel(const BlendArg
     }
     if (!DEPTH && red_dst == 9) red_dst = -1;
   }
-  float T = T_final, accum_u = 0.f, last_alpha = 0.f, last_u = 0.f;
+  // Walking state of a pixel: T in front of the entry at hand, and B = "what lies behind it, contracted with the
+  // pixel gradient" (the reference's accum_rec . dL_dpixel, backward.cu:657-691), updated as B += alpha (u - B).
+  // An entry that does not contribute enters with alpha = 0 and leaves both unchanged: no selects.
+  float T = T_final, B = 0.f;
+  const float Tfb = -T_final * bgdot;
+  // shared-memory address of this lane's accumulator column (see the butterfly below)
+  const uint32_t acc_addr = smem_u32(&sm.acc[0][red_dst < 0 ? 0 : red_dst]);
   if (inside && last > nn) {
     // this pixel's walk started in a deeper item: pick it up at the cut from the forward's snapshot.  What lies
     // behind the cut, contracted with the pixel gradient, is (total - in front of the cut) / T at the cut.
@@ -142,7 +148,7 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_bwd_kernel(const BlendArg
     T = sp[0];
     float behind = (tot.x - sp[TILE_PIX]) * g0 + (tot.y - sp[2 * TILE_PIX]) * g1 + (tot.z - sp[3 * TILE_PIX]) * g2;
     if (DEPTH) behind += (tot.w - sp[4 * TILE_PIX]) * gD;
-    accum_u = behind / T;
+    B = behind / T;
   }
   unsigned cntA = 0, cntB = 0, cntD = 0, cntS = 0;
   const float half_w = 0.5f * (float)a.W, half_h = 0.5f * (float)a.H;
@@ -186,7 +192,11 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_bwd_kernel(const BlendArg
         const float4 con_o = recs[jj].q1;
         const float dx = xy.x - pixx, dy = xy.y - pixy;
         const float power = -0.5f * (con_o.x * dx * dx + con_o.z * dy * dy) - con_o.y * dx * dy;
-        const float G = exp(power);
+        // G, alpha and T are rebuilt with the MUFU approximations (ex2 / lg2 / rcp, relative error ~1e-7 -- the
+        // level at which the reference's own forward (__powf) and backward (pow) already disagree); the keep / skip
+        // decision at 1/255 below is the one place where a last-bit difference would change the result visibly,
+        // and is redone exactly there.
+        const float G = ex2_approx(power * 1.4426950408889634f);
         const float test_alpha = con_o.w * G;
         const float my_alpha = min(0.99f, test_alpha);
         float alpha = my_alpha;
@@ -194,21 +204,23 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_bwd_kernel(const BlendArg
         if (INTERP) {
           const float2 tk = *reinterpret_cast<const float2*>(&recs[jj].q3);
           if (tk.x != 1.0f) {
-            // (1-a)^(1/k) as the reference's backward evaluates it with precise pow (backward.cu:631),
-            // here exp2f(y log2f(x)) with the full-precision library functions: same value to a few ulp
-            // without the ~45-instruction slow path; (1-a)^(1/k - 1) = that / (1-a)   (backward.cu:714)
+            // (1-a)^(1/k) (backward.cu:631) and (1-a)^(1/k - 1) = that / (1-a) (backward.cu:714); 1-a is in [0.01, 1]
             const float om = 1.0f - my_alpha;
-            float pw = exp2f(tk.y * log2f(om));
+            float pw = ex2_approx(tk.y * lg2_approx(om));
             alpha = tk.x * my_alpha + (1.0f - tk.x) * (1.0f - pw);
-            // the keep / skip decision below must be the reference's: within reach of the 1/255
-            // threshold (the two evaluations differ by < 1e-6) redo it with powf itself
-            if (fabsf(alpha - 1.0f / 255.0f) < 2e-5f) {
-              pw = powf(om, tk.y);
-              alpha = tk.x * my_alpha + (1.0f - tk.x) * (1.0f - pw);
+            // the keep / skip decision below must be the reference's: within reach of the 1/255 threshold (the
+            // approximation is off by < 2e-7 in alpha) redo it with the reference's expf and powf themselves
+            if (fabsf(alpha - 1.0f / 255.0f) < 1e-6f) {
+              pw = powf(1.0f - min(0.99f, con_o.w * expf(power)), tk.y);
+              alpha = tk.x * min(0.99f, con_o.w * expf(power)) + (1.0f - tk.x) * (1.0f - pw);
             }
             // d alpha / d a = t - (1-a)^(1/k - 1) (t-1) / k
-            opac_mult = tk.x - __fdividef(pw, om) * (tk.x - 1.0f) * tk.y;
+            opac_mult = tk.x - pw * __frcp_approx(om) * (tk.x - 1.0f) * tk.y;
+          } else if (fabsf(alpha - 1.0f / 255.0f) < 2e-8f) {   // ex2.approx vs expf: a few ulp of alpha
+            alpha = min(0.99f, con_o.w * expf(power));
           }
+        } else if (fabsf(alpha - 1.0f / 255.0f) < 2e-8f) {
+          alpha = min(0.99f, con_o.w * expf(power));
         }
         const bool contrib = (nn - 1 - (base + jj) < last) & !(power > 0.0f) & !(alpha < 1.0f / 255.0f);
         if (COUNT) {
@@ -220,33 +232,29 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_bwd_kernel(const BlendArg
         if (!__any_sync(0xffffffffu, contrib)) continue;
         const float4 q2 = recs[jj].q2;
         // 1 - alpha is in [0.01, 1]: the approximate reciprocal plus one Newton step is exact to an ulp there
-        // and needs none of the range checks of a full-range division
-        const float om_a = 1.f - alpha;
+        // (and exactly 1 for alpha = 0) and needs none of the range checks of a full-range division
+        const float a_eff = contrib ? alpha : 0.f;
+        const float om_a = 1.f - a_eff;
         float rcp_om = __frcp_approx(om_a);
         rcp_om = fmaf(fmaf(-om_a, rcp_om, 1.0f), rcp_om, rcp_om);
-        const float Tn = T * rcp_om;
+        T *= rcp_om;
         float u = q2.x * g0 + q2.y * g1 + q2.z * g2;
         if (DEPTH) u += q2.w * gD;
-        const float acc_n = last_alpha * last_u + (1.f - last_alpha) * accum_u;
-        float dL_dalpha = (u - acc_n) * Tn + (-T_final * rcp_om) * bgdot;
-        // clamped alpha passes no gradient (backward.cu:619,693)
-        if (!contrib | (test_alpha > 0.99f)) dL_dalpha = 0.f;
+        const float d = u - B;
+        float dL_dalpha = fmaf(d, T, Tfb * rcp_om);
+        B = fmaf(a_eff, d, B);
+        // clamped alpha passes no gradient (backward.cu:619,693); entries that do not contribute carry Gc = w = 0
+        if (test_alpha > 0.99f) dL_dalpha = 0.f;
         const float Gc = contrib ? G : 0.f;
-        const float w = contrib ? alpha * Tn : 0.f;
-        if (contrib) {
-          T = Tn;
-          accum_u = acc_n;
-          last_u = u;
-          last_alpha = alpha;
-        }
-        const float dL_dG = con_o.w * dL_dalpha;
-        const float gdx = Gc * dx, gdy = Gc * dy;
-        const float v0 = dL_dG * gdx;
-        const float v1 = dL_dG * gdy;
+        const float w = a_eff * T;
+        const float GdA = Gc * dL_dalpha;
+        const float q = con_o.w * GdA;
+        const float v0 = q * dx;
+        const float v1 = q * dy;
         const float v2 = v0 * dx;
         const float v3 = v0 * dy;
         const float v4 = v1 * dy;
-        const float v5 = opac_mult * Gc * dL_dalpha;
+        const float v5 = opac_mult * GdA;
         const float v6 = w * g0;
         const float v7 = w * g1;
         const float v8 = w * g2;
@@ -268,8 +276,9 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_bwd_kernel(const BlendArg
           float t1 = s2 + __shfl_xor_sync(0xffffffffu, s2, 4);
           float u = (h2 ? t1 : t0) + __shfl_xor_sync(0xffffffffu, h2 ? t0 : t1, 2);
           u += __shfl_xor_sync(0xffffffffu, u, 1);
-          // lane (b4 b3 b2 b1 0) now holds the complete sum number red_dst (see below); ten lanes deposit
-          if (red_dst >= 0) atomicAdd(&sm.acc[jj][red_dst], u);
+          // lane (b4 b3 b2 b1 0) now holds the complete sum number red_dst (see above); ten lanes deposit
+          if (red_dst >= 0)
+            asm volatile("red.shared.add.f32 [%0], %1;" ::"r"(acc_addr + (uint32_t)jj * (ACC_W * 4u)), "f"(u) : "memory");
         }
       }
     }

@@ -79,6 +79,17 @@ __device__ __forceinline__ float __frcp_approx(float x) {
   return r;
 }
 
+__device__ __forceinline__ float ex2_approx(float x) {
+  float r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+__device__ __forceinline__ float lg2_approx(float x) {
+  float r;
+  asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+
 // Can the Gaussian of record (q0, q1) reach alpha >= 1/255 anywhere in the pixel block
 // [x0, x0+SUB_W-1] x [y0, y0+SUB_H-1]?  alpha >= 1/255  <=>  a dx^2 + 2 b dx dy + c dy^2 <= 2 ln(255 o) = q0.z
 // (preprocess stores that bound with a small safety margin, +inf for "never cull", negative for "never

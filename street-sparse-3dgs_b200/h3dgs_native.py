@@ -114,12 +114,23 @@ SIGNATURES = {
     "h3dgs_masked_l1_forward": (c_int, [c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "h3dgs_masked_l1_backward": (c_int, [c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_void_p, c_void_p]),
     "h3dgs_blend_stats": (c_int, [c_void_p]),
+    "h3dgs_measure_peaks": (c_int, [POINTER(ctypes.c_double), c_void_p, c_int32, c_void_p]),
     "h3dgs_launch_count": (c_int64, []),
     "h3dgs_profile_enable": (c_int, [c_int]),
     "h3dgs_profile_read": (c_int, [POINTER(ctypes.c_double), POINTER(c_int64), c_int]),
     "h3dgs_profile_name": (c_char_p, [c_int]),
 }
 PROF_KERNELS = 17
+ABI_VERSION = 7
+
+
+def measure_peaks(reps=5):
+    """{"fp32_tflops", "fp32x2_tflops", "mufu_gops", "issue_ginst"} measured on the current device
+    (h3dgs_measure_peaks)."""
+    out = (ctypes.c_double * 4)()
+    scratch = torch.zeros(4, device="cuda")
+    check(lib().h3dgs_measure_peaks(out, scratch.data_ptr(), reps, stream_handle()), "h3dgs_measure_peaks")
+    return {"fp32_tflops": out[0], "fp32x2_tflops": out[1], "mufu_gops": out[2], "issue_ginst": out[3]}
 
 
 def profile_read(reset=True):
@@ -146,7 +157,7 @@ def lib():
             fn = getattr(handle, name)
             fn.restype = res
             fn.argtypes = args
-        if handle.h3dgs_abi_version() != 6:
+        if handle.h3dgs_abi_version() != ABI_VERSION:
             raise H3dgsError("libh3dgs_b200.so ABI version mismatch")
         _lib = handle
     return _lib
