@@ -116,29 +116,35 @@ typedef struct H3dgsGaussians {
 #define H3DGS_ACT_SIGMOID   3
 #define H3DGS_ACT_ABS       4
 
-/* Workspace sizes.  geom: per-slot state (GeometryState, rasterizer_impl.cu:159-175);
+/* Workspace sizes.  geom: per-slot state (GeometryState, rasterizer_impl.cu:159-175) plus the depth sort of
+ * the visible slots -- everything that can be sized before the render's instance count is known;
  * image: per-pixel + per-tile state (ImageState, :177-184);
- * binning: instance keys/values + sort workspace (BinningState, :186-199). */
+ * binning: instance keys/values + sort workspace (BinningState, :186-199), sized by num_rendered. */
 H3DGS_API size_t h3dgs_geom_bytes(int32_t P);
 H3DGS_API size_t h3dgs_image_bytes(int32_t image_width, int32_t image_height);
-H3DGS_API size_t h3dgs_binning_bytes(int64_t num_rendered, int64_t num_visible, int32_t image_width,
-                                     int32_t image_height);
+H3DGS_API size_t h3dgs_binning_bytes(int64_t num_rendered, int32_t image_width, int32_t image_height);
 
 /*
- * Forward, stage 1: preprocess (EWA projection, SH, culling, fused interpolation) + tile-count scan.
- * Replaces FORWARD::preprocess + cub::DeviceScan::InclusiveSum + the num_rendered read-back
- * (rasterizer_impl.cu:275-325).  Writes radii[P] (0 = culled) and, after synchronising `stream`,
- * *num_rendered_host (tile instances, the reference's num_rendered) and *num_visible_host (slots with
- * radii > 0); both size the binning workspace and go to h3dgs_forward_render.
+ * Forward, stage 1: preprocess (EWA projection, SH, culling, fused interpolation), tile-count scan, and -- with the
+ * visible count V taken from DEVICE memory -- compaction of the visible slots, their depth sort and the scan of
+ * their tile counts in depth order.  Replaces FORWARD::preprocess + cub::DeviceScan::InclusiveSum + the
+ * num_rendered read-back (rasterizer_impl.cu:275-325) and the first half of the sort.  Writes radii[P] (0 = culled).
+ *
+ * The instance count R (the reference's num_rendered) sizes the binning workspace, so it must reach the host -- but
+ * the reference's way (a blocking copy, rasterizer_impl.cu:324-325) leaves the GPU without work while the host
+ * wakes up and queues the rest.  Here the copy of counts_host[0] = R, counts_host[1] = V (host memory, pinned for
+ * a truly asynchronous copy) is enqueued right after the scan and counts_event (a cudaEvent_t) is recorded behind
+ * it; ~0.2 ms of kernels that do not need R on the host follow in the same call.  The caller waits for
+ * counts_event, allocates the binning workspace and calls h3dgs_forward_finish while those kernels run.
+ * counts_event == NULL: the call synchronises `stream` itself before it returns.
  */
-H3DGS_API int h3dgs_forward_preprocess(const H3dgsView* view, const H3dgsGaussians* g,
-                             int32_t* radii, void* geom, size_t geom_bytes,
-                             int64_t* num_rendered_host, int64_t* num_visible_host, int debug,
-                             h3dgs_stream_t stream);
+H3DGS_API int h3dgs_forward_begin(const H3dgsView* view, const H3dgsGaussians* g,
+                        int32_t* radii, void* geom, size_t geom_bytes,
+                        int64_t* counts_host, void* counts_event, int debug, h3dgs_stream_t stream);
 
 /*
- * Forward, stage 2: depth sort of the visible slots, ordered instance emission, stable onesweep partition
- * by tile (together: the reference's sort by (tile, depth), bit-identical lists), tile ranges, alpha blend.
+ * Forward, stage 2: ordered instance emission, stable onesweep partition by tile (with stage 1's depth sort: the
+ * reference's sort by (tile, depth), bit-identical lists), tile ranges, alpha blend.
  * Replaces duplicateWithKeys + cub::DeviceRadixSort::SortPairs + identifyTileRanges + FORWARD::render
  * (rasterizer_impl.cu:336-390).  out_color is [3,H,W]; out_invdepth is [1,H,W] or NULL.
  * num_rendered == 0 only fills out_color with the background.
@@ -146,7 +152,7 @@ H3DGS_API int h3dgs_forward_preprocess(const H3dgsView* view, const H3dgsGaussia
  * after which the forward stops using HBM bandwidth, where a caller can fork bandwidth-only side work
  * (h3dgs_zero_fill of the gradient tensors the backward will add into) onto another stream.
  */
-H3DGS_API int h3dgs_forward_render(const H3dgsView* view, const H3dgsGaussians* g,
+H3DGS_API int h3dgs_forward_finish(const H3dgsView* view, const H3dgsGaussians* g,
                          void* geom, void* binning, size_t binning_bytes, void* image,
                          int64_t num_rendered, int64_t num_visible, float* out_color, float* out_invdepth,
                          int debug, h3dgs_stream_t stream, void* pre_blend_event);
@@ -173,6 +179,20 @@ typedef struct H3dgsGrads {
    *     into, [1..n] their ids (duplicates possible) -- feed it to h3dgs_zero_rows before the next reuse. */
   int32_t* dirty_rows;
   int32_t rows_prezeroed;
+  /* Compact gradients (fused-cut mode only, ABI 7; all NULL / 0 = the dense layout above).  A render adds into the
+   * rows of its cut only -- a few % of the store -- yet the dense layout costs a zero fill of every row (4 GB at
+   * 17 M rows) and the optimizer then scans all N rows to find the touched ones again (train_single.py:225-229:
+   * `opacity.grad != 0`, nonzero).  With these fields the per-store-row pointers above address COMPACT tensors
+   * [compact_capacity, width] instead: every store row this render touches (the child and parent rows of its
+   * visible slots, its visible skybox rows) gets one compact row; compact_rows[i] receives the store row of
+   * compact row i and *compact_count their number U (U <= 2 * num_visible, which is therefore always a
+   * sufficient capacity).  Compact rows [0, U) are completely written (zero where a tensor gets no contribution);
+   * rows beyond U are left untouched.  row_map is scratch: int32 [store_rows], all -1 on entry, all -1 again when
+   * the call has finished.  h3dgs_sparse_adam_compact consumes the result without a host round trip. */
+  int64_t* compact_rows;
+  int32_t* compact_count;
+  int32_t* row_map;
+  int32_t compact_capacity;
 } H3dgsGrads;
 
 H3DGS_API size_t h3dgs_backward_workspace_bytes(int32_t P);
@@ -308,6 +328,14 @@ H3DGS_API int h3dgs_unpack_rows(const H3dgsRowTensor* tensors, int32_t num_tenso
 H3DGS_API int h3dgs_sparse_adam(const H3dgsAdamTensor* tensors, int32_t num_tensors,
                       const int64_t* relevant, int64_t num_relevant, int64_t num_rows,
                       h3dgs_stream_t stream);
+
+/* Sparse Adam on COMPACT gradients (H3dgsGrads.compact_*): tensors[k].grad is [capacity, width] and its row i
+ * belongs to store row compact_rows[i], i < *compact_count (a device word: no host read-back).  gate (device,
+ * [capacity], or NULL): rows whose gate value is exactly 0 are skipped -- with the compact opacity gradient this is
+ * the reference's `relevant = (opacity.grad != 0).nonzero()` (train_single.py:225-229) evaluated on the device. */
+H3DGS_API int h3dgs_sparse_adam_compact(const H3dgsAdamTensor* tensors, int32_t num_tensors,
+                              const int64_t* compact_rows, const int32_t* compact_count, int32_t capacity,
+                              const float* gate, h3dgs_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Instrumentation (no reference counterpart).  Launch counting is always on; per-kernel timing wraps

@@ -147,6 +147,8 @@ cudaError_t run_interpolation_weights(int K, const int* indices, float target_si
                                       int* kids, cudaStream_t s);
 cudaError_t run_sparse_adam(const H3dgsAdamTensor* tensors, int n, const long long* relevant,
                             long long num_relevant, long long num_rows, cudaStream_t s);
+cudaError_t run_sparse_adam_compact(const H3dgsAdamTensor* tensors, int n, const long long* rows, const int* count,
+                                    int capacity, const float* gate, cudaStream_t s);
 cudaError_t run_ssim_forward(int C, int H, int W, const float* img1, const float* img2, const float* mask,
                              const float* window, float* ssim_map, float* dm_dmu1, float* dm_de11, float* dm_de12, double* sums,
                              cudaStream_t s);
@@ -241,38 +243,54 @@ const char* h3dgs_last_error(void) { return g_err; }
 
 size_t h3dgs_geom_bytes(int32_t P) { return GeomWs::make(nullptr, P).bytes; }
 size_t h3dgs_image_bytes(int32_t W, int32_t H) { return ImageWs::make(nullptr, W, H).bytes; }
-size_t h3dgs_binning_bytes(int64_t R, int64_t V, int32_t W, int32_t H) { return BinWs::make(nullptr, R, V, W, H).bytes; }
+size_t h3dgs_binning_bytes(int64_t R, int32_t W, int32_t H) { return BinWs::make(nullptr, R, W, H).bytes; }
 size_t h3dgs_backward_workspace_bytes(int32_t P) { return BwdWs::make(nullptr, P).bytes; }
 size_t h3dgs_expand_workspace_bytes(int32_t N) { return expand_ws_bytes(N); }
 
-int h3dgs_forward_preprocess(const H3dgsView* view, const H3dgsGaussians* g, int32_t* radii, void* geom,
-                             size_t geom_bytes, int64_t* num_rendered_host, int64_t* num_visible_host, int debug,
-                             h3dgs_stream_t stream) {
+int h3dgs_forward_begin(const H3dgsView* view, const H3dgsGaussians* g, int32_t* radii, void* geom,
+                        size_t geom_bytes, int64_t* counts_host, void* counts_event, int debug,
+                        h3dgs_stream_t stream) {
   int rc = check_scene(view, g);
   if (rc) return rc;
-  if (!num_rendered_host || !num_visible_host)
-    return fail(H3DGS_EINVAL, "num_rendered_host and num_visible_host are required");
-  *num_rendered_host = 0;
-  *num_visible_host = 0;
-  if (g->P == 0) return 0;
+  if (!counts_host) return fail(H3DGS_EINVAL, "counts_host is required");
+  counts_host[0] = 0;
+  counts_host[1] = 0;
+  cudaStream_t s = (cudaStream_t)stream;
+  if (g->P == 0) {
+    if (counts_event) H3_CUDA(cudaEventRecord((cudaEvent_t)counts_event, s));
+    return 0;
+  }
   if (!radii || !geom) return fail(H3DGS_EINVAL, "radii and geom are required");
   if (geom_bytes < h3dgs_geom_bytes(g->P)) return fail(H3DGS_ENOSPACE, "geom workspace too small");
   if (reinterpret_cast<size_t>(geom) & 15) return fail(H3DGS_EINVAL, "geom must be 16-byte aligned");
-  cudaStream_t s = (cudaStream_t)stream;
   PreArgs a = make_pre(view, g, radii, geom);
+  GeomWs& gw = a.ws;
+  { ProfScope ps(K_MEMSET, s); H3_CUDA(cudaMemsetAsync(gw.zero_base, 0, gw.zero_bytes, s)); }
   H3_CUDA(launch_preprocess_fwd(a, s));
   if ((rc = debug_sync(debug, s, "preprocess_fwd"))) return rc;
-  H3_CUDA(launch_scan_visible(a.ws.tiles_touched, a.ws.offsets, g->P, a.ws.scan_status, a.ws.counters, s));
-  unsigned long long totals[2] = {0, 0};   // V, R
-  H3_CUDA(cudaMemcpyAsync(totals, a.ws.counters + 2, sizeof(totals), cudaMemcpyDeviceToHost, s));
-  H3_CUDA(cudaStreamSynchronize(s));
-  if (totals[1] >= (1ull << 30)) return fail(H3DGS_EINVAL, "more than 2^30 tile instances");
-  *num_visible_host = (int64_t)totals[0];
-  *num_rendered_host = (int64_t)totals[1];
+  H3_CUDA(launch_scan_visible(gw.tiles_touched, gw.offsets, g->P, gw.scan_status, gw.counters, s));
+  // (R, V) leave for the host now; the kernels below take V from the device, so the host can wait for this copy
+  // alone (counts_event) while the GPU goes on with the depth sort
+  static_assert(sizeof(unsigned long long) == sizeof(int64_t), "counter width");
+  H3_CUDA(cudaMemcpyAsync(counts_host + 1, gw.counters + 2, sizeof(int64_t), cudaMemcpyDeviceToHost, s));   // V
+  H3_CUDA(cudaMemcpyAsync(counts_host, gw.counters + 4, sizeof(int64_t), cudaMemcpyDeviceToHost, s));       // R
+  if (counts_event) H3_CUDA(cudaEventRecord((cudaEvent_t)counts_event, s));
+  const unsigned long long* v_dev = reinterpret_cast<const unsigned long long*>(gw.counters + 2);
+  // visible slots -> (depth, slot) order -> inclusive scan of their tile counts in that order
+  H3_CUDA(launch_compact_visible(g->P, gw, s));
+  if ((rc = debug_sync(debug, s, "compact_visible"))) return rc;
+  H3_CUDA(launch_depth_sort(gw, g->P, v_dev, s));
+  if ((rc = debug_sync(debug, s, "depth_sort"))) return rc;
+  H3_CUDA(launch_scan_gather(gw.tiles_touched, gw.dvals[0], gw.soffs, g->P, v_dev, gw.chunk_first, gw.gscan_status,
+                             gw.gscan_counters, s));
+  if (!counts_event) {
+    H3_CUDA(cudaStreamSynchronize(s));
+    if (counts_host[0] >= MAX_INSTANCES) return fail(H3DGS_EINVAL, "more than 2^30 tile instances");
+  }
   return 0;
 }
 
-int h3dgs_forward_render(const H3dgsView* view, const H3dgsGaussians* g, void* geom, void* binning,
+int h3dgs_forward_finish(const H3dgsView* view, const H3dgsGaussians* g, void* geom, void* binning,
                          size_t binning_bytes, void* image, int64_t R, int64_t V, float* out_color,
                          float* out_invdepth, int debug, h3dgs_stream_t stream, void* pre_blend_event) {
   int rc = check_scene(view, g);
@@ -293,22 +311,17 @@ int h3dgs_forward_render(const H3dgsView* view, const H3dgsGaussians* g, void* g
     return 0;
   }
   if (!geom || !binning || !image) return fail(H3DGS_EINVAL, "geom, binning and image are required");
+  if (R >= MAX_INSTANCES) return fail(H3DGS_EINVAL, "more than 2^30 tile instances");
   if (V <= 0 || V > R || V > g->P) return fail(H3DGS_EINVAL, "num_visible must be in [1, min(P, num_rendered)]");
-  if (binning_bytes < h3dgs_binning_bytes(R, V, W, H)) return fail(H3DGS_ENOSPACE, "binning workspace too small");
+  if (binning_bytes < h3dgs_binning_bytes(R, W, H)) return fail(H3DGS_ENOSPACE, "binning workspace too small");
   GeomWs gw = GeomWs::make(geom, g->P);
-  BinWs bw = BinWs::make(binning, R, V, W, H);
+  BinWs bw = BinWs::make(binning, R, W, H);
   ImageWs iw = ImageWs::make(image, W, H);
   const int grid_x = (W + TILE_X - 1) / TILE_X, grid_y = (H + TILE_Y - 1) / TILE_Y;
   const SortPlan plan = make_sort_plan(W, H);
 
-  // visible slots -> (depth, slot) order -> ordered emission -> stable partition by tile
+  // ordered emission -> stable partition by tile
   { ProfScope ps(K_MEMSET, s); H3_CUDA(cudaMemsetAsync(bw.zero_base, 0, bw.zero_bytes, s)); }
-  H3_CUDA(launch_compact_visible(g->P, gw, bw, s));
-  if ((rc = debug_sync(debug, s, "compact_visible"))) return rc;
-  H3_CUDA(launch_depth_sort(bw, V, s));
-  if ((rc = debug_sync(debug, s, "depth_sort"))) return rc;
-  H3_CUDA(launch_scan_gather(gw.tiles_touched, bw.dvals[0], bw.soffs, (int)V, bw.chunk_first, bw.scan_status,
-                             bw.scan_counters, s));
   H3_CUDA(launch_emit_instances(R, V, gw, bw, grid_x, plan.tile_key_bytes, s));
   if ((rc = debug_sync(debug, s, "emit_instances"))) return rc;
   H3_CUDA(launch_tile_sort(bw, R, plan, gw.depth, s));
@@ -349,9 +362,22 @@ int h3dgs_backward(const H3dgsView* view, const H3dgsGaussians* g, const int32_t
   // The N-row zero fill of fused-cut mode is pure HBM write bandwidth (4 GB at 17 M rows) while the blend
   // kernel that follows is issue-bound with ~1 % DRAM utilisation: run the fill on a side stream, forked
   // here and joined before the scatter kernel, so that the two overlap (H3DGS_OVERLAP_ZERO=0 disables).
+  const bool compact = grads->row_map != nullptr || grads->compact_rows != nullptr || grads->compact_count != nullptr;
+  if (compact) {
+    if (!fused) return fail(H3DGS_EINVAL, "compact gradients need the fused-cut mode (render_indices)");
+    if (!grads->row_map || !grads->compact_rows || !grads->compact_count || grads->compact_capacity <= 0)
+      return fail(H3DGS_EINVAL, "compact gradients need row_map, compact_rows, compact_count and a positive capacity");
+    if (grads->dirty_rows) return fail(H3DGS_EINVAL, "dirty_rows and compact gradients exclude each other");
+    if (reinterpret_cast<size_t>(grads->dL_dmeans3D) & 15 || reinterpret_cast<size_t>(grads->dL_dsh) & 15 ||
+        reinterpret_cast<size_t>(grads->dL_dsh_rest) & 15 || reinterpret_cast<size_t>(grads->dL_dopacity) & 15 ||
+        reinterpret_cast<size_t>(grads->dL_dscales) & 15 || reinterpret_cast<size_t>(grads->dL_drotations) & 15 ||
+        reinterpret_cast<size_t>(grads->dL_dcolors) & 15 || reinterpret_cast<size_t>(grads->dL_dcov3D) & 15)
+      return fail(H3DGS_EINVAL, "compact gradient tensors must be 16-byte aligned");
+    H3_CUDA(cudaMemsetAsync(grads->compact_count, 0, sizeof(int32_t), (cudaStream_t)stream));
+  }
   const bool busy = !(P == 0 || R <= 0);
   // (not while per-kernel timing is on: overlapped kernels would be charged each other's time)
-  SideStream* side = (busy && fused && !grads->rows_prezeroed && overlap_zero() && !g_prof.on) ? side_stream() : nullptr;
+  SideStream* side = (busy && fused && !compact && !grads->rows_prezeroed && overlap_zero() && !g_prof.on) ? side_stream() : nullptr;
   cudaStream_t zs = s;
   if (side) {
     H3_CUDA(cudaEventRecord(side->fork, s));
@@ -362,7 +388,7 @@ int h3dgs_backward(const H3dgsView* view, const H3dgsGaussians* g, const int32_t
     return zero_fill(p, n, zs);
   };
   if (grads->dirty_rows) H3_CUDA(cudaMemsetAsync(grads->dirty_rows, 0, sizeof(int32_t), s));
-  if (P == 0 || R <= 0 || (fused && !grads->rows_prezeroed)) {
+  if (!compact && (P == 0 || R <= 0 || (fused && !grads->rows_prezeroed))) {
     ProfScope ps(K_MEMSET, zs);
     // fused-cut mode scatters into store rows; empty renders produce all-zero gradients
     H3_CUDA(zero(grads->dL_dmeans3D, rows * 3));
@@ -385,7 +411,7 @@ int h3dgs_backward(const H3dgsView* view, const H3dgsGaussians* g, const int32_t
   if (workspace_bytes < h3dgs_backward_workspace_bytes(P)) return fail(H3DGS_ENOSPACE, "backward workspace too small");
 
   GeomWs gw = GeomWs::make(const_cast<void*>(geom), P);
-  BinWs bw = BinWs::make(const_cast<void*>(binning), R, 1, W, H);   // the R-sized arrays do not depend on V
+  BinWs bw = BinWs::make(const_cast<void*>(binning), R, W, H);
   ImageWs iw = ImageWs::make(const_cast<void*>(image), W, H);
   BwdWs ww = BwdWs::make(workspace, P);
   { ProfScope ps(K_MEMSET, s); H3_CUDA(cudaMemsetAsync(ww.grad, 0, sizeof(GradRec) * (size_t)P, s)); }
@@ -530,7 +556,7 @@ int h3dgs_debug_view(int32_t P, int32_t W, int32_t H, int64_t R, const void* geo
     out->tile_rects = reinterpret_cast<const uint16_t*>(gw.tile_rect);
   }
   if (binning && R > 0) {
-    BinWs bw = BinWs::make(const_cast<void*>(binning), R, 1, W, H);
+    BinWs bw = BinWs::make(const_cast<void*>(binning), R, W, H);
     out->point_list_keys = reinterpret_cast<const uint64_t*>(bw.keys64);
     out->point_list = bw.tvals[bw.sorted];
   }
@@ -586,6 +612,23 @@ int h3dgs_sparse_adam(const H3dgsAdamTensor* tensors, int32_t num_tensors, const
   if (num_relevant < 0 || num_rows < 0) return fail(H3DGS_EINVAL, "negative row count");
   H3_CUDA(run_sparse_adam(tensors, num_tensors, reinterpret_cast<const long long*>(relevant), num_relevant,
                           num_rows, (cudaStream_t)stream));
+  return 0;
+}
+
+int h3dgs_sparse_adam_compact(const H3dgsAdamTensor* tensors, int32_t num_tensors, const int64_t* compact_rows,
+                              const int32_t* compact_count, int32_t capacity, const float* gate,
+                              h3dgs_stream_t stream) {
+  if (!tensors || num_tensors <= 0 || num_tensors > H3DGS_ADAM_MAX_TENSORS)
+    return fail(H3DGS_EINVAL, "1..H3DGS_ADAM_MAX_TENSORS tensors required");
+  for (int i = 0; i < num_tensors; ++i) {
+    if (!tensors[i].param || !tensors[i].grad || !tensors[i].exp_avg || !tensors[i].exp_avg_sq || tensors[i].width <= 0)
+      return fail(H3DGS_EINVAL, "adam tensor with null pointer or non-positive width");
+  }
+  if (capacity < 0) return fail(H3DGS_EINVAL, "negative capacity");
+  if (capacity == 0) return 0;
+  if (!compact_rows || !compact_count) return fail(H3DGS_EINVAL, "compact_rows and compact_count are required");
+  H3_CUDA(run_sparse_adam_compact(tensors, num_tensors, reinterpret_cast<const long long*>(compact_rows), compact_count,
+                                  capacity, gate, (cudaStream_t)stream));
   return 0;
 }
 

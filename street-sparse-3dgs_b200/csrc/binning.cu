@@ -146,13 +146,13 @@ cudaError_t launch_tile_order(const uint2* ranges, const uint32_t* lengths, int 
   return cudaGetLastError();
 }
 
-cudaError_t launch_compact_visible(int P, const GeomWs& g, BinWs& b, cudaStream_t s) {
+cudaError_t launch_compact_visible(int P, GeomWs& g, cudaStream_t s) {
   if (P <= 0) return cudaSuccess;
   int blocks = (P + 256 * 8 - 1) / (256 * 8);
   if (blocks > 148 * 8) blocks = 148 * 8;
   ProfScope ps(K_EMIT, s);
-  compact_visible_kernel<<<blocks, 256, 0, s>>>(P, g.tiles_touched, g.offsets, g.depth, b.dkeys[0], b.dvals[0],
-                                                b.depth_hist);
+  compact_visible_kernel<<<blocks, 256, 0, s>>>(P, g.tiles_touched, g.offsets, g.depth, g.dkeys[0], g.dvals[0],
+                                                g.depth_hist);
   return cudaGetLastError();
 }
 
@@ -162,11 +162,11 @@ cudaError_t launch_emit_instances(int64_t R, int64_t V, const GeomWs& g, BinWs& 
   const unsigned blocks = (unsigned)((R + EMIT_CHUNK - 1) / EMIT_CHUNK);
   ProfScope ps(K_EMIT, s);
   if (key_bytes == 2)
-    emit_instances_kernel<uint16_t><<<blocks, 256, 0, s>>>(R, V, b.dvals[0], b.soffs, b.chunk_first, g.tile_rect,
+    emit_instances_kernel<uint16_t><<<blocks, 256, 0, s>>>(R, V, g.dvals[0], g.soffs, g.chunk_first, g.tile_rect,
                                                            grid_x, reinterpret_cast<uint16_t*>(b.tkeys[0]),
                                                            b.tvals[0]);
   else
-    emit_instances_kernel<uint32_t><<<blocks, 256, 0, s>>>(R, V, b.dvals[0], b.soffs, b.chunk_first, g.tile_rect,
+    emit_instances_kernel<uint32_t><<<blocks, 256, 0, s>>>(R, V, g.dvals[0], g.soffs, g.chunk_first, g.tile_rect,
                                                            grid_x, reinterpret_cast<uint32_t*>(b.tkeys[0]),
                                                            b.tvals[0]);
   return cudaGetLastError();

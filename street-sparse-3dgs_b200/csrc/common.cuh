@@ -44,6 +44,15 @@ constexpr int SCAN_THREADS = 256;
 constexpr int SCAN_ITEMS = 16;
 constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
 
+// ---- two-level instance sort geometry (radix_sort.cu / binning.cu) ----
+constexpr int SORT_RADIX_BITS = 8;
+constexpr int SORT_RADIX = 1 << SORT_RADIX_BITS;
+constexpr int SORT_THREADS = 512;
+constexpr int SORT_ITEMS = 12;
+constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;
+constexpr int SORT_MAX_PASSES = 4;
+constexpr int SORT_DEPTH_PASSES = 4;   // 32 depth bits, 8 per pass
+constexpr int EMIT_CHUNK = 2048;       // instances written per CTA of the emission kernel
 constexpr long long MAX_INSTANCES = 1ll << 30;   // a render with more tile instances is rejected
 
 // Everything whose size is known before the render's instance count R is: per-slot state and the depth sort of

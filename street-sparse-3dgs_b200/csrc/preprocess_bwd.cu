@@ -119,6 +119,35 @@ __global__ void __launch_bounds__(256) list_visible_kernel(const PreBwdArgs b) {
   const int M = a.M;
   if (a.radii[t_idx] > 0) {
     b.vis_list[a.ws.offsets[t_idx] - 1u] = (uint32_t)t_idx;
+    if (FUSED && o.row_map != nullptr) {
+      // compact gradients: every store row this slot adds into gets a compact row.  The first thread to turn a
+      // row's map entry from -1 into its (negative) tag owns the row, takes the next compact id and publishes it;
+      // ids are only read by the next kernel.
+      size_t r;
+      long long p = -1;
+      bool lerp = false;
+      const int K = a.P - a.skyboxnum;
+      if (t_idx >= K) {
+        r = (size_t)(a.rows - a.skyboxnum + (t_idx - K));
+      } else {
+        r = (size_t)__ldg(a.idx + t_idx);
+        if (a.pidx != nullptr) {
+          p = __ldg(a.pidx + t_idx);
+          if (p >= 0) lerp = __fsub_rn(1.0f, __ldg(a.ts + t_idx)) != 0.0f;
+        }
+      }
+      const int tag = -2 - 2 * t_idx;
+      for (int side = 0; side < (lerp ? 2 : 1); ++side) {
+        const size_t row = side ? (size_t)p : r;
+        if (atomicCAS(o.row_map + row, -1, tag - side) == -1) {
+          const int id = atomicAdd(o.compact_count, 1);
+          if (id < o.compact_capacity) {
+            o.compact_rows[id] = (long long)row;
+            o.row_map[row] = id;
+          }
+        }
+      }
+    }
     return;
   }
   if (o.dL_dmeans2D) {
@@ -183,6 +212,15 @@ __global__ void __launch_bounds__(256, 2) preprocess_bwd_kernel(const PreBwdArgs
     }
   }
   const size_t pr = (size_t)(p < 0 ? 0 : p);
+  // rows of the OUTPUT tensors: the store rows themselves, or their compact rows (H3dgsGrads.compact_*)
+  size_t wr = r, wpr = pr;
+  if (FUSED && o.row_map != nullptr) {
+    const int cr = o.row_map[r];
+    const int cpr = lerp ? o.row_map[pr] : cr;
+    if (cr < 0 || cr >= o.compact_capacity || cpr < 0 || cpr >= o.compact_capacity) return;   // capacity exceeded
+    wr = (size_t)cr;
+    wpr = (size_t)cpr;
+  }
 
   // The kernel is a long chain of dependent arithmetic fed by ~25 scattered rows (child and parent parameters,
   // then the same rows of the gradient tensors): without help every row is a separate DRAM round trip in the
@@ -200,17 +238,18 @@ __global__ void __launch_bounds__(256, 2) preprocess_bwd_kernel(const PreBwdArgs
     const int wsh = split ? (M - 1) * 3 : M * 3;
     for (int side = 0; side < (lerp ? 2 : 1); ++side) {
       const size_t row = side ? pr : r;
+      const size_t wrow = side ? wpr : wr;
       pf_row(a.means, row, 3);
       pf_row(a.scales, row, 3);
       pf_row(a.rots, row, 4);
       pf_row(a.opac, row, 1);
       pf_row(split ? a.shs_rest : a.shs, row, wsh);
-      pf_row(o.dL_dmeans3D, row, 3);
-      pf_row(o.dL_dscales, row, 3);
-      pf_row(o.dL_drotations, row, 4);
-      pf_row(o.dL_dopacity, row, 1);
-      pf_row(split ? o.dL_dsh_rest : o.dL_dsh, row, wsh);
-      if (split) { pf_row(a.shs, row, 3); pf_row(o.dL_dsh, row, 3); }
+      pf_row(o.dL_dmeans3D, wrow, 3);
+      pf_row(o.dL_dscales, wrow, 3);
+      pf_row(o.dL_drotations, wrow, 4);
+      pf_row(o.dL_dopacity, wrow, 1);
+      pf_row(split ? o.dL_dsh_rest : o.dL_dsh, wrow, wsh);
+      if (split) { pf_row(a.shs, row, 3); pf_row(o.dL_dsh, wrow, 3); }
     }
   }
 
@@ -390,7 +429,7 @@ __global__ void __launch_bounds__(256, 2) preprocess_bwd_kernel(const PreBwdArgs
         v[3 * k] = w * dL_dRGB.x; v[3 * k + 1] = w * dL_dRGB.y; v[3 * k + 2] = w * dL_dRGB.z;
       }
       for (int side = 0; side < (lerp ? 2 : 1); ++side) {
-        const size_t row = side ? pr : r;
+        const size_t row = side ? wpr : wr;
         const float sc = lerp ? (side ? omt : t) : 1.0f;
         if (split) {
           red_row3(o.dL_dsh + row * 3, sc * v[0], sc * v[1], sc * v[2]);
@@ -426,25 +465,25 @@ __global__ void __launch_bounds__(256, 2) preprocess_bwd_kernel(const PreBwdArgs
         }
       }
     } else if (split) {
-      put<FUSED>(o.dL_dsh, r, 3, 0, bs[0] * dL_dRGB.x, pr, lerp, t, omt);
-      put<FUSED>(o.dL_dsh, r, 3, 1, bs[0] * dL_dRGB.y, pr, lerp, t, omt);
-      put<FUSED>(o.dL_dsh, r, 3, 2, bs[0] * dL_dRGB.z, pr, lerp, t, omt);
+      put<FUSED>(o.dL_dsh, wr, 3, 0, bs[0] * dL_dRGB.x, wpr, lerp, t, omt);
+      put<FUSED>(o.dL_dsh, wr, 3, 1, bs[0] * dL_dRGB.y, wpr, lerp, t, omt);
+      put<FUSED>(o.dL_dsh, wr, 3, 2, bs[0] * dL_dRGB.z, wpr, lerp, t, omt);
       const int Wd = (M - 1) * 3;
       for (int k = 1; k < M; ++k) {
         const float w = (k < n) ? bs[k] : 0.f;
         if (!FUSED || k < n) {   // in fused mode the rows are pre-zeroed: skip the zero atomics
-          put<FUSED>(o.dL_dsh_rest, r, Wd, 3 * k - 3, w * dL_dRGB.x, pr, lerp, t, omt);
-          put<FUSED>(o.dL_dsh_rest, r, Wd, 3 * k - 2, w * dL_dRGB.y, pr, lerp, t, omt);
-          put<FUSED>(o.dL_dsh_rest, r, Wd, 3 * k - 1, w * dL_dRGB.z, pr, lerp, t, omt);
+          put<FUSED>(o.dL_dsh_rest, wr, Wd, 3 * k - 3, w * dL_dRGB.x, wpr, lerp, t, omt);
+          put<FUSED>(o.dL_dsh_rest, wr, Wd, 3 * k - 2, w * dL_dRGB.y, wpr, lerp, t, omt);
+          put<FUSED>(o.dL_dsh_rest, wr, Wd, 3 * k - 1, w * dL_dRGB.z, wpr, lerp, t, omt);
         }
       }
     } else {
       for (int k = 0; k < M; ++k) {
         const float w = (k < n) ? bs[k] : 0.f;
         if (!FUSED || k < n) {
-          put<FUSED>(o.dL_dsh, r, M * 3, 3 * k + 0, w * dL_dRGB.x, pr, lerp, t, omt);
-          put<FUSED>(o.dL_dsh, r, M * 3, 3 * k + 1, w * dL_dRGB.y, pr, lerp, t, omt);
-          put<FUSED>(o.dL_dsh, r, M * 3, 3 * k + 2, w * dL_dRGB.z, pr, lerp, t, omt);
+          put<FUSED>(o.dL_dsh, wr, M * 3, 3 * k + 0, w * dL_dRGB.x, wpr, lerp, t, omt);
+          put<FUSED>(o.dL_dsh, wr, M * 3, 3 * k + 1, w * dL_dRGB.y, wpr, lerp, t, omt);
+          put<FUSED>(o.dL_dsh, wr, M * 3, 3 * k + 2, w * dL_dRGB.z, wpr, lerp, t, omt);
         }
       }
     }
@@ -526,22 +565,22 @@ __global__ void __launch_bounds__(256, 2) preprocess_bwd_kernel(const PreBwdArgs
       o.dL_dcolors[r * 3] = 0.f; o.dL_dcolors[r * 3 + 1] = 0.f; o.dL_dcolors[r * 3 + 2] = 0.f;
     }
   } else {
-    put<FUSED>(o.dL_dcolors, r, 3, 0, dL_dRGB.x, pr, lerp, t, omt);
-    put<FUSED>(o.dL_dcolors, r, 3, 1, dL_dRGB.y, pr, lerp, t, omt);
-    put<FUSED>(o.dL_dcolors, r, 3, 2, dL_dRGB.z, pr, lerp, t, omt);
+    put<FUSED>(o.dL_dcolors, wr, 3, 0, dL_dRGB.x, wpr, lerp, t, omt);
+    put<FUSED>(o.dL_dcolors, wr, 3, 1, dL_dRGB.y, wpr, lerp, t, omt);
+    put<FUSED>(o.dL_dcolors, wr, 3, 2, dL_dRGB.z, wpr, lerp, t, omt);
     if (!FUSED && o.dL_dsh && !o.dL_dsh_rest) for (int i = 0; i < M * 3; ++i) o.dL_dsh[r * (size_t)M * 3 + i] = 0.f;
   }
 
   if (FUSED && o.dL_dmeans3D != nullptr) {
     const float sc = lerp ? t : 1.0f;
-    red_row3(o.dL_dmeans3D + r * 3, sc * dL_dmean.x, sc * dL_dmean.y, sc * dL_dmean.z);
-    if (lerp) red_row3(o.dL_dmeans3D + pr * 3, omt * dL_dmean.x, omt * dL_dmean.y, omt * dL_dmean.z);
+    red_row3(o.dL_dmeans3D + wr * 3, sc * dL_dmean.x, sc * dL_dmean.y, sc * dL_dmean.z);
+    if (lerp) red_row3(o.dL_dmeans3D + wpr * 3, omt * dL_dmean.x, omt * dL_dmean.y, omt * dL_dmean.z);
   } else {
-    put<FUSED>(o.dL_dmeans3D, r, 3, 0, dL_dmean.x, pr, lerp, t, omt);
-    put<FUSED>(o.dL_dmeans3D, r, 3, 1, dL_dmean.y, pr, lerp, t, omt);
-    put<FUSED>(o.dL_dmeans3D, r, 3, 2, dL_dmean.z, pr, lerp, t, omt);
+    put<FUSED>(o.dL_dmeans3D, wr, 3, 0, dL_dmean.x, wpr, lerp, t, omt);
+    put<FUSED>(o.dL_dmeans3D, wr, 3, 1, dL_dmean.y, wpr, lerp, t, omt);
+    put<FUSED>(o.dL_dmeans3D, wr, 3, 2, dL_dmean.z, wpr, lerp, t, omt);
   }
-  put2<FUSED>(o.dL_dopacity, r, 1, 0, tc * dL_dopacity_out * act_scalar_grad(a.act_opac, o_raw, o_act), pr,
+  put2<FUSED>(o.dL_dopacity, wr, 1, 0, tc * dL_dopacity_out * act_scalar_grad(a.act_opac, o_raw, o_act), wpr,
               lerp, omt * dL_dopacity_out * act_scalar_grad(a.act_opac, op_raw, op_act));
 
   // ---------------- 3D covariance -> scale / rotation (backward.cu:330-393) ----------------
@@ -614,30 +653,60 @@ __global__ void __launch_bounds__(256, 2) preprocess_bwd_kernel(const PreBwdArgs
     }
     if (FUSED) {
       if (o.dL_dscales != nullptr) {
-        red_row3(o.dL_dscales + r * 3, gs0, gs1, gs2);
-        if (lerp) red_row3(o.dL_dscales + pr * 3, gp0, gp1, gp2);
+        red_row3(o.dL_dscales + wr * 3, gs0, gs1, gs2);
+        if (lerp) red_row3(o.dL_dscales + wpr * 3, gp0, gp1, gp2);
       }
       if (o.dL_drotations != nullptr) {
-        red4(o.dL_drotations + r * 4, gc.x, gc.y, gc.z, gc.w);
-        if (lerp) red4(o.dL_drotations + pr * 4, gp.x, gp.y, gp.z, gp.w);
+        red4(o.dL_drotations + wr * 4, gc.x, gc.y, gc.z, gc.w);
+        if (lerp) red4(o.dL_drotations + wpr * 4, gp.x, gp.y, gp.z, gp.w);
       }
     } else {
-      put2<FUSED>(o.dL_dscales, r, 3, 0, gs0, pr, lerp, gp0);
-      put2<FUSED>(o.dL_dscales, r, 3, 1, gs1, pr, lerp, gp1);
-      put2<FUSED>(o.dL_dscales, r, 3, 2, gs2, pr, lerp, gp2);
-      put2<FUSED>(o.dL_drotations, r, 4, 0, gc.x, pr, lerp, gp.x);
-      put2<FUSED>(o.dL_drotations, r, 4, 1, gc.y, pr, lerp, gp.y);
-      put2<FUSED>(o.dL_drotations, r, 4, 2, gc.z, pr, lerp, gp.z);
-      put2<FUSED>(o.dL_drotations, r, 4, 3, gc.w, pr, lerp, gp.w);
+      put2<FUSED>(o.dL_dscales, wr, 3, 0, gs0, wpr, lerp, gp0);
+      put2<FUSED>(o.dL_dscales, wr, 3, 1, gs1, wpr, lerp, gp1);
+      put2<FUSED>(o.dL_dscales, wr, 3, 2, gs2, wpr, lerp, gp2);
+      put2<FUSED>(o.dL_drotations, wr, 4, 0, gc.x, wpr, lerp, gp.x);
+      put2<FUSED>(o.dL_drotations, wr, 4, 1, gc.y, wpr, lerp, gp.y);
+      put2<FUSED>(o.dL_drotations, wr, 4, 2, gc.z, wpr, lerp, gp.z);
+      put2<FUSED>(o.dL_drotations, wr, 4, 3, gc.w, wpr, lerp, gp.w);
     }
     if (!FUSED && o.dL_dcov3D) for (int i = 0; i < 6; ++i) o.dL_dcov3D[r * 6 + i] = dcov[i];
   } else {
-    for (int i = 0; i < 6; ++i) put<FUSED>(o.dL_dcov3D, r, 6, i, dcov[i], pr, lerp, t, omt);
+    for (int i = 0; i < 6; ++i) put<FUSED>(o.dL_dcov3D, wr, 6, i, dcov[i], wpr, lerp, t, omt);
     if (!FUSED) {
       if (o.dL_dscales) { o.dL_dscales[r * 3] = 0.f; o.dL_dscales[r * 3 + 1] = 0.f; o.dL_dscales[r * 3 + 2] = 0.f; }
       if (o.dL_drotations) *reinterpret_cast<float4*>(o.dL_drotations + r * 4) = make_float4(0.f, 0.f, 0.f, 0.f);
     }
   }
+}
+
+// Compact gradients: zero the first U rows of every compact tensor (U lives on the device), and afterwards put the
+// row map back to all -1 by visiting the U rows that were claimed.
+struct CompactZero {
+  float* base[8];
+  int width[8];
+  int n;
+};
+__global__ void __launch_bounds__(256) zero_compact_kernel(const CompactZero z, const int* __restrict__ count,
+                                                           int capacity) {
+  const long long U = min(*count, capacity);
+  const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (int k = 0; k < z.n; ++k) {
+    // rows [0, U) of a compact tensor are one contiguous span; the tensors come from the caching allocator
+    // (512-byte aligned), so the span starts on a 16-byte boundary
+    const long long n = U * z.width[k];
+    float4* q = reinterpret_cast<float4*>(z.base[k]);
+    const long long n4 = n >> 2;
+    for (long long i = tid; i < n4; i += stride) q[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (tid < (n & 3)) z.base[k][n4 * 4 + tid] = 0.f;
+  }
+}
+__global__ void __launch_bounds__(256) reset_row_map_kernel(int* __restrict__ row_map,
+                                                            const long long* __restrict__ rows,
+                                                            const int* __restrict__ count, int capacity) {
+  const long long U = min(*count, capacity);
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < U; i += stride) row_map[rows[i]] = -1;
 }
 
 }  // namespace
@@ -646,7 +715,21 @@ cudaError_t launch_preprocess_bwd(const PreBwdArgs& b, cudaStream_t s) {
   if (b.f.P <= 0) return cudaSuccess;
   const int blocks = (b.f.P + 255) / 256;
   ProfScope ps(K_PREPROCESS_BWD, s);
-  if (b.f.idx != nullptr) {
+  if (b.f.idx != nullptr && b.out.row_map != nullptr) {
+    const H3dgsGrads& o = b.out;
+    list_visible_kernel<true><<<blocks, 256, 0, s>>>(b);
+    CompactZero z;
+    z.n = 0;
+    const int M = b.f.M;
+    const bool split = b.f.shs_rest != nullptr;
+    auto add = [&](float* p, int w) { if (p != nullptr && w > 0) { z.base[z.n] = p; z.width[z.n] = w; ++z.n; } };
+    add(o.dL_dmeans3D, 3); add(o.dL_dsh, split ? 3 : M * 3); add(o.dL_dsh_rest, split ? (M - 1) * 3 : 0);
+    add(o.dL_dcolors, 3); add(o.dL_dopacity, 1); add(o.dL_dscales, 3); add(o.dL_drotations, 4); add(o.dL_dcov3D, 6);
+    zero_compact_kernel<<<148 * 8, 256, 0, s>>>(z, o.compact_count, o.compact_capacity);
+    preprocess_bwd_kernel<true><<<blocks, 256, 0, s>>>(b);
+    reset_row_map_kernel<<<148 * 4, 256, 0, s>>>(o.row_map, reinterpret_cast<const long long*>(o.compact_rows),
+                                                 o.compact_count, o.compact_capacity);
+  } else if (b.f.idx != nullptr) {
     list_visible_kernel<true><<<blocks, 256, 0, s>>>(b);
     preprocess_bwd_kernel<true><<<blocks, 256, 0, s>>>(b);
   } else {

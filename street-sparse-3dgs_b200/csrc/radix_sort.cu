@@ -80,17 +80,22 @@ template <typename K, int OUT>
 __global__ void __launch_bounds__(SORT_THREADS, 3) onesweep_kernel(
     const K* __restrict__ kin, K* __restrict__ kout, const uint32_t* __restrict__ vin,
     uint32_t* __restrict__ vout, unsigned long long* __restrict__ kout64,
-    const uint32_t* __restrict__ depth_bits, long long n, int shift, uint32_t mask,
-    const uint32_t* __restrict__ digit_base, volatile uint32_t* status, uint32_t* counter) {
+    const uint32_t* __restrict__ depth_bits, long long n_host, const unsigned long long* __restrict__ n_dev,
+    int shift, uint32_t mask, const uint32_t* __restrict__ digit_base, volatile uint32_t* status,
+    uint32_t* counter) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   SweepSmem<K>& sm = *reinterpret_cast<SweepSmem<K>*>(smem_raw);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
+  // element count: known to the host (tile passes over the R instances) or left on the device by the visible
+  // scan (depth passes over the V visible slots: the grid then covers the P slots and the surplus CTAs leave)
+  const long long n = n_dev ? (long long)*n_dev : n_host;
   if (tid == 0) sm.tile = atomicAdd(counter, 1u);
   for (int i = tid; i < WARPS * RADIX; i += SORT_THREADS) (&sm.cnt[0][0])[i] = 0;
   __syncthreads();
   const uint32_t tile = sm.tile;
   const long long tile_base = (long long)tile * SORT_TILE;
+  if (tile_base >= n) return;
   const long long remaining = n - tile_base;
   const int tile_valid = (int)(remaining < SORT_TILE ? remaining : SORT_TILE);
 
@@ -203,8 +208,9 @@ __global__ void __launch_bounds__(SORT_THREADS, 3) onesweep_kernel(
 
 template <typename K, int OUT>
 cudaError_t launch_pass(const K* kin, K* kout, const uint32_t* vin, uint32_t* vout, unsigned long long* kout64,
-                        const uint32_t* depth_bits, long long n, int shift, uint32_t mask,
-                        const uint32_t* digit_base, uint32_t* status, uint32_t* counter, cudaStream_t s) {
+                        const uint32_t* depth_bits, long long n, const unsigned long long* n_dev, int shift,
+                        uint32_t mask, const uint32_t* digit_base, uint32_t* status, uint32_t* counter,
+                        cudaStream_t s) {
   auto k = onesweep_kernel<K, OUT>;
   const size_t smem = sizeof(SweepSmem<K>);
   static bool attr_done = false;   // one flag per template instantiation
@@ -215,7 +221,7 @@ cudaError_t launch_pass(const K* kin, K* kout, const uint32_t* vin, uint32_t* vo
   }
   const long long tiles = (n + SORT_TILE - 1) / SORT_TILE;
   ProfScope ps(K_SORT_PASS, s);
-  k<<<(unsigned)tiles, SORT_THREADS, smem, s>>>(kin, kout, vin, vout, kout64, depth_bits, n, shift, mask,
+  k<<<(unsigned)tiles, SORT_THREADS, smem, s>>>(kin, kout, vin, vout, kout64, depth_bits, n, n_dev, shift, mask,
                                                 digit_base, status, counter);
   return cudaGetLastError();
 }
@@ -250,12 +256,12 @@ cudaError_t tile_sort(BinWs& b, int64_t R, const SortPlan& plan, const uint32_t*
     const int src = p & 1, dst = src ^ 1;
     uint32_t* status = b.tile_status + (size_t)p * tiles * RADIX;
     if (p + 1 < plan.tile_passes)
-      e = launch_pass<K, 0>(keys[src], keys[dst], b.tvals[src], b.tvals[dst], nullptr, nullptr, R, sh.shift[p],
-                            sh.mask[p], b.tile_hist + (size_t)p * RADIX, status, b.counters + 8 + p, s);
+      e = launch_pass<K, 0>(keys[src], keys[dst], b.tvals[src], b.tvals[dst], nullptr, nullptr, R, nullptr,
+                            sh.shift[p], sh.mask[p], b.tile_hist + (size_t)p * RADIX, status, b.counters + p, s);
     else
-      e = launch_pass<K, 2>(keys[src], keys[dst], b.tvals[src], b.tvals[dst], b.keys64, depth_bits, R,
+      e = launch_pass<K, 2>(keys[src], keys[dst], b.tvals[src], b.tvals[dst], b.keys64, depth_bits, R, nullptr,
                             sh.shift[p], sh.mask[p], b.tile_hist + (size_t)p * RADIX, status,
-                            b.counters + 8 + p, s);
+                            b.counters + p, s);
     if (e != cudaSuccess) return e;
   }
   return cudaSuccess;
@@ -263,24 +269,24 @@ cudaError_t tile_sort(BinWs& b, int64_t R, const SortPlan& plan, const uint32_t*
 
 }  // namespace
 
-// Sort the V compacted (depth bits, slot) pairs in b.dkeys[0] / b.dvals[0]; the digit histograms were
-// accumulated by the compaction kernel.  The sorted slot order ends up in b.dvals[0] (4 passes).
-cudaError_t launch_depth_sort(BinWs& b, int64_t V, cudaStream_t s) {
-  if (V <= 0) return cudaSuccess;
+// Sort the V compacted (depth bits, slot) pairs in g.dkeys[0] / g.dvals[0]; the digit histograms were
+// accumulated by the compaction kernel.  V lives on the device (*v_dev); the grids cover the P slots.  The
+// sorted slot order ends up in g.dvals[0] (4 passes).
+cudaError_t launch_depth_sort(GeomWs& g, int P, const unsigned long long* v_dev, cudaStream_t s) {
+  if (P <= 0) return cudaSuccess;
   { ProfScope ps(K_SORT_SCAN, s);
-    scan_hist_kernel<<<SORT_DEPTH_PASSES, RADIX, 0, s>>>(b.depth_hist); }
+    scan_hist_kernel<<<SORT_DEPTH_PASSES, RADIX, 0, s>>>(g.depth_hist); }
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return e;
-  const size_t tiles = (size_t)((V + SORT_TILE - 1) / SORT_TILE);
   for (int p = 0; p < SORT_DEPTH_PASSES; ++p) {
     const int src = p & 1, dst = src ^ 1;
-    uint32_t* status = b.depth_status + (size_t)p * tiles * RADIX;
+    uint32_t* status = g.depth_status + (size_t)p * g.sort_tiles * RADIX;
     if (p + 1 < SORT_DEPTH_PASSES)
-      e = launch_pass<uint32_t, 0>(b.dkeys[src], b.dkeys[dst], b.dvals[src], b.dvals[dst], nullptr, nullptr, V,
-                                   8 * p, 0xffu, b.depth_hist + (size_t)p * RADIX, status, b.counters + p, s);
+      e = launch_pass<uint32_t, 0>(g.dkeys[src], g.dkeys[dst], g.dvals[src], g.dvals[dst], nullptr, nullptr, P, v_dev,
+                                   8 * p, 0xffu, g.depth_hist + (size_t)p * RADIX, status, g.dcounters + p, s);
     else
-      e = launch_pass<uint32_t, 1>(b.dkeys[src], b.dkeys[dst], b.dvals[src], b.dvals[dst], nullptr, nullptr, V,
-                                   8 * p, 0xffu, b.depth_hist + (size_t)p * RADIX, status, b.counters + p, s);
+      e = launch_pass<uint32_t, 1>(g.dkeys[src], g.dkeys[dst], g.dvals[src], g.dvals[dst], nullptr, nullptr, P, v_dev,
+                                   8 * p, 0xffu, g.depth_hist + (size_t)p * RADIX, status, g.dcounters + p, s);
     if (e != cudaSuccess) return e;
   }
   static_assert((SORT_DEPTH_PASSES & 1) == 0, "sorted order must land in dvals[0]");

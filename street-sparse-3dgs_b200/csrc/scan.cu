@@ -22,15 +22,20 @@ __device__ __forceinline__ void mark_chunks(uint32_t* __restrict__ chunk_first, 
 // itself into counters[4..5] (the instance total).   MODE 2: scan in[idx[i]] (tile counts in depth order).
 template <int MODE>
 __global__ void __launch_bounds__(SCAN_THREADS) scan_lookback_kernel(
-    const uint32_t* __restrict__ in, const uint32_t* __restrict__ idx, uint32_t* __restrict__ out, int n,
-    uint32_t* __restrict__ chunk_first, volatile unsigned long long* status, uint32_t* counters) {
+    const uint32_t* __restrict__ in, const uint32_t* __restrict__ idx, uint32_t* __restrict__ out, int n_host,
+    const unsigned long long* __restrict__ n_dev, uint32_t* __restrict__ chunk_first,
+    volatile unsigned long long* status, uint32_t* counters) {
   __shared__ uint32_t s_tile;
+  // element count from the host, or left on the device by an earlier kernel (then the grid covers n_host and the
+  // surplus CTAs leave: look-back only ever reads the tiles in front of a tile)
+  const int n = n_dev ? (int)*n_dev : n_host;
   __shared__ unsigned long long s_warp[SCAN_THREADS / 32];
   __shared__ unsigned long long s_prefix;
 
   if (threadIdx.x == 0) s_tile = atomicAdd(&counters[0], 1u);
   __syncthreads();
   const uint32_t tile = s_tile;
+  if ((size_t)tile * SCAN_TILE >= (size_t)n) return;
   const size_t base = (size_t)tile * SCAN_TILE + (size_t)threadIdx.x * SCAN_ITEMS;
 
   uint32_t v[SCAN_ITEMS];
@@ -150,7 +155,8 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_lookback_kernel(
 
 template <int MODE>
 static cudaError_t launch_scan(const uint32_t* in, const uint32_t* idx, uint32_t* out, int n,
-                               uint32_t* chunk_first, unsigned long long* status, uint32_t* counters, cudaStream_t s) {
+                               const unsigned long long* n_dev, uint32_t* chunk_first, unsigned long long* status,
+                               uint32_t* counters, cudaStream_t s) {
   if (n <= 0) return cudaSuccess;
   const int tiles = (n + SCAN_TILE - 1) / SCAN_TILE;
   cudaError_t e = cudaMemsetAsync(status, 0, sizeof(unsigned long long) * (size_t)(tiles + 1), s);
@@ -158,22 +164,22 @@ static cudaError_t launch_scan(const uint32_t* in, const uint32_t* idx, uint32_t
   e = cudaMemsetAsync(counters, 0, 8 * sizeof(uint32_t), s);
   if (e != cudaSuccess) return e;
   ProfScope ps(K_SCAN, s);
-  scan_lookback_kernel<MODE><<<tiles, SCAN_THREADS, 0, s>>>(in, idx, out, n, chunk_first, status, counters);
+  scan_lookback_kernel<MODE><<<tiles, SCAN_THREADS, 0, s>>>(in, idx, out, n, n_dev, chunk_first, status, counters);
   return cudaGetLastError();
 }
 
 cudaError_t launch_scan_inclusive(const uint32_t* in, uint32_t* out, int n, unsigned long long* status,
                                   uint32_t* counters, cudaStream_t s) {
-  return launch_scan<0>(in, nullptr, out, n, nullptr, status, counters, s);
+  return launch_scan<0>(in, nullptr, out, n, nullptr, nullptr, status, counters, s);
 }
 cudaError_t launch_scan_visible(const uint32_t* tiles_touched, uint32_t* rank, int n,
                                 unsigned long long* status, uint32_t* counters, cudaStream_t s) {
-  return launch_scan<1>(tiles_touched, nullptr, rank, n, nullptr, status, counters, s);
+  return launch_scan<1>(tiles_touched, nullptr, rank, n, nullptr, nullptr, status, counters, s);
 }
-cudaError_t launch_scan_gather(const uint32_t* tiles_touched, const uint32_t* order, uint32_t* out, int n,
-                               uint32_t* chunk_first, unsigned long long* status, uint32_t* counters,
-                               cudaStream_t s) {
-  return launch_scan<2>(tiles_touched, order, out, n, chunk_first, status, counters, s);
+cudaError_t launch_scan_gather(const uint32_t* tiles_touched, const uint32_t* order, uint32_t* out, int n_cap,
+                               const unsigned long long* n_dev, uint32_t* chunk_first, unsigned long long* status,
+                               uint32_t* counters, cudaStream_t s) {
+  return launch_scan<2>(tiles_touched, order, out, n_cap, n_dev, chunk_first, status, counters, s);
 }
 
 }  // namespace h3dgs

@@ -53,6 +53,40 @@ __global__ void __launch_bounds__(256) sparse_adam_kernel(const AdamPack pk,
   T.param[off] = p;
 }
 
+// compact gradients: row i of every grad tensor belongs to store row rows[i]; the row count lives on the device
+__global__ void __launch_bounds__(256) sparse_adam_compact_kernel(const AdamPack pk,
+                                                                  const long long* __restrict__ rows,
+                                                                  const int* __restrict__ count,
+                                                                  const float* __restrict__ gate) {
+  const int total_w = pk.start[pk.n];
+  const long long U = *count;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x; gid < U * total_w; gid += stride) {
+    const long long k = gid / total_w;
+    if (gate != nullptr && gate[k] == 0.0f) continue;
+    const int e = (int)(gid - k * total_w);
+    int ti = 0;
+#pragma unroll
+    for (int i = 1; i < H3DGS_ADAM_MAX_TENSORS; ++i)
+      if (i < pk.n && e >= pk.start[i]) ti = i;
+    const H3dgsAdamTensor& T = pk.t[ti];
+    const int w = e - pk.start[ti];
+    const size_t off = (size_t)rows[k] * T.width + w;
+    const float g = T.grad[(size_t)k * T.width + w];
+    float m = T.exp_avg[off];
+    float v = T.exp_avg_sq[off];
+    float p = T.param[off];
+    m = __fmaf_rn(T.one_minus_beta1, g, __fmul_rn(m, T.beta1));
+    v = __fmaf_rn(__fmul_rn(T.one_minus_beta2, g), g, __fmul_rn(v, T.beta2));
+    const float inv_bc2 = 1.0f / T.bias_correction2_sqrt;
+    const float denom = __fadd_rn(__fmul_rn(sqrtf(v), inv_bc2), T.eps);
+    p = __fmaf_rn(-T.step_size, m / denom, p);
+    T.exp_avg[off] = m;
+    T.exp_avg_sq[off] = v;
+    T.param[off] = p;
+  }
+}
+
 struct RowPack {
   H3dgsRowTensor t[8];
   int start[9];   // prefix sums of widths
@@ -96,6 +130,27 @@ cudaError_t run_pack_rows(const H3dgsRowTensor* tensors, int n, const long long*
   ProfScope ps(K_ADAM, s);
   if (pack) pack_rows_kernel<true><<<(unsigned)blocks, 256, 0, s>>>(pk, rows, K, packed, scale);
   else pack_rows_kernel<false><<<(unsigned)blocks, 256, 0, s>>>(pk, rows, K, packed, scale);
+  return cudaGetLastError();
+}
+
+cudaError_t run_sparse_adam_compact(const H3dgsAdamTensor* tensors, int n, const long long* rows, const int* count,
+                                    int capacity, const float* gate, cudaStream_t s) {
+  AdamPack pk;
+  pk.n = n;
+  int acc = 0;
+  for (int i = 0; i < n; ++i) {
+    pk.t[i] = tensors[i];
+    pk.start[i] = acc;
+    acc += tensors[i].width;
+  }
+  for (int i = n; i <= H3DGS_ADAM_MAX_TENSORS; ++i) pk.start[i] = acc;
+  const long long work = (long long)capacity * acc;
+  if (work <= 0) return cudaSuccess;
+  // the grid covers the capacity; the kernel stops at the device-side row count
+  long long blocks = (work + 255) / 256;
+  if (blocks > 148 * 64) blocks = 148 * 64;
+  ProfScope ps(K_ADAM, s);
+  sparse_adam_compact_kernel<<<(unsigned)blocks, 256, 0, s>>>(pk, rows, count, gate);
   return cudaGetLastError();
 }
 

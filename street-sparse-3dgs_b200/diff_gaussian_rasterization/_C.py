@@ -138,9 +138,73 @@ class _Prezero:
 
 PREZERO = os.environ.get("H3DGS_PREZERO", "1") != "0"
 
-# sizes of the most recent forward (slots, visible slots, tile instances): the glue packages use the visible
-# count to compact per-slot results without a device->host round trip
-last_forward = {"P": 0, "V": 0, "R": 0}
+
+class _Aux:
+    """What a forward hands to its own backward besides the opaque buffers: the pre-zeroed gradient tensors (or
+    None) and the number of visible slots."""
+
+    def __init__(self, prezero, V):
+        self.prezero, self.V = prezero, V
+
+
+class SparseGradients:
+    """Compact gradients of one fused-cut render (H3dgsGrads.compact_*): ``rows`` int64 [capacity] holds the store
+    row of each compact row, ``count`` (device int32 [1]) how many are valid, ``grads`` maps a name to its
+    [capacity, ...] tensor and ``params`` the same name to the parameter tensor it belongs to.  Filled by the
+    backward of a render made with ``sparse=<this object>``; consumed by ``scene.OurAdam.Adam.step_sparse``."""
+
+    def __init__(self):
+        self.rows = self.count = None
+        self.grads, self.params = {}, {}
+        self.capacity = 0
+        self.ready = False
+
+    def dense(self, name):
+        """The equivalent dense [N, ...] gradient (tests / debugging; costs a sync)."""
+        g, p = self.grads[name], self.params[name]
+        U = int(self.count.item())
+        out = torch.zeros_like(p)
+        out.index_add_(0, self.rows[:U], g[:U].reshape((U,) + tuple(p.shape[1:])))
+        return out
+
+
+_row_maps = {}
+
+
+def _row_map(dev, rows):
+    """int32 [rows] scratch of the compact-gradient mode, all -1 between calls (the library restores it)."""
+    key = (dev.index, rows)
+    m = _row_maps.get(key)
+    if m is None:
+        for k in [k for k in _row_maps if k[0] == dev.index]:
+            del _row_maps[k]
+        m = _row_maps[key] = torch.full((rows,), -1, dtype=torch.int32, device=dev)
+    return m
+
+
+class _Counts:
+    """Pinned host words + CUDA event through which a forward's (num_rendered, num_visible) reach the host
+    (h3dgs_forward_begin).  A small free list: renders in flight on different streams each hold their own."""
+
+    _free = []
+
+    def __init__(self):
+        self.host = torch.zeros(2, dtype=torch.int64).pin_memory()
+        self.event = torch.cuda.Event()
+
+    @classmethod
+    def get(cls):
+        c = cls._free.pop() if cls._free else cls()
+        c.event.record()   # materialises the CUDA event; the library re-records it behind the copy
+        return c
+
+    def read(self):
+        """Wait for the copy alone (the GPU keeps working on the depth sort) and return (R, V)."""
+        self.event.synchronize()
+        R, V = int(self.host[0]), int(self.host[1])
+        _Counts._free.append(self)
+        return R, V
+
 
 
 def rasterize_gaussians_ex(bg, indices, parent_indices, ts, kids, means3D, colors, opacity, scales,
@@ -156,19 +220,22 @@ def rasterize_gaussians_ex(bg, indices, parent_indices, ts, kids, means3D, color
                            rotations, scale_modifier, cov3D_precomp, viewmatrix, projmatrix, tan_fovx,
                            tan_fovy, H, W, sh, degree, campos, skyboxnum, sh_rest, acts)
     P = g.P
-    out_color = torch.empty((NUM_CHANNELS, H, W), dtype=torch.float32, device=dev)
-    out_invdepth = torch.empty((1 if do_depth else 0, H, W), dtype=torch.float32, device=dev)
     radii = torch.empty((P,), dtype=torch.int32, device=dev)
     geom = torch.empty((L.h3dgs_geom_bytes(P),), dtype=torch.uint8, device=dev)
-    img = torch.empty((L.h3dgs_image_bytes(W, H),), dtype=torch.uint8, device=dev)
     stream = nat.stream_handle()
-    R, V = ctypes.c_int64(0), ctypes.c_int64(0)
-    nat.check(L.h3dgs_forward_preprocess(ctypes.byref(view), ctypes.byref(g), nat.ptr(radii), nat.ptr(geom),
-                                         geom.numel(), ctypes.byref(R), ctypes.byref(V), int(bool(debug)), stream),
-              "h3dgs_forward_preprocess")
-    R, V = int(R.value), int(V.value)
-    last_forward.update(P=P, V=V, R=R)
-    binning = torch.empty((L.h3dgs_binning_bytes(R, V, W, H) if R > 0 else 0,), dtype=torch.uint8, device=dev)
+    counts = _Counts.get()
+    nat.check(L.h3dgs_forward_begin(ctypes.byref(view), ctypes.byref(g), nat.ptr(radii), nat.ptr(geom),
+                                    geom.numel(), counts.host.data_ptr(), counts.event.cuda_event,
+                                    int(bool(debug)), stream), "h3dgs_forward_begin")
+    # everything that does not need R is allocated while the preprocess kernels run; then wait for the counts
+    # alone -- the depth sort of the visible slots is already queued behind them
+    img = torch.empty((L.h3dgs_image_bytes(W, H),), dtype=torch.uint8, device=dev)
+    out_color = torch.empty((NUM_CHANNELS, H, W), dtype=torch.float32, device=dev)
+    out_invdepth = torch.empty((1 if do_depth else 0, H, W), dtype=torch.float32, device=dev)
+    R, V = counts.read()
+    if R >= (1 << 30):
+        raise nat.H3dgsError("more than 2^30 tile instances")
+    binning = torch.empty((L.h3dgs_binning_bytes(R, W, H) if R > 0 else 0,), dtype=torch.uint8, device=dev)
     pre, fork = None, None
     if prezero_means2D_rows is not None and prezero_means2D_rows >= 0 and PREZERO and not _null(indices) \
             and R > 0 and P > 0 and not _arena.enabled():
@@ -177,15 +244,15 @@ def rasterize_gaussians_ex(bg, indices, parent_indices, ts, kids, means3D, color
                                                   rotations, cov3D_precomp), prezero_means2D_rows, P)
         fork = torch.cuda.Event()
         fork.record()   # creates the CUDA event; the library re-records it in front of the blend kernel
-    nat.check(L.h3dgs_forward_render(ctypes.byref(view), ctypes.byref(g), nat.ptr(geom), nat.ptr(binning),
+    nat.check(L.h3dgs_forward_finish(ctypes.byref(view), ctypes.byref(g), nat.ptr(geom), nat.ptr(binning),
                                      binning.numel(), nat.ptr(img), R, V, nat.ptr(out_color),
                                      nat.ptr(out_invdepth), int(bool(debug)), stream,
                                      fork.cuda_event if fork is not None else None),
-              "h3dgs_forward_render")
+              "h3dgs_forward_finish")
     if pre is not None:
         pre.fill(dev, fork, P)
     if prezero_means2D_rows is not None:
-        return R, out_color, radii, geom, binning, img, out_invdepth, pre
+        return R, out_color, radii, geom, binning, img, out_invdepth, _Aux(pre, V)
     return R, out_color, radii, geom, binning, img, out_invdepth
 
 
@@ -291,9 +358,11 @@ def rasterize_gaussians_backward_ex(bg, indices, parent_indices, ts, kids, means
                                     opacities, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,
                                     projmatrix, tan_fovx, tan_fovy, dL_dout_color, dL_dout_invdepth, sh,
                                     degree, campos, geomBuffer, R, binningBuffer, imageBuffer, debug,
-                                    skyboxnum=0, sh_rest=None, acts=None, prezero=None):
+                                    skyboxnum=0, sh_rest=None, acts=None, prezero=None, sparse=None, num_visible=0):
     """With ``sh_rest`` the returned dL_dsh is the pair (dL_dfeatures_dc, dL_dfeatures_rest).  ``prezero``: the
-    gradient tensors the forward allocated and zero-filled (``_Prezero``); dL_dmeans2D then has its rows."""
+    gradient tensors the forward allocated and zero-filled (``_Prezero``); dL_dmeans2D then has its rows.
+    ``sparse`` (a ``SparseGradients``, fused-cut mode): the per-store-row gradients are produced in compact form
+    into it -- no N-row tensors exist -- and the returned per-row gradients are None."""
     L = nat.lib()
     dev = means3D.device
     H, W = dL_dout_color.size(1), dL_dout_color.size(2)
@@ -306,6 +375,11 @@ def rasterize_gaussians_backward_ex(bg, indices, parent_indices, ts, kids, means
     # per-store-row gradients; only those of inputs that exist are materialised, the others come back empty
     shapes = _grad_shapes(rows, M, sh, sh_rest, colors, scales, rotations, cov3D_precomp)
     fused = not _null(indices)
+    if sparse is not None:
+        if not fused:
+            raise RuntimeError("sparse gradients need a hierarchy-cut render (render_indices)")
+        return _backward_sparse(L, dev, view, g, shapes, sparse, num_visible, radii, geomBuffer, binningBuffer,
+                                imageBuffer, R, dL_dout_color, dL_dout_invdepth, debug, split)
     if prezero is not None and not (fused and P > 0 and R > 0 and prezero.done is not None):
         prezero = None
     dL_dmeans2D = prezero.means2D if prezero is not None else torch.empty((P, 3), **opts)
@@ -343,6 +417,32 @@ def rasterize_gaussians_backward_ex(bg, indices, parent_indices, ts, kids, means
     if split:
         dL_dsh = (dL_dsh, dL_dsh_rest)
     return dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drot
+
+
+def _backward_sparse(L, dev, view, g, shapes, sparse, V, radii, geomBuffer, binningBuffer, imageBuffer, R,
+                     dL_dout_color, dL_dout_invdepth, debug, split):
+    P, rows = g.P, g.store_rows
+    opts = dict(dtype=torch.float32, device=dev)
+    cap = max(2 * int(V), 1)   # a visible slot adds into at most two store rows (child, parent)
+    t = {k: torch.empty((cap,) + tuple(v[1:]), **opts) for k, v in shapes.items() if v is not None}
+    sparse.rows = torch.empty((cap,), dtype=torch.int64, device=dev)
+    sparse.count = torch.empty((1,), dtype=torch.int32, device=dev)
+    sparse.capacity = cap
+    sparse.grads = t
+    dL_dmeans2D = torch.empty((P, 3), **opts)
+    grads = nat.Grads(nat.ptr(dL_dmeans2D), nat.ptr(t["means3D"]), nat.ptr(t.get("sh")), nat.ptr(t.get("colors")),
+                      nat.ptr(t["opacity"]), nat.ptr(t.get("scales")), nat.ptr(t.get("rot")), nat.ptr(t.get("cov3D")),
+                      nat.ptr(t.get("sh_rest")), None, 0,
+                      sparse.rows.data_ptr(), sparse.count.data_ptr(), _row_map(dev, rows).data_ptr(), cap)
+    ws = torch.empty((L.h3dgs_backward_workspace_bytes(P),), dtype=torch.uint8, device=dev)
+    dcol = nat.as_f32(dL_dout_color, "dL_dout_color")
+    ddep = nat.as_f32(dL_dout_invdepth, "dL_dout_invdepth")
+    nat.check(L.h3dgs_backward(ctypes.byref(view), ctypes.byref(g), nat.ptr(radii), nat.ptr(geomBuffer),
+                               nat.ptr(binningBuffer), nat.ptr(imageBuffer), int(R), nat.ptr(dcol), nat.ptr(ddep),
+                               ctypes.byref(grads), nat.ptr(ws), ws.numel(), int(bool(debug)), nat.stream_handle()),
+              "h3dgs_backward")
+    sparse.ready = True
+    return dL_dmeans2D, None, None, None, None, (None, None) if split else None, None, None
 
 
 def rasterize_gaussians_backward(bg, indices, parent_indices, ts, kids, means3D, radii, colors, opacities,

@@ -9,46 +9,64 @@ import torch
 import torch.nn as nn
 
 from . import _C
+from ._C import SparseGradients  # noqa: F401
+
+
+def _with_count(out):
+    """(color, radii, invdepth) as the reference returns them; the number of visible slots, which the forward knows
+    anyway, rides on ``radii.num_visible`` so that callers can compact per-slot results without a device->host
+    round trip (``radii[radii > 0]`` in the reference's render glue blocks on the GPU)."""
+    color, radii, invdepth, num_visible = out
+    radii.num_visible = num_visible
+    return color, radii, invdepth
 
 
 def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
                         raster_settings):
-    return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
-                                     cov3Ds_precomp, raster_settings, 0)
+    return _with_count(_RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
+                                                 cov3Ds_precomp, raster_settings, 0, None))
 
 
 def rasterize_gaussians_fused(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
-                              cov3Ds_precomp, raster_settings, skybox_points):
+                              cov3Ds_precomp, raster_settings, skybox_points, sparse=None):
     """Hierarchy-cut render with the child/parent interpolation of ``render_post`` done inside the
     kernels.  Attribute tensors are the whole model store; ``raster_settings.render_indices`` /
     ``parent_indices`` / ``interpolation_weights`` select and blend rows; the last ``skybox_points``
-    store rows are appended un-interpolated.  ``means2D`` has one row per rendered slot."""
-    return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
-                                     cov3Ds_precomp, raster_settings, int(skybox_points))
+    store rows are appended un-interpolated.  ``means2D`` has one row per rendered slot.
+    ``sparse`` (a ``SparseGradients``): the backward leaves the store-row gradients there in compact form instead
+    of returning N-row tensors (the parameters' ``.grad`` stay untouched)."""
+    return _with_count(_RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
+                                                 cov3Ds_precomp, raster_settings, int(skybox_points), sparse))
 
 
 def rasterize_gaussians_raw(xyz, means2D, features_dc, features_rest, opacity_raw, scaling_raw, rotation_raw,
-                            raster_settings, skybox_points, activations):
+                            raster_settings, skybox_points, activations, sparse=None):
     """``rasterize_gaussians_fused`` on the RAW parameter store of a reference ``GaussianModel``
     (scene/gaussian_model.py:121-145): the kernels apply ``activations`` = (scale, rotation, opacity) codes
     (``h3dgs_native.ACT_*``) and the dc/rest concatenation to the rows they gather instead of torch
     activating all N rows per render; gradients come back for the raw parameters."""
-    return _RasterizeGaussiansRaw.apply(xyz, means2D, features_dc, features_rest, opacity_raw, scaling_raw,
-                                        rotation_raw, raster_settings, int(skybox_points), tuple(activations))
+    return _with_count(_RasterizeGaussiansRaw.apply(xyz, means2D, features_dc, features_rest, opacity_raw,
+                                                    scaling_raw, rotation_raw, raster_settings, int(skybox_points),
+                                                    tuple(activations), sparse))
 
 
 class _RasterizeGaussiansRaw(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, xyz, means2D, f_dc, f_rest, opacity, scaling, rotation, raster_settings, skyboxnum, acts):
+    def forward(ctx, xyz, means2D, f_dc, f_rest, opacity, scaling, rotation, raster_settings, skyboxnum, acts,
+                sparse=None):
         rs = raster_settings
         e = torch.Tensor([])
         args = (rs.bg, rs.render_indices, rs.parent_indices, rs.interpolation_weights, rs.num_node_kids,
                 xyz, e, opacity, scaling, rotation, rs.scale_modifier, e, rs.viewmatrix, rs.projmatrix,
                 rs.tanfovx, rs.tanfovy, rs.image_height, rs.image_width, f_dc, rs.sh_degree, rs.campos,
                 rs.prefiltered, rs.debug, rs.do_depth)
-        num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer, invdepths, ctx.prezero = \
+        num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer, invdepths, ctx.aux = \
             _C.rasterize_gaussians_ex(*args, skyboxnum, f_rest, acts,
-                                      means2D.size(0) if any(ctx.needs_input_grad) else -1)
+                                      means2D.size(0) if (any(ctx.needs_input_grad) and sparse is None) else -1)
+        ctx.sparse = sparse
+        if sparse is not None:
+            sparse.params = {"means3D": xyz, "sh": f_dc, "sh_rest": f_rest, "opacity": opacity, "scales": scaling,
+                             "rot": rotation}
         ctx.raster_settings = rs
         ctx.num_rendered = num_rendered
         ctx.skyboxnum = skyboxnum
@@ -57,10 +75,10 @@ class _RasterizeGaussiansRaw(torch.autograd.Function):
         ctx.save_for_backward(xyz, f_dc, f_rest, opacity, scaling, rotation, radii, geomBuffer, binningBuffer,
                               imgBuffer)
         ctx.mark_non_differentiable(radii)
-        return color, radii, invdepths
+        return color, radii, invdepths, ctx.aux.V
 
     @staticmethod
-    def backward(ctx, grad_out_color, _, grad_out_depth):
+    def backward(ctx, grad_out_color, _, grad_out_depth, _v=None):
         rs = ctx.raster_settings
         xyz, f_dc, f_rest, opacity, scaling, rotation, radii, geomBuffer, binningBuffer, imgBuffer = ctx.saved_tensors
         if grad_out_depth is None:
@@ -70,9 +88,9 @@ class _RasterizeGaussiansRaw(torch.autograd.Function):
                 xyz, radii, e, opacity, scaling, rotation, rs.scale_modifier, e, rs.viewmatrix, rs.projmatrix,
                 rs.tanfovx, rs.tanfovy, grad_out_color, grad_out_depth, f_dc, rs.sh_degree, rs.campos,
                 geomBuffer, ctx.num_rendered, binningBuffer, imgBuffer, rs.debug)
-        prezero, ctx.prezero = ctx.prezero, None   # a second backward through this node allocates afresh
+        prezero, ctx.aux.prezero = ctx.aux.prezero, None   # a second backward through this node allocates afresh
         (grad_means2D, _gc, grad_opacity, grad_xyz, _gcov, grad_sh, grad_scaling, grad_rotation) = \
-            _C.rasterize_gaussians_backward_ex(*args, ctx.skyboxnum, f_rest, ctx.acts, prezero)
+            _C.rasterize_gaussians_backward_ex(*args, ctx.skyboxnum, f_rest, ctx.acts, prezero, ctx.sparse, ctx.aux.V)
         grad_dc, grad_rest = grad_sh
         if grad_means2D.size(0) != ctx.means2D_rows:
             full = torch.zeros((ctx.means2D_rows, 3), dtype=grad_means2D.dtype, device=grad_means2D.device)
@@ -80,22 +98,26 @@ class _RasterizeGaussiansRaw(torch.autograd.Function):
             full[:n] = grad_means2D[:n]
             grad_means2D = full
         return (grad_xyz, grad_means2D, grad_dc, grad_rest, grad_opacity, grad_scaling, grad_rotation,
-                None, None, None)
+                None, None, None, None)
 
 
 class _RasterizeGaussians(torch.autograd.Function):
     @staticmethod
     def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
-                raster_settings, skyboxnum):
+                raster_settings, skyboxnum, sparse=None):
         rs = raster_settings
         # argument order of the C++ entry point (HR/rasterize_points.h:18-43)
         args = (rs.bg, rs.render_indices, rs.parent_indices, rs.interpolation_weights, rs.num_node_kids,
                 means3D, colors_precomp, opacities, scales, rotations, rs.scale_modifier, cov3Ds_precomp,
                 rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, rs.image_height, rs.image_width, sh,
                 rs.sh_degree, rs.campos, rs.prefiltered, rs.debug, rs.do_depth)
-        num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer, invdepths, ctx.prezero = \
+        num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer, invdepths, ctx.aux = \
             _C.rasterize_gaussians_ex(*args, skyboxnum, None, None,
-                                      means2D.size(0) if any(ctx.needs_input_grad) else -1)
+                                      means2D.size(0) if (any(ctx.needs_input_grad) and sparse is None) else -1)
+        ctx.sparse = sparse
+        if sparse is not None:
+            sparse.params = {"means3D": means3D, "sh": sh, "colors": colors_precomp, "opacity": opacities,
+                             "scales": scales, "rot": rotations, "cov3D": cov3Ds_precomp}
         ctx.raster_settings = rs
         ctx.num_rendered = num_rendered
         ctx.skyboxnum = skyboxnum
@@ -103,10 +125,10 @@ class _RasterizeGaussians(torch.autograd.Function):
         ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh,
                               opacities, geomBuffer, binningBuffer, imgBuffer)
         ctx.mark_non_differentiable(radii)
-        return color, radii, invdepths
+        return color, radii, invdepths, ctx.aux.V
 
     @staticmethod
-    def backward(ctx, grad_out_color, _, grad_out_depth):
+    def backward(ctx, grad_out_color, _, grad_out_depth, _v=None):
         rs = ctx.raster_settings
         (colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, opacities, geomBuffer,
          binningBuffer, imgBuffer) = ctx.saved_tensors
@@ -117,10 +139,10 @@ class _RasterizeGaussians(torch.autograd.Function):
                 cov3Ds_precomp, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, grad_out_color,
                 grad_out_depth, sh, rs.sh_degree, rs.campos, geomBuffer, ctx.num_rendered, binningBuffer,
                 imgBuffer, rs.debug)
-        prezero, ctx.prezero = ctx.prezero, None   # a second backward through this node allocates afresh
+        prezero, ctx.aux.prezero = ctx.aux.prezero, None   # a second backward through this node allocates afresh
         (grad_means2D, grad_colors_precomp, grad_opacities, grad_means3D, grad_cov3Ds_precomp, grad_sh,
          grad_scales, grad_rotations) = _C.rasterize_gaussians_backward_ex(*args, ctx.skyboxnum, None, None,
-                                                                           prezero)
+                                                                           prezero, ctx.sparse, ctx.aux.V)
 
         if grad_means2D.size(0) != ctx.means2D_rows:
             # index mode called with a store-sized means2D: slots map to its leading rows
@@ -130,11 +152,11 @@ class _RasterizeGaussians(torch.autograd.Function):
             grad_means2D = full
 
         def opt(g, x):
-            return g if x.numel() != 0 else None
+            return g if (g is not None and x.numel() != 0) else None
 
         return (grad_means3D, grad_means2D, opt(grad_sh, sh), opt(grad_colors_precomp, colors_precomp),
                 grad_opacities, opt(grad_scales, scales), opt(grad_rotations, rotations),
-                opt(grad_cov3Ds_precomp, cov3Ds_precomp), None, None)
+                opt(grad_cov3Ds_precomp, cov3Ds_precomp), None, None, None)
 
 
 class GaussianRasterizationSettings(NamedTuple):

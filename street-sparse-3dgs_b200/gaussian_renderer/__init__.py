@@ -126,14 +126,14 @@ def _settings(viewpoint_camera, pc, bg_color, scaling_modifier, debug, do_depth,
 
 
 def _visible(radii):
-    """(mask, indices) of the slots with radii > 0.  The forward already knows how many there are, so the
-    indices come from ``nonzero_static`` -- no device->host sync, the host keeps queueing the loss and the
-    backward while the blend kernel runs (the reference's ``radii[radii > 0]`` blocks on the GPU)."""
-    from diff_gaussian_rasterization import _C
+    """(mask, indices) of the slots with radii > 0.  The forward already knows how many there are
+    (``radii.num_visible``, set by the rasterizer wrappers), so the indices come from ``nonzero_static`` -- no
+    device->host sync, the host keeps queueing the loss and the backward while the blend kernel runs (the
+    reference's ``radii[radii > 0]`` blocks on the GPU)."""
     mask = radii > 0
-    info = _C.last_forward
-    if info["P"] == radii.numel():
-        return mask, torch.nonzero_static(mask, size=info["V"]).flatten()
+    n = getattr(radii, "num_visible", None)
+    if n is not None:
+        return mask, torch.nonzero_static(mask, size=int(n)).flatten()
     return mask, mask.nonzero().flatten()
 
 
@@ -142,7 +142,7 @@ def _empty(dtype):
 
 
 def _rasterize(settings, means3D, means2D, opacity, shs, colors_precomp, scales, rotations, cov3D_precomp,
-               skybox_points=None):
+               skybox_points=None, sparse=None):
     e = torch.Tensor([])
     if skybox_points is None:
         return GaussianRasterizer(raster_settings=settings)(
@@ -151,7 +151,7 @@ def _rasterize(settings, means3D, means2D, opacity, shs, colors_precomp, scales,
     return rasterize_gaussians_fused(
         means3D, means2D, e if shs is None else shs, e if colors_precomp is None else colors_precomp,
         opacity, e if scales is None else scales, e if rotations is None else rotations,
-        e if cov3D_precomp is None else cov3D_precomp, settings, skybox_points)
+        e if cov3D_precomp is None else cov3D_precomp, settings, skybox_points, sparse)
 
 
 def _as_index(t):
@@ -214,9 +214,21 @@ def render(viewpoint_camera, pc, pipe, bg_color: torch.Tensor, scaling_modifier=
 def render_post(viewpoint_camera, pc, pipe, bg_color: torch.Tensor, scaling_modifier=1.0, override_color=None,
                 render_indices=torch.Tensor([]).int(), parent_indices=torch.Tensor([]).int(),
                 interpolation_weights=torch.Tensor([]).float(), num_node_kids=torch.Tensor([]).int(),
-                interp_python=True, use_trained_exp=False, do_depth=False):
-    """Render the scene from a hierarchy cut (gaussian_renderer/__init__.py:138-304)."""
-    screenspace_points = _screenspace_points(pc)
+                interp_python=True, use_trained_exp=False, do_depth=False, sparse_grads=None):
+    """Render the scene from a hierarchy cut (gaussian_renderer/__init__.py:138-304).
+
+    ``sparse_grads`` (extension; a ``diff_gaussian_rasterization.SparseGradients``): the backward leaves the
+    gradients of the store parameters there in compact form -- one row per store row the render touched -- instead of
+    materialising N-row ``.grad`` tensors (4 GB of zero fill per step on a 17 M-row store, plus the optimizer's scan
+    for the touched rows).  ``scene.OurAdam.Adam.step_sparse`` consumes it.  ``viewspace_points`` then has one row
+    per rendered slot instead of one per store row."""
+    if sparse_grads is not None and not (render_indices.size(0) != 0 and interp_python):
+        raise RuntimeError("sparse_grads needs a hierarchy cut rendered with interp_python=True")
+    if sparse_grads is not None:
+        n_slots = render_indices.size(0) + int(pc.skybox_points)
+        screenspace_points = torch.zeros((n_slots, 3), dtype=pc.get_xyz.dtype, requires_grad=True, device="cuda")
+    else:
+        screenspace_points = _screenspace_points(pc)
     means2D = screenspace_points
     # Hierarchy cut with Python-style interpolation on a reference GaussianModel: hand the RAW parameters to
     # the kernels, which activate only the rows of the cut (the reference activates all N rows per render).
@@ -254,10 +266,10 @@ def render_post(viewpoint_camera, pc, pipe, bg_color: torch.Tensor, scaling_modi
     if raw is not None:
         (xyz, f_dc, f_rest, op_raw, sc_raw, rot_raw), acts = raw
         rendered_image, radii, depth_image = rasterize_gaussians_raw(xyz, means2D, f_dc, f_rest, op_raw, sc_raw,
-                                                                     rot_raw, settings, skybox, acts)
+                                                                     rot_raw, settings, skybox, acts, sparse_grads)
     else:
         rendered_image, radii, depth_image = _rasterize(settings, means3D, means2D, opacity, shs, colors_precomp,
-                                                        scales, rotations, cov3D_precomp, skybox)
+                                                        scales, rotations, cov3D_precomp, skybox, sparse_grads)
 
     if use_trained_exp and pc.pretrained_exposures:
         try:

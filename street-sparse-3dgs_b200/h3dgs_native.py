@@ -45,7 +45,9 @@ class Grads(Structure):
     _fields_ = [("dL_dmeans2D", c_void_p), ("dL_dmeans3D", c_void_p), ("dL_dsh", c_void_p),
                 ("dL_dcolors", c_void_p), ("dL_dopacity", c_void_p), ("dL_dscales", c_void_p),
                 ("dL_drotations", c_void_p), ("dL_dcov3D", c_void_p), ("dL_dsh_rest", c_void_p),
-                ("dirty_rows", c_void_p), ("rows_prezeroed", c_int32)]
+                ("dirty_rows", c_void_p), ("rows_prezeroed", c_int32),
+                ("compact_rows", c_void_p), ("compact_count", c_void_p), ("row_map", c_void_p),
+                ("compact_capacity", c_int32)]
 
 
 class RowTensor(Structure):
@@ -79,11 +81,11 @@ SIGNATURES = {
     "h3dgs_last_error": (c_char_p, []),
     "h3dgs_geom_bytes": (c_size_t, [c_int32]),
     "h3dgs_image_bytes": (c_size_t, [c_int32, c_int32]),
-    "h3dgs_binning_bytes": (c_size_t, [c_int64, c_int64, c_int32, c_int32]),
+    "h3dgs_binning_bytes": (c_size_t, [c_int64, c_int32, c_int32]),
     "h3dgs_backward_workspace_bytes": (c_size_t, [c_int32]),
-    "h3dgs_forward_preprocess": (c_int, [POINTER(View), POINTER(Gaussians), c_void_p, c_void_p, c_size_t,
-                                          POINTER(c_int64), POINTER(c_int64), c_int, c_void_p]),
-    "h3dgs_forward_render": (c_int, [POINTER(View), POINTER(Gaussians), c_void_p, c_void_p, c_size_t,
+    "h3dgs_forward_begin": (c_int, [POINTER(View), POINTER(Gaussians), c_void_p, c_void_p, c_size_t,
+                                     c_void_p, c_void_p, c_int, c_void_p]),
+    "h3dgs_forward_finish": (c_int, [POINTER(View), POINTER(Gaussians), c_void_p, c_void_p, c_size_t,
                                       c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
     "h3dgs_backward": (c_int, [POINTER(View), POINTER(Gaussians), c_void_p, c_void_p, c_void_p, c_void_p,
                                 c_int64, c_void_p, c_void_p, POINTER(Grads), c_void_p, c_size_t, c_int,
@@ -105,6 +107,7 @@ SIGNATURES = {
     "h3dgs_hier_write": (c_int, [c_char_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_void_p,
                                   c_void_p, c_void_p, c_void_p, c_int]),
     "h3dgs_sparse_adam": (c_int, [POINTER(AdamTensor), c_int32, c_void_p, c_int64, c_int64, c_void_p]),
+    "h3dgs_sparse_adam_compact": (c_int, [POINTER(AdamTensor), c_int32, c_void_p, c_void_p, c_int32, c_void_p, c_void_p]),
     "h3dgs_pack_rows": (c_int, [POINTER(RowTensor), c_int32, c_void_p, c_int64, c_void_p, c_void_p]),
     "h3dgs_unpack_rows": (c_int, [POINTER(RowTensor), c_int32, c_void_p, c_int64, c_void_p, c_float, c_void_p]),
     "h3dgs_ssim_forward": (c_int, [c_int32, c_int32, c_int32, c_void_p, c_void_p, c_void_p, POINTER(c_float), c_void_p,

@@ -48,6 +48,62 @@ class Adam(Optimizer):
             for s in state_values:
                 s['step'] = torch.tensor(float(s['step']))
 
+    def _update_terms(self, group, p):
+        """Advance the parameter's step count and return the host-side terms of the update
+        (scene/OurAdam.py:309-325: bias corrections in double precision on the host)."""
+        beta1, beta2 = group['betas']
+        state = self.state[p]
+        if len(state) == 0:
+            state['step'] = torch.tensor(0.)
+            state['exp_avg'] = torch.zeros_like(p, memory_format=torch.preserve_format)
+            state['exp_avg_sq'] = torch.zeros_like(p, memory_format=torch.preserve_format)
+        state['step'] += 1
+        step = state['step'].item()  # CPU tensor: no device sync
+        bias_correction1 = 1 - beta1 ** step
+        bias_correction2 = 1 - beta2 ** step
+        return state, group['lr'] / bias_correction1, math.sqrt(bias_correction2), beta1, beta2
+
+    @torch.no_grad()
+    def step_sparse(self, sparse_grads, gate="opacity"):
+        """One step from COMPACT gradients (``diff_gaussian_rasterization.SparseGradients``, filled by the backward
+        of ``render_post(..., sparse_grads=...)``): the rows the render touched are updated, every other row keeps
+        its parameter and (stale) moments -- what ``step(relevant)`` does with
+        ``relevant = (opacity.grad != 0).nonzero()`` (train_single.py:225-233), here without N-row gradient tensors
+        and without a host round trip: the row list and its length stay on the device.  ``gate``: name of the
+        compact gradient whose zero rows are skipped (the opacity gradient, as in the reference); None updates
+        every touched row."""
+        sg = sparse_grads
+        if sg is None or not sg.ready:
+            raise RuntimeError("step_sparse: the SparseGradients object has not been filled by a backward pass")
+        by_ptr = {sg.params[k].data_ptr(): k for k in sg.grads if k in sg.params and sg.params[k].numel()}
+        batch = []
+        for group in self.param_groups:
+            if group['amsgrad'] or group['maximize'] or group['weight_decay'] != 0 or group['capturable'] \
+                    or group['foreach']:
+                raise NotImplementedError("the fused sparse Adam implements the options the reference training uses")
+            for p in group['params']:
+                name = by_ptr.get(p.data_ptr())
+                if name is None:
+                    continue
+                if not p.is_cuda or p.dtype != torch.float32 or not p.is_contiguous():
+                    raise RuntimeError("fused sparse Adam needs contiguous float32 CUDA parameters (no CPU fallback)")
+                state, step_size, bc2_sqrt, beta1, beta2 = self._update_terms(group, p)
+                g = sg.grads[name]
+                width = p.numel() // max(p.size(0), 1)
+                batch.append(nat.AdamTensor(p.data_ptr(), g.data_ptr(), state['exp_avg'].data_ptr(),
+                                            state['exp_avg_sq'].data_ptr(), width, step_size, bc2_sqrt, beta1, beta2,
+                                            group['eps'], 1 - beta1, 1 - beta2))
+        if not batch:
+            return
+        gate_t = sg.grads.get(gate) if gate is not None else None
+        L = nat.lib()
+        for i in range(0, len(batch), nat.ADAM_MAX_TENSORS):
+            chunk = batch[i:i + nat.ADAM_MAX_TENSORS]
+            arr = (nat.AdamTensor * len(chunk))(*chunk)
+            nat.check(L.h3dgs_sparse_adam_compact(arr, len(chunk), sg.rows.data_ptr(), sg.count.data_ptr(),
+                                                  sg.capacity, nat.ptr(gate_t), nat.stream_handle()),
+                      "h3dgs_sparse_adam_compact")
+
     @torch.no_grad()
     def step(self, relevant, closure=None):
         """One optimisation step over the rows in ``relevant`` (1-D LongTensor of row indices; empty

@@ -35,7 +35,9 @@ def test_workspace_queries_are_sane():
     assert L.h3dgs_geom_bytes(0) > 0
     assert L.h3dgs_geom_bytes(2_000_000) > L.h3dgs_geom_bytes(1_000_000) >= 1_000_000 * (64 + 4 + 24)
     assert L.h3dgs_image_bytes(1920, 1080) >= 1920 * 1080 * 24
-    assert L.h3dgs_binning_bytes(1_000_000, 200_000, 1920, 1080) >= 20 * 1_000_000 + 20 * 200_000
+    assert L.h3dgs_binning_bytes(1_000_000, 1920, 1080) >= 20 * 1_000_000
+    # the depth sort of the visible slots is part of the geometry workspace (sized by P, before R is known)
+    assert L.h3dgs_geom_bytes(1_000_000) >= 1_000_000 * (64 + 4 + 24 + 20)
     assert L.h3dgs_backward_workspace_bytes(1000) >= 48 * 1000
     assert L.h3dgs_expand_workspace_bytes(1000) >= 8 * 1000
 
@@ -44,7 +46,7 @@ def test_usage_errors_are_reported_not_crashed():
     import ctypes
     import h3dgs_native as nat
     L = nat.lib()
-    rc = L.h3dgs_forward_preprocess(None, None, None, None, 0, None, None, 0, None)
+    rc = L.h3dgs_forward_begin(None, None, None, None, 0, None, None, 0, None)
     assert rc == -1 and b"null" in L.h3dgs_last_error()
     cnt = ctypes.c_int32(7)
     assert L.h3dgs_expand_to_size(-5, 1.0, None, None, None, None, None, None, None, 0, ctypes.byref(cnt), None) == -1

@@ -491,3 +491,83 @@ def test_tile_launch_orders_are_permutations():
         # heavy first: a later tile is never more than one bucket (a quarter octave, x 1.25) heavier than an earlier one
         running_min = torch.cummin(w.clamp(min=4), dim=0).values
         assert bool((w.clamp(min=4).double() <= running_min.double() * 1.26 + 1).all())
+
+
+@pytest.mark.parametrize("raw", [True, False])
+def test_sparse_gradients_match_dense_path(raw):
+    """render_post(sparse_grads=...) + Adam.step_sparse against the dense drop-in path (N-row .grad tensors,
+    relevant = opacity.grad != 0, Adam.step(relevant)): same gradients scattered to the same rows, same parameters
+    and moments after the optimizer step, untouched rows untouched, the scratch row map back to all -1."""
+    import diff_gaussian_rasterization as dgr
+    import gaussian_hierarchy
+    from gaussian_renderer import render_post
+    from scene.OurAdam import Adam
+    sky = 700
+    attrs = workload.build_scene(15, sky, 9, DEV)
+    cam = scenes.street_camera(800, 600, seed=3, device=DEV, yaw_deg=5.0, x=-12.0)
+    bg = torch.tensor([0.1, 0.0, 0.2], device=DEV)
+    n = attrs["means3D"].size(0)
+    g = torch.Generator().manual_seed(4)
+    dcol = (torch.randn(3, 600, 800, generator=g) / 480000).to(DEV)
+    ddep = (torch.randn(1, 600, 800, generator=g) / 480000).to(DEV)
+    make = (lambda: workload.HierModel(attrs, sky)) if raw else (lambda: workload.ActivatedModel(attrs, sky))
+    m_d, m_s = make(), make()
+    limit = workload.find_limit(gaussian_hierarchy._C, m_d, cam, 12000, DEV)
+
+    def run(model, sparse):
+        cut = workload.Cut(n, DEV)
+        cut.compute(gaussian_hierarchy._C, model, cam, limit)
+        K = cut.count
+        out = render_post(cam, model, scenes.Pipe, bg, render_indices=cut.render_indices[:K],
+                          parent_indices=cut.parent_indices[:K], interpolation_weights=cut.interpolation_weights,
+                          num_node_kids=cut.num_siblings, do_depth=True, sparse_grads=sparse)
+        ((out["render"] * dcol).sum() + (out["depth"] * ddep).sum()).backward()
+        return out, K
+
+    out_d, K = run(m_d, None)
+    sg = dgr.SparseGradients()
+    out_s, _ = run(m_s, sg)
+    torch.cuda.synchronize()
+    assert torch.equal(bits(out_d["render"]), bits(out_s["render"]))
+    assert sg.ready and all(p.grad is None for p in m_s.parameters()), "sparse mode must not materialise .grad"
+    U = int(sg.count.item())
+    assert 0 < U <= sg.capacity
+    rows = sg.rows[:U]
+    assert rows.unique().numel() == U, "a store row got two compact rows"
+    assert bool((dgr._C._row_map(torch.device(DEV, torch.cuda.current_device()), n) == -1).all()), "row map not restored"
+    names = ["means3D", "sh", "sh_rest", "opacity", "scales", "rot"] if raw else ["means3D", "sh", "opacity", "scales", "rot"]
+    for name, p in zip(names, m_d.parameters()):
+        dense = sg.dense(name)
+        assert dense.shape == p.grad.shape
+        touched = torch.zeros(n, dtype=torch.bool, device=DEV)
+        touched[rows] = True
+        assert not bool(p.grad[~touched].any()), f"{name}: the dense path touched a row the compact list misses"
+        den = float(p.grad.abs().max())
+        assert float((dense - p.grad).abs().max()) <= 2e-4 * den, name   # float reduction order only
+    # slots map to the leading rows of the dense path's store-sized screen-space gradient
+    gs, gd = out_s["viewspace_points"].grad, out_d["viewspace_points"].grad
+    assert gs.shape == (K + sky, 3) and float((gs - gd[:K + sky]).abs().max()) <= 2e-4 * float(gd.abs().max())
+
+    # optimizer: Adam.step(relevant) on the dense gradients vs Adam.step_sparse on the compact ones
+    lrs = [1.6e-4, 2.5e-3, 1.25e-4, 0.05, 5e-3, 1e-3][:len(names)]
+    opt_d = Adam([{"params": [p], "lr": lr} for p, lr in zip(m_d.parameters(), lrs)], lr=0.0, eps=1e-15)
+    opt_s = Adam([{"params": [p], "lr": lr} for p, lr in zip(m_s.parameters(), lrs)], lr=0.0, eps=1e-15)
+    before = [p.detach().clone() for p in m_s.parameters()]
+    op_grad = m_d.parameters()[names.index("opacity")].grad
+    relevant = (op_grad.flatten() != 0).nonzero().flatten().long()
+    opt_d.step(relevant)
+    opt_s.step_sparse(sg)
+    torch.cuda.synchronize()
+    moved = torch.zeros(n, dtype=torch.bool, device=DEV)
+    moved[relevant] = True
+    for name, pd, ps, b in zip(names, m_d.parameters(), m_s.parameters(), before):
+        assert torch.equal(ps.detach()[~moved], b[~moved]), f"{name}: a row outside `relevant` moved"
+        # Adam normalises the step: rows whose gradient is pure rounding noise can differ in sign, so compare the
+        # moments (linear in the gradient) tightly and the parameters by the size of a step
+        sd, ss = opt_d.state[pd], opt_s.state[ps]
+        assert float((sd["exp_avg"] - ss["exp_avg"]).abs().max()) <= 2e-4 * float(sd["exp_avg"].abs().max()), name
+        assert float(ss["step"]) == 1.0
+        lr = lrs[names.index(name)]
+        assert float((pd.detach() - ps.detach()).abs().max()) <= 2.0 * lr + 1e-12, name
+        frac_close = float(((pd.detach() - ps.detach()).abs() <= 1e-3 * lr).float().mean())
+        assert frac_close > 0.999, f"{name}: only {frac_close:.4f} of the entries agree"
