@@ -50,6 +50,8 @@ def parse():
                     help="e2e: compute each step's cut at the top of the step instead of one step ahead")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-raster-only", action="store_true")
+    ap.add_argument("--e2e-dropin", action="store_true",
+                    help="e2e (ours): time the unchanged train_post.py loop body (dense gradients) as the headline e2e")
     ap.add_argument("--no-profile", action="store_true")
     return ap.parse_args()
 
@@ -181,6 +183,12 @@ def main():
     if dp:
         import h3dgs_parallel as par
 
+    # ours: compact gradients (render_post(sparse_grads=...)): the per-row gradients of a render are produced for the
+    # rows of its cut only; `value_dropin` below is the same step with the dense N-row .grad tensors of the drop-in API
+    res_mode = {"sparse": args.impl == "ours" and not dp}
+    if args.impl == "ours":
+        import diff_gaussian_rasterization as dgr_mod
+
     def resident_step(i, collect=False):
         # camera-batch data parallel: every rank takes a different camera of the same chunk
         k = (i * world + rank) % len(cams) if dp else i % len(cams)
@@ -188,9 +196,20 @@ def main():
         cut = cuts[k]
         for p in model.parameters():
             p.grad = None
-        out = render_post(c, model, bg, cut, do_depth=True)
+        sg = dgr_mod.SparseGradients() if res_mode["sparse"] else None
+        if sg is not None:
+            out = render_post(c, model, bg, cut, do_depth=True, sparse_grads=sg)
+        else:
+            out = render_post(c, model, bg, cut, do_depth=True)
         loss = (out["render"] * dcol).sum() + (out["depth"] * ddep).sum()
         loss.backward()
+        if collect and sg is not None:
+            stats.setdefault("P", []).append(cut.count + args.skybox)
+            stats.setdefault("V", []).append(int(out["visibility_filter"].sum()))
+            U = int(sg.count.item())
+            stats.setdefault("compact_rows", []).append(U)
+            stats.setdefault("grad_rows", []).append(int((sg.grads["opacity"][:U] != 0).sum()))
+            return
         if dp:   # the exchange step: sum the gradients of the rows any rank's cut touched (NCCL over NVLink)
             par.allreduce_sparse_rows([p.grad for p in model.parameters()],
                                       model.parameters()[2].grad.flatten() != 0)
@@ -241,6 +260,17 @@ def main():
     gpu_launches = int(timed.launches) if args.impl == "ours" else None
     ms_per_step = ms_total / args.steps
     value = world * 1000.0 / ms_per_step if args.mode == "chunks" else 1000.0 / ms_per_step * world
+    value_dropin = None
+    if res_mode["sparse"]:
+        res_mode["sparse"] = False
+        ms_d, _ = timed(resident_step, args.steps, max(args.warmup, 3))
+        value_dropin = {"value": world * 1000.0 / (ms_d / args.steps), "unit": "renders/s", "ms_per_step": ms_d / args.steps,
+                        "what": "the same step with the dense N-row .grad tensors of the drop-in API (zero fill of "
+                                "236 B x store rows per backward, overlapped with the forward blend)"}
+        res_mode["sparse"] = True
+        for p in model.parameters():
+            p.grad = None
+        torch.cuda.empty_cache()
 
     # workload statistics (untimed): P, V, R per camera
     for i in range(len(cams)):
@@ -294,6 +324,9 @@ def main():
             "scan": 8 * Pm + 8 * Vm,
             "memset": 236 * n_store,
         }
+        if res_mode["sparse"]:   # compact gradients: no N-row fill; what is left are the per-slot accumulators and sort counters
+            alg["memset"] = 48 * Pm
+            alg["preprocess_bwd"] += 2 * 236 * avg_or(stats.get("compact_rows"), 0)
         # instrumented pass (untimed): how far every evaluated (pixel, entry) pair gets -> FLOP of the blend kernels
         # by the contract of SURVEY.md 8(d) (interp + depth variants): forward 11 / 30 / 32 / 49 FLOP for a pair
         # rejected at power > 0 / at alpha < 1/255 / at the T test / blended; backward 11 / 30 / 100
@@ -356,7 +389,7 @@ def main():
         torch.cuda.empty_cache()
 
     # ---------------- end-to-end measurement (host inputs every step) ----------------
-    e2e = None
+    e2e, e2e_dropin = None, None
     if not args.no_e2e:
         del model
         torch.cuda.empty_cache()
@@ -444,6 +477,16 @@ def main():
             def loss_fn(image, gt):
                 return loss_reference.l1_ssim_loss(image, gt, 0.2)[0]
 
+        # ours: compact gradients (render_post(sparse_grads=...) + Adam.step_sparse: no N-row gradient tensors, no
+        # zero fill, no row scan) and the loss value read back through pinned memory one step late, so the host never
+        # waits for the step it has just queued; --e2e-dropin times the unchanged train_post.py loop body instead
+        # (dense .grad tensors, relevant = opacity.grad != 0, loss.item()).  The reference arm is always the latter.
+        mode = {"sparse": args.impl == "ours" and not dp}
+        loss_host = [torch.zeros(1).pin_memory() for _ in range(2)]
+        loss_ready = [torch.cuda.Event() for _ in range(2)]
+        if args.impl == "ours":
+            import diff_gaussian_rasterization as dgr
+
         def e2e_step(i):
             step_i = i
             k = cam_index(i)
@@ -467,7 +510,11 @@ def main():
                 cut.compute(gh, hm, c, limit, campos_host=cam_host[i % len(cams)][32:35])
             for p in hm.parameters():
                 p.grad = None
-            out = render_post(c, hm, bg, this_cut, do_depth=False)
+            sg = dgr.SparseGradients() if mode["sparse"] else None
+            if sg is not None:
+                out = render_post(c, hm, bg, this_cut, do_depth=False, sparse_grads=sg)
+            else:
+                out = render_post(c, hm, bg, this_cut, do_depth=False)
             torch.cuda.current_stream().wait_event(ready[n % 2])
             loss = loss_fn(out["render"], gt_dev[n % 2])
             loss.backward()
@@ -475,6 +522,16 @@ def main():
             if cut_ahead:
                 cut_free[b].record()
                 launch_cut(step_i + 1)
+            if sg is not None:
+                opt.step_sparse(sg)
+                # device -> host read of this step's loss: asynchronous copy into pinned memory, picked up one step
+                # later (the last one after the timed region's final synchronize)
+                loss_host[n % 2].copy_(loss.detach().reshape(1), non_blocking=True)
+                loss_ready[n % 2].record()
+                if n > 0:
+                    loss_ready[(n - 1) % 2].synchronize()
+                    losses.append(float(loss_host[(n - 1) % 2]))
+                return
             if dp:
                 relevant = par.allreduce_sparse_rows([p.grad for p in hm.parameters()],
                                                      hm._opacity.grad.flatten() != 0)
@@ -483,13 +540,27 @@ def main():
             opt.step(relevant)
             losses.append(loss.item())
 
+        e2e_dropin = None
+        if mode["sparse"]:
+            mode["sparse"] = False
+            ms_d, _ = timed(e2e_step, args.steps, max(args.warmup, 3))
+            e2e_dropin = {"value": world * 1000.0 / (ms_d / args.steps), "unit": "renders/s",
+                          "ms_per_step": ms_d / args.steps,
+                          "step": "the unchanged train_post.py loop body on the drop-in packages: dense N-row .grad "
+                                  "tensors, relevant = (opacity.grad != 0).nonzero(), Adam.step(relevant), loss.item()"}
+            mode["sparse"] = not args.e2e_dropin
+            for p in hm.parameters():
+                p.grad = None
+            torch.cuda.empty_cache()
         ms_e2e, clocks_e2e = timed(e2e_step, args.steps, max(args.warmup, 3))
         e2e_value = world * 1000.0 / (ms_e2e / args.steps)
         e2e = {"value": e2e_value, "unit": "renders/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
                "ms_per_step": ms_e2e / args.steps, "clocks": clocks_e2e,
                "step": "cut + render_post + " + ("0.8 L1 + 0.2 (1 - SSIM)" if args.loss == "l1ssim" else "L1") +
-                       " + backward + sparse Adam + loss.item(); ground-truth image prefetched "
-                       "one step ahead on a copy stream (one 24.9 MB H2D per step)" +
+                       " + backward + sparse Adam + loss read-back" +
+                       (" (compact gradients: render_post(sparse_grads=...) + Adam.step_sparse; the loss value crosses "
+                        "through pinned memory and is read one step late)" if mode["sparse"] else " (loss.item())") +
+                       "; ground-truth image prefetched one step ahead on a copy stream (one 24.9 MB H2D per step)" +
                        ("; the cut of the next step runs on a side stream under this step's backward"
                         if cut_ahead else "")}
 
@@ -521,12 +592,14 @@ def main():
                                     "one chunk replicated, one camera per rank, NCCL all-reduce of the union of touched gradient rows"},
             "clocks": clocks, "e2e": e2e, "gpu_launches": gpu_launches, "roofline": roofline,
             "kernels": kernels, "cpu_baseline": cpu_baseline, "rasterizer_only": raster_only,
+            "e2e_dropin": e2e_dropin, "value_dropin": value_dropin,
             # run statistics of the workload (measured, not configuration): slots, visible slots, tile instances, ...
             "workload_stats": {
                 "P_mean": avg(stats.get("P")), "V_mean": avg(stats.get("V")), "R_mean": avg(stats.get("R")),
                 "mean_tile_list_length": (avg(stats["R"]) / (((W + 15) // 16) * ((H + 15) // 16))) if stats.get("R") else None,
                 "mean_last_contributor_per_pixel": avg(stats.get("n_contrib")),
                 "rows_with_gradient_mean": avg(stats.get("grad_rows")),
+                "compact_rows_mean": avg(stats.get("compact_rows")),
                 "pairs_per_render": stats.get("pairs")},
             "measured_peaks": measured,
         }
@@ -536,6 +609,10 @@ def main():
     if world > 1:
         dist.destroy_process_group()
     return 0
+
+
+def avg_or(x, default):
+    return sum(x) / len(x) if x else default
 
 
 def workload_R(cams, cuts, model, bg, args, render_post):

@@ -200,12 +200,13 @@ def find_limit(gh, model, cam, target, device, iters=30):
     return math.sqrt(lo * hi)
 
 
-def ours_render_post(cam, model, bg, cut, do_depth=True):
+def ours_render_post(cam, model, bg, cut, do_depth=True, sparse_grads=None):
     from gaussian_renderer import render_post
     K = cut.count
     return render_post(cam, model, scenes.Pipe, bg, render_indices=cut.render_indices[:K],
                        parent_indices=cut.parent_indices[:K], interpolation_weights=cut.interpolation_weights,
-                       num_node_kids=cut.num_siblings, use_trained_exp=False, do_depth=do_depth)
+                       num_node_kids=cut.num_siblings, use_trained_exp=False, do_depth=do_depth,
+                       sparse_grads=sparse_grads)
 
 
 def ref_render_post(cam, model, bg, cut, do_depth=True):

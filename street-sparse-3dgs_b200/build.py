@@ -65,5 +65,43 @@ def build(force=False, verbose=False):
     return LIB
 
 
+EXT_NAME = "_h3dgs_torch"
+EXT = os.path.join(OUT_DIR, EXT_NAME + ".so")
+
+
+def build_torch_ext(force=False, verbose=False):
+    """The torch extension (csrc/torch_binding.cpp -> lib/_h3dgs_torch.so): host C++ over the C ABI, linked against
+    lib/libh3dgs_b200.so through an $ORIGIN rpath.  In-tree output, like the library itself."""
+    import shutil
+    build()
+    src = os.path.join(CSRC, "torch_binding.cpp")
+    stamp = os.path.join(OUT_DIR, "ext.sha256")
+    h = hashlib.sha256()
+    for f in (src, os.path.join(HERE, "..", "include", "h3dgs_b200.h")):
+        h.update(open(f, "rb").read())
+    import torch
+    h.update(torch.__version__.encode())
+    dg = h.hexdigest()
+    if not force and os.path.exists(EXT) and os.path.exists(stamp) and open(stamp).read().strip() == dg:
+        return EXT
+    import subprocess
+    import sysconfig
+    from torch.utils.cpp_extension import include_paths, library_paths
+    inc = include_paths() + [sysconfig.get_paths()["include"], "/usr/local/cuda/include",
+                             os.path.join(HERE, "..", "include")]
+    cmd = (["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-fvisibility=hidden", "-Wno-interference-size", "-DTORCH_EXTENSION_NAME=" + EXT_NAME,
+            "-DTORCH_API_INCLUDE_EXTENSION_H", "-D_GLIBCXX_USE_CXX11_ABI=" + str(int(torch._C._GLIBCXX_USE_CXX11_ABI))]
+           + ["-I" + d for d in inc] + [src, "-o", EXT, "-L" + OUT_DIR, "-lh3dgs_b200", "-Wl,-rpath,$ORIGIN"]
+           + ["-L" + d for d in library_paths()] + ["-lc10", "-lc10_cuda", "-ltorch_cpu", "-ltorch", "-ltorch_python",
+                                                     "-L/usr/local/cuda/lib64", "-lcudart"])
+    if verbose:
+        print(" ".join(cmd))
+    subprocess.run(cmd, check=True)
+    with open(stamp, "w") as fh:
+        fh.write(dg)
+    return EXT
+
+
 if __name__ == "__main__":
     print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    print(build_torch_ext(force="--force" in sys.argv, verbose="-v" in sys.argv))

@@ -87,9 +87,12 @@ __global__ void __launch_bounds__(SORT_THREADS, 3) onesweep_kernel(
   SweepSmem<K>& sm = *reinterpret_cast<SweepSmem<K>*>(smem_raw);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
-  // element count: known to the host (tile passes over the R instances) or left on the device by the visible
-  // scan (depth passes over the V visible slots: the grid then covers the P slots and the surplus CTAs leave)
+  // element count: known to the host (tile passes over the R instances: one CTA per tile) or left on the device by
+  // the visible scan (depth passes over the V visible slots: a persistent grid whose CTAs keep taking tiles from
+  // the dynamic counter until the V elements are covered -- tiles are handed out in order, every CTA is resident,
+  // so the look-back always waits on a tile that is being worked on)
   const long long n = n_dev ? (long long)*n_dev : n_host;
+  for (;;) {
   if (tid == 0) sm.tile = atomicAdd(counter, 1u);
   for (int i = tid; i < WARPS * RADIX; i += SORT_THREADS) (&sm.cnt[0][0])[i] = 0;
   __syncthreads();
@@ -204,6 +207,9 @@ __global__ void __launch_bounds__(SORT_THREADS, 3) onesweep_kernel(
     vout[g] = v;
     if (OUT == 2) kout64[g] = ((unsigned long long)k << 32) | (unsigned long long)__ldg(depth_bits + v);
   }
+  if (n_dev == nullptr) return;
+  __syncthreads();   // shared memory is reused by the next tile
+  }
 }
 
 template <typename K, int OUT>
@@ -219,7 +225,12 @@ cudaError_t launch_pass(const K* kin, K* kout, const uint32_t* vin, uint32_t* vo
     if (e != cudaSuccess) return e;
     attr_done = true;
   }
-  const long long tiles = (n + SORT_TILE - 1) / SORT_TILE;
+  long long tiles = (n + SORT_TILE - 1) / SORT_TILE;
+  if (n_dev != nullptr) {   // persistent grid: 3 CTAs per SM are resident (launch bounds), never more CTAs than tiles
+    int dev = 0, sms = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (tiles > (long long)sms * 3) tiles = (long long)sms * 3;
+  }
   ProfScope ps(K_SORT_PASS, s);
   k<<<(unsigned)tiles, SORT_THREADS, smem, s>>>(kin, kout, vin, vout, kout64, depth_bits, n, n_dev, shift, mask,
                                                 digit_base, status, counter);

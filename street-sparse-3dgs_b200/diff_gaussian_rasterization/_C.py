@@ -18,6 +18,49 @@ import h3dgs_native as nat
 
 NUM_CHANNELS = 3
 
+# Host path of the two hot calls.  "ext" (default when lib/_h3dgs_torch.so exists): csrc/torch_binding.cpp, one C++
+# call per forward / backward.  "ctypes": the Python binding below, kept as the reference binding of the C ABI.
+# Both drive the same libh3dgs_b200.so entry points in the same order; tests/test_gpu_host_paths.py compares them.
+HOST = os.environ.get("H3DGS_HOST", "auto")
+_ext_mod = None
+
+
+def ext():
+    """The torch extension module, or None when the ctypes host path is selected / the extension is not built."""
+    global _ext_mod
+    if HOST == "ctypes":
+        return None
+    if _ext_mod is None:
+        path = os.path.join(os.path.dirname(nat.LIB_PATH), "_h3dgs_torch.so")
+        if not os.path.exists(path):
+            if HOST == "ext":
+                raise nat.H3dgsError(f"{path} not found: build it with `python street-sparse-3dgs_b200/build.py`")
+            return None
+        import importlib.machinery
+        import importlib.util
+        nat.lib()   # libh3dgs_b200.so first (and its ABI check)
+        loader = importlib.machinery.ExtensionFileLoader("_h3dgs_torch", path)
+        mod = importlib.util.module_from_spec(importlib.util.spec_from_loader("_h3dgs_torch", loader))
+        loader.exec_module(mod)
+        if mod.abi_version() != nat.ABI_VERSION:
+            raise nat.H3dgsError("_h3dgs_torch.so was built against another ABI version")
+        _ext_mod = mod
+    return _ext_mod
+
+
+_none = {}
+
+
+def _t(x, like):
+    """None -> an empty tensor (the extension's 'absent')."""
+    if x is not None:
+        return x
+    key = like.device
+    e = _none.get(key)
+    if e is None:
+        e = _none[key] = torch.empty(0, device=like.device)
+    return e
+
 
 def _null(t):
     return t is None or t.numel() == 0
@@ -173,6 +216,9 @@ _row_maps = {}
 
 def _row_map(dev, rows):
     """int32 [rows] scratch of the compact-gradient mode, all -1 between calls (the library restores it)."""
+    E = ext()
+    if E is not None:
+        return E.row_map(torch.empty(0, device=dev), rows)
     key = (dev.index, rows)
     m = _row_maps.get(key)
     if m is None:
@@ -213,6 +259,20 @@ def rasterize_gaussians_ex(bg, indices, parent_indices, ts, kids, means3D, color
                            do_depth, skyboxnum=0, sh_rest=None, acts=None, prezero_means2D_rows=None):
     """``prezero_means2D_rows`` (fused-cut mode, set by the autograd wrapper when a backward will follow):
     also allocate the backward's gradient tensors and start their zero fill; an 8th return value carries them."""
+    E = ext()
+    if E is not None and means3D.is_cuda:
+        a = acts if acts is not None else (0, 0, 0)
+        want = prezero_means2D_rows is not None and prezero_means2D_rows >= 0 and PREZERO and not _arena.enabled()
+        m = means3D
+        R, color, radii, geom, binning, img, invdepth, V, pre = E.rasterize_forward(
+            _t(bg, m), _t(indices, m), _t(parent_indices, m), _t(ts, m), _t(kids, m), m, _t(colors, m),
+            _t(opacity, m), _t(scales, m), _t(rotations, m), float(scale_modifier), _t(cov3D_precomp, m), viewmatrix,
+            projmatrix, float(tan_fovx), float(tan_fovy), int(image_height), int(image_width), _t(sh, m), int(degree),
+            campos, bool(prefiltered), bool(debug), bool(do_depth), int(skyboxnum), _t(sh_rest, m), int(a[0]),
+            int(a[1]), int(a[2]), int(prezero_means2D_rows) if want else -1)
+        if prezero_means2D_rows is not None:
+            return R, color, radii, geom, binning, img, invdepth, _Aux(pre, V)
+        return R, color, radii, geom, binning, img, invdepth
     L = nat.lib()
     dev = means3D.device
     H, W = int(image_height), int(image_width)
@@ -363,6 +423,14 @@ def rasterize_gaussians_backward_ex(bg, indices, parent_indices, ts, kids, means
     gradient tensors the forward allocated and zero-filled (``_Prezero``); dL_dmeans2D then has its rows.
     ``sparse`` (a ``SparseGradients``, fused-cut mode): the per-store-row gradients are produced in compact form
     into it -- no N-row tensors exist -- and the returned per-row gradients are None."""
+    E = ext()
+    if E is not None and means3D.is_cuda and not isinstance(prezero, _Prezero) and not _arena.enabled():
+        return _backward_ext(E, bg, indices, parent_indices, ts, kids, means3D, radii, colors, opacities, scales,
+                             rotations, scale_modifier, cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy,
+                             dL_dout_color, dL_dout_invdepth, sh, degree, campos, geomBuffer, R, binningBuffer,
+                             imageBuffer, debug, skyboxnum, sh_rest, acts, prezero, sparse, num_visible)
+    if prezero is not None and not isinstance(prezero, _Prezero):
+        prezero = None   # made by the extension's forward; this path fills its own
     L = nat.lib()
     dev = means3D.device
     H, W = dL_dout_color.size(1), dL_dout_color.size(2)
@@ -417,6 +485,37 @@ def rasterize_gaussians_backward_ex(bg, indices, parent_indices, ts, kids, means
     if split:
         dL_dsh = (dL_dsh, dL_dsh_rest)
     return dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drot
+
+
+_SPARSE_NAMES = ("means3D", "sh", "sh_rest", "colors", "opacity", "scales", "rot", "cov3D")
+
+
+def _backward_ext(E, bg, indices, parent_indices, ts, kids, means3D, radii, colors, opacities, scales, rotations,
+                  scale_modifier, cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color,
+                  dL_dout_invdepth, sh, degree, campos, geomBuffer, R, binningBuffer, imageBuffer, debug, skyboxnum,
+                  sh_rest, acts, prezero, sparse, num_visible):
+    a = acts if acts is not None else (0, 0, 0)
+    m = means3D
+    split = not _null(sh_rest)
+    if sparse is not None and _null(indices):
+        raise RuntimeError("sparse gradients need a hierarchy-cut render (render_indices)")
+    (m2, dcolors, dopac, dmeans3D, dcov, dsh, dsh_rest, dscales, drot, crow, ccount) = E.rasterize_backward(
+        _t(bg, m), _t(indices, m), _t(parent_indices, m), _t(ts, m), _t(kids, m), m, _t(radii, m), _t(colors, m),
+        _t(opacities, m), _t(scales, m), _t(rotations, m), float(scale_modifier), _t(cov3D_precomp, m), viewmatrix,
+        projmatrix, float(tan_fovx), float(tan_fovy), dL_dout_color, _t(dL_dout_invdepth, m), _t(sh, m), int(degree),
+        campos, geomBuffer, int(R), binningBuffer, imageBuffer, bool(debug), int(skyboxnum), _t(sh_rest, m),
+        int(a[0]), int(a[1]), int(a[2]), prezero, 1 if sparse is not None else 0, int(num_visible))
+    if sparse is not None:
+        present = {"means3D": dmeans3D, "opacity": dopac, "sh": dsh if not _null(sh) else None, "sh_rest": dsh_rest,
+                   "colors": dcolors if not _null(colors) else None, "scales": dscales if not _null(scales) else None,
+                   "rot": drot if not _null(rotations) else None, "cov3D": dcov if not _null(cov3D_precomp) else None}
+        sparse.grads = {k: v for k, v in present.items() if v is not None}
+        sparse.rows, sparse.count, sparse.capacity = crow, ccount, crow.numel()
+        sparse.ready = True
+        return m2, None, None, None, None, (None, None) if split else None, None, None
+    if split:
+        dsh = (dsh, dsh_rest)
+    return m2, dcolors, dopac, dmeans3D, dcov, dsh, dscales, drot
 
 
 def _backward_sparse(L, dev, view, g, shapes, sparse, V, radii, geomBuffer, binningBuffer, imageBuffer, R,

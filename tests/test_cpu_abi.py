@@ -235,3 +235,15 @@ def test_hier_files_match_reference_writer_and_loader_fixture(tmp_path):
     """Host-side .hier I/O against files written / read by the reference's own C++ classes (tests/hier_fixture.py)."""
     from tests import hier_fixture
     hier_fixture.check(tmp_path, "cpu")
+
+
+def test_torch_extension_loads_and_matches_the_abi():
+    """lib/_h3dgs_torch.so (csrc/torch_binding.cpp) is the default host path: it must be built, import without a
+    GPU, resolve libh3dgs_b200.so through its $ORIGIN rpath and agree on the ABI version."""
+    import diff_gaussian_rasterization as dgr
+    import h3dgs_native as nat
+    E = dgr._C.ext()
+    assert E is not None, "torch extension not built (python street-sparse-3dgs_b200/build.py)"
+    assert E.abi_version() == nat.ABI_VERSION
+    for name in ("rasterize_forward", "rasterize_backward", "row_map", "Prezero"):
+        assert hasattr(E, name)
