@@ -36,6 +36,9 @@ def parse():
     ap.add_argument("--steps", type=int, default=64)
     ap.add_argument("--warmup", type=int, default=8)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", type=int, default=4, choices=[2, 3, 4],
+                    help="BASELINE.json config: 4 = train_post step (the headline), 2 = train_single step, "
+                         "3 = render_hierarchy forward-only over a batch of views")
     ap.add_argument("--mode", default="chunks", choices=["chunks", "dp"])
     ap.add_argument("--levels", type=int, default=23, help="hierarchy has 2**levels leaves")
     ap.add_argument("--target", type=int, default=5_000_000, help="cut size")
@@ -45,6 +48,9 @@ def parse():
     ap.add_argument("--cameras", type=int, default=8)
     ap.add_argument("--loss", default="l1ssim", choices=["l1ssim", "l1"],
                     help="e2e loss: train_post.py's 0.8 L1 + 0.2 (1 - SSIM), or L1 alone")
+    ap.add_argument("--single-gaussians", type=int, default=1_000_000, help="config 2: Gaussians in the chunk")
+    ap.add_argument("--views", type=int, default=64, help="config 3: views per batch")
+    ap.add_argument("--tau", type=float, default=6.0, help="config 3: granularity in pixels")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--serial-cut", action="store_true",
                     help="e2e: compute each step's cut at the top of the step instead of one step ahead")
@@ -56,67 +62,14 @@ def parse():
     return ap.parse_args()
 
 
-class ClockSampler:
-    """SM clock / throttle-reason sampling while a timed region runs (B200_PROFILING.md): NVML polled from
-    a thread every 5 ms (nvidia-smi -lms cannot sample a region shorter than its period)."""
-
-    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
-
-    def __init__(self, index):
-        self.index = index
-        self.samples = []
-        self.stop_flag = threading.Event()
-        self.thread = None
-        self.handle = None
-        self.sm_max = None
-        try:
-            import pynvml
-            pynvml.nvmlInit()
-            self.nv = pynvml
-            # LOCAL_RANK indexes the visible devices; NVML enumerates all of them
-            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
-            phys = int(vis.split(",")[index]) if vis and vis.split(",")[index].isdigit() else index
-            self.handle = pynvml.nvmlDeviceGetHandleByIndex(phys)
-            self.sm_max = float(pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM))
-        except Exception:
-            self.handle = None
-
-    def _poll(self):
-        nv = self.nv
-        reasons = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or \
-            nv.nvmlDeviceGetCurrentClocksThrottleReasons
-        while not self.stop_flag.is_set():
-            try:
-                self.samples.append((float(nv.nvmlDeviceGetClockInfo(self.handle, nv.NVML_CLOCK_SM)),
-                                     int(reasons(self.handle))))
-            except Exception:
-                pass
-            time.sleep(0.005)
-
-    def start(self):
-        if self.handle is None:
-            return
-        self.thread = threading.Thread(target=self._poll, daemon=True)
-        self.thread.start()
-
-    def stop(self):
-        out = {"sm_mhz": None, "sm_max_mhz": self.sm_max, "reasons": [], "samples": 0}
-        if self.thread is None:
-            return out
-        self.stop_flag.set()
-        self.thread.join(timeout=2)
-        if self.samples:
-            sm = sorted(x[0] for x in self.samples)
-            mask = 0
-            for _, m in self.samples:
-                mask |= m
-            out.update(sm_mhz=sm[len(sm) // 2], reasons=sorted(n for b, n in self.REASONS.items() if mask & b),
-                       samples=len(sm))
-        return out
+from harness.clocks import ClockSampler  # noqa: E402
 
 
 def main():
     args = parse()
+    if args.config != 4:
+        from harness import bench_configs
+        return bench_configs.run(args)
     import torch
     import torch.distributed as dist
 

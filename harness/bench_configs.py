@@ -1,0 +1,290 @@
+"""bench.py --config 2|3: the two other single-GPU workloads BASELINE.json names, both arms.
+
+config 2  train_single.py:100-233 iteration body on a 1 M-Gaussian chunk (+100 k skybox rows at the front of the
+          store) at 1920x1080: render() with learnable exposure and depth output, 0.8 L1 + 0.2 (1 - SSIM) on
+          image * alpha_mask plus the masked inverse-depth L1, backward, `relevant = opacity.grad != 0`, sparse Adam.
+          value = steps/s with everything resident; stages (rasterizer fwd / loss fwd+bwd / rasterizer bwd / optimizer)
+          timed with CUDA events inside a second loop that splits the autograd graph at the rendered image.
+config 3  render_hierarchy.py:60-99 loop body, forward only, over 64 views of the level-23 (16.9 M-node) hierarchy:
+          expand_to_size at tau = 6 px -> get_interpolation_weights -> render_post(do_depth=True) -> clamp.
+          value = views/s; stages (cut / weights / render) timed with CUDA events.
+
+`--impl reference` runs the same loops on the unmodified reference extensions (oracle/_ref) under the restated
+reference glue (harness/refglue.py) and torch-formula losses."""
+import json
+import os
+
+import torch
+
+from harness import refglue, scenes, workload
+from harness.clocks import ClockSampler
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _timed(fn, steps, warmup, local_rank):
+    for i in range(warmup):
+        fn(i)
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        fn(warmup + i)
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1), sampler.stop()
+
+
+class _Stages:
+    """CUDA-event stage timer: mark(name) closes the running stage."""
+
+    def __init__(self):
+        self.pairs, self.last = [], None
+
+    def begin(self):
+        self.last = torch.cuda.Event(enable_timing=True)
+        self.last.record()
+
+    def mark(self, name):
+        e = torch.cuda.Event(enable_timing=True)
+        e.record()
+        self.pairs.append((name, self.last, e))
+        self.last = e
+
+    def read(self, steps):
+        torch.cuda.synchronize()
+        out = {}
+        for name, a, b in self.pairs:
+            out[name] = out.get(name, 0.0) + a.elapsed_time(b)
+        return {k: v / steps for k, v in out.items()}
+
+
+def _launches(impl):
+    if impl != "ours":
+        return 0
+    import h3dgs_native
+    return h3dgs_native.lib().h3dgs_launch_count()
+
+
+def _need_reference():
+    if refglue.ref_gh() is None or refglue.ref_hr() is None:
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/*.so not built (run oracle/build_ref.py "
+                          "where /root/reference exists)"}))
+        return False
+    return True
+
+
+def run_config2(args, dev, local_rank):
+    impl = args.impl
+    W, H = args.width, args.height
+    n, sky = args.single_gaussians, args.skybox
+    sc = workload.single_chunk_scene(n, sky, 6, dev)
+    cams = [scenes.street_camera(W, H, seed=40 + i, device=dev, yaw_deg=[8.0, 96.0, 184.0, 262.0][i % 4],
+                                 x=-30.0 + 60.0 * ((i * 0.6180339887) % 1.0)) for i in range(args.cameras)]
+    for i, c in enumerate(cams):
+        c.image_name = f"cam{i}"
+    model = workload.SingleModel(sc, sky, camera_names=tuple(c.image_name for c in cams))
+    del sc
+    g = torch.Generator().manual_seed(17)
+    gts = [torch.rand(3, H, W, generator=g).to(dev) for _ in range(2)]
+    alpha_mask = (torch.rand(1, H, W, generator=g) > 0.1).float().to(dev)
+    mono = torch.rand(1, H, W, generator=g).to(dev)
+    depth_mask = (torch.rand(1, H, W, generator=g) > 0.3).float().to(dev)
+    bg = torch.zeros(3, device=dev)
+    depth_w = 0.7
+    if impl == "ours":
+        from scene.OurAdam import Adam
+        from utils.loss_utils import fused_l1_ssim_loss, masked_l1_loss
+        opt = Adam(model.param_groups(), lr=0.0, eps=1e-15)
+        render = workload.ours_render
+
+        def loss_of(image, depth, gt):
+            photo, _ = fused_l1_ssim_loss(image, gt, 0.2, mask=alpha_mask)
+            return photo + depth_w * masked_l1_loss(depth, mono, depth_mask)
+    else:
+        from harness.ref_adam import RefSparseAdam
+        from oracle import loss_reference as lr   # the reference arm's torch-formula losses
+        opt = RefSparseAdam(model.param_groups(), eps=1e-15)
+        render = workload.ref_render
+
+        def loss_of(image, depth, gt):
+            photo, _ = lr.l1_ssim_loss(image, gt, 0.2, mask=alpha_mask)
+            return photo + depth_w * lr.depth_l1(depth, mono, depth_mask)
+    exp_opt = torch.optim.Adam([model._exposure], lr=1e-3)   # scene/gaussian_model.py:298 exposure_optimizer
+    stats = {"V": [], "relevant": []}
+
+    def optimizer_step(collect):
+        exp_opt.step()
+        exp_opt.zero_grad(set_to_none=True)
+        # train_single.py:217-221 (skybox_locked) and :225-233
+        if sky:
+            for p in model.parameters():
+                p.grad[:sky].zero_()
+        relevant = (model._opacity.grad.flatten() != 0).nonzero().flatten().long()
+        if collect:
+            stats["relevant"].append(int(relevant.numel()))
+        opt.step(relevant)
+        for p in model.parameters():
+            p.grad = None
+
+    def step(i, st=None, collect=False):
+        c, gt = cams[i % len(cams)], gts[i % 2]
+        if st:
+            st.begin()
+        out = render(c, model, bg, use_trained_exp=True)
+        if st:   # split the graph at the rendered image so that the loss and the rasterizer backward time apart
+            st.mark("rasterizer_fwd")
+            img = out["render"].detach().requires_grad_(True)
+            dep = out["depth"].detach().requires_grad_(True)
+            loss_of(img, dep, gt).backward()
+            st.mark("loss_fwd_bwd")
+            torch.autograd.backward([out["render"], out["depth"]], [img.grad, dep.grad])
+            st.mark("rasterizer_bwd")
+        else:
+            loss_of(out["render"], out["depth"], gt).backward()
+        if collect:
+            stats["V"].append(int(out["visibility_filter"].numel()))
+        optimizer_step(collect)
+        if st:
+            st.mark("optimizer")
+
+    l0 = None
+    ms, clocks = None, None
+    warm = max(args.warmup, 3)
+    for i in range(warm):
+        step(i)
+    torch.cuda.synchronize()
+    l0 = _launches(impl)
+    ms, clocks = _timed(step, args.steps, 0, local_rank)
+    launches = _launches(impl) - l0
+    st = _Stages()
+    n_st = 2 * len(cams)
+    for i in range(n_st):
+        step(i, st=st)
+    stages = st.read(n_st)
+    for i in range(len(cams)):
+        step(i, collect=True)
+    torch.cuda.synchronize()
+    ms_step = ms / args.steps
+    line = {
+        "metric": "train_single steps/sec at 1920x1080, 1M-Gaussian chunk (BASELINE.json config 2)",
+        "value": 1000.0 / ms_step, "unit": "steps/s", "n_gpus": 1, "steps": args.steps, "warmup": warm,
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic", "impl": impl,
+        "config": {"workload": "config 2: train_single iteration body, render() + exposure + depth, 0.8 L1 + 0.2 (1-SSIM) "
+                               "on image*alpha_mask + 0.7 masked inverse-depth L1, skybox-locked sparse Adam",
+                   "gaussians": n, "skybox": sky, "width": W, "height": H, "cameras": len(cams), "sh_degree": 3,
+                   "l2": "per-step working set (1.1 M rows x 236 B + moments + 25 MB images) exceeds the 126 MB L2"},
+        "clocks": clocks, "gpu_launches": int(launches) if impl == "ours" else None,
+        "stages_ms": stages,
+        "workload_stats": {"visible": sum(stats["V"]) / len(stats["V"]),
+                           "relevant_rows": sum(stats["relevant"]) / len(stats["relevant"])},
+    }
+    print(json.dumps(line))
+    return 0
+
+
+def run_config3(args, dev, local_rank):
+    impl = args.impl
+    W, H = args.width, args.height
+    if impl == "ours":
+        import gaussian_hierarchy
+        gh = gaussian_hierarchy._C
+        render_post = workload.ours_render_post
+    else:
+        gh = refglue.ref_gh()
+        render_post = workload.ref_render_post
+    attrs = workload.build_scene(args.levels, args.skybox, 0, dev, free_corridor=True)
+    n_store = attrs["means3D"].size(0)
+    model = workload.HierModel(attrs, args.skybox)
+    for p in model.parameters():
+        p.requires_grad_(False)
+    del attrs
+    views = workload.cameras(W, H, args.views, dev)
+    bg = torch.zeros(3, device=dev)
+    cut = workload.Cut(n_store, dev)
+    zeros3 = torch.zeros(3)
+    host_centers = [c.camera_center.cpu() for c in views]   # render_hierarchy.py:82 passes camera_center.cpu()
+    stats = {"K": [], "V": []}
+    sink = torch.zeros((), device=dev)
+
+    @torch.no_grad()
+    def view(i, st=None, collect=False):
+        k = i % len(views)
+        c = views[k]
+        thr = workload.threshold_for_tau(c, args.tau)
+        if st:
+            st.begin()
+        K = gh.expand_to_size(model.nodes, model.boxes, thr, c.camera_center, zeros3, cut.render_indices,
+                              cut.parent_indices, cut.nodes_for_render_indices)
+        cut.count = K
+        if st:
+            st.mark("expand_to_size")
+        gh.get_interpolation_weights(cut.nodes_for_render_indices[:K].contiguous(), thr, model.nodes, model.boxes,
+                                     host_centers[k], zeros3, cut.interpolation_weights, cut.num_siblings)
+        if st:
+            st.mark("get_interpolation_weights")
+        out = render_post(c, model, bg, cut, do_depth=True)
+        image = torch.clamp(out["render"], 0.0, 1.0)
+        sink.add_(image[0, 0, 0] + out["depth"][0, 0, 0])
+        if st:
+            st.mark("render_post")
+        if collect:
+            stats["K"].append(int(K))
+            stats["V"].append(int(out["visibility_filter"].numel()) if out["visibility_filter"].dtype != torch.bool
+                              else int(out["visibility_filter"].sum()))
+
+    steps = args.steps
+    warm = max(args.warmup, 3)
+
+    def batch(i):
+        for v in range(len(views)):
+            view(v)
+
+    for i in range(warm):
+        view(i)
+    torch.cuda.synchronize()
+    l0 = _launches(impl)
+    ms, clocks = _timed(batch, steps, 0, local_rank)
+    launches = _launches(impl) - l0
+    st = _Stages()
+    for v in range(len(views)):
+        view(v, st=st)
+    stages = st.read(len(views))
+    for v in range(len(views)):
+        view(v, collect=True)
+    torch.cuda.synchronize()
+    ms_batch = ms / steps
+    line = {
+        "metric": "render_hierarchy forward-only views/sec at 1920x1080, tau = %g px (BASELINE.json config 3)" % args.tau,
+        "value": len(views) * 1000.0 / ms_batch, "unit": "views/s", "n_gpus": 1, "steps": steps, "warmup": warm,
+        "ms_per_step": ms_batch, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic", "impl": impl,
+        "config": {"workload": "config 3: expand_to_size -> get_interpolation_weights -> render_post(do_depth) -> clamp, "
+                               "one step = a batch of %d views" % len(views),
+                   "hierarchy_nodes": int(model.nodes.size(0)), "store_rows": n_store, "skybox": args.skybox,
+                   "tau_px": args.tau, "width": W, "height": H, "views": len(views),
+                   "l2": "each view reads a different cut of a 4 GB store; the working set exceeds the 126 MB L2"},
+        "clocks": clocks, "gpu_launches": int(launches) if impl == "ours" else None,
+        "stages_ms_per_view": stages,
+        "workload_stats": {"cut_size": sum(stats["K"]) / len(stats["K"]), "cut_min": min(stats["K"]),
+                           "cut_max": max(stats["K"]), "visible": sum(stats["V"]) / len(stats["V"])},
+    }
+    print(json.dumps(line))
+    return 0
+
+
+def run(args):
+    if not torch.cuda.is_available():
+        print(json.dumps({"error": "no CUDA device: the product path has no CPU fallback"}))
+        return 1
+    if int(os.environ.get("RANK", "0")) != 0:
+        return 0   # configs 2 and 3 are single-GPU workloads
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if args.impl == "reference" and not _need_reference():
+        return 0
+    return run_config2(args, dev, local_rank) if args.config == 2 else run_config3(args, dev, local_rank)
