@@ -26,7 +26,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 OUT = os.path.join(HERE, "_ref")
 
 
-TOOL_SOURCES = ("hierarchy_writer.cpp", "hierarchy_loader.cpp")
+TOOL_SOURCES = ("hierarchy_writer.cpp", "hierarchy_loader.cpp", "PointbasedKdTreeGenerator.cpp", "ClusterMerger.cpp",
+                "rotation_aligner.cpp", "writer.cpp")
 
 
 def build_tool(verbose=True):
