@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define H3DGS_ABI_VERSION 7
+#define H3DGS_ABI_VERSION 8
 
 #if defined(__GNUC__)
 #define H3DGS_API __attribute__((visibility("default")))
@@ -338,10 +338,34 @@ H3DGS_API int h3dgs_sparse_adam_compact(const H3dgsAdamTensor* tensors, int32_t 
                               const float* gate, h3dgs_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * Hierarchy build.  Replaces the tree stages of the offline GaussianHierarchyCreator
+ * (GH/mainHierarchyCreator.cpp:130-141): PointbasedKdTreeGenerator::generate (GH/PointbasedKdTreeGenerator.cpp:16-73),
+ * ClusterMerger::merge (GH/ClusterMerger.cpp:23-165), RotationAligner::align (GH/rotation_aligner.cpp:14-114) and
+ * Writer::makeHierarchy (GH/writer.cpp:18-115), which the reference runs as single-threaded host recursions.
+ *
+ * Input: N ACTIVATED Gaussians on the device (what Loader::loadPly leaves in memory, GH/loader.cpp:102-158):
+ * positions [N,3], shs [N,48], opacities [N], scales [N,3] (not log), rotations [N,4] (w,x,y,z).
+ * Output (device, 2N-1 rows each, pre-order as HierarchyWriter::write expects them): Gaussian rows with LOG scales,
+ * nodes int32 [2N-1,7], boxes fp32 [2N-1,2,4].  out_covariances [2N-1,6] (the moment-matched covariance every merge
+ * accumulated) and out_leaf_order [2N-1] (input index of a leaf row, -1 for merged rows) may be NULL.
+ * align != 0 runs the rotation alignment.  Synchronises `stream` before returning (the error flags of the
+ * merge -- the reference's "Found Nans!" exception -- are read back).
+ * Ties between equal coordinates at a median are broken by Gaussian index (std::nth_element leaves them in an
+ * implementation-defined order).
+ * ------------------------------------------------------------------------------------------------ */
+H3DGS_API size_t h3dgs_hier_build_workspace_bytes(int64_t num_gaussians);
+H3DGS_API int h3dgs_hier_build(int64_t num_gaussians, const float* positions, const float* shs, const float* opacities,
+                     const float* scales, const float* rotations, int32_t align,
+                     float* out_positions, float* out_shs, float* out_opacities, float* out_log_scales,
+                     float* out_rotations, int32_t* out_nodes, float* out_boxes,
+                     float* out_covariances, int32_t* out_leaf_order,
+                     void* workspace, size_t workspace_bytes, h3dgs_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------
  * Instrumentation (no reference counterpart).  Launch counting is always on; per-kernel timing wraps
  * every kernel in a pair of CUDA events on the launching stream while enabled.
  * ------------------------------------------------------------------------------------------------ */
-#define H3DGS_PROF_KERNELS 17
+#define H3DGS_PROF_KERNELS 20
 /*
  * Fused photometric loss.  Replaces utils/loss_utils.py:17-63 (l1_loss, ssim / _ssim: five
  * depthwise conv2d, ~15 elementwise kernels and their autograd) as used by train_single.py:116-141 and

@@ -39,7 +39,8 @@ struct Prof {
 const char* const kKernelNames[K_COUNT] = {
   "preprocess_fwd", "scan", "emit_instances", "sort_histogram", "sort_scan", "sort_onesweep_pass",
   "tile_ranges", "blend_fwd", "blend_bwd", "preprocess_bwd", "cut_mark_nodes", "cut_put_indices",
-  "cut_interp_weights", "sparse_adam", "mark_visible", "memset", "loss"};
+  "cut_interp_weights", "sparse_adam", "mark_visible", "memset", "loss", "hier_build_tree", "hier_build_merge",
+  "densify"};
 }  // namespace
 
 void prof_begin(int id, cudaStream_t s) {

@@ -259,7 +259,7 @@ int cuda_fail(cudaError_t e, const char* what);
 enum KernelId {
   K_PREPROCESS_FWD = 0, K_SCAN, K_EMIT, K_SORT_HIST, K_SORT_SCAN, K_SORT_PASS, K_TILE_RANGES, K_BLEND_FWD,
   K_BLEND_BWD, K_PREPROCESS_BWD, K_CUT_MARK, K_CUT_PUT, K_CUT_WEIGHTS, K_ADAM, K_MARK_VISIBLE, K_MEMSET,
-  K_LOSS, K_COUNT
+  K_LOSS, K_HIER_TREE, K_HIER_MERGE, K_DENSIFY, K_COUNT
 };
 static_assert(K_COUNT == H3DGS_PROF_KERNELS, "kernel id table out of sync with the header");
 void prof_begin(int id, cudaStream_t s);
@@ -314,6 +314,10 @@ cudaError_t launch_tile_ranges(int64_t R, const unsigned long long* keys, uint2*
 // sorts the *v_dev (device u64, at most P) compacted (depth bits, slot) pairs of g.dkeys[0] / g.dvals[0]
 cudaError_t launch_depth_sort(GeomWs& g, int P, const unsigned long long* v_dev, cudaStream_t s);
 cudaError_t launch_tile_sort(BinWs& b, int64_t R, const SortPlan& plan, const float* depth, cudaStream_t s);
+// stable sort of n (u32 key, u32 value) pairs, result in keys[0] / vals[0]; ws = sort_pairs_ws_words(n) u32 words
+size_t sort_pairs_ws_words(long long n);
+cudaError_t launch_sort_pairs(uint32_t* const keys[2], uint32_t* const vals[2], long long n, uint32_t* ws,
+                              cudaStream_t s);
 
 struct BlendArgs {
   int W, H, grid_x, grid_y, P, skyboxnum;

@@ -304,6 +304,35 @@ cudaError_t launch_depth_sort(GeomWs& g, int P, const unsigned long long* v_dev,
   return cudaSuccess;
 }
 
+// Generic stable sort of n (u32 key, u32 value) pairs with the same onesweep passes (hier_build.cu: the three
+// coordinate orders of the KD-tree).  ws: sort_pairs_ws_words(n) u32 words, zeroed here; the sorted pairs end up in
+// keys[0] / vals[0] (4 passes).
+size_t sort_pairs_ws_words(long long n) {
+  const size_t tiles = (size_t)((n + SORT_TILE - 1) / SORT_TILE);
+  return (size_t)SORT_DEPTH_PASSES * RADIX + (size_t)SORT_DEPTH_PASSES * tiles * RADIX + 8;
+}
+cudaError_t launch_sort_pairs(uint32_t* const keys[2], uint32_t* const vals[2], long long n, uint32_t* ws,
+                              cudaStream_t s) {
+  if (n <= 0) return cudaSuccess;
+  const size_t tiles = (size_t)((n + SORT_TILE - 1) / SORT_TILE);
+  uint32_t* hist = ws;
+  uint32_t* status = hist + (size_t)SORT_DEPTH_PASSES * RADIX;
+  uint32_t* counters = status + (size_t)SORT_DEPTH_PASSES * tiles * RADIX;
+  cudaError_t e = cudaMemsetAsync(ws, 0, sort_pairs_ws_words(n) * sizeof(uint32_t), s);
+  if (e != cudaSuccess) return e;
+  SortShifts sh;
+  for (int p = 0; p < SORT_MAX_PASSES; ++p) { sh.shift[p] = 8 * p; sh.mask[p] = 0xffu; }
+  e = launch_hist<uint32_t>(keys[0], n, SORT_DEPTH_PASSES, sh, hist, s);
+  if (e != cudaSuccess) return e;
+  for (int p = 0; p < SORT_DEPTH_PASSES; ++p) {
+    const int src = p & 1, dst = src ^ 1;
+    e = launch_pass<uint32_t, 0>(keys[src], keys[dst], vals[src], vals[dst], nullptr, nullptr, n, nullptr, 8 * p, 0xffu,
+                                 hist + (size_t)p * RADIX, status + (size_t)p * tiles * RADIX, counters + p, s);
+    if (e != cudaSuccess) return e;
+  }
+  return cudaSuccess;
+}
+
 // Stable partition of the R emitted (tile id, slot) pairs by tile id; writes point_list (b.tvals[b.sorted])
 // and point_list_keys (b.keys64).
 cudaError_t launch_tile_sort(BinWs& b, int64_t R, const SortPlan& plan, const float* depth, cudaStream_t s) {

@@ -121,3 +121,40 @@ def get_interpolation_weights(indices, size, nodes, boxes, viewpoint, viewdir, t
                                             float(vp[0]), float(vp[1]), float(vp[2]), nat.ptr(ts),
                                             nat.ptr(num_kids), nat.stream_handle()),
               "get_interpolation_weights")
+
+
+def build_hierarchy(positions, shs, opacities, scales, rotations, align=True, return_debug=False):
+    """GPU replacement of the tree stages of the reference's offline ``GaussianHierarchyCreator`` executable
+    (GH/mainHierarchyCreator.cpp:130-141: KD-tree, ClusterMerger, RotationAligner, Writer::makeHierarchy); the
+    reference has no Python binding for them.  Takes N ACTIVATED Gaussians as CUDA tensors (scales not log,
+    rotations (w, x, y, z), shs [N,16,3] or [N,48]) and returns the seven tensors ``load_hierarchy`` returns and
+    ``write_hierarchy`` takes -- (pos[2N-1,3], shs[2N-1,16,3], alpha[2N-1,1], log_scale[2N-1,3], rot[2N-1,4],
+    nodes[2N-1,7] int32, boxes[2N-1,2,4]) -- on the device.  With ``return_debug`` also the moment-matched covariances
+    [2N-1,6] and the input index of every leaf row (-1 for merged rows)."""
+    L = nat.lib()
+    positions = nat.as_f32(positions, "positions")
+    N = positions.size(0)
+    shs = nat.as_f32(shs, "shs").reshape(N, 48)
+    opacities = nat.as_f32(opacities, "opacities").reshape(N)
+    scales = nat.as_f32(scales, "scales")
+    rotations = nat.as_f32(rotations, "rotations")
+    if N == 0:
+        raise RuntimeError("build_hierarchy: no Gaussians")
+    if scales.shape != (N, 3) or rotations.shape != (N, 4) or positions.shape != (N, 3):
+        raise RuntimeError("build_hierarchy: expected positions [N,3], scales [N,3], rotations [N,4]")
+    dev = positions.device
+    nn = 2 * N - 1
+    f = dict(dtype=torch.float32, device=dev)
+    o_pos, o_shs, o_op = torch.empty((nn, 3), **f), torch.empty((nn, 16, 3), **f), torch.empty((nn, 1), **f)
+    o_ls, o_rot = torch.empty((nn, 3), **f), torch.empty((nn, 4), **f)
+    o_nodes = torch.empty((nn, 7), dtype=torch.int32, device=dev)
+    o_boxes = torch.empty((nn, 2, 4), **f)
+    o_cov = torch.empty((nn, 6), **f) if return_debug else None
+    o_leaf = torch.empty((nn,), dtype=torch.int32, device=dev) if return_debug else None
+    ws = torch.empty((L.h3dgs_hier_build_workspace_bytes(N),), dtype=torch.uint8, device=dev)
+    nat.check(L.h3dgs_hier_build(N, nat.ptr(positions), nat.ptr(shs), nat.ptr(opacities), nat.ptr(scales),
+                                 nat.ptr(rotations), 1 if align else 0, nat.ptr(o_pos), nat.ptr(o_shs), nat.ptr(o_op),
+                                 nat.ptr(o_ls), nat.ptr(o_rot), nat.ptr(o_nodes), nat.ptr(o_boxes), nat.ptr(o_cov),
+                                 nat.ptr(o_leaf), nat.ptr(ws), ws.numel(), nat.stream_handle()), "build_hierarchy")
+    out = (o_pos, o_shs, o_op, o_ls, o_rot, o_nodes, o_boxes)
+    return out + (o_cov, o_leaf) if return_debug else out

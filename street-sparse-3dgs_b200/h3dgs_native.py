@@ -106,6 +106,10 @@ SIGNATURES = {
                                  c_void_p]),
     "h3dgs_hier_write": (c_int, [c_char_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_void_p,
                                   c_void_p, c_void_p, c_void_p, c_int]),
+    "h3dgs_hier_build_workspace_bytes": (c_size_t, [c_int64]),
+    "h3dgs_hier_build": (c_int, [c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int32, c_void_p, c_void_p,
+                                  c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t,
+                                  c_void_p]),
     "h3dgs_sparse_adam": (c_int, [POINTER(AdamTensor), c_int32, c_void_p, c_int64, c_int64, c_void_p]),
     "h3dgs_sparse_adam_compact": (c_int, [POINTER(AdamTensor), c_int32, c_void_p, c_void_p, c_int32, c_void_p, c_void_p]),
     "h3dgs_pack_rows": (c_int, [POINTER(RowTensor), c_int32, c_void_p, c_int64, c_void_p, c_void_p]),
@@ -123,8 +127,8 @@ SIGNATURES = {
     "h3dgs_profile_read": (c_int, [POINTER(ctypes.c_double), POINTER(c_int64), c_int]),
     "h3dgs_profile_name": (c_char_p, [c_int]),
 }
-PROF_KERNELS = 17
-ABI_VERSION = 7
+PROF_KERNELS = 20
+ABI_VERSION = 8
 
 
 def measure_peaks(reps=5):

@@ -26,7 +26,7 @@ def test_library_exports_every_declared_symbol():
         assert hasattr(handle, n), f"{n} declared in the header but not exported"
         assert n in nat.SIGNATURES, f"{n} has no ctypes prototype"
     assert sorted(nat.SIGNATURES) == names
-    assert nat.lib().h3dgs_abi_version() == 7
+    assert nat.lib().h3dgs_abi_version() == nat.ABI_VERSION == 8
 
 
 def test_workspace_queries_are_sane():
