@@ -36,7 +36,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=64)
     ap.add_argument("--warmup", type=int, default=8)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--config", type=int, default=4, choices=[2, 3, 4],
+    ap.add_argument("--config", type=int, default=4, choices=[1, 2, 3, 4],
                     help="BASELINE.json config: 4 = train_post step (the headline), 2 = train_single step, "
                          "3 = render_hierarchy forward-only over a batch of views")
     ap.add_argument("--mode", default="chunks", choices=["chunks", "dp"])
@@ -48,6 +48,7 @@ def parse():
     ap.add_argument("--cameras", type=int, default=8)
     ap.add_argument("--loss", default="l1ssim", choices=["l1ssim", "l1"],
                     help="e2e loss: train_post.py's 0.8 L1 + 0.2 (1 - SSIM), or L1 alone")
+    ap.add_argument("--build-gaussians", type=int, default=100_000, help="config 1: Gaussians in the chunk")
     ap.add_argument("--single-gaussians", type=int, default=1_000_000, help="config 2: Gaussians in the chunk")
     ap.add_argument("--views", type=int, default=64, help="config 3: views per batch")
     ap.add_argument("--tau", type=float, default=6.0, help="config 3: granularity in pixels")

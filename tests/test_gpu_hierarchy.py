@@ -89,9 +89,9 @@ def _fused_vs_glue(levels, sky, w, h, target, seed, depth=True, raw=None):
     cam = scenes.street_camera(w, h, seed=seed, device=DEV, yaw_deg=4.0, x=-10.0)
     bg = torch.tensor([0.05, 0.1, 0.15], device=DEV)
     if raw is None:
-        m_o, m_r, m_r2, m_r3, m_r4 = (workload.ActivatedModel(attrs, sky) for _ in range(5))
+        m_o, m_r, m_r2, m_r3, m_r4, m_o2, m_o3 = (workload.ActivatedModel(attrs, sky) for _ in range(7))
     else:
-        m_o, m_r, m_r2, m_r3, m_r4 = (_raw_model(attrs, sky, raw) for _ in range(5))
+        m_o, m_r, m_r2, m_r3, m_r4, m_o2, m_o3 = (_raw_model(attrs, sky, raw) for _ in range(7))
     limit = workload.find_limit(gaussian_hierarchy._C, m_o, cam, target, DEV)
     n = attrs["means3D"].size(0)
     g = torch.Generator().manual_seed(11)
@@ -109,6 +109,9 @@ def _fused_vs_glue(levels, sky, w, h, target, seed, depth=True, raw=None):
         return out, cut
 
     out_o, cut_o = run(m_o, workload.ours_render_post, gaussian_hierarchy._C)
+    out_o2, _ = run(m_o2, workload.ours_render_post, gaussian_hierarchy._C)
+    out_o3, _ = run(m_o3, workload.ours_render_post, gaussian_hierarchy._C)
+    assert torch.equal(bits(out_o["render"]), bits(out_o2["render"])) and torch.equal(bits(out_o["render"]), bits(out_o3["render"]))
     out_r, cut_r = run(m_r, workload.ref_render_post, refglue.ref_gh())
     out_r2, _ = run(m_r2, workload.ref_render_post, refglue.ref_gh())
     out_r3, _ = run(m_r3, workload.ref_render_post, refglue.ref_gh())
@@ -124,9 +127,11 @@ def _fused_vs_glue(levels, sky, w, h, target, seed, depth=True, raw=None):
     assert torch.equal(out_o["radii"], out_r["radii"])
     names = ["xyz", "features", "opacity", "scaling", "rotation"] if raw is None else \
         ["xyz", "features_dc", "features_rest", "opacity", "scaling", "rotation"]
-    for name, po, pr, pr2, pr3, pr4 in zip(names, m_o.parameters(), m_r.parameters(), m_r2.parameters(),
-                                           m_r3.parameters(), m_r4.parameters()):
-        util.assert_grad_close(po.grad, pr.grad, pr2.grad, name, more_refs=(pr3.grad, pr4.grad))
+    for name, po, pr, pr2, pr3, pr4, po2, po3 in zip(names, m_o.parameters(), m_r.parameters(), m_r2.parameters(),
+                                                     m_r3.parameters(), m_r4.parameters(), m_o2.parameters(),
+                                                     m_o3.parameters()):
+        util.assert_grad_close(po.grad, pr.grad, pr2.grad, name, more_refs=(pr3.grad, pr4.grad),
+                               ours_again=(po2.grad, po3.grad))
     go = out_o["viewspace_points"].grad
     gr = out_r["viewspace_points"].grad
     gr2 = out_r2["viewspace_points"].grad
