@@ -12,7 +12,8 @@ metric, config 4: interpolation weights + skybox), one process per GPU.
 `--impl reference` runs the same two measurements on the UNMODIFIED reference CUDA extensions built for
 sm_100a under oracle/_ref (the reference has no CPU rasterizer), plus the CPU oracle as
 `cpu_baseline`.  N > 1 is weak scaling: every rank owns an independent street chunk (no collective on the
-data path); `--mode dp` instead replicates one chunk and all-reduces the gradients over NCCL.
+data path); on more than one GPU the line also carries `dp`: one chunk replicated, one camera per rank, gradients
+exchanged through NVLink peer memory (harness/bench_dp.py); `--mode dp` makes that the headline value.
 """
 import argparse
 import json
@@ -60,6 +61,7 @@ def parse():
     ap.add_argument("--e2e-dropin", action="store_true",
                     help="e2e (ours): time the unchanged train_post.py loop body (dense gradients) as the headline e2e")
     ap.add_argument("--no-profile", action="store_true")
+    ap.add_argument("--no-dp", action="store_true", help="on more than one GPU: skip the camera-batch data-parallel measurement")
     return ap.parse_args()
 
 
@@ -100,14 +102,8 @@ def main():
         render_post = workload.ref_render_post
 
     W, H = args.width, args.height
-    seed = rank if args.mode == "chunks" else 0
+    seed = rank
     attrs = workload.build_scene(args.levels, args.skybox, seed, dev, free_corridor=True)
-    if args.mode == "dp" and world > 1:
-        # replicas start from rank 0's parameters, bit for bit (host-side scene generation is not guaranteed to
-        # be bit-reproducible from process to process: harness/diag_stage_modes.py)
-        for k in sorted(attrs):
-            if torch.is_tensor(attrs[k]) and attrs[k].is_cuda:
-                dist.broadcast(attrs[k], src=0)
     n_store = attrs["means3D"].size(0)
     cams = workload.cameras(W, H, args.cameras, dev, seed=seed * 100)
     bg = torch.zeros(3, device=dev)
@@ -133,19 +129,18 @@ def main():
 
     stats = {}
 
-    dp = args.mode == "dp" and world > 1
-    if dp:
-        import h3dgs_parallel as par
+    # camera-batch data parallelism is measured by harness/bench_dp.py after the chunk-parallel numbers (every run on
+    # more than one GPU carries both); `--mode dp` makes it the line's headline value
 
     # ours: compact gradients (render_post(sparse_grads=...)): the per-row gradients of a render are produced for the
     # rows of its cut only; `value_dropin` below is the same step with the dense N-row .grad tensors of the drop-in API
-    res_mode = {"sparse": args.impl == "ours" and not dp}
+    res_mode = {"sparse": args.impl == "ours"}
     if args.impl == "ours":
         import diff_gaussian_rasterization as dgr_mod
 
     def resident_step(i, collect=False):
         # camera-batch data parallel: every rank takes a different camera of the same chunk
-        k = (i * world + rank) % len(cams) if dp else i % len(cams)
+        k = i % len(cams)
         c = cams[k]
         cut = cuts[k]
         for p in model.parameters():
@@ -164,9 +159,6 @@ def main():
             stats.setdefault("compact_rows", []).append(U)
             stats.setdefault("grad_rows", []).append(int((sg.grads["opacity"][:U] != 0).sum()))
             return
-        if dp:   # the exchange step: sum the gradients of the rows any rank's cut touched (NCCL over NVLink)
-            par.allreduce_sparse_rows([p.grad for p in model.parameters()],
-                                      model.parameters()[2].grad.flatten() != 0)
         if collect:
             stats.setdefault("P", []).append(cut.count + args.skybox)
             stats.setdefault("V", []).append(int(out["visibility_filter"].sum()))
@@ -398,7 +390,7 @@ def main():
             cut_state = {"next": None}
 
         def cam_index(i):
-            return (i * world + rank) % len(cams) if dp else i % len(cams)
+            return i % len(cams)
 
         def cam_view(k, buf):
             c0 = cams[k]
@@ -435,7 +427,7 @@ def main():
         # zero fill, no row scan) and the loss value read back through pinned memory one step late, so the host never
         # waits for the step it has just queued; --e2e-dropin times the unchanged train_post.py loop body instead
         # (dense .grad tensors, relevant = opacity.grad != 0, loss.item()).  The reference arm is always the latter.
-        mode = {"sparse": args.impl == "ours" and not dp}
+        mode = {"sparse": args.impl == "ours"}
         loss_host = [torch.zeros(1).pin_memory() for _ in range(2)]
         loss_ready = [torch.cuda.Event() for _ in range(2)]
         if args.impl == "ours":
@@ -486,11 +478,7 @@ def main():
                     loss_ready[(n - 1) % 2].synchronize()
                     losses.append(float(loss_host[(n - 1) % 2]))
                 return
-            if dp:
-                relevant = par.allreduce_sparse_rows([p.grad for p in hm.parameters()],
-                                                     hm._opacity.grad.flatten() != 0)
-            else:
-                relevant = (hm._opacity.grad.flatten() != 0).nonzero().flatten().long()
+            relevant = (hm._opacity.grad.flatten() != 0).nonzero().flatten().long()
             opt.step(relevant)
             losses.append(loss.item())
 
@@ -517,6 +505,16 @@ def main():
                        "; ground-truth image prefetched one step ahead on a copy stream (one 24.9 MB H2D per step)" +
                        ("; the cut of the next step runs on a side stream under this step's backward"
                         if cut_ahead else "")}
+
+    # ---------------- camera-batch data parallelism (SURVEY.md 8e mode B) ----------------
+    dp_line = None
+    if world > 1 and args.impl == "ours" and not args.no_dp:
+        from harness import bench_dp
+        if not args.no_e2e:
+            del hm, opt, cut
+        model = None
+        torch.cuda.empty_cache()
+        dp_line = bench_dp.run(args, dev, rank, world, attrs, timed, dcol, ddep)
 
     # ---------------- CPU baseline (oracle port, bounded sample) ----------------
     cpu_baseline = None
@@ -546,7 +544,7 @@ def main():
                                     "one chunk replicated, one camera per rank, NCCL all-reduce of the union of touched gradient rows"},
             "clocks": clocks, "e2e": e2e, "gpu_launches": gpu_launches, "roofline": roofline,
             "kernels": kernels, "cpu_baseline": cpu_baseline, "rasterizer_only": raster_only,
-            "e2e_dropin": e2e_dropin, "value_dropin": value_dropin,
+            "e2e_dropin": e2e_dropin, "value_dropin": value_dropin, "dp": dp_line,
             # run statistics of the workload (measured, not configuration): slots, visible slots, tile instances, ...
             "workload_stats": {
                 "P_mean": avg(stats.get("P")), "V_mean": avg(stats.get("V")), "R_mean": avg(stats.get("R")),
@@ -557,6 +555,12 @@ def main():
                 "pairs_per_render": stats.get("pairs")},
             "measured_peaks": measured,
         }
+        if args.mode == "dp" and dp_line is not None:
+            line["chunks"] = {"value": line["value"], "ms_per_step": line["ms_per_step"], "e2e": line["e2e"]}
+            line["value"], line["ms_per_step"], line["e2e"] = dp_line["value"], dp_line["ms_per_step"], None
+            line["scaling"] = "weak"
+            line["config"]["multi_gpu"] = ("one chunk replicated, one camera per rank and step, gradients of the union of "
+                                           "touched rows exchanged through NVLink peer memory (see `dp`)")
         if args.impl == "reference":
             line["reference_kind"] = "unmodified reference CUDA extensions (oracle/_ref, sm_100a) under a restatement of its Python glue"
         print(json.dumps(line))

@@ -337,6 +337,32 @@ H3DGS_API int h3dgs_sparse_adam_compact(const H3dgsAdamTensor* tensors, int32_t 
                               const int64_t* compact_rows, const int32_t* compact_count, int32_t capacity,
                               const float* gate, h3dgs_stream_t stream);
 
+/* Camera-batch data parallelism over NVLink peer memory (SURVEY.md 8e mode B): an all-gather of every rank's
+ * gated compact gradient rows that is summed while it is read, then ONE sparse Adam step over the union -- the
+ * semantics of all-reduce(sum)/world of the per-row gradients followed by OurAdam.step(relevant)
+ * (train_post.py:171-190), without N-row tensors and without a host round trip.  All pointers are device pointers;
+ * peer_* may point into ANOTHER GPU's memory (symmetric memory / CUDA IPC mapping): the kernels only load from them.
+ *
+ * h3dgs_dp_pack: compact gradients (H3dgsGrads.compact_*; grads[k].data is [capacity, width]) -> the rows whose gate
+ *   is non-zero (gate NULL: all rows), packed as [count, sum of widths] floats + int32 store rows; *out_count is
+ *   reset by the call; *overflow is set to 1 when out_capacity is too small (the block is then invalid).
+ * h3dgs_dp_accumulate: add one rank's block into the local union; row_map is int32 [store rows], all -1 on entry to
+ *   the first call of a step.  Call once per rank, in rank order, on one stream: every replica then forms identical
+ *   sums.  *union_count must be zero before the first call of a step.
+ * h3dgs_dp_adam: param/moment update of the union rows with gradient = union_packed * scale (tensors[k].grad is
+ *   ignored), and row_map restored to -1 for those rows. */
+H3DGS_API int h3dgs_dp_pack(const H3dgsRowTensor* grads, int32_t num_tensors, const int64_t* compact_rows,
+                  const int32_t* compact_count, int32_t capacity, const float* gate, int32_t* out_rows,
+                  float* out_packed, int32_t* out_count, int32_t out_capacity, int32_t* overflow,
+                  h3dgs_stream_t stream);
+H3DGS_API int h3dgs_dp_accumulate(const int32_t* peer_rows, const float* peer_packed, const int32_t* peer_count,
+                        int32_t peer_capacity, int32_t width, int32_t* row_map, int32_t* union_rows,
+                        float* union_packed, int32_t* union_count, int32_t union_capacity, int32_t* overflow,
+                        h3dgs_stream_t stream);
+H3DGS_API int h3dgs_dp_adam(const H3dgsAdamTensor* tensors, int32_t num_tensors, const int32_t* union_rows,
+                  const int32_t* union_count, const float* union_packed, float scale, int32_t* row_map,
+                  int32_t union_capacity, h3dgs_stream_t stream);
+
 /* ------------------------------------------------------------------------------------------------
  * Hierarchy build.  Replaces the tree stages of the offline GaussianHierarchyCreator
  * (GH/mainHierarchyCreator.cpp:130-141): PointbasedKdTreeGenerator::generate (GH/PointbasedKdTreeGenerator.cpp:16-73),

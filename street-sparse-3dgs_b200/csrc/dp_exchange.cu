@@ -1,0 +1,237 @@
+// Gradient exchange of camera-batch data parallelism over NVLink peer memory (SURVEY.md 8e mode B, BASELINE.json
+// config 4: "camera batch data-parallel with NCCL grad allreduce").  The reference has no in-process parallelism;
+// the semantics are those of an all-reduce(sum) / world of the six per-row gradient tensors followed by
+// OurAdam.step(relevant) (train_post.py:171-190), restricted to the rows some rank's render touched.
+//
+// Every rank's backward leaves COMPACT gradients (H3dgsGrads.compact_*).  Instead of all-reducing N-row tensors or
+// a padded union, the exchange is an all-gather THROUGH PEER MEMORY that is summed while it is read:
+//   1. dp_pack_kernel        the rows whose gate (opacity gradient) is non-zero -> one packed [U, 59] block + row ids
+//                            in this rank's arena (symmetric memory: every peer maps it)
+//   2. (device-side barrier of the symmetric-memory handle: torch plumbing, no data)
+//   3. dp_accumulate_kernel  once per peer, IN RANK ORDER: streams the peer's block over NVLink (contiguous 236-byte
+//                            rows, fully coalesced remote loads) and adds it into a local union buffer; a local
+//                            row -> union-slot map assigns slots on first touch.  A peer lists a row at most once, so
+//                            one launch never adds twice into one slot, and launches are stream-ordered: every rank
+//                            forms the same sums in the same order and the replicas stay bit-identical.
+//   4. dp_adam_kernel        average + sparse Adam over the union, restoring the map to -1 on the way.
+// Bytes over NVLink per rank and step: (world - 1) x U x 240 B, read once, nothing written remotely.
+#include "common.cuh"
+
+namespace h3dgs {
+
+namespace {
+
+struct DpTensors {
+  const float* grad[H3DGS_ADAM_MAX_TENSORS];
+  int width[H3DGS_ADAM_MAX_TENSORS];
+  int start[H3DGS_ADAM_MAX_TENSORS + 1];
+  int n;
+};
+
+// one warp per 32 compact rows: ballot of the gate, one atomic per warp, then the warp copies the surviving rows
+__global__ void __launch_bounds__(256) dp_pack_kernel(const DpTensors t, const long long* __restrict__ compact_rows,
+                                                     const int* __restrict__ compact_count,
+                                                     const float* __restrict__ gate, int* __restrict__ out_rows,
+                                                     float* __restrict__ out_packed, int* __restrict__ out_count,
+                                                     int out_capacity, int* __restrict__ overflow) {
+  const int W = t.start[t.n];
+  const int U = *compact_count;
+  const int lane = threadIdx.x & 31;
+  const int warps = (gridDim.x * blockDim.x) >> 5;
+  for (int base = (((blockIdx.x * blockDim.x) + threadIdx.x) >> 5) * 32; base < U; base += warps * 32) {
+    const int i = base + lane;
+    const bool keep = i < U && (gate == nullptr || gate[i] != 0.0f);
+    const unsigned m = __ballot_sync(0xffffffffu, keep);
+    if (m == 0) continue;
+    int slot0 = 0;
+    if (lane == 0) slot0 = atomicAdd(out_count, __popc(m));
+    slot0 = __shfl_sync(0xffffffffu, slot0, 0);
+    if (slot0 + __popc(m) > out_capacity) {   // the arena is too small for this render: reported, nothing written
+      if (lane == 0) atomicExch(overflow, 1);
+      continue;
+    }
+    if (keep) out_rows[slot0 + __popc(m & ((1u << lane) - 1u))] = (int)compact_rows[i];
+    unsigned rest = m;
+    int slot = slot0;
+    while (rest) {
+      const int src = base + __ffs(rest) - 1;
+      rest &= rest - 1;
+      for (int e = lane; e < W; e += 32) {
+        int ti = 0;
+#pragma unroll
+        for (int k = 1; k < H3DGS_ADAM_MAX_TENSORS; ++k)
+          if (k < t.n && e >= t.start[k]) ti = k;
+        out_packed[(size_t)slot * W + e] = t.grad[ti][(size_t)src * t.width[ti] + (e - t.start[ti])];
+      }
+      ++slot;
+    }
+  }
+}
+
+// one warp per peer row; peer_* may be remote (NVLink) pointers
+__global__ void __launch_bounds__(256) dp_accumulate_kernel(const int* __restrict__ peer_rows,
+                                                           const float* __restrict__ peer_packed,
+                                                           const int* __restrict__ peer_count, int peer_capacity,
+                                                           int W,
+                                                           int* __restrict__ row_map, int* __restrict__ union_rows,
+                                                           float* __restrict__ union_packed,
+                                                           int* __restrict__ union_count, int union_capacity,
+                                                           int* __restrict__ overflow) {
+  int U = *peer_count;
+  if (U > peer_capacity) U = peer_capacity;   // the peer overflowed its arena (it reports that itself)
+  const int lane = threadIdx.x & 31;
+  const int warps = (gridDim.x * blockDim.x) >> 5;
+  for (int i = ((blockIdx.x * blockDim.x) + threadIdx.x) >> 5; i < U; i += warps) {
+    const int row = __ldg(peer_rows + i);
+    int slot = 0, first = 0;
+    if (lane == 0) {
+      slot = row_map[row];
+      if (slot < 0) {
+        slot = atomicAdd(union_count, 1);
+        first = 1;
+        if (slot < union_capacity) { row_map[row] = slot; union_rows[slot] = row; }
+      }
+    }
+    slot = __shfl_sync(0xffffffffu, slot, 0);
+    first = __shfl_sync(0xffffffffu, first, 0);
+    if (slot >= union_capacity) {
+      if (lane == 0) atomicExch(overflow, 2);
+      continue;
+    }
+    const float* src = peer_packed + (size_t)i * W;
+    float* dst = union_packed + (size_t)slot * W;
+    for (int e = lane; e < W; e += 32) {
+      const float v = src[e];
+      dst[e] = first ? v : __fadd_rn(dst[e], v);
+    }
+  }
+}
+
+struct DpAdam {
+  H3dgsAdamTensor t[H3DGS_ADAM_MAX_TENSORS];
+  int start[H3DGS_ADAM_MAX_TENSORS + 1];
+  int n;
+};
+
+// sparse Adam over the union: gradient = union_packed * scale (the 1/world average), arithmetic as sparse_adam.cu
+__global__ void __launch_bounds__(256) dp_adam_kernel(const DpAdam pk, const int* __restrict__ union_rows,
+                                                     const int* __restrict__ union_count,
+                                                     const float* __restrict__ union_packed, float scale,
+                                                     int* __restrict__ row_map, int union_capacity) {
+  const int W = pk.start[pk.n];
+  long long U = *union_count;
+  if (U > union_capacity) U = union_capacity;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x; gid < U * W; gid += stride) {
+    const long long k = gid / W;
+    const int e = (int)(gid - k * W);
+    int ti = 0;
+#pragma unroll
+    for (int i = 1; i < H3DGS_ADAM_MAX_TENSORS; ++i)
+      if (i < pk.n && e >= pk.start[i]) ti = i;
+    const H3dgsAdamTensor& T = pk.t[ti];
+    const int row = union_rows[k];
+    if (e == 0 && row_map != nullptr) row_map[row] = -1;
+    const size_t off = (size_t)row * T.width + (e - pk.start[ti]);
+    const float g = __fmul_rn(union_packed[gid], scale);
+    float m = T.exp_avg[off];
+    float v = T.exp_avg_sq[off];
+    float p = T.param[off];
+    m = __fmaf_rn(T.one_minus_beta1, g, __fmul_rn(m, T.beta1));
+    v = __fmaf_rn(__fmul_rn(T.one_minus_beta2, g), g, __fmul_rn(v, T.beta2));
+    const float inv_bc2 = 1.0f / T.bias_correction2_sqrt;
+    const float denom = __fadd_rn(__fmul_rn(sqrtf(v), inv_bc2), T.eps);
+    p = __fmaf_rn(-T.step_size, m / denom, p);
+    T.exp_avg[off] = m;
+    T.exp_avg_sq[off] = v;
+    T.param[off] = p;
+  }
+}
+
+int grid_for(long long threads) {
+  long long blocks = (threads + 255) / 256;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  if (blocks < 1) blocks = 1;
+  return (int)blocks;
+}
+
+}  // namespace
+
+}  // namespace h3dgs
+
+extern "C" {
+
+int h3dgs_dp_pack(const H3dgsRowTensor* grads, int32_t num_tensors, const int64_t* compact_rows,
+                  const int32_t* compact_count, int32_t capacity, const float* gate, int32_t* out_rows,
+                  float* out_packed, int32_t* out_count, int32_t out_capacity, int32_t* overflow,
+                  h3dgs_stream_t stream) {
+  using namespace h3dgs;
+  if (!grads || num_tensors <= 0 || num_tensors > H3DGS_ADAM_MAX_TENSORS || !compact_rows || !compact_count ||
+      !out_rows || !out_packed || !out_count || !overflow || capacity < 0 || out_capacity < 0)
+    return fail(H3DGS_EINVAL, "h3dgs_dp_pack: bad argument");
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  DpTensors t;
+  t.n = num_tensors;
+  int acc = 0;
+  for (int i = 0; i < num_tensors; ++i) {
+    if (!grads[i].data || grads[i].width <= 0) return fail(H3DGS_EINVAL, "h3dgs_dp_pack: bad gradient tensor");
+    t.grad[i] = grads[i].data;
+    t.width[i] = grads[i].width;
+    t.start[i] = acc;
+    acc += grads[i].width;
+  }
+  for (int i = num_tensors; i <= H3DGS_ADAM_MAX_TENSORS; ++i) t.start[i] = acc;
+  H3_CUDA(cudaMemsetAsync(out_count, 0, sizeof(int32_t), s));
+  if (capacity == 0) return 0;
+  ProfScope ps(K_ADAM, s);
+  dp_pack_kernel<<<grid_for(capacity), 256, 0, s>>>(t, reinterpret_cast<const long long*>(compact_rows), compact_count,
+                                                     gate, out_rows, out_packed, out_count, out_capacity, overflow);
+  H3_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int h3dgs_dp_accumulate(const int32_t* peer_rows, const float* peer_packed, const int32_t* peer_count,
+                        int32_t peer_capacity, int32_t width, int32_t* row_map, int32_t* union_rows,
+                        float* union_packed, int32_t* union_count, int32_t union_capacity, int32_t* overflow,
+                        h3dgs_stream_t stream) {
+  using namespace h3dgs;
+  if (!peer_rows || !peer_packed || !peer_count || width <= 0 || !row_map || !union_rows || !union_packed ||
+      !union_count || !overflow || peer_capacity < 0 || union_capacity < 0)
+    return fail(H3DGS_EINVAL, "h3dgs_dp_accumulate: bad argument");
+  if (peer_capacity == 0) return 0;
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  ProfScope ps(K_ADAM, s);
+  dp_accumulate_kernel<<<grid_for((long long)peer_capacity * 32), 256, 0, s>>>(
+      peer_rows, peer_packed, peer_count, peer_capacity, width, row_map, union_rows, union_packed, union_count, union_capacity, overflow);
+  H3_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int h3dgs_dp_adam(const H3dgsAdamTensor* tensors, int32_t num_tensors, const int32_t* union_rows,
+                  const int32_t* union_count, const float* union_packed, float scale, int32_t* row_map,
+                  int32_t union_capacity, h3dgs_stream_t stream) {
+  using namespace h3dgs;
+  if (!tensors || num_tensors <= 0 || num_tensors > H3DGS_ADAM_MAX_TENSORS || !union_rows || !union_count ||
+      !union_packed || union_capacity < 0)
+    return fail(H3DGS_EINVAL, "h3dgs_dp_adam: bad argument");
+  DpAdam pk;
+  pk.n = num_tensors;
+  int acc = 0;
+  for (int i = 0; i < num_tensors; ++i) {
+    if (!tensors[i].param || !tensors[i].exp_avg || !tensors[i].exp_avg_sq || tensors[i].width <= 0)
+      return fail(H3DGS_EINVAL, "h3dgs_dp_adam: bad tensor");
+    pk.t[i] = tensors[i];
+    pk.start[i] = acc;
+    acc += tensors[i].width;
+  }
+  for (int i = num_tensors; i <= H3DGS_ADAM_MAX_TENSORS; ++i) pk.start[i] = acc;
+  if (union_capacity == 0) return 0;
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  ProfScope ps(K_ADAM, s);
+  dp_adam_kernel<<<grid_for((long long)union_capacity * acc), 256, 0, s>>>(pk, union_rows, union_count, union_packed,
+                                                                           scale, row_map, union_capacity);
+  H3_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // extern "C"

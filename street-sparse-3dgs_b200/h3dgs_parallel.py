@@ -96,3 +96,155 @@ def allreduce_sparse_rows(tensors: Sequence[torch.Tensor], row_mask: torch.Tenso
             p.div_(world)
         t.index_copy_(0, rows, p)
     return rows
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Camera-batch data parallelism on compact gradients, exchanged through NVLink peer memory (csrc/dp_exchange.cu)
+# ---------------------------------------------------------------------------------------------------------------
+
+class RowArena:
+    """One rank's exchange block: int32 header (count, overflow flag), int32 store rows and the packed
+    [capacity, width] gradients, double buffered by step parity.  Allocated in torch symmetric memory when a process
+    group is given (every peer then maps it and the accumulate kernels load from it directly over NVLink), as a plain
+    CUDA tensor otherwise (world 1, and the single-process tests that stand several "ranks" side by side)."""
+
+    HEADER = 64   # int32 words in front of each buffer (count at 0, overflow at 1; the rest keeps 256-byte alignment)
+
+    def __init__(self, capacity, width, device, group=None):
+        self.capacity, self.width = int(capacity), int(width)
+        self.words = self.HEADER + self.capacity + self.capacity * self.width
+        self.words += (-self.words) % 64
+        self.handle = None
+        if group is not None and dist.get_world_size(group) > 1:
+            import torch.distributed._symmetric_memory as symm_mem
+            self.buf = symm_mem.empty(2 * self.words, dtype=torch.int32, device=device)
+            self.handle = symm_mem.rendezvous(self.buf, group)
+            self.base_ptrs = [int(p) for p in self.handle.buffer_ptrs]
+            self.rank = dist.get_rank(group)
+        else:
+            self.buf = torch.empty(2 * self.words, dtype=torch.int32, device=device)
+            self.base_ptrs = [self.buf.data_ptr()]
+            self.rank = 0
+        self.buf.zero_()
+
+    def ptrs(self, base, parity):
+        """(count, overflow, rows, packed) device addresses of one buffer of the block that starts at `base`."""
+        b = base + 4 * self.words * parity
+        return b, b + 4, b + 4 * self.HEADER, b + 4 * (self.HEADER + self.capacity)
+
+    def local(self, parity):
+        return self.ptrs(self.base_ptrs[self.rank], parity)
+
+    def barrier(self):
+        if self.handle is not None:
+            self.handle.barrier(channel=0)
+
+
+class CompactRowExchange:
+    """``step(sparse_grads, optimizer)``: this rank's compact gradients (``render_post(sparse_grads=...)``) are summed
+    with every peer's over the union of touched rows, averaged, and applied by ONE sparse Adam step -- the result of
+    ``all_reduce(grad) / world`` + ``optimizer.step(relevant)`` with ``relevant`` = rows whose opacity gradient is
+    non-zero on some rank, bit-identical on every replica.  See csrc/dp_exchange.cu for the data path."""
+
+    def __init__(self, optimizer, store_rows, capacity, group=None, union_capacity=None):
+        import h3dgs_native as nat
+        self.nat = nat
+        self.opt = optimizer
+        params = [p for g in optimizer.param_groups for p in g["params"]]
+        if not params or any(p.size(0) != store_rows for p in params):
+            raise ValueError("every parameter tensor must have `store_rows` rows")
+        self.params = params
+        self.widths = [p.numel() // store_rows for p in params]
+        self.width = sum(self.widths)
+        self.dev = params[0].device
+        self.group = group
+        self.world = dist.get_world_size(group) if (group is not None or dist.is_initialized()) else 1
+        if self.world > 1 and group is None:
+            group = dist.group.WORLD
+        self.arena = RowArena(capacity, self.width, self.dev, group if self.world > 1 else None)
+        self.ucap = int(union_capacity if union_capacity is not None else min(store_rows, capacity * self.world))
+        self.row_map = torch.full((store_rows,), -1, dtype=torch.int32, device=self.dev)
+        self.union_rows = torch.empty(self.ucap, dtype=torch.int32, device=self.dev)
+        self.union_packed = torch.empty((self.ucap, self.width), dtype=torch.float32, device=self.dev)
+        self.flags = torch.zeros(4, dtype=torch.int32, device=self.dev)   # [0] union count, [1] overflow
+        self.parity = 0
+        self.steps = 0
+
+    def pack(self, sg, parity=None, gate="opacity"):
+        """Stage 1: gated compact rows of `sg` -> this rank's arena."""
+        nat = self.nat
+        parity = self.parity if parity is None else parity
+        by_ptr = {sg.params[k].data_ptr(): k for k in sg.grads if k in sg.params}
+        arr = (nat.RowTensor * len(self.params))()
+        for i, p in enumerate(self.params):
+            name = by_ptr.get(p.data_ptr())
+            if name is None:
+                raise RuntimeError("a parameter of the optimizer has no compact gradient in this SparseGradients")
+            arr[i].data = sg.grads[name].data_ptr()
+            arr[i].width = self.widths[i]
+        gate_t = sg.grads.get(gate) if gate is not None else None
+        cnt, ovf, rows, packed = self.arena.local(parity)
+        nat.check(nat.lib().h3dgs_dp_pack(arr, len(self.params), sg.rows.data_ptr(), sg.count.data_ptr(), sg.capacity,
+                                          nat.ptr(gate_t), rows, packed, cnt, self.arena.capacity, ovf,
+                                          nat.stream_handle()), "h3dgs_dp_pack")
+
+    def accumulate(self, bases, parity=None):
+        """Stage 3: add the blocks that start at `bases` (one per rank, rank order) into the local union."""
+        nat = self.nat
+        parity = self.parity if parity is None else parity
+        self.flags[0:1].zero_()   # the union count; the overflow flag is sticky
+        for base in bases:
+            cnt, _, rows, packed = self.arena.ptrs(base, parity)
+            nat.check(nat.lib().h3dgs_dp_accumulate(rows, packed, cnt, self.arena.capacity, self.width,
+                                                    self.row_map.data_ptr(), self.union_rows.data_ptr(),
+                                                    self.union_packed.data_ptr(), self.flags.data_ptr(), self.ucap,
+                                                    self.flags.data_ptr() + 4, nat.stream_handle()),
+                      "h3dgs_dp_accumulate")
+
+    def apply(self, world=None):
+        """Stage 4: averaged sparse Adam over the union."""
+        self.opt.step_union(self.params, self.union_rows, self.flags, self.union_packed,
+                            1.0 / (world if world is not None else self.world), self.row_map, self.ucap)
+
+    def step(self, sg, gate="opacity"):
+        if sg is None or not sg.ready:
+            raise RuntimeError("CompactRowExchange.step: the SparseGradients object has not been filled by a backward pass")
+        self.pack(sg, gate=gate)
+        self.arena.barrier()          # every peer's block of this parity is complete and visible
+        self.accumulate(self.arena.base_ptrs)
+        self.apply()
+        self.parity ^= 1              # a peer may still be reading this buffer: the next step packs into the other one
+        self.steps += 1
+
+    def check_overflow(self):
+        """Host-side check (a sync): raises when an arena or the union was too small at some step."""
+        ovf_local = int(self.arena.buf[1]) | int(self.arena.buf[self.arena.words + 1])
+        if ovf_local or int(self.flags[1]):
+            raise RuntimeError("CompactRowExchange: capacity exceeded (arena %d rows, union %d rows)"
+                               % (self.arena.capacity, self.ucap))
+
+
+class CostBucketSampler:
+    """Camera order for synchronous data parallelism: a step lasts as long as its slowest rank, and street views differ
+    2x in cost (looking along the street vs across it), so cameras are sorted by a cost estimate (tile instances of
+    the previous epoch's render, any monotone proxy) and dealt out in groups of `world` NEIGHBOURS in that order; the
+    groups are then visited in a seeded random order and rotated over the ranks.  `batch(step)` -> the camera index of
+    every rank; identical on all ranks (no communication)."""
+
+    def __init__(self, costs, world, seed=0):
+        import random
+        order = sorted(range(len(costs)), key=lambda i: (-float(costs[i]), i))
+        self.world = world
+        self.groups = [order[i:i + world] for i in range(0, len(order) - len(order) % world, world)]
+        if not self.groups:   # fewer cameras than ranks: wrap around
+            self.groups = [[order[i % len(order)] for i in range(world)]]
+        self.visit = list(range(len(self.groups)))
+        random.Random(seed).shuffle(self.visit)
+
+    def batch(self, step):
+        g = self.groups[self.visit[step % len(self.visit)]]
+        r = (step // len(self.visit)) % self.world
+        return g[r:] + g[:r]
+
+    def camera(self, step, rank):
+        return self.batch(step)[rank]

@@ -105,6 +105,37 @@ class Adam(Optimizer):
                       "h3dgs_sparse_adam_compact")
 
     @torch.no_grad()
+    def step_union(self, params, union_rows, union_count, union_packed, scale, row_map, capacity):
+        """One step from the summed gradients of a data-parallel exchange (h3dgs_parallel.CompactRowExchange):
+        ``union_packed`` [capacity, sum of widths] holds, for each of the ``union_count[0]`` (device) rows listed in
+        ``union_rows``, the concatenated gradients of ``params`` in that order; ``scale`` (1 / world) turns the sum into
+        the average.  ``row_map`` is the exchange's row -> slot scratch, restored to -1 by the kernel."""
+        order = {p.data_ptr(): i for i, p in enumerate(params)}
+        batch = [None] * len(params)
+        for group in self.param_groups:
+            if group['amsgrad'] or group['maximize'] or group['weight_decay'] != 0 or group['capturable'] \
+                    or group['foreach']:
+                raise NotImplementedError("the fused sparse Adam implements the options the reference training uses")
+            for p in group['params']:
+                i = order.get(p.data_ptr())
+                if i is None:
+                    continue
+                if not p.is_cuda or p.dtype != torch.float32 or not p.is_contiguous():
+                    raise RuntimeError("fused sparse Adam needs contiguous float32 CUDA parameters (no CPU fallback)")
+                state, step_size, bc2_sqrt, beta1, beta2 = self._update_terms(group, p)
+                width = p.numel() // max(p.size(0), 1)
+                batch[i] = nat.AdamTensor(p.data_ptr(), None, state['exp_avg'].data_ptr(), state['exp_avg_sq'].data_ptr(),
+                                          width, step_size, bc2_sqrt, beta1, beta2, group['eps'], 1 - beta1, 1 - beta2)
+        if any(b is None for b in batch):
+            raise RuntimeError("step_union: a tensor of the exchange is not a parameter of this optimizer")
+        if len(batch) > nat.ADAM_MAX_TENSORS:
+            raise NotImplementedError("step_union handles up to %d parameter tensors" % nat.ADAM_MAX_TENSORS)
+        arr = (nat.AdamTensor * len(batch))(*batch)
+        nat.check(nat.lib().h3dgs_dp_adam(arr, len(batch), union_rows.data_ptr(), union_count.data_ptr(),
+                                          union_packed.data_ptr(), float(scale), nat.ptr(row_map), int(capacity),
+                                          nat.stream_handle()), "h3dgs_dp_adam")
+
+    @torch.no_grad()
     def step(self, relevant, closure=None):
         """One optimisation step over the rows in ``relevant`` (1-D LongTensor of row indices; empty
         means every row)."""

@@ -69,3 +69,16 @@ def test_single_process_is_a_noop():
     hp.allreduce_dense(t)
     rows = hp.allreduce_sparse_rows(t, torch.tensor([True, False, True, False]))
     assert rows.tolist() == [0, 2] and torch.equal(t[0], torch.ones(4, 3))
+
+
+def test_cost_bucket_sampler_groups_neighbours():
+    import h3dgs_parallel as par
+    costs = [5.0, 1.0, 5.2, 1.1, 4.9, 0.9, 5.1, 1.2]
+    s = par.CostBucketSampler(costs, 2, seed=1)
+    seen = []
+    for step in range(8):
+        b = s.batch(step)
+        assert len(b) == 2 and abs(costs[b[0]] - costs[b[1]]) < 0.5, "a step mixes a heavy and a light camera"
+        seen += b
+    assert sorted(seen) == sorted(list(range(8)) * 2)
+    assert {s.camera(0, 0), s.camera(0, 1)} == {s.camera(4, 0), s.camera(4, 1)} and s.camera(0, 0) == s.camera(4, 1)
