@@ -103,25 +103,35 @@ def run(args, dev, rank, world, attrs, timed, dcol, ddep):
     ex.check_overflow()
     sums = [None] * world
     dist.all_gather_object(sums, _checksum(hm.parameters()))
-    union = int(ex.flags[0])
 
-    # where the exchange time goes: pack / barrier / accumulate per peer / adam, CUDA events on one step
-    sg = render(sampler.camera(0, rank))
-    ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
-    dist.barrier()
-    torch.cuda.synchronize()
-    ev[0].record()
-    ex.pack(sg)
-    ev[1].record()
-    ex.arena.barrier()
-    ev[2].record()
-    ex.accumulate(ex.arena.base_ptrs)
-    ev[3].record()
-    ex.apply()
-    ev[4].record()
-    ex.parity ^= 1
-    torch.cuda.synchronize()
-    stages = {n: ev[i].elapsed_time(ev[i + 1]) for i, n in enumerate(("pack", "barrier", "accumulate", "adam"))}
+    # where the exchange time goes: render / pack / barrier (includes waiting for the slowest rank) / accumulate per
+    # peer / adam, CUDA events on one step of the heaviest and one of the lightest camera group
+    def stage_times(step_index):
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(6)]
+        dist.barrier()
+        torch.cuda.synchronize()
+        ev[0].record()
+        sg = render(sampler.camera(step_index, rank))
+        ev[1].record()
+        ex.pack(sg)
+        ev[2].record()
+        ex.arena.barrier()
+        ev[3].record()
+        ex.accumulate(ex.arena.base_ptrs)
+        ev[4].record()
+        ex.apply()
+        ev[5].record()
+        ex.parity ^= 1
+        torch.cuda.synchronize()
+        out = {n: ev[i].elapsed_time(ev[i + 1]) for i, n in enumerate(("render", "pack", "barrier", "accumulate", "adam"))}
+        out["union_rows"] = int(ex.flags[0])
+        out["cameras"] = sampler.batch(step_index)
+        return out
+    group_cost = [sum(costs[c] for c in sampler.groups[g]) for g in sampler.visit]
+    heavy_step = max(range(len(group_cost)), key=lambda i: group_cost[i])
+    light_step = min(range(len(group_cost)), key=lambda i: group_cost[i])
+    stages = {"heaviest_group": stage_times(heavy_step), "lightest_group": stage_times(light_step)}
+    union = stages["heaviest_group"]["union_rows"]
 
     single = 1000.0 * steps / ms_single
     value = world * 1000.0 * steps / ms_dp

@@ -68,7 +68,10 @@ __global__ void __launch_bounds__(256) dp_pack_kernel(const DpTensors t, const l
   }
 }
 
-// one warp per peer row; peer_* may be remote (NVLink) pointers
+// 32 peer rows per warp iteration: every lane resolves one row's union slot (one warp-aggregated atomic for the new
+// ones), then the warp moves the rows four at a time so that eight remote loads per lane are in flight.  peer_* may
+// be remote (NVLink) pointers; W <= 64.
+constexpr int DP_RB = 4;
 __global__ void __launch_bounds__(256) dp_accumulate_kernel(const int* __restrict__ peer_rows,
                                                            const float* __restrict__ peer_packed,
                                                            const int* __restrict__ peer_count, int peer_capacity,
@@ -81,28 +84,58 @@ __global__ void __launch_bounds__(256) dp_accumulate_kernel(const int* __restric
   if (U > peer_capacity) U = peer_capacity;   // the peer overflowed its arena (it reports that itself)
   const int lane = threadIdx.x & 31;
   const int warps = (gridDim.x * blockDim.x) >> 5;
-  for (int i = ((blockIdx.x * blockDim.x) + threadIdx.x) >> 5; i < U; i += warps) {
-    const int row = __ldg(peer_rows + i);
-    int slot = 0, first = 0;
-    if (lane == 0) {
+  const bool two = lane + 32 < W;
+  for (int base = (((blockIdx.x * blockDim.x) + threadIdx.x) >> 5) * 32; base < U; base += warps * 32) {
+    const int i = base + lane;
+    int slot = -1;
+    bool fresh = false;
+    int row = 0;
+    if (i < U) {
+      row = peer_rows[i];
       slot = row_map[row];
-      if (slot < 0) {
-        slot = atomicAdd(union_count, 1);
-        first = 1;
+      fresh = slot < 0;
+    }
+    const unsigned nm = __ballot_sync(0xffffffffu, fresh);
+    if (nm) {
+      int s0 = 0;
+      if (lane == 0) s0 = atomicAdd(union_count, __popc(nm));
+      s0 = __shfl_sync(0xffffffffu, s0, 0);
+      if (fresh) {
+        slot = s0 + __popc(nm & ((1u << lane) - 1u));
         if (slot < union_capacity) { row_map[row] = slot; union_rows[slot] = row; }
       }
     }
-    slot = __shfl_sync(0xffffffffu, slot, 0);
-    first = __shfl_sync(0xffffffffu, first, 0);
-    if (slot >= union_capacity) {
-      if (lane == 0) atomicExch(overflow, 2);
-      continue;
-    }
-    const float* src = peer_packed + (size_t)i * W;
-    float* dst = union_packed + (size_t)slot * W;
-    for (int e = lane; e < W; e += 32) {
-      const float v = src[e];
-      dst[e] = first ? v : __fadd_rn(dst[e], v);
+    if (i < U && slot >= union_capacity) { atomicExch(overflow, 2); slot = -1; }
+    const int n = min(32, U - base);
+    for (int j = 0; j < n; j += DP_RB) {
+      int sj[DP_RB], fj[DP_RB];
+      float a[DP_RB][2], d[DP_RB][2];
+#pragma unroll
+      for (int r = 0; r < DP_RB; ++r) {
+        sj[r] = __shfl_sync(0xffffffffu, slot, (j + r) & 31);
+        fj[r] = __shfl_sync(0xffffffffu, (int)fresh, (j + r) & 31);
+        if (j + r >= n) sj[r] = -1;
+      }
+#pragma unroll
+      for (int r = 0; r < DP_RB; ++r) {
+        a[r][0] = a[r][1] = d[r][0] = d[r][1] = 0.0f;
+        if (sj[r] < 0) continue;
+        const float* src = peer_packed + (size_t)(base + j + r) * W;
+        const float* dst = union_packed + (size_t)sj[r] * W;
+        a[r][0] = src[lane];
+        if (two) a[r][1] = src[lane + 32];
+        if (!fj[r]) {
+          d[r][0] = dst[lane];
+          if (two) d[r][1] = dst[lane + 32];
+        }
+      }
+#pragma unroll
+      for (int r = 0; r < DP_RB; ++r) {
+        if (sj[r] < 0) continue;
+        float* dst = union_packed + (size_t)sj[r] * W;
+        dst[lane] = fj[r] ? a[r][0] : __fadd_rn(d[r][0], a[r][0]);
+        if (two) dst[lane + 32] = fj[r] ? a[r][1] : __fadd_rn(d[r][1], a[r][1]);
+      }
     }
   }
 }
@@ -113,38 +146,75 @@ struct DpAdam {
   int n;
 };
 
-// sparse Adam over the union: gradient = union_packed * scale (the 1/world average), arithmetic as sparse_adam.cu
+// Sparse Adam over the union: gradient = union_packed * scale (the 1/world average), arithmetic as sparse_adam.cu.
+// A warp takes four rows per iteration, lanes cover a row's W <= 64 floats (two per lane): the 4 x 2 x 4 loads of a
+// lane are issued before the first dependent instruction -- the rows are scattered over a multi-GB store, the kernel
+// lives on memory-level parallelism.
+__device__ __forceinline__ void adam_update(const H3dgsAdamTensor& T, float g, float& m, float& v, float& p) {
+  m = __fmaf_rn(T.one_minus_beta1, g, __fmul_rn(m, T.beta1));
+  v = __fmaf_rn(__fmul_rn(T.one_minus_beta2, g), g, __fmul_rn(v, T.beta2));
+  const float inv_bc2 = 1.0f / T.bias_correction2_sqrt;
+  const float denom = __fadd_rn(__fmul_rn(sqrtf(v), inv_bc2), T.eps);
+  p = __fmaf_rn(-T.step_size, m / denom, p);
+}
+
 __global__ void __launch_bounds__(256) dp_adam_kernel(const DpAdam pk, const int* __restrict__ union_rows,
                                                      const int* __restrict__ union_count,
                                                      const float* __restrict__ union_packed, float scale,
                                                      int* __restrict__ row_map, int union_capacity) {
   const int W = pk.start[pk.n];
-  long long U = *union_count;
+  int U = *union_count;
   if (U > union_capacity) U = union_capacity;
-  const long long stride = (long long)gridDim.x * blockDim.x;
-  for (long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x; gid < U * W; gid += stride) {
-    const long long k = gid / W;
-    const int e = (int)(gid - k * W);
-    int ti = 0;
+  const int lane = threadIdx.x & 31;
+  const int warps = (gridDim.x * blockDim.x) >> 5;
+  // the two elements of a row this lane owns, and the tensor each falls into
+  int ti[2], col[2];
+  bool on[2];
+#pragma unroll
+  for (int q = 0; q < 2; ++q) {
+    const int e = lane + 32 * q;
+    on[q] = e < W;
+    int t = 0;
 #pragma unroll
     for (int i = 1; i < H3DGS_ADAM_MAX_TENSORS; ++i)
-      if (i < pk.n && e >= pk.start[i]) ti = i;
-    const H3dgsAdamTensor& T = pk.t[ti];
-    const int row = union_rows[k];
-    if (e == 0 && row_map != nullptr) row_map[row] = -1;
-    const size_t off = (size_t)row * T.width + (e - pk.start[ti]);
-    const float g = __fmul_rn(union_packed[gid], scale);
-    float m = T.exp_avg[off];
-    float v = T.exp_avg_sq[off];
-    float p = T.param[off];
-    m = __fmaf_rn(T.one_minus_beta1, g, __fmul_rn(m, T.beta1));
-    v = __fmaf_rn(__fmul_rn(T.one_minus_beta2, g), g, __fmul_rn(v, T.beta2));
-    const float inv_bc2 = 1.0f / T.bias_correction2_sqrt;
-    const float denom = __fadd_rn(__fmul_rn(sqrtf(v), inv_bc2), T.eps);
-    p = __fmaf_rn(-T.step_size, m / denom, p);
-    T.exp_avg[off] = m;
-    T.exp_avg_sq[off] = v;
-    T.param[off] = p;
+      if (i < pk.n && e >= pk.start[i]) t = i;
+    ti[q] = t;
+    col[q] = e - pk.start[t];
+  }
+  for (int base = (((blockIdx.x * blockDim.x) + threadIdx.x) >> 5) * DP_RB; base < U; base += warps * DP_RB) {
+    int row[DP_RB];
+    float g[DP_RB][2], m[DP_RB][2], v[DP_RB][2], p[DP_RB][2];
+#pragma unroll
+    for (int r = 0; r < DP_RB; ++r) row[r] = base + r < U ? union_rows[base + r] : -1;
+#pragma unroll
+    for (int r = 0; r < DP_RB; ++r) {
+      if (row[r] < 0) continue;
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        if (!on[q]) continue;
+        const H3dgsAdamTensor& T = pk.t[ti[q]];
+        const size_t off = (size_t)row[r] * T.width + col[q];
+        g[r][q] = union_packed[(size_t)(base + r) * W + lane + 32 * q];
+        m[r][q] = T.exp_avg[off];
+        v[r][q] = T.exp_avg_sq[off];
+        p[r][q] = T.param[off];
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < DP_RB; ++r) {
+      if (row[r] < 0) continue;
+      if (lane == 0 && row_map != nullptr) row_map[row[r]] = -1;
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        if (!on[q]) continue;
+        const H3dgsAdamTensor& T = pk.t[ti[q]];
+        const size_t off = (size_t)row[r] * T.width + col[q];
+        adam_update(T, __fmul_rn(g[r][q], scale), m[r][q], v[r][q], p[r][q]);
+        T.exp_avg[off] = m[r][q];
+        T.exp_avg_sq[off] = v[r][q];
+        T.param[off] = p[r][q];
+      }
+    }
   }
 }
 
@@ -199,9 +269,10 @@ int h3dgs_dp_accumulate(const int32_t* peer_rows, const float* peer_packed, cons
       !union_count || !overflow || peer_capacity < 0 || union_capacity < 0)
     return fail(H3DGS_EINVAL, "h3dgs_dp_accumulate: bad argument");
   if (peer_capacity == 0) return 0;
+  if (width > 64) return fail(H3DGS_EINVAL, "h3dgs_dp_accumulate: rows wider than 64 floats are not supported");
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   ProfScope ps(K_ADAM, s);
-  dp_accumulate_kernel<<<grid_for((long long)peer_capacity * 32), 256, 0, s>>>(
+  dp_accumulate_kernel<<<grid_for((long long)peer_capacity), 256, 0, s>>>(
       peer_rows, peer_packed, peer_count, peer_capacity, width, row_map, union_rows, union_packed, union_count, union_capacity, overflow);
   H3_CUDA(cudaGetLastError());
   return 0;
@@ -226,9 +297,10 @@ int h3dgs_dp_adam(const H3dgsAdamTensor* tensors, int32_t num_tensors, const int
   }
   for (int i = num_tensors; i <= H3DGS_ADAM_MAX_TENSORS; ++i) pk.start[i] = acc;
   if (union_capacity == 0) return 0;
+  if (acc > 64) return fail(H3DGS_EINVAL, "h3dgs_dp_adam: rows wider than 64 floats are not supported");
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   ProfScope ps(K_ADAM, s);
-  dp_adam_kernel<<<grid_for((long long)union_capacity * acc), 256, 0, s>>>(pk, union_rows, union_count, union_packed,
+  dp_adam_kernel<<<grid_for((long long)union_capacity * 32 / DP_RB), 256, 0, s>>>(pk, union_rows, union_count, union_packed,
                                                                            scale, row_map, union_capacity);
   H3_CUDA(cudaGetLastError());
   return 0;

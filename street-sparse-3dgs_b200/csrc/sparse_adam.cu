@@ -53,7 +53,78 @@ __global__ void __launch_bounds__(256) sparse_adam_kernel(const AdamPack pk,
   T.param[off] = p;
 }
 
-// compact gradients: row i of every grad tensor belongs to store row rows[i]; the row count lives on the device
+// compact gradients: row i of every grad tensor belongs to store row rows[i]; the row count lives on the device.
+// A warp takes four rows per iteration and its lanes cover a row's floats (two per lane, rows of up to 64 floats):
+// the 4 x 2 x 4 loads of a lane are issued before the first dependent instruction.  The rows are scattered over a
+// multi-GB store, so the kernel lives on memory-level parallelism, not on occupancy alone.
+constexpr int ADAM_RB = 4;
+__global__ void __launch_bounds__(256) sparse_adam_compact_rows_kernel(const AdamPack pk,
+                                                                       const long long* __restrict__ rows,
+                                                                       const int* __restrict__ count,
+                                                                       const float* __restrict__ gate) {
+  const int W = pk.start[pk.n];
+  const int U = *count;
+  const int lane = threadIdx.x & 31;
+  const int warps = (gridDim.x * blockDim.x) >> 5;
+  int ti[2], col[2];
+  bool on[2];
+#pragma unroll
+  for (int q = 0; q < 2; ++q) {
+    const int e = lane + 32 * q;
+    on[q] = e < W;
+    int t = 0;
+#pragma unroll
+    for (int i = 1; i < H3DGS_ADAM_MAX_TENSORS; ++i)
+      if (i < pk.n && e >= pk.start[i]) t = i;
+    ti[q] = t;
+    col[q] = e - pk.start[t];
+  }
+  for (int base = (((blockIdx.x * blockDim.x) + threadIdx.x) >> 5) * ADAM_RB; base < U; base += warps * ADAM_RB) {
+    long long row[ADAM_RB];
+    float g[ADAM_RB][2], m[ADAM_RB][2], v[ADAM_RB][2], p[ADAM_RB][2];
+#pragma unroll
+    for (int r = 0; r < ADAM_RB; ++r) {
+      const int k = base + r;
+      row[r] = (k < U && (gate == nullptr || gate[k] != 0.0f)) ? rows[k] : -1;
+    }
+#pragma unroll
+    for (int r = 0; r < ADAM_RB; ++r) {
+      if (row[r] < 0) continue;
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        if (!on[q]) continue;
+        const H3dgsAdamTensor& T = pk.t[ti[q]];
+        const size_t off = (size_t)row[r] * T.width + col[q];
+        g[r][q] = T.grad[(size_t)(base + r) * T.width + col[q]];
+        m[r][q] = T.exp_avg[off];
+        v[r][q] = T.exp_avg_sq[off];
+        p[r][q] = T.param[off];
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < ADAM_RB; ++r) {
+      if (row[r] < 0) continue;
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        if (!on[q]) continue;
+        const H3dgsAdamTensor& T = pk.t[ti[q]];
+        const size_t off = (size_t)row[r] * T.width + col[q];
+        float mm = m[r][q], vv = v[r][q], pp = p[r][q];
+        const float gg = g[r][q];
+        mm = __fmaf_rn(T.one_minus_beta1, gg, __fmul_rn(mm, T.beta1));
+        vv = __fmaf_rn(__fmul_rn(T.one_minus_beta2, gg), gg, __fmul_rn(vv, T.beta2));
+        const float inv_bc2 = 1.0f / T.bias_correction2_sqrt;
+        const float denom = __fadd_rn(__fmul_rn(sqrtf(vv), inv_bc2), T.eps);
+        pp = __fmaf_rn(-T.step_size, mm / denom, pp);
+        T.exp_avg[off] = mm;
+        T.exp_avg_sq[off] = vv;
+        T.param[off] = pp;
+      }
+    }
+  }
+}
+
+// general form (rows wider than 64 floats): one thread per element
 __global__ void __launch_bounds__(256) sparse_adam_compact_kernel(const AdamPack pk,
                                                                   const long long* __restrict__ rows,
                                                                   const int* __restrict__ count,
@@ -150,7 +221,14 @@ cudaError_t run_sparse_adam_compact(const H3dgsAdamTensor* tensors, int n, const
   long long blocks = (work + 255) / 256;
   if (blocks > 148 * 64) blocks = 148 * 64;
   ProfScope ps(K_ADAM, s);
-  sparse_adam_compact_kernel<<<(unsigned)blocks, 256, 0, s>>>(pk, rows, count, gate);
+  if (acc <= 64) {
+    long long b2 = ((long long)capacity * 32 / ADAM_RB + 255) / 256;
+    if (b2 > 148 * 16) b2 = 148 * 16;
+    if (b2 < 1) b2 = 1;
+    sparse_adam_compact_rows_kernel<<<(unsigned)b2, 256, 0, s>>>(pk, rows, count, gate);
+  } else {
+    sparse_adam_compact_kernel<<<(unsigned)blocks, 256, 0, s>>>(pk, rows, count, gate);
+  }
   return cudaGetLastError();
 }
 
