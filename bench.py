@@ -61,6 +61,7 @@ def parse():
     ap.add_argument("--e2e-dropin", action="store_true",
                     help="e2e (ours): time the unchanged train_post.py loop body (dense gradients) as the headline e2e")
     ap.add_argument("--no-profile", action="store_true")
+    ap.add_argument("--dp-shard", type=int, default=-1, help="dp: 1 / 0 = sharded / replicated optimizer; -1 = by world size")
     ap.add_argument("--no-dp", action="store_true", help="on more than one GPU: skip the camera-batch data-parallel measurement")
     return ap.parse_args()
 

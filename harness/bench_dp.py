@@ -79,7 +79,8 @@ def run(args, dev, rank, world, attrs, timed, dcol, ddep):
     dist.all_reduce(cap_t, op=dist.ReduceOp.MAX)
     capacity = int(cap_t.item() * 1.25) + 1024
     sampler = par.CostBucketSampler(costs, world, seed=0)
-    ex = par.CompactRowExchange(opt, n_store, capacity, group=dist.group.WORLD)
+    ex = par.CompactRowExchange(opt, n_store, capacity, group=dist.group.WORLD,
+                                shard_optimizer=None if args.dp_shard < 0 else bool(args.dp_shard))
 
     def single_step(i):   # what one GPU does alone with the same kernels: no exchange
         sg = render(i % n_cams)
@@ -107,7 +108,7 @@ def run(args, dev, rank, world, attrs, timed, dcol, ddep):
     # where the exchange time goes: render / pack / barrier (includes waiting for the slowest rank) / accumulate per
     # peer / adam, CUDA events on one step of the heaviest and one of the lightest camera group
     def stage_times(step_index):
-        ev = [torch.cuda.Event(enable_timing=True) for _ in range(6)]
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(7)]
         dist.barrier()
         torch.cuda.synchronize()
         ev[0].record()
@@ -121,9 +122,14 @@ def run(args, dev, rank, world, attrs, timed, dcol, ddep):
         ev[4].record()
         ex.apply()
         ev[5].record()
+        if ex.sharded:
+            ex.pblock.barrier()
+            ex.pull_params()
+        ev[6].record()
         ex.parity ^= 1
         torch.cuda.synchronize()
-        out = {n: ev[i].elapsed_time(ev[i + 1]) for i, n in enumerate(("render", "pack", "barrier", "accumulate", "adam"))}
+        out = {n: ev[i].elapsed_time(ev[i + 1])
+               for i, n in enumerate(("render", "pack", "barrier", "accumulate", "adam", "barrier2+pull_params"))}
         out["union_rows"] = int(ex.flags[0])
         out["cameras"] = sampler.batch(step_index)
         return out
@@ -144,6 +150,9 @@ def run(args, dev, rank, world, attrs, timed, dcol, ddep):
         "sampler": "CostBucketSampler: cameras of similar cost share a step, rotated over the ranks",
         "exchange": "all-gather of gated compact gradient rows through symmetric (NVLink peer) memory, summed in rank "
                     "order while read, one sparse Adam over the union (csrc/dp_exchange.cu); NCCL only for setup",
+        "optimizer": "sharded over rows (row % world == rank): each rank sums and updates the rows it owns and copies its "
+                     "peers' updated rows; moments live on the owner" if ex.sharded else
+                     "replicated: every rank sums and updates the whole union",
         "exchange_stages_ms": stages,
         "gated_rows_per_render_max": max(gated), "arena_capacity_rows": capacity, "union_rows_last_step": union,
         "nvlink_bytes_per_rank_per_step": (world - 1) * (sum(gated) / len(gated)) * (4 * ex.width + 4),

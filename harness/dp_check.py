@@ -34,6 +34,7 @@ def main():
     ap.add_argument("--steps", type=int, default=4)
     ap.add_argument("--levels", type=int, default=17)
     ap.add_argument("--target", type=int, default=60000)
+    ap.add_argument("--shard", type=int, default=-1, help="1 / 0: sharded / replicated optimizer; -1: the default for this world size")
     args = ap.parse_args()
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     local = int(os.environ.get("LOCAL_RANK", rank))
@@ -61,9 +62,10 @@ def main():
     bg = torch.zeros(3, device=dev)
     g = torch.Generator().manual_seed(3)
     dcol = (torch.randn(3, H, W, generator=g) / (W * H)).to(dev)
-    ex = par.CompactRowExchange(optA, n, capacity=400_000, group=dist.group.WORLD)
+    ex = par.CompactRowExchange(optA, n, capacity=400_000, group=dist.group.WORLD,
+                                shard_optimizer=None if args.shard < 0 else bool(args.shard))
     names = ["xyz", "f_dc", "f_rest", "opacity", "scaling", "rotation"]
-    report = {"world": world, "rows": n, "steps": []}
+    report = {"world": world, "rows": n, "sharded_optimizer": ex.sharded, "steps": []}
     for step in range(args.steps):
         cam = cams[(step * world + rank) % len(cams)]
         cut = workload.Cut(n, dev)
@@ -99,8 +101,9 @@ def main():
         ex.check_overflow()
         same = all(torch.equal(a.detach().view(torch.int32), b.detach().view(torch.int32))
                    for a, b in zip(A.parameters(), B.parameters()))
-        mom = all(torch.equal(optA.state[a]["exp_avg_sq"].view(torch.int32), optB.state[b]["exp_avg_sq"].view(torch.int32))
-                  for a, b in zip(A.parameters(), B.parameters()))
+        own = slice(rank, None, world) if ex.sharded else slice(None)   # sharded: a row's moments live on its owner
+        mom = all(torch.equal(optA.state[a][key][own].view(torch.int32), optB.state[b][key][own].view(torch.int32))
+                  for a, b in zip(A.parameters(), B.parameters()) for key in ("exp_avg", "exp_avg_sq"))
         sums = [None] * world
         dist.all_gather_object(sums, digest(A.parameters()))
         report["steps"].append({"step": step, "gated_rows": int(gate.sum()), "union_rows": int(ex.flags[0]),

@@ -70,12 +70,13 @@ __global__ void __launch_bounds__(256) dp_pack_kernel(const DpTensors t, const l
 
 // 32 peer rows per warp iteration: every lane resolves one row's union slot (one warp-aggregated atomic for the new
 // ones), then the warp moves the rows four at a time so that eight remote loads per lane are in flight.  peer_* may
-// be remote (NVLink) pointers; W <= 64.
+// be remote (NVLink) pointers; W <= 64.  owner_mod > 1: only the rows with row % owner_mod == owner_rem are taken
+// (sharded optimizer: every rank sums and updates the rows it owns).
 constexpr int DP_RB = 4;
 __global__ void __launch_bounds__(256) dp_accumulate_kernel(const int* __restrict__ peer_rows,
                                                            const float* __restrict__ peer_packed,
                                                            const int* __restrict__ peer_count, int peer_capacity,
-                                                           int W,
+                                                           int W, int owner_mod, int owner_rem,
                                                            int* __restrict__ row_map, int* __restrict__ union_rows,
                                                            float* __restrict__ union_packed,
                                                            int* __restrict__ union_count, int union_capacity,
@@ -88,12 +89,15 @@ __global__ void __launch_bounds__(256) dp_accumulate_kernel(const int* __restric
   for (int base = (((blockIdx.x * blockDim.x) + threadIdx.x) >> 5) * 32; base < U; base += warps * 32) {
     const int i = base + lane;
     int slot = -1;
-    bool fresh = false;
+    bool fresh = false, mine = false;
     int row = 0;
     if (i < U) {
       row = peer_rows[i];
-      slot = row_map[row];
-      fresh = slot < 0;
+      mine = owner_mod <= 1 || (row % owner_mod) == owner_rem;
+      if (mine) {
+        slot = row_map[row];
+        fresh = slot < 0;
+      }
     }
     const unsigned nm = __ballot_sync(0xffffffffu, fresh);
     if (nm) {
@@ -105,22 +109,24 @@ __global__ void __launch_bounds__(256) dp_accumulate_kernel(const int* __restric
         if (slot < union_capacity) { row_map[row] = slot; union_rows[slot] = row; }
       }
     }
-    if (i < U && slot >= union_capacity) { atomicExch(overflow, 2); slot = -1; }
-    const int n = min(32, U - base);
-    for (int j = 0; j < n; j += DP_RB) {
-      int sj[DP_RB], fj[DP_RB];
+    if (mine && slot >= union_capacity) { atomicExch(overflow, 2); slot = -1; }
+    unsigned todo = __ballot_sync(0xffffffffu, slot >= 0);
+    while (todo) {
+      int lj[DP_RB], sj[DP_RB], fj[DP_RB];
       float a[DP_RB][2], d[DP_RB][2];
 #pragma unroll
       for (int r = 0; r < DP_RB; ++r) {
-        sj[r] = __shfl_sync(0xffffffffu, slot, (j + r) & 31);
-        fj[r] = __shfl_sync(0xffffffffu, (int)fresh, (j + r) & 31);
-        if (j + r >= n) sj[r] = -1;
+        lj[r] = todo ? __ffs(todo) - 1 : -1;
+        if (todo) todo &= todo - 1;
+        sj[r] = __shfl_sync(0xffffffffu, slot, lj[r] & 31);
+        fj[r] = __shfl_sync(0xffffffffu, (int)fresh, lj[r] & 31);
+        if (lj[r] < 0) sj[r] = -1;
       }
 #pragma unroll
       for (int r = 0; r < DP_RB; ++r) {
         a[r][0] = a[r][1] = d[r][0] = d[r][1] = 0.0f;
         if (sj[r] < 0) continue;
-        const float* src = peer_packed + (size_t)(base + j + r) * W;
+        const float* src = peer_packed + (size_t)(base + lj[r]) * W;
         const float* dst = union_packed + (size_t)sj[r] * W;
         a[r][0] = src[lane];
         if (two) a[r][1] = src[lane + 32];
@@ -161,10 +167,13 @@ __device__ __forceinline__ void adam_update(const H3dgsAdamTensor& T, float g, f
 __global__ void __launch_bounds__(256) dp_adam_kernel(const DpAdam pk, const int* __restrict__ union_rows,
                                                      const int* __restrict__ union_count,
                                                      const float* __restrict__ union_packed, float scale,
-                                                     int* __restrict__ row_map, int union_capacity) {
+                                                     int* __restrict__ row_map, int union_capacity,
+                                                     int* __restrict__ out_rows, float* __restrict__ out_packed,
+                                                     int* __restrict__ out_count) {
   const int W = pk.start[pk.n];
   int U = *union_count;
   if (U > union_capacity) U = union_capacity;
+  if (out_count != nullptr && blockIdx.x == 0 && threadIdx.x == 0) *out_count = U;
   const int lane = threadIdx.x & 31;
   const int warps = (gridDim.x * blockDim.x) >> 5;
   // the two elements of a row this lane owns, and the tensor each falls into
@@ -204,6 +213,7 @@ __global__ void __launch_bounds__(256) dp_adam_kernel(const DpAdam pk, const int
     for (int r = 0; r < DP_RB; ++r) {
       if (row[r] < 0) continue;
       if (lane == 0 && row_map != nullptr) row_map[row[r]] = -1;
+      if (lane == 0 && out_rows != nullptr) out_rows[base + r] = row[r];
 #pragma unroll
       for (int q = 0; q < 2; ++q) {
         if (!on[q]) continue;
@@ -213,7 +223,53 @@ __global__ void __launch_bounds__(256) dp_adam_kernel(const DpAdam pk, const int
         T.exp_avg[off] = m[r][q];
         T.exp_avg_sq[off] = v[r][q];
         T.param[off] = p[r][q];
+        if (out_packed != nullptr) out_packed[(size_t)(base + r) * W + lane + 32 * q] = p[r][q];
       }
+    }
+  }
+}
+
+// Sharded optimizer, last stage: the parameter rows a peer owns and has just updated -> the local replica.
+__global__ void __launch_bounds__(256) dp_scatter_params_kernel(const DpAdam pk, const int* __restrict__ peer_rows,
+                                                               const float* __restrict__ peer_packed,
+                                                               const int* __restrict__ peer_count, int peer_capacity) {
+  const int W = pk.start[pk.n];
+  int U = *peer_count;
+  if (U > peer_capacity) U = peer_capacity;
+  const int lane = threadIdx.x & 31;
+  const int warps = (gridDim.x * blockDim.x) >> 5;
+  int ti[2], col[2];
+  bool on[2];
+#pragma unroll
+  for (int q = 0; q < 2; ++q) {
+    const int e = lane + 32 * q;
+    on[q] = e < W;
+    int t = 0;
+#pragma unroll
+    for (int i = 1; i < H3DGS_ADAM_MAX_TENSORS; ++i)
+      if (i < pk.n && e >= pk.start[i]) t = i;
+    ti[q] = t;
+    col[q] = e - pk.start[t];
+  }
+  constexpr int RB = 8;
+  for (int base = (((blockIdx.x * blockDim.x) + threadIdx.x) >> 5) * RB; base < U; base += warps * RB) {
+    int row[RB];
+    float v[RB][2];
+#pragma unroll
+    for (int r = 0; r < RB; ++r) row[r] = base + r < U ? peer_rows[base + r] : -1;
+#pragma unroll
+    for (int r = 0; r < RB; ++r) {
+      if (row[r] < 0) continue;
+#pragma unroll
+      for (int q = 0; q < 2; ++q)
+        if (on[q]) v[r][q] = peer_packed[(size_t)(base + r) * W + lane + 32 * q];
+    }
+#pragma unroll
+    for (int r = 0; r < RB; ++r) {
+      if (row[r] < 0) continue;
+#pragma unroll
+      for (int q = 0; q < 2; ++q)
+        if (on[q]) pk.t[ti[q]].param[(size_t)row[r] * pk.t[ti[q]].width + col[q]] = v[r][q];
     }
   }
 }
@@ -261,26 +317,29 @@ int h3dgs_dp_pack(const H3dgsRowTensor* grads, int32_t num_tensors, const int64_
 }
 
 int h3dgs_dp_accumulate(const int32_t* peer_rows, const float* peer_packed, const int32_t* peer_count,
-                        int32_t peer_capacity, int32_t width, int32_t* row_map, int32_t* union_rows,
+                        int32_t peer_capacity, int32_t width, int32_t owner_mod, int32_t owner_rem,
+                        int32_t* row_map, int32_t* union_rows,
                         float* union_packed, int32_t* union_count, int32_t union_capacity, int32_t* overflow,
                         h3dgs_stream_t stream) {
   using namespace h3dgs;
   if (!peer_rows || !peer_packed || !peer_count || width <= 0 || !row_map || !union_rows || !union_packed ||
-      !union_count || !overflow || peer_capacity < 0 || union_capacity < 0)
+      !union_count || !overflow || peer_capacity < 0 || union_capacity < 0 ||
+      (owner_mod > 1 && (owner_rem < 0 || owner_rem >= owner_mod)))
     return fail(H3DGS_EINVAL, "h3dgs_dp_accumulate: bad argument");
   if (peer_capacity == 0) return 0;
   if (width > 64) return fail(H3DGS_EINVAL, "h3dgs_dp_accumulate: rows wider than 64 floats are not supported");
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   ProfScope ps(K_ADAM, s);
   dp_accumulate_kernel<<<grid_for((long long)peer_capacity), 256, 0, s>>>(
-      peer_rows, peer_packed, peer_count, peer_capacity, width, row_map, union_rows, union_packed, union_count, union_capacity, overflow);
+      peer_rows, peer_packed, peer_count, peer_capacity, width, owner_mod, owner_rem, row_map, union_rows, union_packed, union_count, union_capacity, overflow);
   H3_CUDA(cudaGetLastError());
   return 0;
 }
 
 int h3dgs_dp_adam(const H3dgsAdamTensor* tensors, int32_t num_tensors, const int32_t* union_rows,
                   const int32_t* union_count, const float* union_packed, float scale, int32_t* row_map,
-                  int32_t union_capacity, h3dgs_stream_t stream) {
+                  int32_t union_capacity, int32_t* out_rows, float* out_packed, int32_t* out_count,
+                  h3dgs_stream_t stream) {
   using namespace h3dgs;
   if (!tensors || num_tensors <= 0 || num_tensors > H3DGS_ADAM_MAX_TENSORS || !union_rows || !union_count ||
       !union_packed || union_capacity < 0)
@@ -301,7 +360,35 @@ int h3dgs_dp_adam(const H3dgsAdamTensor* tensors, int32_t num_tensors, const int
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   ProfScope ps(K_ADAM, s);
   dp_adam_kernel<<<grid_for((long long)union_capacity * 32 / DP_RB), 256, 0, s>>>(pk, union_rows, union_count, union_packed,
-                                                                           scale, row_map, union_capacity);
+                                                                           scale, row_map, union_capacity, out_rows,
+                                                                           out_packed, out_count);
+  H3_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int h3dgs_dp_scatter_params(const H3dgsAdamTensor* tensors, int32_t num_tensors, const int32_t* peer_rows,
+                            const float* peer_packed, const int32_t* peer_count, int32_t peer_capacity,
+                            h3dgs_stream_t stream) {
+  using namespace h3dgs;
+  if (!tensors || num_tensors <= 0 || num_tensors > H3DGS_ADAM_MAX_TENSORS || !peer_rows || !peer_packed ||
+      !peer_count || peer_capacity < 0)
+    return fail(H3DGS_EINVAL, "h3dgs_dp_scatter_params: bad argument");
+  DpAdam pk;
+  pk.n = num_tensors;
+  int acc = 0;
+  for (int i = 0; i < num_tensors; ++i) {
+    if (!tensors[i].param || tensors[i].width <= 0) return fail(H3DGS_EINVAL, "h3dgs_dp_scatter_params: bad tensor");
+    pk.t[i] = tensors[i];
+    pk.start[i] = acc;
+    acc += tensors[i].width;
+  }
+  for (int i = num_tensors; i <= H3DGS_ADAM_MAX_TENSORS; ++i) pk.start[i] = acc;
+  if (acc > 64) return fail(H3DGS_EINVAL, "h3dgs_dp_scatter_params: rows wider than 64 floats are not supported");
+  if (peer_capacity == 0) return 0;
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  ProfScope ps(K_ADAM, s);
+  dp_scatter_params_kernel<<<grid_for((long long)peer_capacity * 4), 256, 0, s>>>(pk, peer_rows, peer_packed, peer_count,
+                                                                                  peer_capacity);
   H3_CUDA(cudaGetLastError());
   return 0;
 }

@@ -108,10 +108,11 @@ SIGNATURES = {
                                   c_void_p, c_void_p, c_void_p, c_int]),
     "h3dgs_dp_pack": (c_int, [POINTER(RowTensor), c_int32, c_void_p, c_void_p, c_int32, c_void_p, c_void_p, c_void_p,
                                c_void_p, c_int32, c_void_p, c_void_p]),
-    "h3dgs_dp_accumulate": (c_int, [c_void_p, c_void_p, c_void_p, c_int32, c_int32, c_void_p, c_void_p, c_void_p,
-                                     c_void_p, c_int32, c_void_p, c_void_p]),
+    "h3dgs_dp_accumulate": (c_int, [c_void_p, c_void_p, c_void_p, c_int32, c_int32, c_int32, c_int32, c_void_p,
+                                     c_void_p, c_void_p, c_void_p, c_int32, c_void_p, c_void_p]),
     "h3dgs_dp_adam": (c_int, [POINTER(AdamTensor), c_int32, c_void_p, c_void_p, c_void_p, c_float, c_void_p, c_int32,
-                               c_void_p]),
+                               c_void_p, c_void_p, c_void_p, c_void_p]),
+    "h3dgs_dp_scatter_params": (c_int, [POINTER(AdamTensor), c_int32, c_void_p, c_void_p, c_void_p, c_int32, c_void_p]),
     "h3dgs_hier_build_workspace_bytes": (c_size_t, [c_int64]),
     "h3dgs_hier_build": (c_int, [c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int32, c_void_p, c_void_p,
                                   c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t,

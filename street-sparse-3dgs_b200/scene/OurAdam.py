@@ -105,11 +105,13 @@ class Adam(Optimizer):
                       "h3dgs_sparse_adam_compact")
 
     @torch.no_grad()
-    def step_union(self, params, union_rows, union_count, union_packed, scale, row_map, capacity):
+    def step_union(self, params, union_rows, union_count, union_packed, scale, row_map, capacity, out=None):
         """One step from the summed gradients of a data-parallel exchange (h3dgs_parallel.CompactRowExchange):
         ``union_packed`` [capacity, sum of widths] holds, for each of the ``union_count[0]`` (device) rows listed in
         ``union_rows``, the concatenated gradients of ``params`` in that order; ``scale`` (1 / world) turns the sum into
-        the average.  ``row_map`` is the exchange's row -> slot scratch, restored to -1 by the kernel."""
+        the average.  ``row_map`` is the exchange's row -> slot scratch, restored to -1 by the kernel.  ``out``
+        (sharded optimizer): device addresses (rows, packed, count) of the block that receives the updated parameter
+        rows for the peers."""
         order = {p.data_ptr(): i for i, p in enumerate(params)}
         batch = [None] * len(params)
         for group in self.param_groups:
@@ -133,6 +135,7 @@ class Adam(Optimizer):
         arr = (nat.AdamTensor * len(batch))(*batch)
         nat.check(nat.lib().h3dgs_dp_adam(arr, len(batch), union_rows.data_ptr(), union_count.data_ptr(),
                                           union_packed.data_ptr(), float(scale), nat.ptr(row_map), int(capacity),
+                                          out[0] if out else None, out[1] if out else None, out[2] if out else None,
                                           nat.stream_handle()), "h3dgs_dp_adam")
 
     @torch.no_grad()

@@ -98,6 +98,56 @@ def test_exchange_matches_dense_allreduce_and_adam(world):
         assert torch.equal(sa["exp_avg_sq"].view(torch.int32), sb["exp_avg_sq"].view(torch.int32)), nme
 
 
+def test_sharded_optimizer_exchange_matches_dense(world=2):
+    """ZeRO-1 over rows: rank r sums and updates the rows with row % world == r, publishes the updated parameter rows,
+    and copies its peers' blocks.  Two replicas side by side in one process: both must end with the parameters of the
+    dense formulation, and every row's moments must be right on its owner."""
+    import copy
+    import h3dgs_parallel as par
+    from scene.OurAdam import Adam
+    model, opt, sgs, n = _renders(world)
+    ref, ref_opt, n_rel = _dense_step(model, sgs, world)
+    names = ["_xyz", "_features_dc", "_features_rest", "_opacity", "_scaling", "_rotation"]
+    cap = max(sg.capacity for sg in sgs)
+    replicas, exs = [], []
+    for r in range(world):
+        m = copy.copy(model)
+        for nme in names:
+            setattr(m, nme, getattr(model, nme).detach().clone().requires_grad_(True))
+        o = Adam(m.param_groups(), lr=0.0, eps=1e-15)
+        ex = par.CompactRowExchange(o, n, cap, group=None, union_capacity=n // world + 1)
+        ex.sharded, ex.world, ex.rank = True, world, r
+        ex.pblock = par.RowArena(ex.ucap, ex.width, torch.device(DEV))
+        replicas.append((m, o))
+        exs.append(ex)
+    # stage 1 on every "rank": its own gradients into its own arena (the compact gradients refer to `model`'s
+    # parameters: the pack only needs their widths and order, taken from the replica's optimizer)
+    for r, ex in enumerate(exs):
+        sg = sgs[r]
+        remap = copy.copy(sg)
+        remap.params = {k: getattr(replicas[r][0], [nme for nme in names if getattr(model, nme).data_ptr() == v.data_ptr()][0])
+                        for k, v in sg.params.items()}
+        ex.pack(remap, parity=0)
+    bases = [ex.arena.base_ptrs[0] for ex in exs]
+    for ex in exs:
+        ex.accumulate(bases, parity=0)
+        ex.apply(world=world)
+    assert sum(int(ex.flags[0]) for ex in exs) == n_rel
+    pbases = [ex.pblock.base_ptrs[0] for ex in exs]
+    for ex in exs:
+        ex.pblock.base_ptrs = pbases
+        ex.pull_params()
+    torch.cuda.synchronize()
+    for r, (m, o) in enumerate(replicas):
+        for nme in names:
+            a, b = getattr(m, nme).detach(), getattr(ref, nme).detach()
+            assert torch.equal(a.view(torch.int32), b.view(torch.int32)), f"replica {r} {nme}: parameters differ"
+            sa, sb = o.state[getattr(m, nme)], ref_opt.state[getattr(ref, nme)]
+            for key in ("exp_avg", "exp_avg_sq"):
+                assert torch.equal(sa[key][r::world].view(torch.int32), sb[key][r::world].view(torch.int32)), (r, nme, key)
+        assert bool((exs[r].row_map == -1).all())
+
+
 def test_exchange_reports_a_too_small_arena():
     import h3dgs_parallel as par
     model, opt, sgs, n = _renders(1)
