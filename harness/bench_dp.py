@@ -150,7 +150,7 @@ def run(args, dev, rank, world, attrs, timed, dcol, ddep):
         "sampler": "CostBucketSampler: cameras of similar cost share a step, rotated over the ranks",
         "exchange": "all-gather of gated compact gradient rows through symmetric (NVLink peer) memory, summed in rank "
                     "order while read, one sparse Adam over the union (csrc/dp_exchange.cu); NCCL only for setup",
-        "optimizer": "sharded over rows (row % world == rank): each rank sums and updates the rows it owns and copies its "
+        "optimizer": "sharded over rows ((row >> 6) % world == rank): each rank sums and updates the rows it owns and copies its "
                      "peers' updated rows; moments live on the owner" if ex.sharded else
                      "replicated: every rank sums and updates the whole union",
         "exchange_stages_ms": stages,

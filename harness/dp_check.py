@@ -101,7 +101,8 @@ def main():
         ex.check_overflow()
         same = all(torch.equal(a.detach().view(torch.int32), b.detach().view(torch.int32))
                    for a, b in zip(A.parameters(), B.parameters()))
-        own = slice(rank, None, world) if ex.sharded else slice(None)   # sharded: a row's moments live on its owner
+        # sharded: a row's moments live on its owner
+        own = (par.owner_of(torch.arange(n, device=dev), world) == rank) if ex.sharded else slice(None)
         mom = all(torch.equal(optA.state[a][key][own].view(torch.int32), optB.state[b][key][own].view(torch.int32))
                   for a, b in zip(A.parameters(), B.parameters()) for key in ("exp_avg", "exp_avg_sq"))
         sums = [None] * world

@@ -353,9 +353,11 @@ H3DGS_API int h3dgs_sparse_adam_compact(const H3dgsAdamTensor* tensors, int32_t 
  *   ignored), and row_map restored to -1 for those rows.
  * Sharded optimizer (ZeRO-1 over rows; the replicated update costs every rank the whole union, 3.6 M scattered rows
  * for 8 cameras): h3dgs_dp_accumulate with owner_mod = world, owner_rem = rank takes only the rows this rank owns
- * (row % world == rank); h3dgs_dp_adam with out_* non-NULL also leaves the updated parameter rows as a packed block
+ * ((row >> H3DGS_DP_OWNER_SHIFT) % world == rank: runs of 64 consecutive rows share an owner, so that neighbouring
+ * rows -- which share DRAM sectors in the narrow tensors -- are written together); h3dgs_dp_adam with out_* non-NULL also leaves the updated parameter rows as a packed block
  * (out_rows / out_packed / *out_count, in symmetric memory); h3dgs_dp_scatter_params copies a peer's block into the
  * local parameter tensors.  Moments of a row are then valid on its owner only. */
+#define H3DGS_DP_OWNER_SHIFT 6
 H3DGS_API int h3dgs_dp_pack(const H3dgsRowTensor* grads, int32_t num_tensors, const int64_t* compact_rows,
                   const int32_t* compact_count, int32_t capacity, const float* gate, int32_t* out_rows,
                   float* out_packed, int32_t* out_count, int32_t out_capacity, int32_t* overflow,

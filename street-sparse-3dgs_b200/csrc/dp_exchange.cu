@@ -70,8 +70,9 @@ __global__ void __launch_bounds__(256) dp_pack_kernel(const DpTensors t, const l
 
 // 32 peer rows per warp iteration: every lane resolves one row's union slot (one warp-aggregated atomic for the new
 // ones), then the warp moves the rows four at a time so that eight remote loads per lane are in flight.  peer_* may
-// be remote (NVLink) pointers; W <= 64.  owner_mod > 1: only the rows with row % owner_mod == owner_rem are taken
-// (sharded optimizer: every rank sums and updates the rows it owns).
+// be remote (NVLink) pointers; W <= 64.  owner_mod > 1: only the rows with (row >> 6) % owner_mod == owner_rem are
+// taken (sharded optimizer: every rank sums and updates the rows it owns; runs of 64 consecutive rows share an owner so
+// that the rows of one 32-byte sector of a 12-byte-per-row tensor are written by one kernel, close together in time).
 constexpr int DP_RB = 4;
 __global__ void __launch_bounds__(256) dp_accumulate_kernel(const int* __restrict__ peer_rows,
                                                            const float* __restrict__ peer_packed,
@@ -93,7 +94,7 @@ __global__ void __launch_bounds__(256) dp_accumulate_kernel(const int* __restric
     int row = 0;
     if (i < U) {
       row = peer_rows[i];
-      mine = owner_mod <= 1 || (row % owner_mod) == owner_rem;
+      mine = owner_mod <= 1 || ((row >> H3DGS_DP_OWNER_SHIFT) % owner_mod) == owner_rem;
       if (mine) {
         slot = row_map[row];
         fresh = slot < 0;

@@ -102,6 +102,14 @@ def allreduce_sparse_rows(tensors: Sequence[torch.Tensor], row_mask: torch.Tenso
 # Camera-batch data parallelism on compact gradients, exchanged through NVLink peer memory (csrc/dp_exchange.cu)
 # ---------------------------------------------------------------------------------------------------------------
 
+OWNER_SHIFT = 6   # H3DGS_DP_OWNER_SHIFT: runs of 64 consecutive rows share an owner
+
+
+def owner_of(rows, world):
+    """Rank that owns each store row under the sharded optimizer."""
+    return (rows >> OWNER_SHIFT) % world
+
+
 class RowArena:
     """One rank's exchange block: int32 header (count, overflow flag), int32 store rows and the packed
     [capacity, width] gradients, double buffered by step parity.  Allocated in torch symmetric memory when a process
@@ -148,7 +156,7 @@ class CompactRowExchange:
 
     ``shard_optimizer`` (default on): ZeRO-1 over rows.  The replicated form makes every rank sum and update
     the WHOLE union (3.6 M scattered 236-byte rows for 8 street cameras: 6.5 ms); sharded, rank r sums and updates
-    only the rows with ``row % world == r`` and publishes the updated parameter rows in a second symmetric-memory block
+    only the rows with ``(row >> 6) % world == r`` and publishes the updated parameter rows in a second symmetric-memory block
     that the peers copy into their replicas.  Parameters stay bit-identical on all ranks; the Adam moments of a row
     live on its owner only (``gather_moments()`` rebuilds full moment tensors, e.g. for a checkpoint)."""
 
@@ -233,10 +241,13 @@ class CompactRowExchange:
         for i, p in enumerate(self.params):
             arr[i].param = p.data_ptr()
             arr[i].width = self.widths[i]
-        for r, base in enumerate(self.pblock.base_ptrs):
-            if r == self.rank:
-                continue
-            cnt, _, rows, packed = self.pblock.ptrs(base, 0)
+        # staggered: rank r starts with peer r + 1, so that at any moment every GPU's NVLink egress serves ONE reader
+        # (all ranks reading peer 0, then peer 1, ... shares one GPU's 900 GB/s among world - 1 readers: measured
+        # 2.7 ms instead of 0.6 ms for 7 x 105 MB on 8 GPUs); the blocks hold disjoint rows, the order is free
+        world = len(self.pblock.base_ptrs)
+        for k in range(1, world):
+            r = (self.rank + k) % world
+            cnt, _, rows, packed = self.pblock.ptrs(self.pblock.base_ptrs[r], 0)
             nat.check(nat.lib().h3dgs_dp_scatter_params(arr, len(self.params), rows, packed, cnt, self.pblock.capacity,
                                                         nat.stream_handle()), "h3dgs_dp_scatter_params")
 
