@@ -452,6 +452,9 @@ H3DGS_API int h3dgs_blend_stats(void* counters);
  * out[1] the same with packed fma.rn.f32x2 (FFMA2), out[2] MUFU.EX2 results in G/s, out[3] warp instructions issued
  * per second (G/s) by the FFMA kernel.  scratch: device pointer to at least one float. */
 H3DGS_API int h3dgs_measure_peaks(double* out4, void* scratch, int32_t reps, h3dgs_stream_t stream);
+/* Diagnostics switch: key 1 = backward blend variant (1 = one pixel per lane, 2 = two pixels per lane, the default;
+ * env H3DGS_BWD); returns the previous value, -1 for an unknown key. */
+H3DGS_API int h3dgs_debug_set(int key, int value);
 H3DGS_API int64_t h3dgs_launch_count(void);          /* kernels launched by this library so far (process-wide) */
 H3DGS_API int h3dgs_profile_enable(int enable);      /* returns the previous setting */
 /* Synchronises pending events and adds their durations; ms[i] / launches[i] are per kernel id

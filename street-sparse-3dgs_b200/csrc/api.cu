@@ -61,6 +61,7 @@ void prof_end(int id, cudaStream_t s) {
 static unsigned long long* g_blend_stats = nullptr;
 
 // H3DGS_STAGE=tma|ldgsts selects how the blend kernels stage records into shared memory.
+int set_bwd_variant(int v);   // blend_bwd.cu
 int blend_stage_mode() {
   static int mode = -1;
   if (mode < 0) {
@@ -712,6 +713,10 @@ int h3dgs_measure_peaks(double* out4, void* scratch, int32_t reps, h3dgs_stream_
   return 0;
 }
 
+int h3dgs_debug_set(int key, int value) {
+  if (key == 1) return h3dgs::set_bwd_variant(value);
+  return -1;
+}
 int64_t h3dgs_launch_count(void) { return g_prof.launches_total; }
 int h3dgs_profile_enable(int enable) {
   const int prev = g_prof.on ? 1 : 0;

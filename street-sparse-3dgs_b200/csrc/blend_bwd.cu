@@ -12,6 +12,8 @@
 // Gradient reduction: per (warp, Gaussian) the ten partial sums are reduced with warp shuffles, added
 // into a per-CTA shared-memory accumulator, and flushed once per (tile, Gaussian) with three vector
 // red.global.add instructions -- instead of the reference's ten global atomics per (pixel, Gaussian).
+#include <cstdlib>
+
 #include "blend_common.cuh"
 
 namespace h3dgs {
@@ -191,7 +193,7 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_bwd_kernel(const BlendArg
         const float2 xy = *reinterpret_cast<const float2*>(&recs[jj].q0);
         const float4 con_o = recs[jj].q1;
         const float dx = xy.x - pixx, dy = xy.y - pixy;
-        const float power = -0.5f * (con_o.x * dx * dx + con_o.z * dy * dy) - con_o.y * dx * dy;
+        const float power = blend_power(con_o, dx, dy);
         // G, alpha and T are rebuilt with the MUFU approximations (ex2 / lg2 / rcp, relative error ~1e-7 -- the
         // level at which the reference's own forward (__powf) and backward (pow) already disagree); the keep / skip
         // decision at 1/255 below is the one place where a last-bit difference would change the result visibly,
@@ -353,8 +355,25 @@ cudaError_t launch2(const BlendArgs& a, bool tma, cudaStream_t s) {
 
 int blend_stage_mode();
 
+// H3DGS_BWD=1 selects this file's one-pixel-per-lane kernel; the default is blend_bwd2.cu (two pixels per lane,
+// one cross-lane reduction per 64 pixels).  The bulk-copy staging mode exists in this kernel only.
+static int g_bwd_variant = -1;
+static int bwd_variant() {
+  if (g_bwd_variant < 0) {
+    const char* e = std::getenv("H3DGS_BWD");
+    g_bwd_variant = (e && e[0] == '1') ? 1 : 2;
+  }
+  return g_bwd_variant;
+}
+int set_bwd_variant(int v) {   // diagnostics (h3dgs_debug_set): returns the previous variant
+  const int prev = bwd_variant();
+  if (v == 1 || v == 2) g_bwd_variant = v;
+  return prev;
+}
+
 cudaError_t launch_blend_bwd(const BlendArgs& a, cudaStream_t s) {
   const bool tma = blend_stage_mode() == 1;
+  if (!tma && bwd_variant() == 2) return launch_blend_bwd2(a, s);
   const bool depth = a.dL_dinvdepth != nullptr;
   if (a.interp) return depth ? launch2<true, true>(a, tma, s) : launch2<true, false>(a, tma, s);
   return depth ? launch2<false, true>(a, tma, s) : launch2<false, false>(a, tma, s);

@@ -90,6 +90,16 @@ __device__ __forceinline__ float lg2_approx(float x) {
   return r;
 }
 
+// power = -0.5 (a dx^2 + c dy^2) - b dx dy with the roundings of the reference build (HR/cuda_rasterizer/forward.cu:529,
+// backward.cu:611 as nvcc contracts them for sm_100a: a dx^2 is fused into the rounded c dy^2, the cross term is
+// rounded on its own).  Written out because the keep / skip decision at alpha = 1/255 hangs on the last bit, and
+// nvcc's own choice of which product to fuse depends on the surrounding code (it fused the other one in
+// blend_bwd2.cu: two Gaussians of a 100 k scene came out 10 % different).
+__device__ __forceinline__ float blend_power(const float4& con_o, float dx, float dy) {
+  const float s = __fmaf_rn(dx, __fmul_rn(dx, con_o.x), __fmul_rn(dy, __fmul_rn(dy, con_o.z)));
+  return __fsub_rn(__fmul_rn(s, -0.5f), __fmul_rn(dy, __fmul_rn(dx, con_o.y)));
+}
+
 // Can the Gaussian of record (q0, q1) reach alpha >= 1/255 anywhere in the pixel block
 // [x0, x0+SUB_W-1] x [y0, y0+SUB_H-1]?  alpha >= 1/255  <=>  a dx^2 + 2 b dx dy + c dy^2 <= 2 ln(255 o) = q0.z
 // (preprocess stores that bound with a small safety margin, +inf for "never cull", negative for "never

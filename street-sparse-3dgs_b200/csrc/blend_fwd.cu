@@ -128,7 +128,7 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_fwd_kernel(const BlendArg
           const float2 xy = *reinterpret_cast<const float2*>(&recs[jj].q0);
           const float4 con_o = recs[jj].q1;
           const float dx = xy.x - pixx, dy = xy.y - pixy;
-          const float power = -0.5f * (con_o.x * dx * dx + con_o.z * dy * dy) - con_o.y * dx * dy;
+          const float power = blend_power(con_o, dx, dy);
           const float my_alpha = min(0.99f, con_o.w * exp(power));
           alpha = my_alpha;
           if (INTERP) {

@@ -336,6 +336,7 @@ struct BlendArgs {
 };
 cudaError_t launch_blend_fwd(const BlendArgs& a, cudaStream_t s);
 cudaError_t launch_blend_bwd(const BlendArgs& a, cudaStream_t s);
+cudaError_t launch_blend_bwd2(const BlendArgs& a, cudaStream_t s);   // two pixels per lane (blend_bwd2.cu)
 
 struct PreBwdArgs {
   PreArgs f;

@@ -129,6 +129,7 @@ SIGNATURES = {
     "h3dgs_masked_l1_backward": (c_int, [c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_void_p, c_void_p]),
     "h3dgs_blend_stats": (c_int, [c_void_p]),
     "h3dgs_measure_peaks": (c_int, [POINTER(ctypes.c_double), c_void_p, c_int32, c_void_p]),
+    "h3dgs_debug_set": (c_int, [c_int, c_int]),
     "h3dgs_launch_count": (c_int64, []),
     "h3dgs_profile_enable": (c_int, [c_int]),
     "h3dgs_profile_read": (c_int, [POINTER(ctypes.c_double), POINTER(c_int64), c_int]),
