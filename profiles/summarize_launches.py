@@ -17,7 +17,7 @@ def main(path):
         print("fewer than two steps in the launch list")
         return
     # the last segment that holds a whole step (forward AND backward): the bench ends with forward-only passes
-    segs = [(a, b) for a, b in zip(starts[:-1], starts[1:]) if any("blend_bwd_kernel" in n for n in names[a:b])]
+    segs = [(a, b) for a, b in zip(starts[:-1], starts[1:]) if any("blend_bwd" in n for n in names[a:b])]
     if not segs:
         print("no forward+backward step in the launch list")
         return

@@ -25,7 +25,7 @@ KEEP = [
     "smsp__average_warps_issue_stalled_wait_per_issue_active.ratio",
 ]
 # kernel-name fragment -> kernel id of bench.py's per-kernel table
-IDS = [("preprocess_fwd_kernel", "preprocess_fwd"), ("blend_fwd_kernel", "blend_fwd"), ("blend_bwd_kernel", "blend_bwd"),
+IDS = [("preprocess_fwd_kernel", "preprocess_fwd"), ("blend_fwd_kernel", "blend_fwd"), ("blend_bwd_kernel", "blend_bwd"), ("blend_bwd2_kernel", "blend_bwd"),
        ("preprocess_bwd_kernel", "preprocess_bwd"), ("fill_spans_kernel", "memset")]
 UNIT = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}
 
