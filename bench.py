@@ -357,20 +357,12 @@ def main():
         cam_dev = torch.empty(35, device=dev)
         # host pipeline: the ground-truth image of step i+1 crosses PCIe on a copy stream while
         # step i computes; every step still issues exactly one 24.9 MB host->device copy inside the timed region
-        gt_dev = [torch.empty(3, H, W, device=dev) for _ in range(2)]
-        copy_stream = torch.cuda.Stream(device=dev)
-        ready = [torch.cuda.Event() for _ in range(2)]
-        consumed = [torch.cuda.Event() for _ in range(2)]
-        for ev in consumed:
-            ev.record()
+        import h3dgs_pipeline as pl   # street-sparse-3dgs_b200/h3dgs_pipeline.py: the host pipeline lives in the package
+        pf = pl.HostPrefetcher({"gt": ((3, H, W), torch.float32)}, dev)
         pipe_state = {"n": 0, "primed": False}
 
         def prefetch(j):
-            buf = j % 2
-            copy_stream.wait_event(consumed[buf])
-            with torch.cuda.stream(copy_stream):
-                gt_dev[buf].copy_(gt_host[buf], non_blocking=True)
-                ready[buf].record(copy_stream)
+            pf.fetch(j, {"gt": gt_host[j % 2]})
         from types import SimpleNamespace
         h2d = gt_host[0].numel() * 4 + 35 * 4
         losses = []
@@ -381,33 +373,17 @@ def main():
         # Every step still runs exactly one cut and copies its own camera from pinned host memory.
         cut_ahead = args.impl == "ours" and not args.serial_cut
         if cut_ahead:
-            cuts2 = [cut, workload.Cut(n_store, dev)]
-            cam_dev2 = [cam_dev, torch.empty(35, device=dev)]
-            cut_stream = torch.cuda.Stream(device=dev)
-            cut_done = [torch.cuda.Event() for _ in range(2)]
-            cut_free = [torch.cuda.Event() for _ in range(2)]
-            for ev in cut_free:
-                ev.record()
-            cut_state = {"next": None}
+            ca = pl.CutAhead(gh, hm.nodes, hm.boxes, n_store, dev)
 
         def cam_index(i):
             return i % len(cams)
 
         def cam_view(k, buf):
-            c0 = cams[k]
-            return SimpleNamespace(image_width=W, image_height=H, FoVx=c0.FoVx, FoVy=c0.FoVy,
-                                   world_view_transform=buf[:16].view(4, 4),
-                                   full_proj_transform=buf[16:32].view(4, 4), camera_center=buf[32:35],
-                                   image_name=c0.image_name)
+            return pl.camera_view(cams[k], buf)
 
         def launch_cut(i):
-            k, b = cam_index(i), i % 2
-            cut_stream.wait_event(cut_free[b])   # the render that last read these buffers has been back-propagated
-            with torch.cuda.stream(cut_stream):
-                cam_dev2[b].copy_(cam_host[k], non_blocking=True)
-                cuts2[b].compute(gh, hm, cam_view(k, cam_dev2[b]), limit, campos_host=cam_host[k][32:35])
-                cut_done[b].record(cut_stream)
-            cut_state["next"] = i
+            k = cam_index(i)
+            ca.launch(i, cams[k], cam_host[k], limit)
 
         # the loss of train_post.py:132-137: (1 - lambda_dssim) L1 + lambda_dssim (1 - SSIM), lambda_dssim = 0.2
         if args.loss == "l1":
@@ -429,8 +405,7 @@ def main():
         # waits for the step it has just queued; --e2e-dropin times the unchanged train_post.py loop body instead
         # (dense .grad tensors, relevant = opacity.grad != 0, loss.item()).  The reference arm is always the latter.
         mode = {"sparse": args.impl == "ours"}
-        loss_host = [torch.zeros(1).pin_memory() for _ in range(2)]
-        loss_ready = [torch.cuda.Event() for _ in range(2)]
+        readback = pl.LossReadback()
         if args.impl == "ours":
             import diff_gaussian_rasterization as dgr
 
@@ -446,11 +421,8 @@ def main():
                 pipe_state["primed"] = True
             prefetch(n + 1)
             if cut_ahead:
-                if cut_state["next"] != step_i:
-                    launch_cut(step_i)
-                b = step_i % 2
-                torch.cuda.current_stream().wait_event(cut_done[b])
-                c, this_cut = cam_view(k, cam_dev2[b]), cuts2[b]
+                launch_cut(step_i)            # a no-op when the previous step already launched it
+                c, this_cut = ca.get(step_i)
             else:
                 cam_dev.copy_(cam_host[i % len(cams)], non_blocking=True)
                 c, this_cut = cam_view(k, cam_dev), cut
@@ -462,22 +434,18 @@ def main():
                 out = render_post(c, hm, bg, this_cut, do_depth=False, sparse_grads=sg)
             else:
                 out = render_post(c, hm, bg, this_cut, do_depth=False)
-            torch.cuda.current_stream().wait_event(ready[n % 2])
-            loss = loss_fn(out["render"], gt_dev[n % 2])
+            loss = loss_fn(out["render"], pf.get(n)["gt"])
             loss.backward()
-            consumed[n % 2].record()
+            pf.done(n)
             if cut_ahead:
-                cut_free[b].record()
+                ca.done(step_i)
                 launch_cut(step_i + 1)
             if sg is not None:
                 opt.step_sparse(sg)
                 # device -> host read of this step's loss: asynchronous copy into pinned memory, picked up one step
                 # later (the last one after the timed region's final synchronize)
-                loss_host[n % 2].copy_(loss.detach().reshape(1), non_blocking=True)
-                loss_ready[n % 2].record()
-                if n > 0:
-                    loss_ready[(n - 1) % 2].synchronize()
-                    losses.append(float(loss_host[(n - 1) % 2]))
+                readback.push(loss)
+                losses.extend(readback.pop_ready(keep_newest=1))
                 return
             relevant = (hm._opacity.grad.flatten() != 0).nonzero().flatten().long()
             opt.step(relevant)

@@ -433,6 +433,15 @@ H3DGS_API int h3dgs_ssim_backward(int32_t C, int32_t H, int32_t W, const float* 
  * caller).  Backward: dL_dpred = upstream * scale * mask * sign((pred - target) mask); upstream is a DEVICE scalar or
  * NULL (= 1); for the mean, scale = 1 / n.
  */
+/* Exposure affine + clamp of the render glue (gaussian_renderer/__init__.py:115-118, 277-281):
+ * out = clamp(matmul(image.permute(1,2,0), E[:3,:3]).permute(2,0,1) + E[:3,3,None,None], 0, 1), image [3,H,W],
+ * exposure E device [3,4] row-major or NULL (clamp alone).  Backward: grad_image [3,H,W]; grad_exposure device [12]
+ * is ADDED into (caller zeroes it) or NULL.  Replaces permute / matmul / permute / add / clamp and their autograd. */
+H3DGS_API int h3dgs_exposure_clamp_forward(int32_t H, int32_t W, const float* image, const float* exposure, float* out,
+                                 h3dgs_stream_t stream);
+H3DGS_API int h3dgs_exposure_clamp_backward(int32_t H, int32_t W, const float* image, const float* exposure,
+                                  const float* grad_out, float* grad_image, float* grad_exposure,
+                                  h3dgs_stream_t stream);
 H3DGS_API int h3dgs_masked_l1_forward(int64_t n, const float* pred, const float* target, const float* mask, double* sum,
                             h3dgs_stream_t stream);
 H3DGS_API int h3dgs_masked_l1_backward(int64_t n, const float* pred, const float* target, const float* mask,

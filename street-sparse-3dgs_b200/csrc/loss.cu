@@ -218,6 +218,88 @@ __global__ void __launch_bounds__(256) masked_l1_bwd_kernel(long long n, const f
   }
 }
 
+// Exposure affine + clamp of the render glue (gaussian_renderer/__init__.py:115-118, :277-281):
+//   out[c] = clamp(sum_k in[k] E[k][c] + E[c][3], 0, 1)        (matmul(image.permute(1,2,0), E[:3,:3]) + E[:3,3])
+// exposure: device [3,4] row-major, or NULL for the clamp alone.  One thread per pixel, all three channels.
+struct Expo {
+  float m[3][3];   // m[k][c] = E[k][c]
+  float t[3];      // t[c] = E[c][3]
+};
+__device__ __forceinline__ Expo load_expo(const float* __restrict__ e) {
+  Expo x;
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+#pragma unroll
+    for (int c = 0; c < 3; ++c) x.m[k][c] = e ? __ldg(e + 4 * k + c) : (k == c ? 1.0f : 0.0f);
+    x.t[k] = e ? __ldg(e + 4 * k + 3) : 0.0f;
+  }
+  return x;
+}
+// torch.matmul of a [.., 3] row with a 3x3 matrix: fp32 dot product, k ascending, fused multiply-adds (cuBLAS sgemv /
+// gemm inner loop); then the offset as a separate add
+__device__ __forceinline__ float expo_apply(const Expo& x, int c, float r0, float r1, float r2) {
+  return __fadd_rn(fmaf(r2, x.m[2][c], fmaf(r1, x.m[1][c], __fmul_rn(r0, x.m[0][c]))), x.t[c]);
+}
+
+__global__ void __launch_bounds__(256) exposure_clamp_fwd_kernel(long long npix, const float* __restrict__ in,
+                                                                const float* __restrict__ exposure,
+                                                                float* __restrict__ out) {
+  const Expo x = load_expo(exposure);
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < npix; i += (long long)gridDim.x * blockDim.x) {
+    const float r0 = __ldg(in + i), r1 = __ldg(in + npix + i), r2 = __ldg(in + 2 * npix + i);
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      const float v = exposure ? expo_apply(x, c, r0, r1, r2) : (c == 0 ? r0 : c == 1 ? r1 : r2);
+      out[c * npix + i] = fminf(fmaxf(v, 0.0f), 1.0f);
+    }
+  }
+}
+
+// grad_in[k] = sum_c gate_c grad_out[c] E[k][c];  grad_E[k][c] += sum_pix gate_c grad_out[c] in[k],
+// grad_E[c][3] += sum_pix gate_c grad_out[c];  gate_c = 1 where the unclamped value lies in [0, 1] (torch's clamp
+// backward passes the gradient at the bounds themselves)
+__global__ void __launch_bounds__(256) exposure_clamp_bwd_kernel(long long npix, const float* __restrict__ in,
+                                                                const float* __restrict__ exposure,
+                                                                const float* __restrict__ grad_out,
+                                                                float* __restrict__ grad_in,
+                                                                float* __restrict__ grad_exposure) {
+  __shared__ float red[8][12];
+  const Expo x = load_expo(exposure);
+  float acc[12];
+#pragma unroll
+  for (int j = 0; j < 12; ++j) acc[j] = 0.0f;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < npix; i += (long long)gridDim.x * blockDim.x) {
+    const float r[3] = {__ldg(in + i), __ldg(in + npix + i), __ldg(in + 2 * npix + i)};
+    float g[3];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      const float v = exposure ? expo_apply(x, c, r[0], r[1], r[2]) : r[c];
+      g[c] = (v >= 0.0f && v <= 1.0f) ? __ldg(grad_out + c * npix + i) : 0.0f;
+    }
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      grad_in[k * npix + i] = exposure ? fmaf(g[2], x.m[k][2], fmaf(g[1], x.m[k][1], g[0] * x.m[k][0])) : g[k];
+      if (grad_exposure) {
+#pragma unroll
+        for (int c = 0; c < 3; ++c) acc[4 * k + c] = fmaf(g[c], r[k], acc[4 * k + c]);
+        acc[4 * k + 3] += g[k];
+      }
+    }
+  }
+  if (grad_exposure == nullptr) return;
+#pragma unroll
+  for (int j = 0; j < 12; ++j) {
+    const float v = warp_sum(acc[j]);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5][j] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x < 12) {
+    float t = 0.0f;
+    for (int w = 0; w < 8; ++w) t += red[w][threadIdx.x];
+    atomicAdd(grad_exposure + threadIdx.x, t);
+  }
+}
+
 LossArgs make_args(int C, int H, int W, const float* img1, const float* img2, const float* mask,
                    const float* window) {
   LossArgs a;
@@ -267,4 +349,39 @@ cudaError_t run_masked_l1(long long n, const float* pred, const float* target, c
   return cudaGetLastError();
 }
 
+cudaError_t run_exposure_clamp(long long npix, const float* in, const float* exposure, float* out,
+                               const float* grad_out, float* grad_in, float* grad_exposure, cudaStream_t s) {
+  if (npix <= 0) return cudaSuccess;
+  long long blocks = (npix + 256 * 4 - 1) / (256 * 4);
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  ProfScope ps(K_LOSS, s);
+  if (grad_in) exposure_clamp_bwd_kernel<<<(unsigned)blocks, 256, 0, s>>>(npix, in, exposure, grad_out, grad_in, grad_exposure);
+  else exposure_clamp_fwd_kernel<<<(unsigned)blocks, 256, 0, s>>>(npix, in, exposure, out);
+  return cudaGetLastError();
+}
+
 }  // namespace h3dgs
+
+extern "C" {
+
+int h3dgs_exposure_clamp_forward(int32_t H, int32_t W, const float* image, const float* exposure, float* out,
+                                 h3dgs_stream_t stream) {
+  using namespace h3dgs;
+  if (H < 0 || W < 0 || !image || !out) return fail(H3DGS_EINVAL, "h3dgs_exposure_clamp_forward: bad argument");
+  cudaError_t e = run_exposure_clamp((long long)H * W, image, exposure, out, nullptr, nullptr, nullptr,
+                                     reinterpret_cast<cudaStream_t>(stream));
+  return e == cudaSuccess ? 0 : cuda_fail(e, "h3dgs_exposure_clamp_forward");
+}
+
+int h3dgs_exposure_clamp_backward(int32_t H, int32_t W, const float* image, const float* exposure,
+                                  const float* grad_out, float* grad_image, float* grad_exposure,
+                                  h3dgs_stream_t stream) {
+  using namespace h3dgs;
+  if (H < 0 || W < 0 || !image || !grad_out || !grad_image || (grad_exposure && !exposure))
+    return fail(H3DGS_EINVAL, "h3dgs_exposure_clamp_backward: bad argument");
+  cudaError_t e = run_exposure_clamp((long long)H * W, image, exposure, nullptr, grad_out, grad_image, grad_exposure,
+                                     reinterpret_cast<cudaStream_t>(stream));
+  return e == cudaSuccess ? 0 : cuda_fail(e, "h3dgs_exposure_clamp_backward");
+}
+
+}  // extern "C"

@@ -19,6 +19,46 @@ from diff_gaussian_rasterization import (GaussianRasterizationSettings, Gaussian
                                          rasterize_gaussians_fused, rasterize_gaussians_raw)
 
 
+
+class _ExposureClamp(torch.autograd.Function):
+    """clamp(matmul(image.permute(1, 2, 0), E[:3, :3]).permute(2, 0, 1) + E[:3, 3, None, None], 0, 1) -- the tail of
+    the reference's render() / render_post() (gaussian_renderer/__init__.py:115-118, 277-281) -- as one kernel forward
+    and one backward (h3dgs_exposure_clamp_*), instead of permute, matmul, permute, add, clamp and their autograd."""
+
+    @staticmethod
+    def forward(ctx, image, exposure):
+        image = image.contiguous()
+        E = None if exposure is None else exposure[:3, :4].contiguous()
+        out = torch.empty_like(image)
+        nat.check(nat.lib().h3dgs_exposure_clamp_forward(image.size(1), image.size(2), image.data_ptr(), nat.ptr(E),
+                                                         out.data_ptr(), nat.stream_handle()), "exposure_clamp")
+        ctx.save_for_backward(image, E if E is not None else torch.empty(0, device=image.device))
+        ctx.has_e = E is not None
+        return out
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        image, E = ctx.saved_tensors
+        E = E if ctx.has_e else None
+        grad_out = grad_out.contiguous()
+        grad_image = torch.empty_like(image)
+        want_e = ctx.has_e and ctx.needs_input_grad[1]
+        grad_e = torch.zeros((3, 4), dtype=torch.float32, device=image.device) if want_e else None
+        nat.check(nat.lib().h3dgs_exposure_clamp_backward(image.size(1), image.size(2), image.data_ptr(), nat.ptr(E),
+                                                          grad_out.data_ptr(), grad_image.data_ptr(), nat.ptr(grad_e),
+                                                          nat.stream_handle()), "exposure_clamp backward")
+        return grad_image, grad_e
+
+
+def exposure_clamp(image, exposure=None):
+    """Fused exposure affine (``exposure``: [3,4] or None) + clamp to [0, 1] of a rendered [3,H,W] image."""
+    if image.dim() != 3 or image.size(0) != 3 or not image.is_cuda or image.dtype != torch.float32:
+        raise RuntimeError("exposure_clamp expects a float32 CUDA image [3, H, W]")
+    if exposure is not None and (exposure.dim() != 2 or exposure.size(0) < 3 or exposure.size(1) < 4):
+        raise RuntimeError("exposure must be a [3, 4] matrix")
+    return _ExposureClamp.apply(image, exposure)
+
+
 def _raw_store(pc, pipe, override_color):
     """The raw parameter tensors + activation codes of a reference-style ``GaussianModel``
     (scene/gaussian_model.py:40-48,121-145,411-412) when the kernels can apply its activations themselves;
@@ -189,11 +229,9 @@ def render(viewpoint_camera, pc, pipe, bg_color: torch.Tensor, scaling_modifier=
             rendered_image, radii, depth_image = _rasterize(settings, means3D, means2D, opacity, shs, colors_precomp,
                                                             scales, rotations, cov3D_precomp)
 
-    if use_trained_exp:
-        exposure = pc.get_exposure_from_name(viewpoint_camera.image_name)
-        rendered_image = torch.matmul(rendered_image.permute(1, 2, 0), exposure[:3, :3]).permute(2, 0, 1) + \
-            exposure[:3, 3, None, None]
-    rendered_image = rendered_image.clamp(0, 1)
+    # exposure affine + clamp (gaussian_renderer/__init__.py:115-118) in one kernel forward and one backward
+    exposure = pc.get_exposure_from_name(viewpoint_camera.image_name) if use_trained_exp else None
+    rendered_image = exposure_clamp(rendered_image, exposure)
 
     subfilter, visible = _visible(radii)
     if indices is not None:
@@ -271,14 +309,13 @@ def render_post(viewpoint_camera, pc, pipe, bg_color: torch.Tensor, scaling_modi
         rendered_image, radii, depth_image = _rasterize(settings, means3D, means2D, opacity, shs, colors_precomp,
                                                         scales, rotations, cov3D_precomp, skybox, sparse_grads)
 
+    exposure = None
     if use_trained_exp and pc.pretrained_exposures:
         try:
             exposure = pc.pretrained_exposures[viewpoint_camera.image_name]
-            rendered_image = torch.matmul(rendered_image.permute(1, 2, 0), exposure[:3, :3]).permute(2, 0, 1) + \
-                exposure[:3, 3, None, None]
         except Exception:
             print(f"Exposures should be optimized in single. Missing exposure for image {viewpoint_camera.image_name}")
-    rendered_image = rendered_image.clamp(0, 1)
+    rendered_image = exposure_clamp(rendered_image, exposure)   # :277-281, one kernel each way
 
     vis_filter, visible = _visible(radii)
     out = {"render": rendered_image,

@@ -125,6 +125,8 @@ SIGNATURES = {
                                     c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "h3dgs_ssim_backward": (c_int, [c_int32, c_int32, c_int32, c_void_p, c_void_p, c_void_p, POINTER(c_float), c_void_p,
                                      c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_float, c_void_p, c_void_p]),
+    "h3dgs_exposure_clamp_forward": (c_int, [c_int32, c_int32, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "h3dgs_exposure_clamp_backward": (c_int, [c_int32, c_int32, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "h3dgs_masked_l1_forward": (c_int, [c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "h3dgs_masked_l1_backward": (c_int, [c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_void_p, c_void_p]),
     "h3dgs_blend_stats": (c_int, [c_void_p]),

@@ -145,3 +145,34 @@ def test_ssim_gradient_of_second_image_and_other_windows():
         assert got is not None
         assert float((got - want).abs().max()) <= 1e-4 * float(want.abs().max())
     assert abs(float(lu.ssim(a0, b0, 7)) - float(lu._ssim_torch(a0, b0, 7, True))) == 0.0
+
+
+def test_exposure_clamp_matches_torch_ops():
+    """The tail of render(): matmul(image.permute(1,2,0), E[:3,:3]).permute(2,0,1) + E[:3,3,None,None], clamp(0,1)
+    (gaussian_renderer/__init__.py:115-118) fused; values and all gradients against the torch ops."""
+    from gaussian_renderer import exposure_clamp
+    g = torch.Generator().manual_seed(9)
+    for H, W in ((37, 53), (1080, 1920)):
+        img = (torch.rand(3, H, W, generator=g) * 1.6 - 0.3).to(DEV)          # values outside [0, 1] on both sides
+        img[0, 0, 0], img[1, 0, 1] = 0.0, 1.0                                   # the bounds themselves pass gradient
+        E = (torch.eye(3, 4) + 0.1 * torch.randn(3, 4, generator=g)).to(DEV)
+        up = torch.randn(3, H, W, generator=g).to(DEV)
+        for use_e in (True, False):
+            a, ea = img.clone().requires_grad_(True), E.clone().requires_grad_(True)
+            b, eb = img.clone().requires_grad_(True), E.clone().requires_grad_(True)
+            ours = exposure_clamp(a, ea if use_e else None)
+            pre = b
+            if use_e:
+                pre = torch.matmul(pre.permute(1, 2, 0), eb[:3, :3]).permute(2, 0, 1) + eb[:3, 3, None, None]
+            ref = pre.clamp(0, 1)
+            assert float((ours - ref).abs().max()) <= 5e-7
+            (ours * up).sum().backward()
+            (ref * up).sum().backward()
+            # a pixel whose unclamped value sits within rounding of a bound may gate differently on the two sides
+            away = ((pre.detach().abs() > 1e-6) & ((pre.detach() - 1).abs() > 1e-6)).all(dim=0)
+            if not use_e:
+                away = torch.ones_like(away)   # no arithmetic in front of the clamp: the gates are identical
+            assert float(away.float().mean()) > 0.999
+            assert float(((a.grad - b.grad).abs() * away).max()) <= 2e-6 * float(b.grad.abs().max())
+            if use_e:
+                assert float((ea.grad - eb.grad).abs().max()) <= 1e-4 * float(eb.grad.abs().max())
