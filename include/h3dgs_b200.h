@@ -376,6 +376,46 @@ H3DGS_API int h3dgs_dp_scatter_params(const H3dgsAdamTensor* tensors, int32_t nu
                             h3dgs_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * Densification: statistics every iteration, selection + rebuild every densification interval
+ * (train_single.py:191-197, scene/gaussian_model.py:560-760,780-794).
+ *
+ * h3dgs_densify_stats: for the k-th visible row r = visible_rows[k]: max_radii2D[r] = max(max_radii2D[r], radii[k]),
+ *   xyz_gradient_accum[r] = max(||viewspace_grad[r, :2]||, xyz_gradient_accum[r]), denom[r] += 1.  viewspace_grad is
+ *   [rows,3]; radii / max_radii2D may be NULL (statistics only).
+ * h3dgs_densify_select: clone / split / prune decisions of densify_and_prune for every row and the prefix sums of the
+ *   three categories; synchronises `stream` and returns the sizes (rows kept, clones, splits) -- the caller
+ *   allocates [kept + clones + 2 splits]-row tensors.  dense_extent = percent_dense * scene_extent.  Rows below
+ *   scaffold_points are never cloned, split or pruned.  min_opacity must not exceed 0.15 (the selection's own bound).
+ * h3dgs_densify_split_std: stds [2 splits, 3] of the split samples (get_scaling[selected].repeat(2, 1)); the caller
+ *   draws torch.normal(0, stds) -- the same call the reference makes, so the random stream is consumed identically.
+ * h3dgs_densify_build: writes every tensor's new rows in the reference's final order [kept | clones | split children,
+ *   first copies | second copies]; moments of kept rows are carried over, of new rows zero.
+ * ------------------------------------------------------------------------------------------------ */
+typedef struct H3dgsDensifyTensor {
+  const float* param;       /* [rows,width] */
+  const float* exp_avg;     /* [rows,width] or NULL (no optimizer state yet) */
+  const float* exp_avg_sq;
+  float* new_param;         /* [kept + clones + 2 splits, width] */
+  float* new_exp_avg;       /* same shape, or NULL */
+  float* new_exp_avg_sq;
+  int32_t width;
+} H3dgsDensifyTensor;
+H3DGS_API int h3dgs_densify_stats(int64_t num_visible, const int64_t* visible_rows, const int32_t* radii,
+                        const float* viewspace_grad, float* xyz_gradient_accum, float* denom, float* max_radii2D,
+                        h3dgs_stream_t stream);
+H3DGS_API size_t h3dgs_densify_workspace_bytes(int64_t num_rows);
+H3DGS_API int h3dgs_densify_select(int32_t num_rows, const float* xyz_gradient_accum, const float* max_radii2D,
+                         const float* opacity_raw, int32_t opacity_activation, const float* scaling_raw,
+                         float grad_threshold, float min_opacity, float dense_extent, int32_t scaffold_points,
+                         void* workspace, size_t workspace_bytes, int32_t* counts_host, h3dgs_stream_t stream);
+H3DGS_API int h3dgs_densify_split_std(int32_t num_rows, const float* scaling_raw, const void* workspace,
+                            int32_t num_splits, float* stds, h3dgs_stream_t stream);
+H3DGS_API int h3dgs_densify_build(int32_t num_rows, const H3dgsDensifyTensor* tensors, int32_t num_tensors,
+                        int32_t xyz_index, int32_t scaling_index, int32_t rotation_index, const void* workspace,
+                        int32_t kept, int32_t clones, int32_t splits, const float* split_samples,
+                        h3dgs_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------
  * Hierarchy build.  Replaces the tree stages of the offline GaussianHierarchyCreator
  * (GH/mainHierarchyCreator.cpp:130-141): PointbasedKdTreeGenerator::generate (GH/PointbasedKdTreeGenerator.cpp:16-73),
  * ClusterMerger::merge (GH/ClusterMerger.cpp:23-165), RotationAligner::align (GH/rotation_aligner.cpp:14-114) and

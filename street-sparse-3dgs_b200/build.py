@@ -21,7 +21,7 @@ ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden",
           "-Xptxas", "-v", "--expt-relaxed-constexpr"]
 SOURCES = ["api.cu", "preprocess_fwd.cu", "scan.cu", "binning.cu", "radix_sort.cu", "blend_fwd.cu",
-           "blend_bwd.cu", "blend_bwd2.cu", "preprocess_bwd.cu", "cut.cu", "sparse_adam.cu", "loss.cu", "peaks.cu", "hier_build.cu", "dp_exchange.cu",
+           "blend_bwd.cu", "blend_bwd2.cu", "preprocess_bwd.cu", "cut.cu", "sparse_adam.cu", "loss.cu", "peaks.cu", "hier_build.cu", "dp_exchange.cu", "densify.cu",
            "hier_io.cpp"]
 
 

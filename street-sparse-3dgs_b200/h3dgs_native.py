@@ -73,6 +73,11 @@ class AdamTensor(Structure):
                 ("one_minus_beta1", c_float), ("one_minus_beta2", c_float)]
 
 
+class DensifyTensor(Structure):
+    _fields_ = [("param", c_void_p), ("exp_avg", c_void_p), ("exp_avg_sq", c_void_p), ("new_param", c_void_p),
+                ("new_exp_avg", c_void_p), ("new_exp_avg_sq", c_void_p), ("width", c_int32)]
+
+
 ADAM_MAX_TENSORS = 8
 
 # name -> (restype, argtypes); every symbol include/h3dgs_b200.h declares
@@ -113,6 +118,13 @@ SIGNATURES = {
     "h3dgs_dp_adam": (c_int, [POINTER(AdamTensor), c_int32, c_void_p, c_void_p, c_void_p, c_float, c_void_p, c_int32,
                                c_void_p, c_void_p, c_void_p, c_void_p]),
     "h3dgs_dp_scatter_params": (c_int, [POINTER(AdamTensor), c_int32, c_void_p, c_void_p, c_void_p, c_int32, c_void_p]),
+    "h3dgs_densify_stats": (c_int, [c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "h3dgs_densify_workspace_bytes": (c_size_t, [c_int64]),
+    "h3dgs_densify_select": (c_int, [c_int32, c_void_p, c_void_p, c_void_p, c_int32, c_void_p, c_float, c_float, c_float,
+                                      c_int32, c_void_p, c_size_t, POINTER(c_int32), c_void_p]),
+    "h3dgs_densify_split_std": (c_int, [c_int32, c_void_p, c_void_p, c_int32, c_void_p, c_void_p]),
+    "h3dgs_densify_build": (c_int, [c_int32, POINTER(DensifyTensor), c_int32, c_int32, c_int32, c_int32, c_void_p,
+                                     c_int32, c_int32, c_int32, c_void_p, c_void_p]),
     "h3dgs_hier_build_workspace_bytes": (c_size_t, [c_int64]),
     "h3dgs_hier_build": (c_int, [c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int32, c_void_p, c_void_p,
                                   c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t,
