@@ -247,3 +247,31 @@ def test_torch_extension_loads_and_matches_the_abi():
     assert E.abi_version() == nat.ABI_VERSION
     for name in ("rasterize_forward", "rasterize_backward", "row_map", "Prezero"):
         assert hasattr(E, name)
+
+
+def test_overlay_installer_replaces_three_files_and_restores_them(tmp_path):
+    """Python puts the script's directory first, so the reference's own gaussian_renderer /
+    scene / utils win over PYTHONPATH; the three pure-Python drop-ins are overlaid into the checkout instead."""
+    import importlib.util
+    import os
+    pkg = os.path.join(ROOT, "street-sparse-3dgs_b200")
+    spec = importlib.util.spec_from_file_location("h3dgs_install", os.path.join(pkg, "install_into_reference.py"))
+    inst = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(inst)
+    for rel in inst.FILES + ("scene/__init__.py", "utils/general_utils.py"):
+        p = tmp_path / rel
+        p.parent.mkdir(parents=True, exist_ok=True)
+        p.write_text("# reference " + rel + "\n")
+    assert inst.main([str(tmp_path)]) == 0
+    for rel in inst.FILES:
+        text = (tmp_path / rel).read_text()
+        assert text.startswith(inst.MARK) and open(os.path.join(pkg, rel)).read() in text
+        assert (tmp_path / (rel + ".reference_orig")).read_text() == "# reference " + rel + "\n"
+    assert (tmp_path / "scene/__init__.py").read_text() == "# reference scene/__init__.py\n"   # untouched
+    assert inst.main([str(tmp_path), "--undo"]) == 0
+    for rel in inst.FILES:
+        assert (tmp_path / rel).read_text() == "# reference " + rel + "\n"
+    # what the reference imports from utils.loss_utils across its scripts (train_*.py, render_hierarchy_final.py:5,154)
+    src = open(os.path.join(pkg, "utils", "loss_utils.py")).read()
+    for name in ("def l1_loss", "def l2_loss", "def ssim(", "def ssim_masked", "def create_window", "def gaussian("):
+        assert name in src, name
