@@ -114,18 +114,20 @@ template <bool FUSED>
 __global__ void __launch_bounds__(256) list_visible_kernel(const PreBwdArgs b) {
   const PreArgs& a = b.f;
   const int t_idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t_idx >= a.P) return;
   const H3dgsGrads& o = b.out;
   const int M = a.M;
-  if (a.radii[t_idx] > 0) {
-    b.vis_list[a.ws.offsets[t_idx] - 1u] = (uint32_t)t_idx;
-    if (FUSED && o.row_map != nullptr) {
-      // compact gradients: every store row this slot adds into gets a compact row.  The first thread to turn a
-      // row's map entry from -1 into its (negative) tag owns the row, takes the next compact id and publishes it;
-      // ids are only read by the next kernel.
-      size_t r;
-      long long p = -1;
-      bool lerp = false;
+  const bool valid = t_idx < a.P;
+  const bool visible = valid && a.radii[t_idx] > 0;
+  if (visible) b.vis_list[a.ws.offsets[t_idx] - 1u] = (uint32_t)t_idx;
+  if (FUSED && o.row_map != nullptr) {
+    // compact gradients: every store row a visible slot adds into gets a compact row.  The first thread to turn a
+    // row's map entry from -1 into its (negative) tag owns the row; the owners of a warp take their ids with ONE
+    // atomic on the row counter (one per row serialised 1.7 M atomics on a single address) and publish them; ids are
+    // only read by the next kernel.  Whole warps walk through here together (no early return above).
+    size_t r = 0;
+    long long p = -1;
+    bool lerp = false;
+    if (visible) {
       const int K = a.P - a.skyboxnum;
       if (t_idx >= K) {
         r = (size_t)(a.rows - a.skyboxnum + (t_idx - K));
@@ -136,20 +138,29 @@ __global__ void __launch_bounds__(256) list_visible_kernel(const PreBwdArgs b) {
           if (p >= 0) lerp = __fsub_rn(1.0f, __ldg(a.ts + t_idx)) != 0.0f;
         }
       }
-      const int tag = -2 - 2 * t_idx;
-      for (int side = 0; side < (lerp ? 2 : 1); ++side) {
-        const size_t row = side ? (size_t)p : r;
-        if (atomicCAS(o.row_map + row, -1, tag - side) == -1) {
-          const int id = atomicAdd(o.compact_count, 1);
-          if (id < o.compact_capacity) {
-            o.compact_rows[id] = (long long)row;
-            o.row_map[row] = id;
-          }
+    }
+    const int tag = -2 - 2 * t_idx;
+    const int lane_id = threadIdx.x & 31;
+#pragma unroll
+    for (int side = 0; side < 2; ++side) {
+      const bool want = visible && (side == 0 || lerp);
+      const size_t row = side ? (size_t)(p < 0 ? 0 : p) : r;
+      const bool won = want && atomicCAS(o.row_map + row, -1, tag - side) == -1;
+      const unsigned m = __ballot_sync(0xffffffffu, won);
+      if (m == 0) continue;
+      int base = 0;
+      if (lane_id == __ffs(m) - 1) base = atomicAdd(o.compact_count, __popc(m));
+      base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
+      if (won) {
+        const int id = base + __popc(m & ((1u << lane_id) - 1u));
+        if (id < o.compact_capacity) {
+          o.compact_rows[id] = (long long)row;
+          o.row_map[row] = id;
         }
       }
     }
-    return;
   }
+  if (!valid || visible) return;
   if (o.dL_dmeans2D) {
     o.dL_dmeans2D[(size_t)t_idx * 3] = 0.f;
     o.dL_dmeans2D[(size_t)t_idx * 3 + 1] = 0.f;
