@@ -280,6 +280,24 @@ H3DGS_API int h3dgs_interpolation_weights(int32_t num_entries, const int32_t* no
                                 float vx, float vy, float vz,
                                 float* ts, int32_t* kids, h3dgs_stream_t stream);
 
+/* Incremental cut: ONE refinement step of an existing cut, as the reference's streaming viewer
+ * applies per frame instead of recomputing the cut.  Replaces Switching::changeToSizeStep and its kernels
+ * changeNodesOnce / putNodes / countRenderIndicesIndexed / putRenderIndicesIndexed with their CUB scan and select
+ * (GH/runtime_switching.cu:145-400).  node_indices [num_cut_nodes] is the current node list (start from {0}, the
+ * root, and split all zero); split is int32 [num_nodes], updated in place.  A node larger than target_size that is
+ * not split yet is joined by its children; a node whose PARENT is smaller than target_size drops out (the parent,
+ * still in the list, renders again).  Nodes with start_children == -1 (children not resident) are listed in
+ * nodes_to_expand (may be NULL) instead.  Writes the new node list (capacity max_nodes) and its render / parent /
+ * node-of-render index arrays.  Synchronises `stream` (the new sizes must reach the host, as in the reference).
+ * out_host[4] = {success, new node count, render entries, nodes needing expansion}; success == 0 when the new list
+ * does not fit max_nodes (then only split[] and the counts have been touched, exactly like the reference). */
+H3DGS_API size_t h3dgs_cut_step_workspace_bytes(int32_t max_nodes);
+H3DGS_API int h3dgs_cut_step(int32_t num_cut_nodes, const int32_t* node_indices, int32_t* new_node_indices,
+                   int32_t max_nodes, const int32_t* nodes, const float* boxes, const float* viewpoint_dev,
+                   float target_size, int32_t* split, int32_t* render_indices, int32_t* parent_indices,
+                   int32_t* nodes_of_render_indices, int32_t* nodes_to_expand, void* workspace,
+                   size_t workspace_bytes, int32_t* out_host, h3dgs_stream_t stream);
+
 /* Host function on HOST nodes: DFS pre-order leaf/merged cut.  Call with out == NULL to get the
  * count; returns the number of indices (>= 0) or a negative error. */
 H3DGS_API int64_t h3dgs_expand_to_target(int32_t num_nodes, const int32_t* nodes_host, int32_t target,

@@ -6,6 +6,8 @@ only build products land in ``oracle/_ref/`` (git-ignored, but shipped to the GP
 
     oracle/_ref/ref_hr_C.so   <- submodules/hierarchy-rasterizer  (rasterize_gaussians[_backward])
     oracle/_ref/ref_gh_C.so   <- submodules/gaussianhierarchy     (expand_to_size, get_interpolation_weights, ...)
+    oracle/_ref/ref_switch_tool <- submodules/gaussianhierarchy/runtime_switching.cu under oracle/reftool/ref_switch_tool.cu
+                                 (Switching::changeToSizeStep, the viewer's incremental cut) -- nvcc, no torch
     oracle/_ref/ref_gh_tool   <- submodules/gaussianhierarchy host C++ (HierarchyWriter / HierarchyLoader, the
                                  hierarchy Creator's CPU stages) under the command-line driver
                                  oracle/reftool/ref_gh_tool.cpp -- plain g++, no torch
@@ -52,12 +54,37 @@ def build_tool(verbose=True):
     return True
 
 
+def build_switch_tool(verbose=True):
+    """nvcc on the reference's runtime_switching.cu where it lies + our driver; output oracle/_ref/ref_switch_tool
+    (Switching::changeToSizeStep, the viewer's incremental cut, has no Python binding in the reference)."""
+    import hashlib
+    import subprocess
+    gh = os.path.join(REF, "submodules/gaussianhierarchy")
+    driver = os.path.join(HERE, "reftool", "ref_switch_tool.cu")
+    out = os.path.join(OUT, "ref_switch_tool")
+    stamp = out + ".sha256"
+    h = hashlib.sha256(open(driver, "rb").read()).hexdigest()
+    if os.path.exists(out) and os.path.exists(stamp) and open(stamp).read().strip() == h:
+        return True
+    os.makedirs(OUT, exist_ok=True)
+    cmd = [os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc"), "-gencode", "arch=compute_100a,code=sm_100a", "-O2",
+           "-std=c++17", "-w", "-I" + gh, "-I" + os.path.join(gh, "dependencies/eigen"), driver,
+           os.path.join(gh, "runtime_switching.cu"), "-o", out]
+    if verbose:
+        print("[build_ref]", " ".join(cmd))
+    subprocess.run(cmd, check=True)
+    with open(stamp, "w") as fh:
+        fh.write(h)
+    return True
+
+
 def build(which=("hr", "gh", "tool"), verbose=True):
     if not os.path.isdir(REF):
         print(f"[build_ref] {REF} not present; nothing to do", file=sys.stderr)
         return False
     if "tool" in which:
         build_tool(verbose)
+        build_switch_tool(verbose)
     os.environ["TORCH_CUDA_ARCH_LIST"] = "10.0a"
     os.environ.setdefault("MAX_JOBS", str(os.cpu_count() or 4))
     from torch.utils.cpp_extension import load

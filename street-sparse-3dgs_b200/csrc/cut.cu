@@ -105,7 +105,171 @@ __global__ void __launch_bounds__(256) interpolation_weights_kernel(
   kids[i] = nk;
 }
 
+// ---- incremental cut: one refinement step of an existing cut (Switching::changeToSizeStep and its kernels,
+// GH/runtime_switching.cu:145-400; the viewer moves the cut a level per frame instead of recomputing it) ----
+
+// changeNodesOnce (:145-207): per cut node, stay (1), split into itself + its children (1 + count_children), or
+// collapse into the parent (0); nodes whose children are not resident (start_children == -1) are flagged instead
+__global__ void __launch_bounds__(256) cut_step_decide_kernel(int N, const int* __restrict__ indices,
+                                                             const int* __restrict__ nodes,
+                                                             const float* __restrict__ boxes,
+                                                             const float* __restrict__ viewpoint, float target_size,
+                                                             int* __restrict__ split, uint32_t* __restrict__ counts,
+                                                             uint32_t* __restrict__ need) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N) return;
+  const float vx = __ldg(viewpoint), vy = __ldg(viewpoint + 1), vz = __ldg(viewpoint + 2);
+  const int id = __ldg(indices + i);
+  const int* p = nodes + (size_t)id * 7;
+  const int depth = __ldg(p), parent = __ldg(p + 1), start_children = __ldg(p + 5), count_children = __ldg(p + 6);
+  const float size = projected_size(boxes, (size_t)id, vx, vy, vz);
+  uint32_t count = 1, need_child = 0;
+  if (size >= target_size) {
+    if (depth > 0 && split[id] == 0) {
+      if (start_children == -1) {
+        need_child = 1;
+      } else {
+        count += (uint32_t)count_children;
+        split[id] = 1;
+      }
+    }
+  } else if (parent != -1) {
+    if (projected_size(boxes, (size_t)parent, vx, vy, vz) < target_size) {   // collapse
+      split[parent] = 0;
+      count = 0;
+    }
+  }
+  counts[i] = count;
+  need[i] = need_child;
+}
+
+// putNodes (:209-230) + the DeviceSelect::Flagged of the nodes that need their children loaded
+__global__ void __launch_bounds__(256) cut_step_put_nodes_kernel(int N, const int* __restrict__ indices,
+                                                                const int* __restrict__ nodes,
+                                                                const uint32_t* __restrict__ counts,
+                                                                const uint32_t* __restrict__ offsets,
+                                                                const uint32_t* __restrict__ need,
+                                                                const uint32_t* __restrict__ need_offsets,
+                                                                int* __restrict__ next_nodes, int max_nodes,
+                                                                int* __restrict__ nodes_to_expand) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N) return;
+  const int id = __ldg(indices + i);
+  if (need[i] && nodes_to_expand) nodes_to_expand[need_offsets[i] - 1u] = id;
+  const uint32_t count = counts[i];
+  if (count == 0) return;
+  const uint32_t off = i == 0 ? 0u : offsets[i - 1];
+  if (off + count > (uint32_t)max_nodes) return;   // the caller is told through new_N > max_nodes
+  next_nodes[off] = id;
+  const int start_children = __ldg(nodes + (size_t)id * 7 + 5);
+  for (uint32_t k = 1; k < count; ++k) next_nodes[off + k] = start_children + (int)k - 1;
+}
+
+// countRenderIndicesIndexed (:232-246)
+__global__ void __launch_bounds__(256) cut_step_count_render_kernel(int N, const int* __restrict__ indices,
+                                                                   const int* __restrict__ nodes,
+                                                                   const int* __restrict__ split,
+                                                                   uint32_t* __restrict__ counts) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N) return;
+  const int id = __ldg(indices + i);
+  const int* p = nodes + (size_t)id * 7;
+  int count = __ldg(p + 3);
+  if (__ldg(p) > 0 && split[id] == 0) count += __ldg(p + 4);
+  counts[i] = (uint32_t)count;
+}
+
+// putRenderIndicesIndexed (:248-281)
+__global__ void __launch_bounds__(256) cut_step_put_render_kernel(int N, const int* __restrict__ indices,
+                                                                 const int* __restrict__ nodes,
+                                                                 const uint32_t* __restrict__ counts,
+                                                                 const uint32_t* __restrict__ offsets,
+                                                                 int* __restrict__ render_indices,
+                                                                 int* __restrict__ parent_indices,
+                                                                 int* __restrict__ nodes_of_render_indices) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N) return;
+  const int id = __ldg(indices + i);
+  const int* p = nodes + (size_t)id * 7;
+  const int parent = __ldg(p + 1), start = __ldg(p + 2);
+  const int parent_gaussian = parent != -1 ? __ldg(nodes + (size_t)parent * 7 + 2) : -1;
+  const uint32_t off = i == 0 ? 0u : offsets[i - 1];
+  for (uint32_t k = 0; k < counts[i]; ++k) {
+    render_indices[off + k] = start + (int)k;
+    if (parent_indices) parent_indices[off + k] = parent_gaussian;
+    if (nodes_of_render_indices) nodes_of_render_indices[off + k] = id;
+  }
+}
+
 }  // namespace
+
+struct CutStepWs {
+  uint32_t *counts, *offsets, *need, *need_offsets;
+  unsigned long long* status;
+  uint32_t* counters;
+  size_t bytes;
+  static CutStepWs make(void* base, int max_nodes) {
+    CutStepWs w;
+    char* p = reinterpret_cast<char*>(base);
+    char* p0 = p;
+    const size_t n = (size_t)(max_nodes > 0 ? max_nodes : 1);
+    carve(p, w.counts, n); carve(p, w.offsets, n); carve(p, w.need, n); carve(p, w.need_offsets, n);
+    carve(p, w.status, (n + SCAN_TILE - 1) / SCAN_TILE + 1);
+    carve(p, w.counters, 8);
+    w.bytes = (size_t)(p - p0) + 256;
+    return w;
+  }
+};
+
+size_t cut_step_ws_bytes(int max_nodes) { return CutStepWs::make(nullptr, max_nodes).bytes; }
+
+// -> out_host[0] = success (0 when the new node list would exceed max_nodes: nothing else is written),
+//    [1] = new node count, [2] = render entries, [3] = nodes that need their children loaded
+cudaError_t run_cut_step(int N, const int* node_indices, int* new_node_indices, int max_nodes, const int* nodes,
+                         const float* boxes, const float* viewpoint, float target_size, int* split,
+                         int* render_indices, int* parent_indices, int* nodes_of_render_indices, int* nodes_to_expand,
+                         void* workspace, int* out_host, cudaStream_t s) {
+  out_host[0] = 1; out_host[1] = out_host[2] = out_host[3] = 0;
+  if (N <= 0) return cudaSuccess;
+  CutStepWs w = CutStepWs::make(workspace, max_nodes);
+  const int blocks = (N + 255) / 256;
+  { ProfScope ps(K_CUT_MARK, s);
+    cut_step_decide_kernel<<<blocks, 256, 0, s>>>(N, node_indices, nodes, boxes, viewpoint, target_size, split,
+                                                  w.counts, w.need); }
+  cudaError_t e = launch_scan_inclusive(w.need, w.need_offsets, N, w.status, w.counters, s);
+  if (e != cudaSuccess) return e;
+  e = launch_scan_inclusive(w.counts, w.offsets, N, w.status, w.counters, s);
+  if (e != cudaSuccess) return e;
+  uint32_t last[2] = {0, 0};
+  e = cudaMemcpyAsync(&last[0], w.need_offsets + N - 1, 4, cudaMemcpyDeviceToHost, s);
+  if (e != cudaSuccess) return e;
+  e = cudaMemcpyAsync(&last[1], w.offsets + N - 1, 4, cudaMemcpyDeviceToHost, s);
+  if (e != cudaSuccess) return e;
+  e = cudaStreamSynchronize(s);   // the reference synchronises here too (:345-347): the new list may not fit
+  if (e != cudaSuccess) return e;
+  out_host[3] = (int)last[0];
+  out_host[1] = (int)last[1];
+  if ((int)last[1] > max_nodes) { out_host[0] = 0; return cudaSuccess; }
+  const int newN = (int)last[1];
+  { ProfScope ps(K_CUT_PUT, s);
+    cut_step_put_nodes_kernel<<<blocks, 256, 0, s>>>(N, node_indices, nodes, w.counts, w.offsets, w.need,
+                                                     w.need_offsets, new_node_indices, max_nodes, nodes_to_expand); }
+  if (newN == 0) return cudaGetLastError();
+  const int rblocks = (newN + 255) / 256;
+  { ProfScope ps(K_CUT_MARK, s);
+    cut_step_count_render_kernel<<<rblocks, 256, 0, s>>>(newN, new_node_indices, nodes, split, w.counts); }
+  e = launch_scan_inclusive(w.counts, w.offsets, newN, w.status, w.counters, s);
+  if (e != cudaSuccess) return e;
+  { ProfScope ps(K_CUT_PUT, s);
+    cut_step_put_render_kernel<<<rblocks, 256, 0, s>>>(newN, new_node_indices, nodes, w.counts, w.offsets,
+                                                       render_indices, parent_indices, nodes_of_render_indices); }
+  e = cudaMemcpyAsync(&last[0], w.offsets + newN - 1, 4, cudaMemcpyDeviceToHost, s);
+  if (e != cudaSuccess) return e;
+  e = cudaStreamSynchronize(s);
+  if (e != cudaSuccess) return e;
+  out_host[2] = (int)last[0];
+  return cudaGetLastError();
+}
 
 struct ExpandWs {
   uint32_t* counts;
@@ -164,3 +328,27 @@ cudaError_t run_interpolation_weights(int K, const int* indices, float target_si
 }
 
 }  // namespace h3dgs
+
+extern "C" {
+
+size_t h3dgs_cut_step_workspace_bytes(int32_t max_nodes) { return h3dgs::cut_step_ws_bytes(max_nodes); }
+
+int h3dgs_cut_step(int32_t num_cut_nodes, const int32_t* node_indices, int32_t* new_node_indices, int32_t max_nodes,
+                   const int32_t* nodes, const float* boxes, const float* viewpoint_dev, float target_size,
+                   int32_t* split, int32_t* render_indices, int32_t* parent_indices,
+                   int32_t* nodes_of_render_indices, int32_t* nodes_to_expand, void* workspace,
+                   size_t workspace_bytes, int32_t* out_host, h3dgs_stream_t stream) {
+  using namespace h3dgs;
+  if (num_cut_nodes < 0 || max_nodes < num_cut_nodes || !out_host)
+    return fail(H3DGS_EINVAL, "h3dgs_cut_step: bad sizes");
+  if (num_cut_nodes > 0 && (!node_indices || !new_node_indices || !nodes || !boxes || !viewpoint_dev || !split ||
+                            !render_indices || !workspace))
+    return fail(H3DGS_EINVAL, "h3dgs_cut_step: NULL argument");
+  if (workspace_bytes < cut_step_ws_bytes(max_nodes)) return fail(H3DGS_ENOSPACE, "h3dgs_cut_step: workspace too small");
+  cudaError_t e = run_cut_step(num_cut_nodes, node_indices, new_node_indices, max_nodes, nodes, boxes, viewpoint_dev,
+                               target_size, split, render_indices, parent_indices, nodes_of_render_indices,
+                               nodes_to_expand, workspace, out_host, reinterpret_cast<cudaStream_t>(stream));
+  return e == cudaSuccess ? 0 : cuda_fail(e, "h3dgs_cut_step");
+}
+
+}  // extern "C"

@@ -158,3 +158,45 @@ def build_hierarchy(positions, shs, opacities, scales, rotations, align=True, re
                                  nat.ptr(o_leaf), nat.ptr(ws), ws.numel(), nat.stream_handle()), "build_hierarchy")
     out = (o_pos, o_shs, o_op, o_ls, o_rot, o_nodes, o_boxes)
     return out + (o_cov, o_leaf) if return_debug else out
+
+
+class IncrementalCut:
+    """The reference viewer's frame-to-frame cut maintenance (Switching::changeToSizeStep, GH/runtime_switching.cu:283-400;
+    no Python binding in the reference): keeps a node list and its split flags on the device and moves the cut one
+    level per ``step`` towards the cut of ``expand_to_size`` for the current viewpoint."""
+
+    def __init__(self, nodes, boxes, max_nodes=None):
+        self.nodes = nat.as_i32(nodes, "nodes")
+        self.boxes = nat.as_f32(boxes, "boxes")
+        dev = self.nodes.device
+        n = self.nodes.size(0)
+        self.max_nodes = int(max_nodes if max_nodes is not None else n)
+        i32 = dict(dtype=torch.int32, device=dev)
+        self.node_indices = [torch.zeros(self.max_nodes, **i32), torch.zeros(self.max_nodes, **i32)]
+        self.split = torch.zeros(n, **i32)
+        self.render_indices = torch.zeros(n, **i32)
+        self.parent_indices = torch.zeros(n, **i32)
+        self.nodes_of_render_indices = torch.zeros(n, **i32)
+        self.nodes_to_expand = torch.zeros(self.max_nodes, **i32)
+        self.ws = torch.empty(nat.lib().h3dgs_cut_step_workspace_bytes(self.max_nodes), dtype=torch.uint8, device=dev)
+        self.cur, self.count, self.rendered, self.need_expansion = 0, 1, 0, 0   # the list starts as {root}
+
+    def step(self, target_size, viewpoint):
+        """One refinement step; ``viewpoint``: CUDA float tensor [3].  -> (success, node count, render entries)."""
+        vp = nat.as_f32(viewpoint, "viewpoint")
+        out = (ctypes.c_int32 * 4)()
+        src, dst = self.node_indices[self.cur], self.node_indices[self.cur ^ 1]
+        nat.check(nat.lib().h3dgs_cut_step(self.count, nat.ptr(src), nat.ptr(dst), self.max_nodes, nat.ptr(self.nodes),
+                                           nat.ptr(self.boxes), nat.ptr(vp), float(target_size), nat.ptr(self.split),
+                                           nat.ptr(self.render_indices), nat.ptr(self.parent_indices),
+                                           nat.ptr(self.nodes_of_render_indices), nat.ptr(self.nodes_to_expand),
+                                           nat.ptr(self.ws), self.ws.numel(), out, nat.stream_handle()), "cut_step")
+        self.need_expansion = int(out[3])
+        if out[0]:
+            self.cur ^= 1
+            self.count, self.rendered = int(out[1]), int(out[2])
+        return bool(out[0]), self.count, self.rendered
+
+    @property
+    def current_nodes(self):
+        return self.node_indices[self.cur][:self.count]

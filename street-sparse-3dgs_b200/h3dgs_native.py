@@ -105,6 +105,9 @@ SIGNATURES = {
                                       c_void_p, c_void_p, c_size_t, POINTER(c_int32), c_void_p]),
     "h3dgs_interpolation_weights": (c_int, [c_int32, c_void_p, c_float, c_void_p, c_void_p, c_float,
                                              c_float, c_float, c_void_p, c_void_p, c_void_p]),
+    "h3dgs_cut_step_workspace_bytes": (c_size_t, [c_int32]),
+    "h3dgs_cut_step": (c_int, [c_int32, c_void_p, c_void_p, c_int32, c_void_p, c_void_p, c_void_p, c_float, c_void_p,
+                                c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, POINTER(c_int32), c_void_p]),
     "h3dgs_expand_to_target": (c_int64, [c_int32, c_void_p, c_int32, c_void_p, c_int64]),
     "h3dgs_hier_read_header": (c_int, [c_char_p, POINTER(c_int64), POINTER(c_int64), POINTER(c_int)]),
     "h3dgs_hier_read": (c_int, [c_char_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
