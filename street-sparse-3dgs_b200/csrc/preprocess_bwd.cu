@@ -14,6 +14,10 @@ namespace h3dgs {
 
 namespace {
 
+#ifndef PRE_BWD_CTAS
+#define PRE_BWD_CTAS 2   // resident CTAs per SM of the per-slot backward kernel (register budget 65536 / (256 x CTAs))
+#endif
+
 __device__ __forceinline__ float sq(float x) { return x * x; }
 
 __device__ __forceinline__ float3 ld3(const float* __restrict__ p, size_t row) {
@@ -192,7 +196,7 @@ __global__ void __launch_bounds__(256) list_visible_kernel(const PreBwdArgs b) {
 // three lanes in four idle through ~1500 instructions of a latency-bound kernel).  The grid covers P; CTAs
 // beyond the visible count, which the forward left in the geometry workspace, exit at once.
 template <bool FUSED>
-__global__ void __launch_bounds__(256, 2) preprocess_bwd_kernel(const PreBwdArgs b) {
+__global__ void __launch_bounds__(256, PRE_BWD_CTAS) preprocess_bwd_kernel(const PreBwdArgs b) {
   const PreArgs& a = b.f;
   const unsigned long long V = *reinterpret_cast<const unsigned long long*>(a.ws.counters + 2);
   const unsigned long long vi = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
