@@ -54,6 +54,10 @@ def test_train_single_step_values_match_reference(n, sky, w, h, monkeypatch):
                         staticmethod(lambda *a, **k: (calls.append(1), orig(*a, **k))[1]))
     m_o, out_o, loss_o = _step("ours", sc, cam, sky, gt, alpha_mask, mono, depth_mask, 0.7)
     assert calls, "render() did not take the raw-store path"
+    # two more runs of ours: both arms reduce with float atomics (tests/util.py assert_grad_close, ours_again)
+    again = [_step("ours", sc, cam, sky, gt, alpha_mask, mono, depth_mask, 0.7) for _ in range(2)]
+    for m2, out2, _ in again:
+        assert torch.equal(bits(out2["render"]), bits(out_o["render"]))
     refs = [_step("ref", sc, cam, sky, gt, alpha_mask, mono, depth_mask, 0.7) for _ in range(3)]
     m_r, out_r, loss_r = refs[0]
     assert set(out_o) == set(out_r) == {"render", "depth", "viewspace_points", "visibility_filter", "radii"}
@@ -68,7 +72,8 @@ def test_train_single_step_values_match_reference(n, sky, w, h, monkeypatch):
     names = ["xyz", "features_dc", "features_rest", "opacity", "scaling", "rotation"]
     for i, name in enumerate(names):
         util.assert_grad_close(m_o.parameters()[i].grad, refs[0][0].parameters()[i].grad,
-                               refs[1][0].parameters()[i].grad, name, more_refs=(refs[2][0].parameters()[i].grad,))
+                               refs[1][0].parameters()[i].grad, name, more_refs=(refs[2][0].parameters()[i].grad,),
+                               ours_again=tuple(x[0].parameters()[i].grad for x in again))
     util.assert_grad_close(m_o._exposure.grad, refs[0][0]._exposure.grad, refs[1][0]._exposure.grad, "exposure",
                            more_refs=(refs[2][0]._exposure.grad,))
     util.assert_grad_close(out_o["viewspace_points"].grad, refs[0][1]["viewspace_points"].grad,
