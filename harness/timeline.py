@@ -24,10 +24,19 @@ def main():
     ap.add_argument("--target", type=int, default=5_000_000)
     ap.add_argument("--skybox", type=int, default=100_000)
     ap.add_argument("--e2e", action="store_true")
+    ap.add_argument("--dp", action="store_true", help="under torchrun: the data-parallel step, rank 0 prints its timeline")
+    ap.add_argument("--dp-capacity", type=int, default=1_500_000)
     ap.add_argument("--steps", type=int, default=4)
     ap.add_argument("--step-index", type=int, default=2)
     args = ap.parse_args()
-    dev = torch.device("cuda", 0)
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if args.dp:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
     W, H = 1920, 1080
     import gaussian_hierarchy
     gh = gaussian_hierarchy._C
@@ -36,7 +45,7 @@ def main():
     cams = workload.cameras(W, H, 4, dev, seed=0)
     bg = torch.zeros(3, device=dev)
     g = torch.Generator().manual_seed(1234)
-    if args.e2e:
+    if args.e2e or args.dp:
         from scene.OurAdam import Adam
         model = workload.HierModel(attrs, args.skybox)
         opt = Adam(model.param_groups(), lr=0.0, eps=1e-15)
@@ -45,7 +54,7 @@ def main():
     limit = workload.find_limit(gh, model, cams[0], args.target, dev)
     cut = workload.Cut(n_store, dev)
     cuts = []
-    if not args.e2e:
+    if not (args.e2e or args.dp):
         for c in cams:
             k = workload.Cut(n_store, dev)
             k.compute(gh, model, c, limit)
@@ -58,73 +67,51 @@ def main():
                            c.camera_center.flatten().cpu()]).pin_memory() for c in cams]
     cam_dev = torch.empty(35, device=dev)
 
-    # the e2e step mirrors bench.py's: fused L1 + SSIM loss, ground truth prefetched on a copy stream, the cut of
-    # step i+1 launched on a side stream right after step i's backward
-    if args.e2e:
+    # the e2e step mirrors bench.py's: host pipeline from the package (h3dgs_pipeline: image prefetch, cut one step
+    # ahead, late loss read-back), compact gradients, fused L1 + SSIM loss, Adam.step_sparse; with --dp (under torchrun)
+    # the optimizer step is the peer-memory exchange of h3dgs_parallel.CompactRowExchange
+    if args.e2e or args.dp:
+        import diff_gaussian_rasterization as dgr
+        import h3dgs_pipeline as pl
         from utils.loss_utils import fused_l1_ssim_loss
-        gt_dev2 = [torch.empty(3, H, W, device=dev) for _ in range(2)]
-        cam_dev2 = [torch.empty(35, device=dev) for _ in range(2)]
-        cuts2 = [workload.Cut(n_store, dev) for _ in range(2)]
-        copy_stream, cut_stream = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
-        ready = [torch.cuda.Event() for _ in range(2)]
-        consumed = [torch.cuda.Event() for _ in range(2)]
-        cut_done = [torch.cuda.Event() for _ in range(2)]
-        cut_free = [torch.cuda.Event() for _ in range(2)]
-        for ev in consumed + cut_free:
-            ev.record()
-        state = {"gt": -1, "cut": -1}
+        pf = pl.HostPrefetcher({"gt": ((3, H, W), torch.float32)}, dev)
+        ca = pl.CutAhead(gh, model.nodes, model.boxes, n_store, dev)
+        rb = pl.LossReadback()
+        ex = None
+        if args.dp:
+            import torch.distributed as dist
+            import h3dgs_parallel as par
+            ex = par.CompactRowExchange(opt, n_store, args.dp_capacity, group=dist.group.WORLD)
 
-        def view(k, buf):
-            c0 = cams[k]
-            return SimpleNamespace(image_width=W, image_height=H, FoVx=c0.FoVx, FoVy=c0.FoVy,
-                                   world_view_transform=buf[:16].view(4, 4), full_proj_transform=buf[16:32].view(4, 4),
-                                   camera_center=buf[32:35], image_name=c0.image_name)
-
-        def prefetch(j):
-            if state["gt"] >= j:
-                return
-            copy_stream.wait_event(consumed[j % 2])
-            with torch.cuda.stream(copy_stream):
-                gt_dev2[j % 2].copy_(gt_host, non_blocking=True)
-                ready[j % 2].record(copy_stream)
-            state["gt"] = j
-
-        def launch_cut(j):
-            if state["cut"] >= j:
-                return
-            k, b = j % len(cams), j % 2
-            cut_stream.wait_event(cut_free[b])
-            with torch.cuda.stream(cut_stream):
-                cam_dev2[b].copy_(cam_host[k], non_blocking=True)
-                cuts2[b].compute(gh, model, view(k, cam_dev2[b]), limit, campos_host=cam_host[k][32:35])
-                cut_done[b].record(cut_stream)
-            state["cut"] = j
+        def cam_of(i):
+            return (i * world + rank) % len(cams) if args.dp else i % len(cams)
 
     def step(i):
         with torch.profiler.record_function(f"STEP{i}"):
-            c0 = cams[i % len(cams)]
             for p in model.parameters():
                 p.grad = None
-            if not args.e2e:
-                out = workload.ours_render_post(c0, model, bg, cuts[i % len(cams)], do_depth=True)
+            if not (args.e2e or args.dp):
+                out = workload.ours_render_post(cams[i % len(cams)], model, bg, cuts[i % len(cams)], do_depth=True)
                 loss = (out["render"] * dcol).sum() + (out["depth"] * ddep).sum()
                 loss.backward()
                 return
-            b = i % 2
-            prefetch(i)
-            prefetch(i + 1)
-            launch_cut(i)
-            torch.cuda.current_stream().wait_event(cut_done[b])
-            out = workload.ours_render_post(view(i % len(cams), cam_dev2[b]), model, bg, cuts2[b], do_depth=False)
-            torch.cuda.current_stream().wait_event(ready[b])
-            loss = fused_l1_ssim_loss(out["render"], gt_dev2[b], 0.2)[0]
+            pf.fetch(i, {"gt": gt_host})
+            pf.fetch(i + 1, {"gt": gt_host})
+            ca.launch(i, cams[cam_of(i)], cam_host[cam_of(i)], limit)
+            c, this_cut = ca.get(i)
+            sg = dgr.SparseGradients()
+            out = workload.ours_render_post(c, model, bg, this_cut, do_depth=False, sparse_grads=sg)
+            loss = fused_l1_ssim_loss(out["render"], pf.get(i)["gt"], 0.2)[0]
             loss.backward()
-            consumed[b].record()
-            cut_free[b].record()
-            launch_cut(i + 1)
-            relevant = (model._opacity.grad.flatten() != 0).nonzero().flatten().long()
-            opt.step(relevant)
-            loss.item()
+            pf.done(i)
+            ca.done(i)
+            ca.launch(i + 1, cams[cam_of(i + 1)], cam_host[cam_of(i + 1)], limit)
+            if ex is not None:
+                ex.step(sg)
+            else:
+                opt.step_sparse(sg)
+            rb.push(loss)
+            rb.pop_ready(keep_newest=1)
 
     for i in range(4):
         step(i)
@@ -135,6 +122,8 @@ def main():
         for i in range(args.steps):
             step(base_i + i)
         torch.cuda.synchronize()
+    if rank != 0:
+        return 0
     path = os.path.join(tempfile.mkdtemp(), "trace.json")
     prof.export_chrome_trace(path)
     ev = json.load(open(path))["traceEvents"]
