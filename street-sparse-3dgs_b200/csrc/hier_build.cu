@@ -73,7 +73,6 @@ struct HbWs {
   int* level_fill;        // [HB_MAX_LEVELS] append cursors
   float* scale;           // [nn,3] scale of every row (leaf: input; merged: sqrt |eigenvalue|), log taken at the end
   float* weight;          // [nn,2] normalised merge weights of the node's two children
-  int* leaf_of_node;      // [nn] input Gaussian of a leaf node
   int* row_of_gaussian;   // [N] pre-order row of every input Gaussian
   float* cov;             // [nn,6] when the caller does not ask for the covariances
   int* errflag;
@@ -93,11 +92,11 @@ struct HbWs {
     carve(p, w.bsum, 3 * sblocks + 4);
     carve(p, w.sort_ws, sort_pairs_ws_words((long long)n));
     carve(p, w.lo, 3 * n); carve(p, w.hi, 3 * n);
-    carve(p, w.nd.nodes, 1);   // the node table itself is an output; placeholder keeps the struct uniform
+    w.nd.nodes = nullptr;      // the node table itself is an output, set by the driver
     carve(p, w.nd.begin, nn); carve(p, w.nd.size, nn); carve(p, w.nd.krank, nn);
     carve(p, w.nd.box, 6 * nn); carve(p, w.nd.axis, nn); carve(p, w.nd.level, nn);
     carve(p, w.level_nodes, nn); carve(p, w.level_fill, HB_MAX_LEVELS);
-    carve(p, w.scale, 3 * nn); carve(p, w.weight, 2 * nn); carve(p, w.leaf_of_node, nn);
+    carve(p, w.scale, 3 * nn); carve(p, w.weight, 2 * nn);
     carve(p, w.row_of_gaussian, n); carve(p, w.cov, 6 * nn); carve(p, w.errflag, 4);
     w.bytes = (size_t)(p - p0) + 256;
     return w;
@@ -556,14 +555,12 @@ __global__ void __launch_bounds__(HB_THREADS) hb_leaf_rows_kernel(int N, const u
                                                                  const float* __restrict__ opac,
                                                                  const float* __restrict__ scale,
                                                                  const float* __restrict__ rot, HbRows out,
-                                                                 int* __restrict__ leaf_of_node,
                                                                  int* __restrict__ row_of_gaussian,
                                                                  int* __restrict__ leaf_order) {
   const int g = blockIdx.x * HB_THREADS + threadIdx.x;
   if (g >= N) return;
   const uint32_t node = node_of[g];
   const int row = nodes[(size_t)node * 7 + 2];
-  leaf_of_node[node] = g;
   row_of_gaussian[g] = row;
   if (leaf_order) leaf_order[row] = g;
   float s[3], q[4], c[6];
@@ -848,7 +845,7 @@ cudaError_t run_hier_build(long long N64, const float* pos, const float* shs, co
                                                   l, w.lscan);
       cur ^= 1;
     }
-    hb_leaf_rows_kernel<<<gN, HB_THREADS, 0, s>>>(N, w.node_of[cur], o_nodes, pos, opac, scale, rot, R, w.leaf_of_node,
+    hb_leaf_rows_kernel<<<gN, HB_THREADS, 0, s>>>(N, w.node_of[cur], o_nodes, pos, opac, scale, rot, R,
                                                   w.row_of_gaussian, o_leaf_order);
     hb_leaf_shs_kernel<<<(unsigned)((N64 * 12 + HB_THREADS - 1) / HB_THREADS), HB_THREADS, 0, s>>>(
         N64 * 12, w.row_of_gaussian, reinterpret_cast<const float4*>(shs), reinterpret_cast<float4*>(o_shs));

@@ -111,3 +111,30 @@ def test_statistics_step_matches_torch_ops():
     dr.add_stats(state, grad, vis, radii)
     assert _close(m.xyz_gradient_accum, state["xyz_gradient_accum"], 2e-7)
     assert torch.equal(m.denom, state["denom"]) and torch.equal(m.max_radii2D, state["max_radii2D"])
+
+
+def test_nothing_selected_and_everything_split():
+    """Edge cases of the selection: a threshold nothing reaches (only the opacity prune acts; no samples are drawn) and
+    a threshold everything reaches with a zero dense extent (every unpruned row above the opacity bound splits)."""
+    import h3dgs_densify as hd
+    state, x, want = load_case("c", DEV)
+    n = state["params"]["xyz"].shape[0]
+    op = torch.sigmoid(state["params"]["opacity"]).flatten()
+    m = _model(state, None)
+    info = hd.densify_and_prune(m, 1e9, 0.005, 4.0)
+    assert info["clones"] == 0 and info["splits"] == 0 and info["samples"].shape == (0, 3)
+    keep = op >= 0.005
+    assert info["kept"] == int(keep.sum()) == m._xyz.shape[0]
+    assert torch.equal(m._xyz.detach(), state["params"]["xyz"][keep])
+    assert m._features_rest not in m.optimizer.state   # case c carries no optimizer state: nothing to hand over
+    m = _model(state, None, percent_dense=0.0)
+    state["xyz_gradient_accum"][:] = 1.0
+    m.xyz_gradient_accum = state["xyz_gradient_accum"].clone()
+    m.max_radii2D = torch.full((n,), 10.0, device=DEV)
+    torch.manual_seed(1)
+    info = hd.densify_and_prune(m, 1e-9, 0.005, 4.0)
+    sel = op > 0.15
+    assert info["splits"] == int(sel.sum()) and info["clones"] == 0
+    assert info["kept"] == int(((op >= 0.005) & ~sel).sum())
+    assert m._xyz.shape[0] == info["kept"] + 2 * info["splits"]
+    assert torch.isfinite(m._xyz).all() and torch.isfinite(m._scaling).all()
