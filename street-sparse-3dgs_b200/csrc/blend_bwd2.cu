@@ -18,6 +18,9 @@ constexpr int B2_THREADS = 128;
 constexpr int B2_BATCH = 128;      // list entries staged per round (one per thread)
 constexpr int B2_SUB = 8;          // 8x8 pixel block per warp
 constexpr int ACC_W = 12;
+#ifndef B2_MIN_CTAS
+#define B2_MIN_CTAS 9   // resident CTAs per SM the register allocation aims at (56 registers, 8 bytes spilled): 1.32 -> 1.27 ms; 10 (51 registers) is slower (1.35)
+#endif
 
 struct Bwd2Smem {
   Rec rec[2][B2_BATCH];
@@ -115,7 +118,7 @@ __device__ __forceinline__ void pixel_terms(const PixA& r, const float4 con_o, c
 }
 
 template <bool INTERP, bool DEPTH, bool COUNT = false>
-__global__ void __launch_bounds__(B2_THREADS) blend_bwd2_kernel(const BlendArgs a) {
+__global__ void __launch_bounds__(B2_THREADS, B2_MIN_CTAS) blend_bwd2_kernel(const BlendArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   Bwd2Smem& sm = *reinterpret_cast<Bwd2Smem*>(smem_raw);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
