@@ -278,12 +278,12 @@ int h3dgs_forward_begin(const H3dgsView* view, const H3dgsGaussians* g, int32_t*
   H3_CUDA(cudaMemcpyAsync(counts_host, gw.counters + 4, sizeof(int64_t), cudaMemcpyDeviceToHost, s));       // R
   if (counts_event) H3_CUDA(cudaEventRecord((cudaEvent_t)counts_event, s));
   const unsigned long long* v_dev = reinterpret_cast<const unsigned long long*>(gw.counters + 2);
-  // visible slots -> (depth, slot) order -> inclusive scan of their tile counts in that order
+  // visible slots -> (depth, slot) order -> inclusive scan of their strip-record counts in that order
   H3_CUDA(launch_compact_visible(g->P, gw, s));
   if ((rc = debug_sync(debug, s, "compact_visible"))) return rc;
   H3_CUDA(launch_depth_sort(gw, g->P, v_dev, s));
   if ((rc = debug_sync(debug, s, "depth_sort"))) return rc;
-  H3_CUDA(launch_scan_gather(gw.tiles_touched, gw.dvals[0], gw.soffs, g->P, v_dev, gw.chunk_first, gw.gscan_status,
+  H3_CUDA(launch_scan_strips(gw.tile_rect, gw.dvals[0], gw.soffs, g->P, v_dev, gw.chunk_first, gw.gscan_status,
                              gw.gscan_counters, s));
   if (!counts_event) {
     H3_CUDA(cudaStreamSynchronize(s));
@@ -322,14 +322,14 @@ int h3dgs_forward_finish(const H3dgsView* view, const H3dgsGaussians* g, void* g
   const int grid_x = (W + TILE_X - 1) / TILE_X, grid_y = (H + TILE_Y - 1) / TILE_Y;
   const SortPlan plan = make_sort_plan(W, H);
 
-  // ordered emission -> stable partition by tile
+  // ordered emission of strip records -> stable partition by strip -> expansion into the tiles' lists
   { ProfScope ps(K_MEMSET, s); H3_CUDA(cudaMemsetAsync(bw.zero_base, 0, bw.zero_bytes, s)); }
-  H3_CUDA(launch_emit_instances(R, V, gw, bw, grid_x, plan.tile_key_bytes, s));
-  if ((rc = debug_sync(debug, s, "emit_instances"))) return rc;
-  H3_CUDA(launch_tile_sort(bw, R, plan, gw.depth, s));
-  if ((rc = debug_sync(debug, s, "tile_sort"))) return rc;
-  H3_CUDA(launch_tile_ranges(R, bw.keys64, iw.ranges, grid_x * grid_y, s));
-  if ((rc = debug_sync(debug, s, "tile_ranges"))) return rc;
+  H3_CUDA(launch_emit_strips(R, V, gw, bw, plan, s));
+  if ((rc = debug_sync(debug, s, "emit_strips"))) return rc;
+  H3_CUDA(launch_strip_sort(bw, R, reinterpret_cast<const unsigned long long*>(gw.gscan_counters + 2), plan, s));
+  if ((rc = debug_sync(debug, s, "strip_sort"))) return rc;
+  H3_CUDA(launch_expand(R, gw, bw, plan, grid_x, grid_y, iw.ranges, s));
+  if ((rc = debug_sync(debug, s, "expand"))) return rc;
   H3_CUDA(launch_tile_order(iw.ranges, nullptr, grid_x * grid_y, iw.order_fwd, s));
   H3_CUDA(cudaMemsetAsync(iw.tile_last, 0, sizeof(uint32_t) * (size_t)(grid_x * grid_y), s));
 
@@ -337,7 +337,7 @@ int h3dgs_forward_finish(const H3dgsView* view, const H3dgsGaussians* g, void* g
   std::memset(&b, 0, sizeof(b));
   b.W = W; b.H = H; b.grid_x = grid_x; b.grid_y = grid_y; b.P = g->P; b.skyboxnum = g->skyboxnum;
   b.interp = (g->ts != nullptr && g->kids != nullptr) ? 1 : 0;
-  b.ranges = iw.ranges; b.point_list = bw.tvals[bw.sorted]; b.rec = gw.rec; b.bg = view->background;
+  b.ranges = iw.ranges; b.point_list = bw.point_list; b.rec = gw.rec; b.bg = view->background;
   b.final_T = iw.final_T; b.n_contrib = iw.n_contrib; b.accum = iw.accum;
   b.out_color = out_color; b.out_invdepth = out_invdepth;
   b.order = iw.order_fwd; b.tile_last = iw.tile_last; b.stats = g_blend_stats;
@@ -423,12 +423,12 @@ int h3dgs_backward(const H3dgsView* view, const H3dgsGaussians* g, const int32_t
   b.W = W; b.H = H; b.grid_x = (W + TILE_X - 1) / TILE_X; b.grid_y = (H + TILE_Y - 1) / TILE_Y;
   b.P = P; b.skyboxnum = g->skyboxnum;
   b.interp = (g->ts != nullptr && g->kids != nullptr) ? 1 : 0;
-  b.ranges = iw.ranges; b.point_list = bw.tvals[bw.sorted]; b.rec = gw.rec; b.bg = view->background;
+  b.ranges = iw.ranges; b.point_list = bw.point_list; b.rec = gw.rec; b.bg = view->background;
   b.final_T = iw.final_T; b.n_contrib = iw.n_contrib; b.accum = iw.accum;
   b.dL_dcolor = dL_dout_color; b.dL_dinvdepth = dL_dout_invdepth; b.grad = ww.grad;
   H3_CUDA(launch_tile_order(nullptr, iw.tile_last, b.grid_x * b.grid_y, iw.order_bwd, s));
   b.order = iw.order_bwd; b.stats = g_blend_stats;
-  b.snap = bw.snap; b.keys64 = bw.keys64; b.nseg = R > 0 ? (int)((R - 1) / BLEND_SEG) : 0;
+  b.snap = bw.snap; b.seg_tile = bw.seg_tile; b.nseg = R > 0 ? (int)((R - 1) / BLEND_SEG) : 0;
   H3_CUDA(launch_blend_bwd(b, s));
   if ((rc = debug_sync(debug, s, "blend_bwd"))) return rc;
 
@@ -559,8 +559,17 @@ int h3dgs_debug_view(int32_t P, int32_t W, int32_t H, int64_t R, const void* geo
   }
   if (binning && R > 0) {
     BinWs bw = BinWs::make(const_cast<void*>(binning), R, W, H);
-    out->point_list_keys = reinterpret_cast<const uint64_t*>(bw.keys64);
-    out->point_list = bw.tvals[bw.sorted];
+    out->point_list = bw.point_list;
+    if (geom && image) {
+      // the 64-bit keys are not part of the product path any more: materialise them for the parity tests
+      GeomWs gw = GeomWs::make(const_cast<void*>(geom), P);
+      ImageWs iw = ImageWs::make(const_cast<void*>(image), W, H);
+      const int tiles = ((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
+      H3_CUDA(cudaDeviceSynchronize());
+      H3_CUDA(launch_fill_keys64(iw.ranges, tiles, bw.point_list, gw.depth, bw.keys64, (cudaStream_t)0));
+      H3_CUDA(cudaDeviceSynchronize());
+      out->point_list_keys = reinterpret_cast<const uint64_t*>(bw.keys64);
+    }
   }
   if (image) {
     ImageWs iw = ImageWs::make(const_cast<void*>(image), W, H);

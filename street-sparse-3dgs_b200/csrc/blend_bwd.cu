@@ -42,7 +42,7 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_bwd_kernel(const BlendArg
   int tile, k = 0;
   if ((int)blockIdx.x < a.nseg) {
     const unsigned x = blockIdx.x + 1;
-    tile = (int)(a.keys64[(size_t)x * BLEND_SEG] >> 32);
+    tile = (int)a.seg_tile[x];
     const uint2 r = a.ranges[tile];
     k = (int)x - (int)(r.x / BLEND_SEG);
     if (k < 1 || r.x + (unsigned)k * BLEND_SEG >= r.y) return;

@@ -125,7 +125,7 @@ __global__ void __launch_bounds__(B2_THREADS, B2_MIN_CTAS) blend_bwd2_kernel(con
   int tile, k = 0;
   if ((int)blockIdx.x < a.nseg) {   // work items that start at a list cut lead the grid (blend_bwd.cu)
     const unsigned x = blockIdx.x + 1;
-    tile = (int)(a.keys64[(size_t)x * BLEND_SEG] >> 32);
+    tile = (int)a.seg_tile[x];
     const uint2 r = a.ranges[tile];
     k = (int)x - (int)(r.x / BLEND_SEG);
     if (k < 1 || r.x + (unsigned)k * BLEND_SEG >= r.y) return;

@@ -52,7 +52,9 @@ constexpr int SORT_ITEMS = 12;
 constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;
 constexpr int SORT_MAX_PASSES = 4;
 constexpr int SORT_DEPTH_PASSES = 4;   // 32 depth bits, 8 per pass
-constexpr int EMIT_CHUNK = 2048;       // instances written per CTA of the emission kernel
+constexpr int EMIT_CHUNK = 2048;       // strip records written per CTA of the emission kernel
+constexpr int STRIP_TILES = 64;        // tiles of one tile row that a warp expands together (two per lane)
+constexpr int EXPAND_CHUNK = 512;      // strip records per warp of the expansion kernels
 constexpr long long MAX_INSTANCES = 1ll << 30;   // a render with more tile instances is rejected
 
 // Everything whose size is known before the render's instance count R is: per-slot state and the depth sort of
@@ -71,7 +73,7 @@ struct GeomWs {
   // depth sort of the visible slots
   uint32_t* dkeys[2];               // depth bits of the visible slots, double buffered
   uint32_t* dvals[2];               // visible slots; dvals[0] ends up in (depth, slot) order
-  uint32_t* soffs;                  // inclusive scan of tiles_touched in that order
+  uint32_t* soffs;                  // inclusive scan of the strip-record counts in that order
   uint32_t* chunk_first;            // [MAX_INSTANCES / EMIT_CHUNK + 2] first position (in that order) reaching into each chunk
   unsigned long long* gscan_status; // look-back words of the gathered scan
   uint32_t* gscan_counters;
@@ -155,56 +157,58 @@ struct SortShifts {
 };
 
 struct SortPlan {
-  int tile_bits_total;             // bits of a tile id, as the reference counts them
-  int tile_passes;                 // ceil(tile_bits_total / 8)
-  int tile_shift[SORT_MAX_PASSES];
-  int tile_bits[SORT_MAX_PASSES];
-  int tile_key_bytes;              // 2 (tile ids fit 16 bits) or 4
+  int strips_per_row;              // ceil(grid_x / STRIP_TILES)
+  int strips;                      // strips_per_row * grid_y
+  int passes;                      // ceil(bits of a strip id / 8)
+  int shift[SORT_MAX_PASSES];
+  int bits[SORT_MAX_PASSES];
+  int key_bytes;                   // 2 (strip ids fit 16 bits) or 4
 };
 
-// Number of key bits that matter above the 32 depth bits: the reference's getHigherMsb
-// (HR/cuda_rasterizer/rasterizer_impl.cu:35-50,349) of the tile count.
-inline uint32_t higher_msb(uint32_t n) {
-  uint32_t msb = sizeof(n) * 4;
-  uint32_t step = msb;
-  while (step > 1) {
-    step /= 2;
-    if (n >> msb) msb += step; else msb -= step;
-  }
-  if (n >> msb) msb++;
-  return msb;
-}
-
 inline SortPlan make_sort_plan(int W, int H) {
-  uint32_t tiles = (uint32_t)((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
+  const int grid_x = (W + TILE_X - 1) / TILE_X, grid_y = (H + TILE_Y - 1) / TILE_Y;
   SortPlan pl;
-  int total = (int)higher_msb(tiles);
-  if (total < 1) total = 1;
-  pl.tile_bits_total = total;
-  pl.tile_passes = (total + SORT_RADIX_BITS - 1) / SORT_RADIX_BITS;
-  const int base = total / pl.tile_passes, extra = total % pl.tile_passes;
+  pl.strips_per_row = (grid_x + STRIP_TILES - 1) / STRIP_TILES;
+  pl.strips = pl.strips_per_row * grid_y;
+  int total = 1;
+  while (total < 32 && (1ll << total) < (long long)pl.strips) ++total;
+  pl.passes = (total + SORT_RADIX_BITS - 1) / SORT_RADIX_BITS;
+  const int base = total / pl.passes, extra = total % pl.passes;
   int sft = 0;
   for (int i = 0; i < SORT_MAX_PASSES; ++i) {
-    pl.tile_bits[i] = i < pl.tile_passes ? base + (i < extra ? 1 : 0) : 0;
-    pl.tile_shift[i] = sft;
-    sft += pl.tile_bits[i];
+    pl.bits[i] = i < pl.passes ? base + (i < extra ? 1 : 0) : 0;
+    pl.shift[i] = sft;
+    sft += pl.bits[i];
   }
-  pl.tile_key_bytes = total <= 16 ? 2 : 4;
+  pl.key_bytes = total <= 16 ? 2 : 4;
   return pl;
 }
 
-// Binning workspace: everything sized by the instance count R (allocated once the host has read R).
+// Binning workspace: everything sized by the instance count R (allocated once the host has read R).  The number
+// of strip records (one per visible slot, tile row and 64-tile strip its rectangle reaches into) is only known on
+// the device; it never exceeds R, which sizes their buffers.
 struct BinWs {
-  void* tkeys[2];               // tile ids of the emitted instances (u16 or u32), double buffered
-  uint32_t* tvals[2];           // slot of each instance, double buffered; tvals[sorted] is point_list
-  unsigned long long* keys64;   // point_list_keys: (tile << 32) | depth bits, sorted
+  void* skeys[2];               // strip ids of the emitted records (u16 or u32), double buffered
+  uint32_t* svals[2];           // slot of each record, double buffered
+  uint32_t* point_list;         // [R] slots of all instances, by tile, (depth, slot) order inside a tile
+  unsigned long long* keys64;   // [R] point_list_keys: (tile << 32) | depth bits -- filled for h3dgs_debug_view only
   float* snap;                  // [R / BLEND_SEG + 2][SNAP_FLOATS] forward snapshots at the list cuts
-  char* zero_base;              // tile_hist .. counters are contiguous: one memset
+  uint32_t* seg_tile;           // [R / BLEND_SEG + 2] tile whose list holds instance x * BLEND_SEG
+  uint32_t* chunk_strip;        // [max_chunks] strip of each expansion chunk
+  uint32_t* counts;             // [STRIP_TILES * max_chunks] instances per (strip, tile of the strip, chunk), ragged
+  uint32_t* offs;               // inclusive scan of counts
+  unsigned long long* cscan_status;
+  uint32_t* cscan_counters;
+  char* zero_base;              // strip_hist .. strip_range are contiguous: one memset
   size_t zero_bytes;
-  uint32_t* tile_hist;          // [SORT_MAX_PASSES][SORT_RADIX]
-  uint32_t* tile_status;        // [tile_passes][tiles(R)][SORT_RADIX]
-  uint32_t* counters;           // [0..3]: dynamic tile ids of the tile passes
-  int sorted;                   // index (0/1) of the tvals buffer holding point_list
+  uint32_t* strip_hist;         // [SORT_MAX_PASSES][SORT_RADIX]
+  uint32_t* strip_status;       // [passes][tiles(R)][SORT_RADIX]
+  uint32_t* counters;           // [0..3]: dynamic tile ids of the strip passes; [4..5] u64 scan length, [6] chunks
+  uint2* strip_range;           // [strips] records of each strip in the sorted order
+  uint32_t* strip_nch;          // [strips] expansion chunks of each strip
+  uint32_t* strip_cbase;        // [strips] first chunk of each strip
+  int sorted;                   // index (0/1) of the skeys / svals buffers holding the sorted records
+  size_t max_chunks;
   size_t bytes;
   static BinWs make(void* base, int64_t R, int W, int H) {
     BinWs w;
@@ -213,19 +217,30 @@ struct BinWs {
     char* p0 = p;
     const size_t n = (size_t)(R > 0 ? R : 1);
     const size_t tiles_r = (n + SORT_TILE - 1) / SORT_TILE;
+    w.max_chunks = n / EXPAND_CHUNK + (size_t)pl.strips + 1;
     char* tk;
-    carve(p, tk, n * pl.tile_key_bytes); w.tkeys[0] = tk;
-    carve(p, tk, n * pl.tile_key_bytes); w.tkeys[1] = tk;
-    carve(p, w.tvals[0], n);
-    carve(p, w.tvals[1], n);
+    carve(p, tk, n * pl.key_bytes); w.skeys[0] = tk;
+    carve(p, tk, n * pl.key_bytes); w.skeys[1] = tk;
+    carve(p, w.svals[0], n);
+    carve(p, w.svals[1], n);
+    carve(p, w.point_list, n);
     carve(p, w.keys64, n);
     carve(p, w.snap, (n / BLEND_SEG + 2) * (size_t)SNAP_FLOATS);
-    w.sorted = pl.tile_passes & 1;
-    carve(p, w.tile_hist, (size_t)SORT_MAX_PASSES * SORT_RADIX);
-    w.zero_base = reinterpret_cast<char*>(w.tile_hist);
-    carve(p, w.tile_status, (size_t)pl.tile_passes * tiles_r * SORT_RADIX);
+    carve(p, w.seg_tile, n / BLEND_SEG + 2);
+    carve(p, w.chunk_strip, w.max_chunks);
+    carve(p, w.counts, w.max_chunks * STRIP_TILES);
+    carve(p, w.offs, w.max_chunks * STRIP_TILES);
+    carve(p, w.cscan_status, (w.max_chunks * STRIP_TILES + SCAN_TILE - 1) / SCAN_TILE + 1);
+    carve(p, w.cscan_counters, 8);
+    w.sorted = pl.passes & 1;
+    carve(p, w.strip_hist, (size_t)SORT_MAX_PASSES * SORT_RADIX);
+    w.zero_base = reinterpret_cast<char*>(w.strip_hist);
+    carve(p, w.strip_status, (size_t)pl.passes * tiles_r * SORT_RADIX);
     carve(p, w.counters, 8);
+    carve(p, w.strip_range, (size_t)pl.strips);
     w.zero_bytes = (size_t)(p - w.zero_base);
+    carve(p, w.strip_nch, (size_t)pl.strips);
+    carve(p, w.strip_cbase, (size_t)pl.strips);
     w.bytes = (size_t)(p - p0) + 256;
     return w;
   }
@@ -296,24 +311,31 @@ cudaError_t launch_scan_inclusive(const uint32_t* in, uint32_t* out, int n, unsi
 // rank (inclusive) of every visible slot among the visible ones; totals: counters[2..3] = V, counters[4..5] = R
 cudaError_t launch_scan_visible(const uint32_t* tiles_touched, uint32_t* rank, int n,
                                 unsigned long long* status, uint32_t* counters, cudaStream_t s);
-// inclusive scan of tiles_touched[order[i]], i < *n_dev (a device u64; at most n_cap)
-cudaError_t launch_scan_gather(const uint32_t* tiles_touched, const uint32_t* order, uint32_t* out, int n_cap,
+// inclusive scan of the strip-record counts of slots order[i], i < *n_dev (a device u64; at most n_cap); the total
+// is left at counters[2..3]
+cudaError_t launch_scan_strips(const ushort4* tile_rect, const uint32_t* order, uint32_t* out, int n_cap,
                                const unsigned long long* n_dev, uint32_t* chunk_first, unsigned long long* status,
                                uint32_t* counters, cudaStream_t s);
+// inclusive scan of in[0 .. *n_dev) (at most n_cap)
+cudaError_t launch_scan_counts(const uint32_t* in, uint32_t* out, long long n_cap, const unsigned long long* n_dev,
+                               unsigned long long* status, uint32_t* counters, cudaStream_t s);
 
-// binning.cu: visible slots -> (depth bits, slot) pairs + depth digit histograms; ordered emission
+// binning.cu: visible slots -> (depth bits, slot) pairs + depth digit histograms; ordered emission of strip
+// records; expansion of the sorted records into point_list, ranges and seg_tile
 cudaError_t launch_compact_visible(int P, GeomWs& g, cudaStream_t s);
-cudaError_t launch_emit_instances(int64_t R, int64_t V, const GeomWs& g, BinWs& b, int grid_x, int key_bytes,
-                                  cudaStream_t s);
+cudaError_t launch_emit_strips(int64_t R, int64_t V, const GeomWs& g, BinWs& b, const SortPlan& plan, cudaStream_t s);
+cudaError_t launch_expand(int64_t R, const GeomWs& g, BinWs& b, const SortPlan& plan, int grid_x, int grid_y,
+                          uint2* ranges, cudaStream_t s);
+cudaError_t launch_fill_keys64(const uint2* ranges, int tiles, const uint32_t* point_list, const float* depth,
+                               unsigned long long* keys64, cudaStream_t s);
 // order[] = tile ids sorted by descending work (ranges given: list length; else lengths[] itself), 64 log buckets
 cudaError_t launch_tile_order(const uint2* ranges, const uint32_t* lengths, int tiles, uint32_t* order,
                               cudaStream_t s);
-cudaError_t launch_tile_ranges(int64_t R, const unsigned long long* keys, uint2* ranges, int tiles,
-                               cudaStream_t s);
 // radix_sort.cu
 // sorts the *v_dev (device u64, at most P) compacted (depth bits, slot) pairs of g.dkeys[0] / g.dvals[0]
 cudaError_t launch_depth_sort(GeomWs& g, int P, const unsigned long long* v_dev, cudaStream_t s);
-cudaError_t launch_tile_sort(BinWs& b, int64_t R, const SortPlan& plan, const float* depth, cudaStream_t s);
+cudaError_t launch_strip_sort(BinWs& b, int64_t n_cap, const unsigned long long* n_dev, const SortPlan& plan,
+                              cudaStream_t s);
 // stable sort of n (u32 key, u32 value) pairs, result in keys[0] / vals[0]; ws = sort_pairs_ws_words(n) u32 words
 size_t sort_pairs_ws_words(long long n);
 cudaError_t launch_sort_pairs(uint32_t* const keys[2], uint32_t* const vals[2], long long n, uint32_t* ws,
@@ -330,7 +352,7 @@ struct BlendArgs {
   const uint32_t* order;   // CTA i processes tile order[i] (heavy tiles first); NULL = identity
   uint32_t* tile_last;     // fwd: per-tile max of n_contrib (pre-zeroed)
   float* snap;             // fwd writes, bwd reads: per-pixel state at the list cuts (BinWs::snap)
-  const unsigned long long* keys64;  // bwd: sorted keys, tile id in the high word (finds the tile of a cut)
+  const uint32_t* seg_tile;  // bwd: tile whose list holds instance x * BLEND_SEG (finds the tile of a cut)
   int nseg;                // bwd: work items that start at a cut, (R - 1) / BLEND_SEG; they lead the grid
   unsigned long long* stats;  // instrumented pass (h3dgs_blend_stats): pair-category counters, else NULL
 };

@@ -2,11 +2,12 @@
 //
 // The reference sorts R (tile << 32 | depth) keys with cub::DeviceRadixSort::SortPairs
 // (HR/cuda_rasterizer/rasterizer_impl.cu:352-357): 45 key bits at 1920x1080, i.e. 6 (CUB, 8-bit digits)
-// sweeps over 12-byte pairs.  The same ordered list is produced here in two levels (see binning.cu):
+// sweeps over 12-byte pairs.  The same ordered list is produced here in levels (see binning.cu):
 //   1. the V visible slots are sorted by depth (32-bit keys, 4 sweeps over V 8-byte pairs, V << R);
-//   2. instances are emitted in that order and stably partitioned by tile id alone: ceil(tile bits / 8)
-//      sweeps (2 at 1080p) over R 6-byte pairs; the last sweep writes the 64-bit key next to the slot id.
-// Equal (tile, depth) keys keep slot order in both levels, exactly as the stable CUB sort leaves them.
+//   2. one record per (slot, tile row, 64-tile strip) is emitted in that order and stably partitioned by strip id:
+//      ceil(strip bits / 8) sweeps (1 at 1080p) over ~R / 3 6-byte pairs;
+//   3. the records of a strip are expanded into its tiles' lists by bit-matrix transposes (binning.cu).
+// Equal keys keep their order in every level, exactly as the stable CUB sort leaves them.
 //
 // One kernel per digit: a CTA ranks a 6144-element tile in shared memory, resolves its global offsets with a
 // decoupled look-back over the preceding tiles' per-digit counts and scatters; every element is read and
@@ -25,8 +26,10 @@ constexpr uint32_t ST_VAL = (1u << 30) - 1;
 
 // per-pass digit histograms of n keys: hist[p][d]
 template <typename K>
-__global__ void __launch_bounds__(512) digit_hist_kernel(const K* __restrict__ keys, long long n, int passes,
+__global__ void __launch_bounds__(512) digit_hist_kernel(const K* __restrict__ keys, long long n_host,
+                                                         const unsigned long long* __restrict__ n_dev, int passes,
                                                          SortShifts sh, uint32_t* __restrict__ hist) {
+  const long long n = n_dev ? (long long)*n_dev : n_host;
   __shared__ uint32_t h[SORT_MAX_PASSES * RADIX];
   for (int i = threadIdx.x; i < passes * RADIX; i += blockDim.x) h[i] = 0;
   __syncthreads();
@@ -75,22 +78,20 @@ struct SweepSmem {
 };
 
 // OUT 0: write (key, value).  OUT 1: write value only (last depth pass: only the order is needed).
-// OUT 2: write value and the 64-bit key (key << 32 | depth bits of the slot) -- last tile pass.
 template <typename K, int OUT>
 __global__ void __launch_bounds__(SORT_THREADS, 3) onesweep_kernel(
     const K* __restrict__ kin, K* __restrict__ kout, const uint32_t* __restrict__ vin,
-    uint32_t* __restrict__ vout, unsigned long long* __restrict__ kout64,
-    const uint32_t* __restrict__ depth_bits, long long n_host, const unsigned long long* __restrict__ n_dev,
+    uint32_t* __restrict__ vout, long long n_host, const unsigned long long* __restrict__ n_dev,
     int shift, uint32_t mask, const uint32_t* __restrict__ digit_base, volatile uint32_t* status,
     uint32_t* counter) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   SweepSmem<K>& sm = *reinterpret_cast<SweepSmem<K>*>(smem_raw);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
-  // element count: known to the host (tile passes over the R instances: one CTA per tile) or left on the device by
-  // the visible scan (depth passes over the V visible slots: a persistent grid whose CTAs keep taking tiles from
-  // the dynamic counter until the V elements are covered -- tiles are handed out in order, every CTA is resident,
-  // so the look-back always waits on a tile that is being worked on)
+  // element count: known to the host (one CTA per tile) or left on the device by a scan (the V visible slots of the
+  // depth passes, the strip records of the strip passes: a persistent grid whose CTAs keep taking tiles from the
+  // dynamic counter until the elements are covered -- tiles are handed out in order, every CTA is resident, so
+  // the look-back always waits on a tile that is being worked on)
   const long long n = n_dev ? (long long)*n_dev : n_host;
   for (;;) {
   if (tid == 0) sm.tile = atomicAdd(counter, 1u);
@@ -205,7 +206,6 @@ __global__ void __launch_bounds__(SORT_THREADS, 3) onesweep_kernel(
     const uint32_t v = sm.vals[p];
     if (OUT == 0) kout[g] = k;
     vout[g] = v;
-    if (OUT == 2) kout64[g] = ((unsigned long long)k << 32) | (unsigned long long)__ldg(depth_bits + v);
   }
   if (n_dev == nullptr) return;
   __syncthreads();   // shared memory is reused by the next tile
@@ -213,8 +213,8 @@ __global__ void __launch_bounds__(SORT_THREADS, 3) onesweep_kernel(
 }
 
 template <typename K, int OUT>
-cudaError_t launch_pass(const K* kin, K* kout, const uint32_t* vin, uint32_t* vout, unsigned long long* kout64,
-                        const uint32_t* depth_bits, long long n, const unsigned long long* n_dev, int shift,
+cudaError_t launch_pass(const K* kin, K* kout, const uint32_t* vin, uint32_t* vout, long long n,
+                        const unsigned long long* n_dev, int shift,
                         uint32_t mask, const uint32_t* digit_base, uint32_t* status, uint32_t* counter,
                         cudaStream_t s) {
   auto k = onesweep_kernel<K, OUT>;
@@ -232,19 +232,19 @@ cudaError_t launch_pass(const K* kin, K* kout, const uint32_t* vin, uint32_t* vo
     if (tiles > (long long)sms * 3) tiles = (long long)sms * 3;
   }
   ProfScope ps(K_SORT_PASS, s);
-  k<<<(unsigned)tiles, SORT_THREADS, smem, s>>>(kin, kout, vin, vout, kout64, depth_bits, n, n_dev, shift, mask,
-                                                digit_base, status, counter);
+  k<<<(unsigned)tiles, SORT_THREADS, smem, s>>>(kin, kout, vin, vout, n, n_dev, shift, mask, digit_base, status,
+                                                counter);
   return cudaGetLastError();
 }
 
 template <typename K>
-cudaError_t launch_hist(const K* keys, long long n, int passes, const SortShifts& sh, uint32_t* hist,
-                        cudaStream_t s) {
+cudaError_t launch_hist(const K* keys, long long n, const unsigned long long* n_dev, int passes,
+                        const SortShifts& sh, uint32_t* hist, cudaStream_t s) {
   int blocks = (int)((n + 512 * 16 - 1) / (512 * 16));
   if (blocks > 148 * 4) blocks = 148 * 4;
   if (blocks < 1) blocks = 1;
   { ProfScope ps(K_SORT_HIST, s);
-    digit_hist_kernel<K><<<blocks, 512, 0, s>>>(keys, n, passes, sh, hist); }
+    digit_hist_kernel<K><<<blocks, 512, 0, s>>>(keys, n, n_dev, passes, sh, hist); }
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return e;
   { ProfScope ps(K_SORT_SCAN, s);
@@ -253,26 +253,22 @@ cudaError_t launch_hist(const K* keys, long long n, int passes, const SortShifts
 }
 
 template <typename K>
-cudaError_t tile_sort(BinWs& b, int64_t R, const SortPlan& plan, const uint32_t* depth_bits, cudaStream_t s) {
-  K* keys[2] = {reinterpret_cast<K*>(b.tkeys[0]), reinterpret_cast<K*>(b.tkeys[1])};
+cudaError_t strip_sort(BinWs& b, int64_t n_cap, const unsigned long long* n_dev, const SortPlan& plan,
+                       cudaStream_t s) {
+  K* keys[2] = {reinterpret_cast<K*>(b.skeys[0]), reinterpret_cast<K*>(b.skeys[1])};
   SortShifts sh;
   for (int p = 0; p < SORT_MAX_PASSES; ++p) {
-    sh.shift[p] = p < plan.tile_passes ? plan.tile_shift[p] : 0;
-    sh.mask[p] = p < plan.tile_passes ? ((1u << plan.tile_bits[p]) - 1u) : 0u;
+    sh.shift[p] = p < plan.passes ? plan.shift[p] : 0;
+    sh.mask[p] = p < plan.passes ? ((1u << plan.bits[p]) - 1u) : 0u;
   }
-  cudaError_t e = launch_hist<K>(keys[0], R, plan.tile_passes, sh, b.tile_hist, s);
+  cudaError_t e = launch_hist<K>(keys[0], n_cap, n_dev, plan.passes, sh, b.strip_hist, s);
   if (e != cudaSuccess) return e;
-  const size_t tiles = (size_t)((R + SORT_TILE - 1) / SORT_TILE);
-  for (int p = 0; p < plan.tile_passes; ++p) {
+  const size_t tiles = (size_t)((n_cap + SORT_TILE - 1) / SORT_TILE);
+  for (int p = 0; p < plan.passes; ++p) {
     const int src = p & 1, dst = src ^ 1;
-    uint32_t* status = b.tile_status + (size_t)p * tiles * RADIX;
-    if (p + 1 < plan.tile_passes)
-      e = launch_pass<K, 0>(keys[src], keys[dst], b.tvals[src], b.tvals[dst], nullptr, nullptr, R, nullptr,
-                            sh.shift[p], sh.mask[p], b.tile_hist + (size_t)p * RADIX, status, b.counters + p, s);
-    else
-      e = launch_pass<K, 2>(keys[src], keys[dst], b.tvals[src], b.tvals[dst], b.keys64, depth_bits, R, nullptr,
-                            sh.shift[p], sh.mask[p], b.tile_hist + (size_t)p * RADIX, status,
-                            b.counters + p, s);
+    e = launch_pass<K, 0>(keys[src], keys[dst], b.svals[src], b.svals[dst], n_cap, n_dev, sh.shift[p], sh.mask[p],
+                          b.strip_hist + (size_t)p * RADIX, b.strip_status + (size_t)p * tiles * RADIX,
+                          b.counters + p, s);
     if (e != cudaSuccess) return e;
   }
   return cudaSuccess;
@@ -293,10 +289,10 @@ cudaError_t launch_depth_sort(GeomWs& g, int P, const unsigned long long* v_dev,
     const int src = p & 1, dst = src ^ 1;
     uint32_t* status = g.depth_status + (size_t)p * g.sort_tiles * RADIX;
     if (p + 1 < SORT_DEPTH_PASSES)
-      e = launch_pass<uint32_t, 0>(g.dkeys[src], g.dkeys[dst], g.dvals[src], g.dvals[dst], nullptr, nullptr, P, v_dev,
+      e = launch_pass<uint32_t, 0>(g.dkeys[src], g.dkeys[dst], g.dvals[src], g.dvals[dst], P, v_dev,
                                    8 * p, 0xffu, g.depth_hist + (size_t)p * RADIX, status, g.dcounters + p, s);
     else
-      e = launch_pass<uint32_t, 1>(g.dkeys[src], g.dkeys[dst], g.dvals[src], g.dvals[dst], nullptr, nullptr, P, v_dev,
+      e = launch_pass<uint32_t, 1>(g.dkeys[src], g.dkeys[dst], g.dvals[src], g.dvals[dst], P, v_dev,
                                    8 * p, 0xffu, g.depth_hist + (size_t)p * RADIX, status, g.dcounters + p, s);
     if (e != cudaSuccess) return e;
   }
@@ -322,24 +318,24 @@ cudaError_t launch_sort_pairs(uint32_t* const keys[2], uint32_t* const vals[2], 
   if (e != cudaSuccess) return e;
   SortShifts sh;
   for (int p = 0; p < SORT_MAX_PASSES; ++p) { sh.shift[p] = 8 * p; sh.mask[p] = 0xffu; }
-  e = launch_hist<uint32_t>(keys[0], n, SORT_DEPTH_PASSES, sh, hist, s);
+  e = launch_hist<uint32_t>(keys[0], n, nullptr, SORT_DEPTH_PASSES, sh, hist, s);
   if (e != cudaSuccess) return e;
   for (int p = 0; p < SORT_DEPTH_PASSES; ++p) {
     const int src = p & 1, dst = src ^ 1;
-    e = launch_pass<uint32_t, 0>(keys[src], keys[dst], vals[src], vals[dst], nullptr, nullptr, n, nullptr, 8 * p, 0xffu,
+    e = launch_pass<uint32_t, 0>(keys[src], keys[dst], vals[src], vals[dst], n, nullptr, 8 * p, 0xffu,
                                  hist + (size_t)p * RADIX, status + (size_t)p * tiles * RADIX, counters + p, s);
     if (e != cudaSuccess) return e;
   }
   return cudaSuccess;
 }
 
-// Stable partition of the R emitted (tile id, slot) pairs by tile id; writes point_list (b.tvals[b.sorted])
-// and point_list_keys (b.keys64).
-cudaError_t launch_tile_sort(BinWs& b, int64_t R, const SortPlan& plan, const float* depth, cudaStream_t s) {
-  if (R <= 0) return cudaSuccess;
-  const uint32_t* dbits = reinterpret_cast<const uint32_t*>(depth);
-  if (plan.tile_key_bytes == 2) return tile_sort<uint16_t>(b, R, plan, dbits, s);
-  return tile_sort<uint32_t>(b, R, plan, dbits, s);
+// Stable partition of the emitted (strip id, slot) records by strip id; *n_dev of them (at most n_cap), sorted
+// records in b.skeys[b.sorted] / b.svals[b.sorted].
+cudaError_t launch_strip_sort(BinWs& b, int64_t n_cap, const unsigned long long* n_dev, const SortPlan& plan,
+                              cudaStream_t s) {
+  if (n_cap <= 0) return cudaSuccess;
+  if (plan.key_bytes == 2) return strip_sort<uint16_t>(b, n_cap, n_dev, plan, s);
+  return strip_sort<uint32_t>(b, n_cap, n_dev, plan, s);
 }
 
 }  // namespace h3dgs

@@ -20,6 +20,8 @@ __device__ __forceinline__ void mark_chunks(uint32_t* __restrict__ chunk_first, 
 
 // MODE 0: scan in[i].   MODE 1: scan (in[i] != 0) -- the rank of every visible slot -- and also add up in[i]
 // itself into counters[4..5] (the instance total).   MODE 2: scan in[idx[i]] (tile counts in depth order).
+// MODE 3: `in` holds the slots' tile rectangles (ushort4); scan the number of strip records of slot idx[i]: one per
+// tile row and STRIP_TILES-wide strip its rectangle reaches into (binning.cu).
 template <int MODE>
 __global__ void __launch_bounds__(SCAN_THREADS) scan_lookback_kernel(
     const uint32_t* __restrict__ in, const uint32_t* __restrict__ idx, uint32_t* __restrict__ out, int n_host,
@@ -39,7 +41,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_lookback_kernel(
   const size_t base = (size_t)tile * SCAN_TILE + (size_t)threadIdx.x * SCAN_ITEMS;
 
   uint32_t v[SCAN_ITEMS];
-  const uint32_t* __restrict__ src = (MODE == 2) ? idx : in;
+  const uint32_t* __restrict__ src = (MODE >= 2) ? idx : in;
   if (base + SCAN_ITEMS <= (size_t)n) {
     const uint4* p = reinterpret_cast<const uint4*>(src + base);
 #pragma unroll
@@ -54,6 +56,19 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_lookback_kernel(
   if (MODE == 2) {
 #pragma unroll
     for (int i = 0; i < SCAN_ITEMS; ++i) v[i] = (base + i < (size_t)n) ? __ldg(in + v[i]) : 0u;
+  }
+  if (MODE == 3) {
+    const uint2* __restrict__ rects = reinterpret_cast<const uint2*>(in);
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; ++i) {
+      uint32_t c = 0;
+      if (base + i < (size_t)n) {
+        const uint2 r = __ldg(rects + v[i]);   // (x0 | y0 << 16, x1 | y1 << 16), x1 > x0 and y1 > y0 for visible slots
+        const uint32_t x0 = r.x & 0xffffu, y0 = r.x >> 16, x1 = r.y & 0xffffu, y1 = r.y >> 16;
+        c = (y1 - y0) * (((x1 - 1u) / STRIP_TILES) - (x0 / STRIP_TILES) + 1u);
+      }
+      v[i] = c;
+    }
   }
   if (MODE == 1) {
     unsigned long long raw = 0;
@@ -122,7 +137,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_lookback_kernel(
 #pragma unroll
     for (int i = 0; i < SCAN_ITEMS / 4; ++i) {
       uint4 x;
-      if (MODE == 2) {
+      if (MODE >= 2) {
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
           mark_chunks(chunk_first, run, run + v[4 * i + k], (uint32_t)(base + 4 * i + k));
@@ -140,7 +155,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_lookback_kernel(
   } else {
 #pragma unroll
     for (int i = 0; i < SCAN_ITEMS; ++i) {
-      if (MODE == 2 && base + i < (size_t)n) mark_chunks(chunk_first, run, run + v[i], (uint32_t)(base + i));
+      if (MODE >= 2 && base + i < (size_t)n) mark_chunks(chunk_first, run, run + v[i], (uint32_t)(base + i));
       run += v[i];
       if (base + i < (size_t)n) out[base + i] = (uint32_t)run;
     }
@@ -176,10 +191,16 @@ cudaError_t launch_scan_visible(const uint32_t* tiles_touched, uint32_t* rank, i
                                 unsigned long long* status, uint32_t* counters, cudaStream_t s) {
   return launch_scan<1>(tiles_touched, nullptr, rank, n, nullptr, nullptr, status, counters, s);
 }
-cudaError_t launch_scan_gather(const uint32_t* tiles_touched, const uint32_t* order, uint32_t* out, int n_cap,
+cudaError_t launch_scan_strips(const ushort4* tile_rect, const uint32_t* order, uint32_t* out, int n_cap,
                                const unsigned long long* n_dev, uint32_t* chunk_first, unsigned long long* status,
                                uint32_t* counters, cudaStream_t s) {
-  return launch_scan<2>(tiles_touched, order, out, n_cap, n_dev, chunk_first, status, counters, s);
+  return launch_scan<3>(reinterpret_cast<const uint32_t*>(tile_rect), order, out, n_cap, n_dev, chunk_first, status,
+                        counters, s);
+}
+cudaError_t launch_scan_counts(const uint32_t* in, uint32_t* out, long long n_cap, const unsigned long long* n_dev,
+                               unsigned long long* status, uint32_t* counters, cudaStream_t s) {
+  if (n_cap > 0x7fffffffll) return cudaErrorInvalidValue;
+  return launch_scan<0>(in, nullptr, out, (int)n_cap, n_dev, nullptr, status, counters, s);
 }
 
 }  // namespace h3dgs

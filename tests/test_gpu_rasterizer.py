@@ -179,7 +179,9 @@ def test_backward_work_item_boundaries(n):
     rot = torch.zeros(n, 4)
     rot[:, 0] = 1.0
     sc = {"means3D": pos.float().to(DEV).contiguous(),
-          "scales": (0.05 * z)[:, None].repeat(1, 3).float().to(DEV).contiguous(),       # ~1.6 px on screen
+          # ~1.6 px on screen; mildly anisotropic: with equal scales the rotation gradient is analytically zero and
+          # both arms return rounding noise for it (relative error of order 1 between two runs of the reference)
+          "scales": ((0.05 * z)[:, None] * torch.tensor([1.0, 0.85, 1.15])).float().to(DEV).contiguous(),
           "rotations": rot.to(DEV), "opacities": torch.full((n, 1), 0.0062, device=DEV),
           "shs": (torch.randn(n, 16, 3, generator=g) * 0.2).to(DEV).contiguous()}
     bg = torch.tensor([0.3, 0.1, 0.2], device=DEV)

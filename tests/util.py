@@ -57,6 +57,13 @@ def assert_grad_close(ours, ref, ref_again, name, more_refs=(), strict=None, our
     diff = (ours - mean).abs()
     err = float(diff.max()) / den
     branch = "strict 1e-4" if strict else ("1e-4" if bound == REL_TOL else "6 x spread")
+    if not strict and noise > 0.05 and err > bound:
+        # The reference's own runs disagree by more than 5 % of the tensor's largest entry: the tensor is the rounding
+        # residue of cancelling terms (e.g. the rotation gradient of isotropic Gaussians, analytically zero) and a
+        # handful of runs estimates its spread within a factor of 10 (0.29 .. 2.2 between sessions on one input).
+        # What can be checked is that ours is residue of the same size.
+        if err <= 20.0 * noise:
+            bound, branch = 20.0 * noise, "no signal (20 x spread)"
     if not strict and err > bound:
         # The spread of a handful of runs is itself a noisy estimate (3-run estimates of one tensor ranged from 6e-5 to
         # 8e-4 between sessions).  Before failing, look at WHERE the error sits: an implementation error shows in the
