@@ -174,6 +174,9 @@ __global__ void __launch_bounds__(256) expand_kernel(const uint32_t* __restrict_
                                                      int strips_per_row, uint32_t* __restrict__ counts,
                                                      const uint32_t* __restrict__ offs, uint32_t* __restrict__ point_list) {
   __shared__ uint32_t s_slot[8][32];
+  // WRITE: the four slots of a 16-byte aligned group of a tile's list are collected here and stored at once (every
+  // lane appends to its own tile's list: scalar stores were one 4-byte L2 write per instance)
+  __shared__ __align__(16) uint32_t s_quad[WRITE ? 8 : 1][WRITE ? STRIP_TILES : 1][4];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const uint32_t chunk = blockIdx.x * 8u + (uint32_t)warp;
   if (chunk >= counters[6]) return;
@@ -186,9 +189,14 @@ __global__ void __launch_bounds__(256) expand_kernel(const uint32_t* __restrict_
   const size_t e0 = (size_t)STRIP_TILES * cbase[s] + (size_t)lane * n + k;
   const size_t e1 = e0 + (size_t)32 * n;
   uint32_t pos0 = 0, pos1 = 0;
+  // positions [lo, hi) of a list are written as whole aligned groups of four, the rest one by one
+  uint32_t lo0 = 0, hi0 = 0, lo1 = 0, hi1 = 0;
   if (WRITE) {
-    pos0 = offs[e0] - counts[e0];
-    pos1 = offs[e1] - counts[e1];
+    const uint32_t end0 = offs[e0], end1 = offs[e1];
+    pos0 = end0 - counts[e0];
+    pos1 = end1 - counts[e1];
+    lo0 = (pos0 + 3u) & ~3u; hi0 = end0 & ~3u;
+    lo1 = (pos1 + 3u) & ~3u; hi1 = end1 & ~3u;
   }
   // software pipeline: the records of the next group are in flight while this one is expanded
   uint32_t slot_n = 0;
@@ -229,13 +237,29 @@ __global__ void __launch_bounds__(256) expand_kernel(const uint32_t* __restrict_
       while (bts) {
         const int e = __ffs(bts) - 1;
         bts &= bts - 1;
-        point_list[pos0++] = s_slot[warp][e];
+        const uint32_t v = s_slot[warp][e];
+        if (pos0 < lo0 || pos0 >= hi0) {
+          point_list[pos0] = v;
+        } else {
+          s_quad[warp][lane][pos0 & 3u] = v;
+          if ((pos0 & 3u) == 3u)
+            *reinterpret_cast<uint4*>(point_list + (pos0 - 3u)) = *reinterpret_cast<const uint4*>(s_quad[warp][lane]);
+        }
+        ++pos0;
       }
       bts = c1;
       while (bts) {
         const int e = __ffs(bts) - 1;
         bts &= bts - 1;
-        point_list[pos1++] = s_slot[warp][e];
+        const uint32_t v = s_slot[warp][e];
+        if (pos1 < lo1 || pos1 >= hi1) {
+          point_list[pos1] = v;
+        } else {
+          s_quad[warp][lane + 32][pos1 & 3u] = v;
+          if ((pos1 & 3u) == 3u)
+            *reinterpret_cast<uint4*>(point_list + (pos1 - 3u)) = *reinterpret_cast<const uint4*>(s_quad[warp][lane + 32]);
+        }
+        ++pos1;
       }
     }
   }
