@@ -274,6 +274,21 @@ H3DGS_API int h3dgs_expand_to_size(int32_t num_nodes, float target_size, const i
                          void* workspace, size_t workspace_bytes,
                          int32_t* count_host, h3dgs_stream_t stream);
 
+/* h3dgs_expand_to_size without a workspace argument and without any allocation.  NO COUNTERPART IN THE REFERENCE:
+ * added for callers that cannot call cudaMalloc (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid it).  The scratch (two u32 per node + scan look-back words,
+ * 8.0 MiB) is a file-scope static __device__ array in the library, resident on every GPU that loads it until exit;
+ * the call rejects num_nodes > H3DGS_STATIC_CUT_MAX_NODES with H3DGS_ENOSPACE.  All calls share that array: calls
+ * that overlap on the GPU (two streams, two host threads) race on it -- serialise them.  Same outputs as
+ * h3dgs_expand_to_size, same synchronisation of `stream` before *count_host is written. */
+#define H3DGS_STATIC_CUT_MAX_NODES (1 << 20)
+H3DGS_API int32_t h3dgs_expand_to_size_static_max_nodes(void);
+H3DGS_API int h3dgs_expand_to_size_static(int32_t num_nodes, float target_size, const int32_t* nodes,
+                         const float* boxes, const float* viewpoint_dev,
+                         int32_t* render_indices, int32_t* parent_indices,
+                         int32_t* nodes_for_render_indices,
+                         int32_t* count_host, h3dgs_stream_t stream);
+
 /* Viewpoint by value (the reference reads it on the host, torch_interface.cpp:116-117). */
 H3DGS_API int h3dgs_interpolation_weights(int32_t num_entries, const int32_t* node_indices, float target_size,
                                 const int32_t* nodes, const float* boxes,

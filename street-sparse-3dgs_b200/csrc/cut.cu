@@ -352,3 +352,73 @@ int h3dgs_cut_step(int32_t num_cut_nodes, const int32_t* node_indices, int32_t* 
 }
 
 }  // extern "C"
+
+// ---- expand_to_size without a caller-side workspace (h3dgs_expand_to_size_static) ----
+// For callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc): the
+// scratch of the cut (per-node counts, their scan, the scan's look-back words) lives in this file-scope device
+// array, which every GPU that loads the library holds until exit.  All calls share it and it keeps the previous
+// call's contents: the counts and offsets are fully rewritten for nodes 0..N-1 by every call and the look-back
+// words and counters are cleared on the stream before the scan (scan.cu launch_scan), so nothing stale is read --
+// but two calls that overlap on the GPU (different streams, different host threads) race on it.
+constexpr size_t STATIC_CUT_BYTES =
+    2 * sizeof(uint32_t) * (size_t)H3DGS_STATIC_CUT_MAX_NODES                                      // counts, offsets
+    + sizeof(unsigned long long) * ((size_t)H3DGS_STATIC_CUT_MAX_NODES / h3dgs::SCAN_TILE + 2)     // look-back words
+    + 8 * sizeof(uint32_t) + 5 * 256;                                                              // counters, carve slack
+static __device__ __align__(256) unsigned char g_static_cut_scratch[STATIC_CUT_BYTES];   // 8.0 MiB per GPU
+
+namespace h3dgs {
+namespace {
+
+// In host code `g_static_cut_scratch` is only a handle; its device address is asked for once per device, with that
+// device current.
+constexpr int STATIC_MAX_DEVICES = 64;
+void* g_static_cut_ptr[STATIC_MAX_DEVICES] = {nullptr};
+
+int static_cut_scratch(void** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return cuda_fail(e, "h3dgs_expand_to_size_static: cudaGetDevice");
+  if (dev < 0 || dev >= STATIC_MAX_DEVICES) return fail(H3DGS_EINVAL, "h3dgs_expand_to_size_static: device ordinal above 63");
+  void* p = __atomic_load_n(&g_static_cut_ptr[dev], __ATOMIC_ACQUIRE);
+  if (p == nullptr) {
+    e = cudaGetSymbolAddress(&p, g_static_cut_scratch);
+    if (e != cudaSuccess) return cuda_fail(e, "h3dgs_expand_to_size_static: cudaGetSymbolAddress");
+    if (p == nullptr || (reinterpret_cast<size_t>(p) & 255))
+      return fail(H3DGS_EINVAL, "h3dgs_expand_to_size_static: scratch address is null or misaligned");
+    __atomic_store_n(&g_static_cut_ptr[dev], p, __ATOMIC_RELEASE);   // every thread would store the same address
+  }
+  *out = p;
+  return 0;
+}
+
+}  // namespace
+}  // namespace h3dgs
+
+extern "C" {
+
+int32_t h3dgs_expand_to_size_static_max_nodes(void) { return H3DGS_STATIC_CUT_MAX_NODES; }
+
+int h3dgs_expand_to_size_static(int32_t N, float target_size, const int32_t* nodes, const float* boxes,
+                                const float* viewpoint_dev, int32_t* render_indices, int32_t* parent_indices,
+                                int32_t* nodes_for_render_indices, int32_t* count_host, h3dgs_stream_t stream) {
+  using namespace h3dgs;
+  if (N < 0) return fail(H3DGS_EINVAL, "negative node count");
+  if (!count_host) return fail(H3DGS_EINVAL, "count_host is required");
+  *count_host = 0;
+  if (N == 0) return 0;
+  if (N > H3DGS_STATIC_CUT_MAX_NODES)
+    return fail(H3DGS_ENOSPACE, "h3dgs_expand_to_size_static: more than H3DGS_STATIC_CUT_MAX_NODES (1048576) nodes; "
+                                "use h3dgs_expand_to_size with a caller-side workspace");
+  if (!nodes || !boxes || !viewpoint_dev || !render_indices)
+    return fail(H3DGS_EINVAL, "nodes, boxes, viewpoint and render_indices are required");
+  if (reinterpret_cast<size_t>(boxes) & 15) return fail(H3DGS_EINVAL, "boxes must be 16-byte aligned");
+  if (expand_ws_bytes(N) > STATIC_CUT_BYTES) return fail(H3DGS_ENOSPACE, "h3dgs_expand_to_size_static: scratch layout exceeds the array");
+  void* scratch = nullptr;
+  int rc = static_cut_scratch(&scratch);
+  if (rc) return rc;
+  cudaError_t e = run_expand_to_size(N, target_size, nodes, boxes, viewpoint_dev, render_indices, parent_indices,
+                                     nodes_for_render_indices, scratch, count_host, reinterpret_cast<cudaStream_t>(stream));
+  return e == cudaSuccess ? 0 : cuda_fail(e, "h3dgs_expand_to_size_static");
+}
+
+}  // extern "C"

@@ -103,6 +103,9 @@ SIGNATURES = {
     "h3dgs_expand_workspace_bytes": (c_size_t, [c_int32]),
     "h3dgs_expand_to_size": (c_int, [c_int32, c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                       c_void_p, c_void_p, c_size_t, POINTER(c_int32), c_void_p]),
+    "h3dgs_expand_to_size_static_max_nodes": (c_int32, []),
+    "h3dgs_expand_to_size_static": (c_int, [c_int32, c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                             c_void_p, POINTER(c_int32), c_void_p]),
     "h3dgs_interpolation_weights": (c_int, [c_int32, c_void_p, c_float, c_void_p, c_void_p, c_float,
                                              c_float, c_float, c_void_p, c_void_p, c_void_p]),
     "h3dgs_cut_step_workspace_bytes": (c_size_t, [c_int32]),
