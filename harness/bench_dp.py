@@ -64,12 +64,15 @@ def run(args, dev, rank, world, attrs, timed, dcol, ddep):
     costs, gated = [], []
     for k in range(n_cams):
         render(k)
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        sg = render(k)
-        e1.record()
-        torch.cuda.synchronize()
-        costs.append(e0.elapsed_time(e1))
+        best = float("inf")
+        for _ in range(2):   # the smaller of two: the first timed render of a process still grows the allocator's pools
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            sg = render(k)
+            e1.record()
+            torch.cuda.synchronize()
+            best = min(best, e0.elapsed_time(e1))
+        costs.append(best)
         U = int(sg.count)
         gated.append(int((sg.grads["opacity"][:U] != 0).sum()))
     t = torch.tensor(costs + [float(max(gated))], device=dev, dtype=torch.float64)
