@@ -535,7 +535,9 @@ H3DGS_API int h3dgs_blend_stats(void* counters);
  * per second (G/s) by the FFMA kernel.  scratch: device pointer to at least one float. */
 H3DGS_API int h3dgs_measure_peaks(double* out4, void* scratch, int32_t reps, h3dgs_stream_t stream);
 /* Diagnostics switch: key 1 = backward blend variant (1 = one pixel per lane, 2 = two pixels per lane, the default;
- * env H3DGS_BWD); returns the previous value, -1 for an unknown key. */
+ * env H3DGS_BWD); key 2 = strip-key layout of the binning sort for tests (bit 0: u32 keys, bit 1: two sort passes --
+ * what an image with more than 65 536 strips would use; buffers sized under one setting must not be used under
+ * another); returns the previous value, -1 for an unknown key. */
 H3DGS_API int h3dgs_debug_set(int key, int value);
 H3DGS_API int64_t h3dgs_launch_count(void);          /* kernels launched by this library so far (process-wide) */
 H3DGS_API int h3dgs_profile_enable(int enable);      /* returns the previous setting */

@@ -139,6 +139,9 @@ bool overlap_zero() {
   return v == 1;
 }
 
+int g_strip_key_debug = 0;
+int strip_key_debug_mode() { return g_strip_key_debug; }
+
 size_t expand_ws_bytes(int N);
 cudaError_t run_expand_to_size(int N, float target_size, const int* nodes, const float* boxes,
                                const float* viewpoint, int* render_indices, int* parent_indices,
@@ -724,6 +727,11 @@ int h3dgs_measure_peaks(double* out4, void* scratch, int32_t reps, h3dgs_stream_
 
 int h3dgs_debug_set(int key, int value) {
   if (key == 1) return h3dgs::set_bwd_variant(value);
+  if (key == 2) {
+    const int prev = h3dgs::g_strip_key_debug;
+    h3dgs::g_strip_key_debug = value & 3;
+    return prev;
+  }
   return -1;
 }
 int64_t h3dgs_launch_count(void) { return g_prof.launches_total; }

@@ -165,6 +165,10 @@ struct SortPlan {
   int key_bytes;                   // 2 (strip ids fit 16 bits) or 4
 };
 
+// diagnostics (h3dgs_debug_set key 2, api.cu): bit 0 = u32 strip keys even when 16 bits would do, bit 1 = at least
+// 16 key bits, i.e. two strip passes -- the paths an image below 65 536 strips never takes
+int strip_key_debug_mode();
+
 inline SortPlan make_sort_plan(int W, int H) {
   const int grid_x = (W + TILE_X - 1) / TILE_X, grid_y = (H + TILE_Y - 1) / TILE_Y;
   SortPlan pl;
@@ -172,6 +176,8 @@ inline SortPlan make_sort_plan(int W, int H) {
   pl.strips = pl.strips_per_row * grid_y;
   int total = 1;
   while (total < 32 && (1ll << total) < (long long)pl.strips) ++total;
+  const int dbg = strip_key_debug_mode();
+  if ((dbg & 2) && total < 16) total = 16;
   pl.passes = (total + SORT_RADIX_BITS - 1) / SORT_RADIX_BITS;
   const int base = total / pl.passes, extra = total % pl.passes;
   int sft = 0;
@@ -180,7 +186,7 @@ inline SortPlan make_sort_plan(int W, int H) {
     pl.shift[i] = sft;
     sft += pl.bits[i];
   }
-  pl.key_bytes = total <= 16 ? 2 : 4;
+  pl.key_bytes = (total <= 16 && !(dbg & 1)) ? 2 : 4;
   return pl;
 }
 

@@ -361,10 +361,10 @@ def test_long_thin_splats_bit_exact():
     assert R > 0
 
 
-def test_more_than_65535_tiles_uses_32_bit_tile_keys():
-    """4112 x 4096 pixels = 257 x 256 = 65 792 tiles: tile ids no longer fit 16 bits, the instance sort switches to
-    u32 tile keys and three tile passes (csrc/common.cuh make_sort_plan).  Keys, list, ranges and image against
-    the reference build, bit for bit."""
+def test_more_than_65535_tiles():
+    """4112 x 4096 pixels = 257 x 256 = 65 792 tiles: tile ids no longer fit 16 bits (the reference's key takes 17
+    tile bits; here 5 strips per tile row, 1280 strips, two sort passes).  Keys, list, ranges and image against the
+    reference build, bit for bit."""
     util.need_ref()
     import diff_gaussian_rasterization as dgr
     n, w, h = 40000, 4112, 4096
@@ -377,3 +377,35 @@ def test_more_than_65535_tiles_uses_32_bit_tile_keys():
     _, _, _, geom, binning, img, _ = dgr._C.rasterize_gaussians(*args)
     dv = dgr._C.debug_view(n, w, h, R, geom, binning, img)
     assert int((dv["point_list_keys"] >> 32).max()) > 65535, "no instance landed in a tile above 65535"
+
+
+@pytest.mark.parametrize("mode", [1, 2, 3])
+def test_wide_strip_keys_and_two_sort_passes(mode):
+    """The binning sort keys one record per (slot, tile row, 64-tile strip) by strip id: u16 keys and one 8-bit pass
+    up to 256 strips.  u32 keys (more than 65 536 strips) and a second pass only appear for images no test can
+    afford; h3dgs_debug_set(2, mode) forces them (bit 0: u32 keys, bit 1: two passes).  Instance list, ranges, keys
+    and image must not change by a bit."""
+    import diff_gaussian_rasterization as dgr
+    import h3dgs_native as nat
+    n, w, h = 30000, 1280, 720
+    sc, cam, _, _ = util.make_scene(n, w, h, seed=12, dev=DEV)
+    bg = torch.tensor([0.05, 0.1, 0.2], device=DEV)
+    rs = _settings(cam, bg)
+    args = util.forward_args(rs, sc)
+
+    def run():
+        R, color, radii, geom, binning, img, invd = dgr._C.rasterize_gaussians(*args)
+        dv = dgr._C.debug_view(n, w, h, R, geom, binning, img)
+        torch.cuda.synchronize()
+        return R, color.clone(), {k: dv[k].clone() for k in ("point_list", "point_list_keys", "ranges", "n_contrib")}
+
+    R0, c0, d0 = run()
+    assert R0 > 0
+    prev = nat.lib().h3dgs_debug_set(2, mode)
+    try:
+        R1, c1, d1 = run()
+    finally:
+        nat.lib().h3dgs_debug_set(2, prev)
+    assert R1 == R0 and torch.equal(bits(c0), bits(c1))
+    for k in d0:
+        assert torch.equal(d0[k], d1[k]), k
