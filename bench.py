@@ -409,7 +409,16 @@ def main():
         if args.impl == "ours":
             import diff_gaussian_rasterization as dgr
 
+        host_prof = {} if os.environ.get("H3DGS_HOST_PROFILE") else None
+        import time as _time
+
+        def _mark(name, t0):
+            if host_prof is not None:
+                host_prof[name] = host_prof.get(name, 0.0) + (_time.perf_counter() - t0)
+            return _time.perf_counter()
+
         def e2e_step(i):
+            t0 = _time.perf_counter()
             step_i = i
             k = cam_index(i)
             c0 = cams[k]
@@ -427,6 +436,7 @@ def main():
                 cam_dev.copy_(cam_host[i % len(cams)], non_blocking=True)
                 c, this_cut = cam_view(k, cam_dev), cut
                 cut.compute(gh, hm, c, limit, campos_host=cam_host[i % len(cams)][32:35])
+            t0 = _mark("prefetch+cut_get", t0)
             for p in hm.parameters():
                 p.grad = None
             sg = dgr.SparseGradients() if mode["sparse"] else None
@@ -434,18 +444,24 @@ def main():
                 out = render_post(c, hm, bg, this_cut, do_depth=False, sparse_grads=sg)
             else:
                 out = render_post(c, hm, bg, this_cut, do_depth=False)
+            t0 = _mark("render_post", t0)
             loss = loss_fn(out["render"], pf.get(n)["gt"])
+            t0 = _mark("loss", t0)
             loss.backward()
+            t0 = _mark("backward", t0)
             pf.done(n)
             if cut_ahead:
                 ca.done(step_i)
                 launch_cut(step_i + 1)
+            t0 = _mark("cut_launch", t0)
             if sg is not None:
                 opt.step_sparse(sg)
+                t0 = _mark("adam", t0)
                 # device -> host read of this step's loss: asynchronous copy into pinned memory, picked up one step
                 # later (the last one after the timed region's final synchronize)
                 readback.push(loss)
                 losses.extend(readback.pop_ready(keep_newest=1))
+                _mark("readback", t0)
                 return
             relevant = (hm._opacity.grad.flatten() != 0).nonzero().flatten().long()
             opt.step(relevant)
@@ -463,7 +479,13 @@ def main():
             for p in hm.parameters():
                 p.grad = None
             torch.cuda.empty_cache()
+        if host_prof is not None:
+            host_prof.clear()
         ms_e2e, clocks_e2e = timed(e2e_step, args.steps, max(args.warmup, 3))
+        if host_prof is not None:
+            calls = args.steps + max(args.warmup, 3)
+            print("host ms per e2e step: " + ", ".join(f"{k} {1000.0 * v / calls:.3f}" for k, v in host_prof.items()),
+                  file=sys.stderr)
         e2e_value = world * 1000.0 / (ms_e2e / args.steps)
         e2e = {"value": e2e_value, "unit": "renders/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
                "ms_per_step": ms_e2e / args.steps, "clocks": clocks_e2e,
