@@ -79,3 +79,67 @@ def test_extension_reports_errors_like_the_ctypes_binding(monkeypatch):
         dgr._C.rasterize_gaussians(*args(z.double()))
     out = dgr._C.rasterize_gaussians(*args(z))
     assert len(out) == 7 and out[1].shape == (3, 64, 64)
+
+
+class _GuardedTorch:
+    """Stands in for the `torch` module inside diff_gaussian_rasterization._C: every 1-D uint8 CUDA buffer (the
+    opaque geometry / binning / image / backward workspaces, sized by the library's own *_bytes queries) is carved
+    out of a larger allocation with 4 KiB of 0xA5 in front and behind."""
+    GUARD = 4096
+
+    def __init__(self):
+        self.blocks = []
+
+    def __getattr__(self, name):
+        return getattr(torch, name)
+
+    def empty(self, *args, **kw):
+        shape = args[0] if args else kw.get("size")
+        if kw.get("dtype") is torch.uint8 and isinstance(shape, tuple) and len(shape) == 1 and \
+                torch.device(kw.get("device", "cpu")).type == "cuda" and len(args) <= 1:
+            n = int(shape[0])
+            pad = (-n) % 256
+            whole = torch.full((n + pad + 2 * self.GUARD,), 0xA5, dtype=torch.uint8, device=kw["device"])
+            self.blocks.append((whole, n))
+            return whole[self.GUARD:self.GUARD + n]
+        return torch.empty(*args, **kw)
+
+    def check(self):
+        assert self.blocks, "no workspace went through the guarded allocator"
+        for whole, n in self.blocks:
+            G = self.GUARD
+            assert bool((whole[:G] == 0xA5).all()), f"a kernel wrote in front of a {n}-byte workspace"
+            assert bool((whole[G + n:] == 0xA5).all()), f"a kernel wrote behind a {n}-byte workspace"
+
+
+@pytest.mark.parametrize("w,h,levels,target", [(800, 600, 15, 12000), (1920, 1080, 17, 60000), (1040, 72, 14, 6000)])
+def test_kernels_stay_inside_their_workspaces(monkeypatch, w, h, levels, target):
+    """compute-sanitizer is not available on the GPU pool: the library's workspace carving (common.cuh GeomWs /
+    BinWs / ImageWs / BwdWs, sized by counts that partly live on the device: strip records, expansion chunks) is
+    checked with guard bands instead.  ctypes host path, forward + backward of a cut with parents, at three image
+    shapes (1920 wide: two 64-tile strips per tile row, the second partly filled; 1040 x 72: 65 tile columns, a
+    one-tile second strip)."""
+    import diff_gaussian_rasterization as dgr
+    import gaussian_hierarchy
+    from gaussian_renderer import render_post
+    monkeypatch.setattr(dgr._C, "HOST", "ctypes")
+    guarded = _GuardedTorch()
+    monkeypatch.setattr(dgr._C, "torch", guarded)
+    sky = 300
+    attrs = workload.build_scene(levels, sky, 5, DEV)
+    cam = scenes.street_camera(w, h, seed=2, device=DEV, yaw_deg=3.0, x=-8.0)
+    bg = torch.tensor([0.1, 0.0, 0.2], device=DEV)
+    n = attrs["means3D"].size(0)
+    model = workload.HierModel(attrs, sky)
+    limit = workload.find_limit(gaussian_hierarchy._C, model, cam, target, DEV)
+    cut = workload.Cut(n, DEV)
+    cut.compute(gaussian_hierarchy._C, model, cam, limit)
+    K = cut.count
+    out = render_post(cam, model, scenes.Pipe, bg, render_indices=cut.render_indices[:K],
+                      parent_indices=cut.parent_indices[:K], interpolation_weights=cut.interpolation_weights,
+                      num_node_kids=cut.num_siblings, do_depth=True)
+    (out["render"].sum() + out["depth"].sum()).backward()
+    torch.cuda.synchronize()
+    assert int(out["radii"].numel()) > 0
+    guarded.check()
+    assert len(guarded.blocks) >= 3, [b[1] for b in guarded.blocks]
