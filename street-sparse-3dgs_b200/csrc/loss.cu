@@ -46,19 +46,31 @@ __device__ __forceinline__ float warp_sum(float v) {
   return v;
 }
 
+// Tiling of the two SSIM kernels: a CTA of 256 threads produces a 32 x 32 output tile from a 42 x 42 input patch
+// (1.72 loads per pixel; 16 x 16 tiles needed 2.64).  Horizontal pass: a thread makes FOUR neighbouring outputs of a
+// row from 14 inputs held in registers (7 shared-memory loads per output and quantity pair instead of 22; the
+// squares and the product of an input are formed once, not once per tap).  Vertical pass: a thread makes four
+// outputs of a column from 14 rows.  Every output is still the sum over k = 0..10 of w[k] * value[k], accumulated
+// in that order with one FMA per tap: bit-identical to the one-output-per-thread form.
+constexpr int ST = 32;             // tile edge
+constexpr int SW = ST + 2 * LH;    // 42
+constexpr int SP = SW + 1;         // row pitch of the input patch in shared memory (odd: conflict-free for both passes)
+constexpr int SR = 4;              // outputs per thread and pass
+constexpr int S_THREADS = 256;
+
 template <bool GRAD>
-__global__ void __launch_bounds__(LT * LT) ssim_fwd_kernel(const LossArgs a) {
-  __shared__ float s1[LW][LW + 1], s2[LW][LW + 1];
-  __shared__ float hz[5][LW][LT];
-  __shared__ float red[2][LT * LT / 32];
-  const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * LT + tx;
-  const int x0 = blockIdx.x * LT, y0 = blockIdx.y * LT, ch = blockIdx.z;
+__global__ void __launch_bounds__(S_THREADS) ssim_fwd_kernel(const LossArgs a) {
+  __shared__ float s1[SW][SP], s2[SW][SP];
+  __shared__ float hz[5][SW][ST + 1];   // +1: the four rows a warp writes in the horizontal pass fall into different banks
+  __shared__ float red[2][S_THREADS / 32];
+  const int tid = threadIdx.x;
+  const int x0 = blockIdx.x * ST, y0 = blockIdx.y * ST, ch = blockIdx.z;
   const size_t plane = (size_t)a.H * a.W;
   const float* __restrict__ p1 = a.img1 + ch * plane;
   const float* __restrict__ p2 = a.img2 + ch * plane;
 
-  for (int i = tid; i < LW * LW; i += LT * LT) {
-    const int ly = i / LW, lx = i - ly * LW;
+  for (int i = tid; i < SW * SW; i += S_THREADS) {
+    const int ly = i / SW, lx = i - ly * SW;
     const int gy = y0 + ly - LH, gx = x0 + lx - LH;
     float v1 = 0.f, v2 = 0.f;
     if (gy >= 0 && gy < a.H && gx >= 0 && gx < a.W) {
@@ -70,72 +82,97 @@ __global__ void __launch_bounds__(LT * LT) ssim_fwd_kernel(const LossArgs a) {
     s2[ly][lx] = v2;
   }
   __syncthreads();
-  for (int i = tid; i < LW * LT; i += LT * LT) {
-    const int row = i / LT, col = i - row * LT;
-    float m1 = 0.f, m2 = 0.f, e11 = 0.f, e22 = 0.f, e12 = 0.f;
+  // horizontal: task = (row of the patch, group of four output columns)
+  for (int i = tid; i < SW * (ST / SR); i += S_THREADS) {
+    const int row = i / (ST / SR), col = (i - row * (ST / SR)) * SR;
+    float u[SR + 10], v[SR + 10], uu[SR + 10], vv[SR + 10], uv[SR + 10];
 #pragma unroll
-    for (int k = 0; k < 11; ++k) {
-      const float wk = a.w[k], u = s1[row][col + k], v = s2[row][col + k];
-      m1 += wk * u;
-      m2 += wk * v;
-      e11 += wk * (u * u);
-      e22 += wk * (v * v);
-      e12 += wk * (u * v);
+    for (int j = 0; j < SR + 10; ++j) {
+      u[j] = s1[row][col + j];
+      v[j] = s2[row][col + j];
+      uu[j] = u[j] * u[j];
+      vv[j] = v[j] * v[j];
+      uv[j] = u[j] * v[j];
     }
-    hz[0][row][col] = m1; hz[1][row][col] = m2; hz[2][row][col] = e11; hz[3][row][col] = e22; hz[4][row][col] = e12;
+#pragma unroll
+    for (int o = 0; o < SR; ++o) {
+      float m1 = 0.f, m2 = 0.f, e11 = 0.f, e22 = 0.f, e12 = 0.f;
+#pragma unroll
+      for (int k = 0; k < 11; ++k) {
+        const float wk = a.w[k];
+        m1 += wk * u[o + k];
+        m2 += wk * v[o + k];
+        e11 += wk * uu[o + k];
+        e22 += wk * vv[o + k];
+        e12 += wk * uv[o + k];
+      }
+      hz[0][row][col + o] = m1; hz[1][row][col + o] = m2; hz[2][row][col + o] = e11; hz[3][row][col + o] = e22;
+      hz[4][row][col + o] = e12;
+    }
   }
   __syncthreads();
-  float mu1 = 0.f, mu2 = 0.f, e11 = 0.f, e22 = 0.f, e12 = 0.f;
+  // vertical: thread = (column, group of four output rows)
+  const int tx = tid & (ST - 1), r0 = (tid / ST) * SR;
+  float acc[5][SR];
 #pragma unroll
-  for (int k = 0; k < 11; ++k) {
-    const float wk = a.w[k];
-    mu1 += wk * hz[0][ty + k][tx];
-    mu2 += wk * hz[1][ty + k][tx];
-    e11 += wk * hz[2][ty + k][tx];
-    e22 += wk * hz[3][ty + k][tx];
-    e12 += wk * hz[4][ty + k][tx];
-  }
-  const int gx = x0 + tx, gy = y0 + ty;
-  const bool inside = gx < a.W && gy < a.H;
-  float map = 0.f, ad = 0.f;
-  if (inside) {
-    // utils/loss_utils.py:43-56
-    const float C1 = 0.01f * 0.01f, C2 = 0.03f * 0.03f;
-    const float mu1_sq = mu1 * mu1, mu2_sq = mu2 * mu2, mu1_mu2 = mu1 * mu2;
-    const float sigma1_sq = e11 - mu1_sq, sigma2_sq = e22 - mu2_sq, sigma12 = e12 - mu1_mu2;
-    const float A = 2.f * mu1_mu2 + C1, B = 2.f * sigma12 + C2;
-    const float Cc = mu1_sq + mu2_sq + C1, D = sigma1_sq + sigma2_sq + C2;
-    const float inv = 1.f / (Cc * D);
-    map = (A * B) * inv;
-    const size_t o = ch * plane + (size_t)gy * a.W + gx;
-    if (a.ssim_map) a.ssim_map[o] = map;
-    ad = fabsf(s1[ty + LH][tx + LH] - s2[ty + LH][tx + LH]);
-    if (GRAD) {
-      // with sigma1_sq = E11 - mu1^2 and sigma12 = E12 - mu1 mu2 substituted
-      a.dm_dmu1[o] = 2.f * mu2 * (B - A) * inv - map * (2.f * mu1 * (D - Cc)) * inv;
-      a.dm_de11[o] = -map / D;
-      a.dm_de12[o] = 2.f * A * inv;
+  for (int q = 0; q < 5; ++q) {
+    float h[SR + 10];
+#pragma unroll
+    for (int j = 0; j < SR + 10; ++j) h[j] = hz[q][r0 + j][tx];
+#pragma unroll
+    for (int o = 0; o < SR; ++o) {
+      float t = 0.f;
+#pragma unroll
+      for (int k = 0; k < 11; ++k) t += a.w[k] * h[o + k];
+      acc[q][o] = t;
     }
   }
-  const float sm = warp_sum(map), sa = warp_sum(ad);
+  const int gx = x0 + tx;
+  float sum_map = 0.f, sum_ad = 0.f;
+#pragma unroll
+  for (int o = 0; o < SR; ++o) {
+    const int ty = r0 + o, gy = y0 + ty;
+    if (gx < a.W && gy < a.H) {
+      // utils/loss_utils.py:43-56
+      const float mu1 = acc[0][o], mu2 = acc[1][o], e11 = acc[2][o], e22 = acc[3][o], e12 = acc[4][o];
+      const float C1 = 0.01f * 0.01f, C2 = 0.03f * 0.03f;
+      const float mu1_sq = mu1 * mu1, mu2_sq = mu2 * mu2, mu1_mu2 = mu1 * mu2;
+      const float sigma1_sq = e11 - mu1_sq, sigma2_sq = e22 - mu2_sq, sigma12 = e12 - mu1_mu2;
+      const float A = 2.f * mu1_mu2 + C1, B = 2.f * sigma12 + C2;
+      const float Cc = mu1_sq + mu2_sq + C1, D = sigma1_sq + sigma2_sq + C2;
+      const float inv = 1.f / (Cc * D);
+      const float map = (A * B) * inv;
+      const size_t oo = ch * plane + (size_t)gy * a.W + gx;
+      if (a.ssim_map) a.ssim_map[oo] = map;
+      sum_map += map;
+      sum_ad += fabsf(s1[ty + LH][tx + LH] - s2[ty + LH][tx + LH]);
+      if (GRAD) {
+        // with sigma1_sq = E11 - mu1^2 and sigma12 = E12 - mu1 mu2 substituted
+        a.dm_dmu1[oo] = 2.f * mu2 * (B - A) * inv - map * (2.f * mu1 * (D - Cc)) * inv;
+        a.dm_de11[oo] = -map / D;
+        a.dm_de12[oo] = 2.f * A * inv;
+      }
+    }
+  }
+  const float sm = warp_sum(sum_map), sa = warp_sum(sum_ad);
   if ((tid & 31) == 0) { red[0][tid >> 5] = sm; red[1][tid >> 5] = sa; }
   __syncthreads();
   if (tid < 2) {
     double t = 0.0;
-    for (int i = 0; i < LT * LT / 32; ++i) t += (double)red[tid][i];
+    for (int i = 0; i < S_THREADS / 32; ++i) t += (double)red[tid][i];
     atomicAdd(a.sums + tid, t);
   }
 }
 
-__global__ void __launch_bounds__(LT * LT) ssim_bwd_kernel(const LossArgs a) {
-  __shared__ float s[3][LW][LW + 1];
-  __shared__ float hz[3][LW][LT];
-  const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * LT + tx;
-  const int x0 = blockIdx.x * LT, y0 = blockIdx.y * LT, ch = blockIdx.z;
+__global__ void __launch_bounds__(S_THREADS) ssim_bwd_kernel(const LossArgs a) {
+  __shared__ float s[3][SW][SP];
+  __shared__ float hz[3][SW][ST + 1];
+  const int tid = threadIdx.x;
+  const int x0 = blockIdx.x * ST, y0 = blockIdx.y * ST, ch = blockIdx.z;
   const size_t plane = (size_t)a.H * a.W;
   const size_t base = ch * plane;
-  for (int i = tid; i < LW * LW; i += LT * LT) {
-    const int ly = i / LW, lx = i - ly * LW;
+  for (int i = tid; i < SW * SW; i += S_THREADS) {
+    const int ly = i / SW, lx = i - ly * SW;
     const int gy = y0 + ly - LH, gx = x0 + lx - LH;
     float v0 = 0.f, v1 = 0.f, v2 = 0.f;
     if (gy >= 0 && gy < a.H && gx >= 0 && gx < a.W) {
@@ -148,39 +185,56 @@ __global__ void __launch_bounds__(LT * LT) ssim_bwd_kernel(const LossArgs a) {
     s[0][ly][lx] = v0; s[1][ly][lx] = v1; s[2][ly][lx] = v2;
   }
   __syncthreads();
-  for (int i = tid; i < LW * LT; i += LT * LT) {
-    const int row = i / LT, col = i - row * LT;
-    float c0 = 0.f, c1 = 0.f, c2 = 0.f;
+  for (int i = tid; i < SW * (ST / SR); i += S_THREADS) {
+    const int row = i / (ST / SR), col = (i - row * (ST / SR)) * SR;
 #pragma unroll
-    for (int k = 0; k < 11; ++k) {
-      const float wk = a.w[k];
-      c0 += wk * s[0][row][col + k];
-      c1 += wk * s[1][row][col + k];
-      c2 += wk * s[2][row][col + k];
+    for (int q = 0; q < 3; ++q) {
+      float h[SR + 10];
+#pragma unroll
+      for (int j = 0; j < SR + 10; ++j) h[j] = s[q][row][col + j];
+#pragma unroll
+      for (int o = 0; o < SR; ++o) {
+        float c = 0.f;
+#pragma unroll
+        for (int k = 0; k < 11; ++k) c += a.w[k] * h[o + k];
+        hz[q][row][col + o] = c;
+      }
     }
-    hz[0][row][col] = c0; hz[1][row][col] = c1; hz[2][row][col] = c2;
   }
   __syncthreads();
-  const int gx = x0 + tx, gy = y0 + ty;
-  if (gx >= a.W || gy >= a.H) return;
-  float c0 = 0.f, c1 = 0.f, c2 = 0.f;
+  const int tx = tid & (ST - 1), r0 = (tid / ST) * SR;
+  float acc[3][SR];
 #pragma unroll
-  for (int k = 0; k < 11; ++k) {
-    const float wk = a.w[k];
-    c0 += wk * hz[0][ty + k][tx];
-    c1 += wk * hz[1][ty + k][tx];
-    c2 += wk * hz[2][ty + k][tx];
+  for (int q = 0; q < 3; ++q) {
+    float h[SR + 10];
+#pragma unroll
+    for (int j = 0; j < SR + 10; ++j) h[j] = hz[q][r0 + j][tx];
+#pragma unroll
+    for (int o = 0; o < SR; ++o) {
+      float c = 0.f;
+#pragma unroll
+      for (int k = 0; k < 11; ++k) c += a.w[k] * h[o + k];
+      acc[q][o] = c;
+    }
   }
-  const size_t o = base + (size_t)gy * a.W + gx;
-  const float m = a.mask ? __ldg(a.mask + (size_t)gy * a.W + gx) : 1.0f;
-  const float x = __ldg(a.img1 + o) * m, y = __ldg(a.img2 + o);
-  const float up = (a.upstream ? __ldg(a.upstream) : 1.0f) * m;   // d (img1 m) / d img1 = m
-  float g = (c0 + 2.f * x * c1 + y * c2) * (a.dL_dmap ? 1.0f : a.ssim_scale);
-  if (a.l1_scale != 0.f) {
-    const float d = x - y;
-    g += a.l1_scale * (d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f));   // torch.abs backward: sign(x - y)
+  const int gx = x0 + tx;
+  const float up0 = a.upstream ? __ldg(a.upstream) : 1.0f;
+#pragma unroll
+  for (int o = 0; o < SR; ++o) {
+    const int gy = y0 + r0 + o;
+    if (gx >= a.W || gy >= a.H) continue;
+    const float c0 = acc[0][o], c1 = acc[1][o], c2 = acc[2][o];
+    const size_t oo = base + (size_t)gy * a.W + gx;
+    const float m = a.mask ? __ldg(a.mask + (size_t)gy * a.W + gx) : 1.0f;
+    const float x = __ldg(a.img1 + oo) * m, y = __ldg(a.img2 + oo);
+    const float up = up0 * m;   // d (img1 m) / d img1 = m
+    float g = (c0 + 2.f * x * c1 + y * c2) * (a.dL_dmap ? 1.0f : a.ssim_scale);
+    if (a.l1_scale != 0.f) {
+      const float d = x - y;
+      g += a.l1_scale * (d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f));   // torch.abs backward: sign(x - y)
+    }
+    a.dL_dimg1[oo] = g * up;
   }
-  a.dL_dimg1[o] = g * up;
 }
 
 // Depth loss of train_single.py:133-139: mean |(pred - target) mask| over n elements.  Forward adds the sum to
@@ -316,7 +370,7 @@ cudaError_t run_ssim_forward(int C, int H, int W, const float* img1, const float
                              cudaStream_t s) {
   LossArgs a = make_args(C, H, W, img1, img2, mask, window);
   a.ssim_map = ssim_map; a.dm_dmu1 = dm_dmu1; a.dm_de11 = dm_de11; a.dm_de12 = dm_de12; a.sums = sums;
-  const dim3 grid((W + LT - 1) / LT, (H + LT - 1) / LT, C), block(LT, LT);
+  const dim3 grid((W + ST - 1) / ST, (H + ST - 1) / ST, C), block(S_THREADS);
   ProfScope ps(K_LOSS, s);
   if (dm_dmu1) ssim_fwd_kernel<true><<<grid, block, 0, s>>>(a);
   else ssim_fwd_kernel<false><<<grid, block, 0, s>>>(a);
@@ -332,7 +386,7 @@ cudaError_t run_ssim_backward(int C, int H, int W, const float* img1, const floa
   a.dm_de12 = const_cast<float*>(dm_de12);
   a.dL_dmap = dL_dmap; a.upstream = upstream; a.ssim_scale = ssim_scale; a.l1_scale = l1_scale;
   a.dL_dimg1 = dL_dimg1;
-  const dim3 grid((W + LT - 1) / LT, (H + LT - 1) / LT, C), block(LT, LT);
+  const dim3 grid((W + ST - 1) / ST, (H + ST - 1) / ST, C), block(S_THREADS);
   ProfScope ps(K_LOSS, s);
   ssim_bwd_kernel<<<grid, block, 0, s>>>(a);
   return cudaGetLastError();
